@@ -1,0 +1,211 @@
+/*
+ * pifpaf_b200.h -- C ABI of libpifpaf_b200.so, the sm_100a CUDA implementation
+ * of the OpenPifPaf CifCaf decoder hot path.
+ *
+ * This library stands where the reference's only native module stands:
+ *   /root/reference/openpifpaf/functional.pyx   (Cython, CPU, 4 live functions)
+ * and additionally moves the numpy/Python stages that call it onto the device:
+ *   decoder/cif_hr.py:26-65        -> pp_cifhr_accumulate
+ *   decoder/cif_seeds.py:23-54     -> pp_cif_seeds
+ *   decoder/caf_scored.py:32-87    -> pp_caf_scored
+ *   decoder/generator/cifcaf.py:84-108,124-307 (+ occupancy.py) -> pp_cifcaf_assemble
+ *   decoder/nms.py:17-57           -> pp_keypoint_nms
+ *   decoder/generator/cifcaf.py:67-122 (whole __call__) -> pp_decode_batch[_host]
+ *
+ * Conventions
+ *   - plain C: pointers, sizes, POD structs; no C++/torch types; nothing throws;
+ *   - every entry returns PP_OK (0) or a negative PP_ERR_* code;
+ *   - all buffers are CALLER-OWNED.  "d_" = device pointer, "h_" = host pointer;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *     device entries only enqueue work and never synchronise;
+ *   - no global mutable state: re-entrant per stream / per workspace;
+ *   - variable-length results use fixed capacities (pp_caps) + per-image counts;
+ *     a capacity overflow is reported in the per-image `status` words
+ *     (PP_STATUS_* bits), which the *_host entry turns into PP_ERR_CAPACITY.
+ *
+ * Tensor layouts (all float32, C-contiguous), matching what the reference's
+ * CifCafCollector emits (network/heads.py:65-88) with a leading batch axis:
+ *   cif  (B, F, 5, H, W)  channels [conf, x, y, logb, scale], x/y in field cells
+ *   caf  (B, L, 9, H, W)  channels [conf, x1, y1, logb1, s1, x2, y2, logb2, s2]
+ *   hr   (B, F, Hh, Wh)   Hh = (H-1)*stride+1, Wh = (W-1)*stride+1
+ */
+#ifndef PIFPAF_B200_H_
+#define PIFPAF_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PP_OK 0
+#define PP_ERR_ARG (-1)       /* bad shape / NULL pointer / unsupported option */
+#define PP_ERR_CAPACITY (-2)  /* a pp_caps capacity was exceeded               */
+#define PP_ERR_CUDA (-3)      /* a CUDA runtime call failed (see pp_last_cuda_error) */
+#define PP_ERR_WORKSPACE (-4) /* workspace too small                           */
+
+#define PP_MAX_F 32           /* keypoint types  */
+#define PP_MAX_L 64           /* CAF links       */
+#define PP_MAX_DEG 16         /* neighbours per joint */
+
+/* per-image status bits written by the device entries */
+#define PP_STATUS_SEED_OVERFLOW 1
+#define PP_STATUS_CAF_OVERFLOW 2
+#define PP_STATUS_ANN_OVERFLOW 4
+#define PP_STATUS_SRC_OVERFLOW 8
+
+typedef struct pp_shape {
+  int32_t B, F, L, H, W, stride;
+} pp_shape;
+
+/* Capacities of the variable-length buffers, per image (0 = worst case). */
+typedef struct pp_caps {
+  int32_t seed_cap; /* seeds per image            (worst case F*H*W) */
+  int32_t caf_cap;  /* candidates per link & direction (worst case H*W) */
+  int32_t ann_cap;  /* annotations per image      (default 256)      */
+  int32_t src_cap;  /* CifHr sources per field    (worst case H*W)   */
+} pp_caps;
+
+/* Decoder knobs; same meaning and defaults-by-configuration as the reference's
+ * class attributes (decoder/factory.py:74-92). */
+typedef struct pp_params {
+  double nms_instance_threshold; /* nms.Keypoints.instance_threshold (float64 compare) */
+  float cif_threshold;           /* CifHr.v_threshold          */
+  float seed_threshold;          /* CifSeeds.threshold         */
+  float seed_score_scale;        /* CifSeeds.score_scale       */
+  float caf_threshold;           /* CafScored.default_score_th */
+  float cif_floor;               /* CafScored cif_floor (0.1)  */
+  float cif_floor_compl;         /* float32(1.0 - cif_floor), computed in double by the host */
+  float keypoint_threshold;      /* CifCaf.keypoint_threshold  */
+  float nms_keypoint_threshold;  /* nms.Keypoints.keypoint_threshold */
+  float nms_suppression;         /* nms.Keypoints.suppression  */
+  float cif_min_scale;           /* FieldConfig.cif_min_scales[i]   (0 = off)  */
+  float caf_min_distance;        /* FieldConfig.caf_min_distances[i] (0 = off) */
+  float caf_max_distance;        /* FieldConfig.caf_max_distances[i] (<=0 = None) */
+  int32_t connection_method;     /* 0 = blend, 1 = max         */
+  int32_t greedy;                /* CifCaf.greedy              */
+  int32_t force_complete;        /* CifCaf.force_complete      */
+  int32_t nms;                   /* 0: CifCaf(nms=None)        */
+  int32_t exp_mode;              /* 1 = deterministic pp_expf (default), 0 = CUDA expf */
+  int32_t reserved;
+} pp_params;
+
+/* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
+ * COCO_PERSON_SKELETON; confidence_scales may be NULL (cifcaf.py:39,52). */
+typedef struct pp_skeleton {
+  int32_t L;
+  int32_t joints[PP_MAX_L][2];
+  int32_t has_confidence_scales;
+  float confidence_scales[PP_MAX_L];
+} pp_skeleton;
+
+/* Result buffers of one batch (device pointers for pp_decode_batch, host
+ * pointers for pp_decode_batch_host).  Any of the optional ones may be NULL. */
+typedef struct pp_outputs {
+  float *hr;            /* optional (B,F,Hh,Wh); if NULL the workspace copy is used */
+  float *seeds;         /* optional (B,seed_cap,5): v, f, x, y, s sorted descending */
+  int32_t *n_seeds;     /* optional (B)                                  */
+  float *caf_fwd;       /* optional (B,L,9,caf_cap)                      */
+  float *caf_bwd;       /* optional (B,L,9,caf_cap)                      */
+  int32_t *n_caf_fwd;   /* optional (B,L)                                */
+  int32_t *n_caf_bwd;   /* optional (B,L)                                */
+  float *ann_data;      /* (B,ann_cap,F,3) x, y, v   -- final annotations, score order */
+  float *ann_scales;    /* (B,ann_cap,F)   joint_scales                  */
+  double *ann_score;    /* optional (B,ann_cap) Annotation.score()       */
+  int32_t *ann_source;  /* optional (B,ann_cap) index into the pre-NMS list */
+  int32_t *n_ann;       /* (B)                                           */
+  float *pre_data;      /* optional (B,ann_cap,F,3) annotations before force-complete/NMS */
+  float *pre_scales;    /* optional (B,ann_cap,F)                        */
+  int32_t *pre_order;   /* optional (B,ann_cap,F,2) decoding_order (start,end), -1 padded */
+  int32_t *n_pre;       /* optional (B)                                  */
+  int32_t *status;      /* (B) PP_STATUS_* bits                          */
+} pp_outputs;
+
+const char *pp_error_string(int code);
+const char *pp_last_cuda_error(void);   /* thread-local text of the last CUDA failure */
+const char *pp_version(void);
+
+/* Fill defaults: params = SURVEY.md 8d decoder settings; caps = worst case. */
+void pp_default_params(pp_params *p);
+int pp_default_caps(const pp_shape *s, pp_caps *c);
+int pp_coco_skeleton(pp_skeleton *sk);
+
+/* Bytes of device scratch pp_decode_batch needs (includes hr when out->hr==NULL). */
+size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c);
+
+/* ---- stage entry points (device pointers, enqueue only) ------------------ */
+
+/* CifHr.fill for one cif head: d_hr <- min(1, sum of clipped Gaussians).
+ * Replaces cif_hr.py:26-65 + functional.pyx:105-141.  Bit-exact. */
+int pp_cifhr_accumulate(const float *d_cif, float *d_hr, void *d_ws, size_t ws_bytes,
+                        const pp_shape *s, const pp_caps *c, const pp_params *p,
+                        int32_t *d_status, void *stream);
+
+/* CifSeeds.fill + get(): sorted seeds (v,f,x,y,s).  cif_seeds.py:23-54. */
+int pp_cif_seeds(const float *d_cif, const float *d_hr, float *d_seeds, int32_t *d_n_seeds,
+                 void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                 const pp_params *p, int32_t *d_status, void *stream);
+
+/* CafScored.fill: forward/backward candidate lists.  caf_scored.py:32-87. */
+int pp_caf_scored(const float *d_caf, const float *d_hr, const pp_skeleton *sk, float score_th,
+                  float *d_fwd, int32_t *d_nfwd, float *d_bwd, int32_t *d_nbwd,
+                  const pp_shape *s, const pp_caps *c, const pp_params *p, int32_t *d_status,
+                  void *stream);
+
+/* Seed loop + _grow + occupancy (+ force-complete) (+ keypoint NMS when p->nms).
+ * cifcaf.py:84-122.  d_fwd2/d_bwd2 (score_th 1e-4 lists) only for force_complete. */
+int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const float *d_fwd,
+                       const int32_t *d_nfwd, const float *d_bwd, const int32_t *d_nbwd,
+                       const float *d_fwd2, const int32_t *d_nfwd2, const float *d_bwd2,
+                       const int32_t *d_nbwd2, const pp_skeleton *sk, const pp_outputs *d_out,
+                       void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                       const pp_params *p, void *stream);
+
+/* nms.Keypoints.annotations on device buffers, in place.  nms.py:17-57. */
+int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
+                    int32_t *d_source, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                    const pp_caps *c, const pp_params *p, void *stream);
+
+/* ---- fused drivers ------------------------------------------------------- */
+
+/* CifCaf.__call__ for a batch, everything device-resident (cifcaf.py:67-122). */
+int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *sk,
+                    const pp_outputs *d_out, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                    const pp_caps *c, const pp_params *p, void *stream);
+
+/* Same, from HOST fields to HOST results: H2D copies, kernels, D2H copies and
+ * one stream synchronise inside.  d_cif/d_caf/d_ws are caller-owned device
+ * staging buffers; d_out are device result buffers, h_out their host mirrors
+ * (only the non-NULL h_out members are copied back).  This is the call the
+ * reference-side binding makes in place of Generator.batch's CPU decode
+ * (decoder/generator/generator.py:84-101). */
+int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, float *d_caf,
+                         const pp_skeleton *sk, const pp_outputs *d_out, const pp_outputs *h_out,
+                         void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                         const pp_params *p, void *stream);
+
+/* ---- parity shim: the reference's live functional.pyx primitives ---------
+ * Same names / argument meaning as functional.pyx, on device buffers. */
+
+/* functional.pyx:105-141; field (fh,fw) updated in place, n sources. */
+int pp_scalar_square_add_gauss_with_max(float *d_field, int fh, int fw, const float *d_x,
+                                        const float *d_y, const float *d_sigma, const float *d_v,
+                                        int n, float truncate, float max_value, void *stream);
+/* functional.pyx:231-244 */
+int pp_scalar_values(const float *d_field, int fh, int fw, const float *d_x, const float *d_y,
+                     int n, float default_value, float *d_out, void *stream);
+/* functional.pyx:338-359; d_out (9,K) compacted in order, *d_count <- kept columns */
+int pp_caf_center_s(const float *d_caf_field, int K, float x, float y, float sigma, float *d_out,
+                    int32_t *d_count, void *stream);
+/* functional.pyx:281-286; result (0/non-zero) written to *d_out */
+int pp_scalar_nonzero_clipped_with_reduction(const uint8_t *d_field, int fh, int fw, float x,
+                                             float y, float r, uint8_t *d_out, void *stream);
+/* decoder/utils.py:61-66 (Occupancy.set's primitive); integer x, y, sigma */
+int pp_scalar_square_add_single(uint8_t *d_field, int fh, int fw, long long x, long long y,
+                                long long sigma, int value, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIFPAF_B200_H_ */

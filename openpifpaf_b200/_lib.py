@@ -1,0 +1,147 @@
+"""ctypes binding of libpifpaf_b200.so (include/pifpaf_b200.h).
+
+There is no CPU fallback: if the library is missing or fails to load, importing
+the decoder raises.  The library is built in-tree by ``openpifpaf_b200/build.py``
+(``__graft_entry__.build()``).
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, 'libpifpaf_b200.so')
+
+PP_MAX_F, PP_MAX_L = 32, 64
+PP_OK, PP_ERR_ARG, PP_ERR_CAPACITY, PP_ERR_CUDA, PP_ERR_WORKSPACE = 0, -1, -2, -3, -4
+STATUS_BITS = {1: 'seed_cap', 2: 'caf_cap', 4: 'ann_cap', 8: 'src_cap'}
+
+
+class Shape(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ('B', 'F', 'L', 'H', 'W', 'stride')]
+
+
+class Caps(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ('seed_cap', 'caf_cap', 'ann_cap', 'src_cap')]
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ('nms_instance_threshold', C.c_double),
+        ('cif_threshold', C.c_float), ('seed_threshold', C.c_float),
+        ('seed_score_scale', C.c_float), ('caf_threshold', C.c_float),
+        ('cif_floor', C.c_float), ('cif_floor_compl', C.c_float),
+        ('keypoint_threshold', C.c_float), ('nms_keypoint_threshold', C.c_float),
+        ('nms_suppression', C.c_float), ('cif_min_scale', C.c_float),
+        ('caf_min_distance', C.c_float), ('caf_max_distance', C.c_float),
+        ('connection_method', C.c_int32), ('greedy', C.c_int32),
+        ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
+        ('reserved', C.c_int32),
+    ]
+
+
+class Skeleton(C.Structure):
+    _fields_ = [
+        ('L', C.c_int32),
+        ('joints', (C.c_int32 * 2) * PP_MAX_L),
+        ('has_confidence_scales', C.c_int32),
+        ('confidence_scales', C.c_float * PP_MAX_L),
+    ]
+
+    @classmethod
+    def from_list(cls, skeleton, confidence_scales=None):
+        if len(skeleton) > PP_MAX_L:
+            raise ValueError('skeleton has %d links, library limit is %d' % (len(skeleton), PP_MAX_L))
+        sk = cls()
+        sk.L = len(skeleton)
+        for i, (a, b) in enumerate(skeleton):
+            sk.joints[i][0], sk.joints[i][1] = int(a), int(b)
+        if confidence_scales is not None:
+            sk.has_confidence_scales = 1
+            for i, v in enumerate(confidence_scales):
+                sk.confidence_scales[i] = float(v)
+        return sk
+
+
+_OUT_FIELDS = ('hr', 'seeds', 'n_seeds', 'caf_fwd', 'caf_bwd', 'n_caf_fwd', 'n_caf_bwd',
+               'ann_data', 'ann_scales', 'ann_score', 'ann_source', 'n_ann', 'pre_data',
+               'pre_scales', 'pre_order', 'n_pre', 'status')
+
+
+class Outputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in _OUT_FIELDS]
+
+
+class PifPafError(RuntimeError):
+    def __init__(self, code, detail=''):
+        self.code = code
+        super().__init__('libpifpaf_b200 error %d: %s%s' % (code, error_string(code),
+                                                            (' -- ' + detail) if detail else ''))
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library (once). Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            'libpifpaf_b200.so is not built (%s). Run `python -c "import __graft_entry__ as g; '
+            'g.build()"` or `python openpifpaf_b200/build.py`. There is no CPU fallback.' % LIB_PATH)
+    l = C.CDLL(LIB_PATH)
+    vp, sz, i32, f32 = C.c_void_p, C.c_size_t, C.c_int, C.c_float
+    P = C.POINTER
+    l.pp_error_string.restype = C.c_char_p
+    l.pp_error_string.argtypes = [i32]
+    l.pp_last_cuda_error.restype = C.c_char_p
+    l.pp_version.restype = C.c_char_p
+    l.pp_default_params.restype = None
+    l.pp_default_params.argtypes = [P(Params)]
+    l.pp_default_caps.argtypes = [P(Shape), P(Caps)]
+    l.pp_coco_skeleton.argtypes = [P(Skeleton)]
+    l.pp_workspace_bytes.restype = sz
+    l.pp_workspace_bytes.argtypes = [P(Shape), P(Caps)]
+    l.pp_cifhr_accumulate.argtypes = [vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp, vp]
+    l.pp_cif_seeds.argtypes = [vp, vp, vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp, vp]
+    l.pp_caf_scored.argtypes = [vp, vp, P(Skeleton), f32, vp, vp, vp, vp, P(Shape), P(Caps),
+                                P(Params), vp, vp]
+    l.pp_cifcaf_assemble.argtypes = [vp] * 10 + [P(Skeleton), P(Outputs), vp, sz, P(Shape), P(Caps),
+                                                 P(Params), vp]
+    l.pp_keypoint_nms.argtypes = [vp, vp, vp, vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp]
+    l.pp_decode_batch.argtypes = [vp, vp, P(Skeleton), P(Outputs), vp, sz, P(Shape), P(Caps),
+                                  P(Params), vp]
+    l.pp_decode_batch_host.argtypes = [vp, vp, vp, vp, P(Skeleton), P(Outputs), P(Outputs), vp, sz,
+                                       P(Shape), P(Caps), P(Params), vp]
+    l.pp_scalar_square_add_gauss_with_max.argtypes = [vp, i32, i32, vp, vp, vp, vp, i32, f32, f32, vp]
+    l.pp_scalar_values.argtypes = [vp, i32, i32, vp, vp, i32, f32, vp, vp]
+    l.pp_caf_center_s.argtypes = [vp, i32, f32, f32, f32, vp, vp, vp]
+    l.pp_scalar_nonzero_clipped_with_reduction.argtypes = [vp, i32, i32, f32, f32, f32, vp, vp]
+    l.pp_scalar_square_add_single.argtypes = [vp, i32, i32, C.c_longlong, C.c_longlong,
+                                              C.c_longlong, i32, vp]
+    _lib = l
+    return l
+
+
+EXPORTS = (
+    'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_cifhr_accumulate', 'pp_cif_seeds',
+    'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
+    'pp_decode_batch_host', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
+    'pp_caf_center_s', 'pp_scalar_nonzero_clipped_with_reduction', 'pp_scalar_square_add_single',
+)
+
+
+def error_string(code):
+    try:
+        return lib().pp_error_string(code).decode()
+    except Exception:  # pylint: disable=broad-except
+        return 'code %d' % code
+
+
+def check(code):
+    if code != PP_OK:
+        detail = ''
+        if code == PP_ERR_CUDA:
+            detail = lib().pp_last_cuda_error().decode()
+        raise PifPafError(code, detail)

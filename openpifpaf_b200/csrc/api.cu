@@ -1,0 +1,322 @@
+// api.cu -- extern "C" surface of libpifpaf_b200.so (see include/pifpaf_b200.h).
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "stages.cuh"
+
+namespace pp {
+
+// ---- error text -------------------------------------------------------------
+static thread_local char g_cuda_err[256] = "";
+
+void set_cuda_error(cudaError_t e, const char *where) {
+  snprintf(g_cuda_err, sizeof g_cuda_err, "%s: %s (%s)", where, cudaGetErrorName(e),
+           cudaGetErrorString(e));
+}
+
+int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess)
+      cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    cached = n > 0 ? n : 148;
+  }
+  return cached;
+}
+
+static bool shape_ok(const pp_shape *s) {
+  return s && s->B > 0 && s->F > 0 && s->F <= PP_MAX_F && s->L >= 0 && s->L <= PP_MAX_L &&
+         s->H > 0 && s->W > 0 && s->stride > 0;
+}
+
+static bool caps_ok(const pp_shape *s, const pp_caps *c) {
+  return c && c->seed_cap > 0 && c->caf_cap > 0 && c->ann_cap > 0 && c->src_cap > 0 &&
+         c->seed_cap < (1 << 24);
+}
+
+// ---- decode workspace layout ---------------------------------------------
+struct DecodeWs {
+  float *hr;                 // (B,F,Hh,Wh)      when the caller passes none
+  float *seeds; int *n_seeds;
+  float *fwd, *bwd; int *nfwd, *nbwd;
+  uint8_t *occ_cnt;
+  float *pre_data, *pre_scales; int *pre_order; int *n_pre;
+  void *stage;               // shared by the cifhr / seeds / nms stages (used one after another)
+  size_t stage_bytes;
+  size_t total;
+};
+
+static size_t max3(size_t a, size_t b, size_t c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+
+static DecodeWs layout(void *base, const pp_shape &s, const pp_caps &c, bool need_hr) {
+  DecodeWs w;
+  char *p = (char *)base;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char *q = p + off; off += align_up(bytes, 256); return (void *)q; };
+  size_t B = s.B;
+  w.hr = need_hr ? (float *)take(B * s.F * hr_h(s) * hr_w(s) * sizeof(float)) : nullptr;
+  w.seeds = (float *)take(B * c.seed_cap * 5 * sizeof(float));
+  w.n_seeds = (int *)take(B * sizeof(int));
+  w.fwd = (float *)take(B * s.L * 9 * c.caf_cap * sizeof(float));
+  w.bwd = (float *)take(B * s.L * 9 * c.caf_cap * sizeof(float));
+  w.nfwd = (int *)take(B * s.L * sizeof(int));
+  w.nbwd = (int *)take(B * s.L * sizeof(int));
+  w.occ_cnt = (uint8_t *)take(B * c.seed_cap);
+  w.pre_data = (float *)take(B * c.ann_cap * s.F * 3 * sizeof(float));
+  w.pre_scales = (float *)take(B * c.ann_cap * s.F * sizeof(float));
+  w.pre_order = (int *)take(B * c.ann_cap * s.F * 2 * sizeof(int));
+  w.n_pre = (int *)take(B * sizeof(int));
+  w.stage_bytes = max3(cifhr_ws_bytes(s, c), seeds_ws_bytes(s, c), nms_ws_bytes(s, c));
+  w.stage = take(w.stage_bytes);
+  w.total = off;
+  return w;
+}
+
+}  // namespace pp
+
+using namespace pp;
+
+extern "C" {
+
+const char *pp_error_string(int code) {
+  switch (code) {
+    case PP_OK: return "ok";
+    case PP_ERR_ARG: return "invalid argument (shape, NULL pointer or unsupported option)";
+    case PP_ERR_CAPACITY: return "a pp_caps capacity was exceeded";
+    case PP_ERR_CUDA: return "CUDA runtime error (see pp_last_cuda_error)";
+    case PP_ERR_WORKSPACE: return "workspace too small";
+    default: return "unknown error code";
+  }
+}
+
+const char *pp_last_cuda_error(void) { return g_cuda_err; }
+const char *pp_version(void) { return "pifpaf_b200 0.1.0 (sm_100a)"; }
+
+void pp_default_params(pp_params *p) {
+  if (!p) return;
+  memset(p, 0, sizeof *p);
+  p->nms_instance_threshold = 0.0;
+  p->cif_threshold = 0.1f;
+  p->seed_threshold = 0.2f;
+  p->seed_score_scale = 1.0f;
+  p->caf_threshold = 0.1f;
+  p->cif_floor = 0.1f;
+  p->cif_floor_compl = (float)(1.0 - 0.1);
+  p->keypoint_threshold = 0.001f;
+  p->nms_keypoint_threshold = 0.001f;
+  p->nms_suppression = 0.0f;
+  p->connection_method = 0;
+  p->nms = 1;
+  p->exp_mode = 1;
+}
+
+int pp_default_caps(const pp_shape *s, pp_caps *c) {
+  if (!shape_ok(s) || !c) return PP_ERR_ARG;
+  long long cells = (long long)s->H * s->W;
+  long long seeds = cells * s->F;
+  if (seeds >= (1 << 24)) seeds = (1 << 24) - 1;
+  c->seed_cap = (int32_t)seeds;
+  c->caf_cap = (int32_t)cells;
+  c->ann_cap = 256;
+  c->src_cap = (int32_t)cells;
+  return PP_OK;
+}
+
+int pp_coco_skeleton(pp_skeleton *sk) {
+  static const int coco[19][2] = {{16, 14}, {14, 12}, {17, 15}, {15, 13}, {12, 13}, {6, 12}, {7, 13},
+                                  {6, 7},   {6, 8},   {7, 9},   {8, 10},  {9, 11},  {2, 3},  {1, 2},
+                                  {1, 3},   {2, 4},   {3, 5},   {4, 6},   {5, 7}};
+  if (!sk) return PP_ERR_ARG;
+  memset(sk, 0, sizeof *sk);
+  sk->L = 19;
+  for (int l = 0; l < 19; l++) { sk->joints[l][0] = coco[l][0]; sk->joints[l][1] = coco[l][1]; }
+  return PP_OK;
+}
+
+size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c) {
+  if (!shape_ok(s) || !caps_ok(s, c)) return 0;
+  return layout(nullptr, *s, *c, true).total;
+}
+
+int pp_cifhr_accumulate(const float *d_cif, float *d_hr, void *d_ws, size_t ws_bytes,
+                        const pp_shape *s, const pp_caps *c, const pp_params *p,
+                        int32_t *d_status, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !d_cif || !d_hr || !d_ws || !d_status) return PP_ERR_ARG;
+  if (ws_bytes < cifhr_ws_bytes(*s, *c)) return PP_ERR_WORKSPACE;
+  return cifhr_launch(d_cif, d_hr, d_ws, *s, *c, *p, d_status, (cudaStream_t)stream);
+}
+
+int pp_cif_seeds(const float *d_cif, const float *d_hr, float *d_seeds, int32_t *d_n_seeds,
+                 void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                 const pp_params *p, int32_t *d_status, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !d_cif || !d_hr || !d_seeds || !d_n_seeds || !d_ws ||
+      !d_status)
+    return PP_ERR_ARG;
+  if (ws_bytes < seeds_ws_bytes(*s, *c)) return PP_ERR_WORKSPACE;
+  return seeds_launch(d_cif, d_hr, d_seeds, d_n_seeds, d_ws, *s, *c, *p, d_status,
+                      (cudaStream_t)stream);
+}
+
+int pp_caf_scored(const float *d_caf, const float *d_hr, const pp_skeleton *sk, float score_th,
+                  float *d_fwd, int32_t *d_nfwd, float *d_bwd, int32_t *d_nbwd,
+                  const pp_shape *s, const pp_caps *c, const pp_params *p, int32_t *d_status,
+                  void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !d_caf || !d_hr || !d_fwd || !d_nfwd ||
+      !d_bwd || !d_nbwd || !d_status || sk->L != s->L)
+    return PP_ERR_ARG;
+  for (int l = 0; l < sk->L; l++)
+    if (sk->joints[l][0] < 1 || sk->joints[l][1] < 1) return PP_ERR_ARG;
+  return caf_scored_launch(d_caf, d_hr, *sk, score_th, d_fwd, d_nfwd, d_bwd, d_nbwd, *s, *c, *p,
+                           d_status, (cudaStream_t)stream);
+}
+
+int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const float *d_fwd,
+                       const int32_t *d_nfwd, const float *d_bwd, const int32_t *d_nbwd,
+                       const float *d_fwd2, const int32_t *d_nfwd2, const float *d_bwd2,
+                       const int32_t *d_nbwd2, const pp_skeleton *sk, const pp_outputs *d_out,
+                       void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                       const pp_params *p, void *stream) {
+  (void)d_fwd2; (void)d_nfwd2; (void)d_bwd2; (void)d_nbwd2;
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !d_out || !d_seeds || !d_n_seeds || !d_fwd ||
+      !d_bwd || !d_nfwd || !d_nbwd || !d_ws || sk->L != s->L)
+    return PP_ERR_ARG;
+  if (!d_out->ann_data || !d_out->ann_scales || !d_out->n_ann || !d_out->status) return PP_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  // workspace: occ counters + pre buffers (when the caller keeps none) + nms scratch
+  size_t B = s->B;
+  size_t need_occ = align_up(B * c->seed_cap, 256);
+  size_t need_pd = align_up(B * c->ann_cap * s->F * 3 * sizeof(float), 256);
+  size_t need_ps = align_up(B * c->ann_cap * s->F * sizeof(float), 256);
+  size_t need_po = align_up(B * c->ann_cap * s->F * 2 * sizeof(int), 256);
+  size_t need_np = align_up(B * sizeof(int), 256);
+  size_t need = need_occ + need_pd + need_ps + need_po + need_np + nms_ws_bytes(*s, *c);
+  if (ws_bytes < need) return PP_ERR_WORKSPACE;
+  char *q = (char *)d_ws;
+  AsmArgs a;
+  a.occ_cnt = (uint8_t *)q; q += need_occ;
+  a.pre_data = d_out->pre_data ? d_out->pre_data : (float *)q; q += need_pd;
+  a.pre_scales = d_out->pre_scales ? d_out->pre_scales : (float *)q; q += need_ps;
+  a.pre_order = d_out->pre_order ? d_out->pre_order : (int *)q; q += need_po;
+  a.n_pre = d_out->n_pre ? d_out->n_pre : (int *)q; q += need_np;
+  a.seeds = d_seeds; a.n_seeds = d_n_seeds;
+  a.fwd = d_fwd; a.bwd = d_bwd; a.nfwd = d_nfwd; a.nbwd = d_nbwd;
+  a.status = d_out->status;
+  a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
+  a.hh = hr_h(*s); a.hw = hr_w(*s);
+  int rc = assemble_launch(a, *sk, s->B, s->F, *p, st);
+  if (rc) return rc;
+  return nms_launch(a.pre_data, a.pre_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
+                    d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p, st);
+}
+
+int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
+                    int32_t *d_source, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                    const pp_caps *c, const pp_params *p, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !d_ann_data || !d_ann_scales || !d_n_ann || !d_ws)
+    return PP_ERR_ARG;
+  if (ws_bytes < nms_ws_bytes(*s, *c)) return PP_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t bc = (size_t)s->B * c->ann_cap;
+  size_t data_bytes = align_up(bc * s->F * 3 * sizeof(float), 256);
+  char *stage = (char *)d_ws + nms_ws_staging_offset(*s, *c);
+  float *in_data = (float *)stage;
+  float *in_scales = (float *)(stage + data_bytes);
+  int *n_in = (int *)(stage + 2 * data_bytes);
+  PP_CUDA_CHECK(cudaMemcpyAsync(in_data, d_ann_data, bc * s->F * 3 * sizeof(float),
+                                cudaMemcpyDeviceToDevice, st));
+  PP_CUDA_CHECK(cudaMemcpyAsync(in_scales, d_ann_scales, bc * s->F * sizeof(float),
+                                cudaMemcpyDeviceToDevice, st));
+  PP_CUDA_CHECK(cudaMemcpyAsync(n_in, d_n_ann, (size_t)s->B * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  return nms_launch(in_data, in_scales, n_in, d_ann_data, d_ann_scales, d_score, d_source, d_n_ann,
+                    d_ws, *s, *c, *p, st);
+}
+
+int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *sk,
+                    const pp_outputs *o, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                    const pp_caps *c, const pp_params *p, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !o || !d_cif || !d_caf || !d_ws ||
+      sk->L != s->L)
+    return PP_ERR_ARG;
+  if (!o->ann_data || !o->ann_scales || !o->n_ann || !o->status) return PP_ERR_ARG;
+  if (p->greedy || p->force_complete) return PP_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool need_hr = o->hr == nullptr;
+  DecodeWs w = layout(d_ws, *s, *c, need_hr);
+  if (ws_bytes < w.total) return PP_ERR_WORKSPACE;
+  float *hr = need_hr ? w.hr : o->hr;
+  float *seeds = o->seeds ? o->seeds : w.seeds;
+  int *n_seeds = o->n_seeds ? o->n_seeds : w.n_seeds;
+  float *fwd = o->caf_fwd ? o->caf_fwd : w.fwd;
+  float *bwd = o->caf_bwd ? o->caf_bwd : w.bwd;
+  int *nfwd = o->n_caf_fwd ? o->n_caf_fwd : w.nfwd;
+  int *nbwd = o->n_caf_bwd ? o->n_caf_bwd : w.nbwd;
+
+  PP_CUDA_CHECK(cudaMemsetAsync(o->status, 0, (size_t)s->B * sizeof(int), st));
+  int rc;
+  if ((rc = cifhr_launch(d_cif, hr, w.stage, *s, *c, *p, o->status, st))) return rc;
+  if ((rc = seeds_launch(d_cif, hr, seeds, n_seeds, w.stage, *s, *c, *p, o->status, st))) return rc;
+  if ((rc = caf_scored_launch(d_caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, *s, *c, *p,
+                              o->status, st)))
+    return rc;
+  AsmArgs a;
+  a.seeds = seeds; a.n_seeds = n_seeds;
+  a.fwd = fwd; a.bwd = bwd; a.nfwd = nfwd; a.nbwd = nbwd;
+  a.occ_cnt = w.occ_cnt;
+  a.pre_data = o->pre_data ? o->pre_data : w.pre_data;
+  a.pre_scales = o->pre_scales ? o->pre_scales : w.pre_scales;
+  a.pre_order = o->pre_order ? o->pre_order : w.pre_order;
+  a.n_pre = o->n_pre ? o->n_pre : w.n_pre;
+  a.status = o->status;
+  a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
+  a.hh = hr_h(*s); a.hw = hr_w(*s);
+  if ((rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
+  return nms_launch(a.pre_data, a.pre_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+                    o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+}
+
+#define PP_D2H(member, bytes)                                                                   \
+  if (h_out->member && d_out->member)                                                           \
+  PP_CUDA_CHECK(cudaMemcpyAsync(h_out->member, d_out->member, (bytes), cudaMemcpyDeviceToHost, st))
+
+int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, float *d_caf,
+                         const pp_skeleton *sk, const pp_outputs *d_out, const pp_outputs *h_out,
+                         void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                         const pp_params *p, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !h_cif || !h_caf || !d_cif || !d_caf || !d_out || !h_out)
+    return PP_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  size_t B = s->B, cells = (size_t)s->H * s->W;
+  PP_CUDA_CHECK(cudaMemcpyAsync(d_cif, h_cif, B * s->F * 5 * cells * sizeof(float),
+                                cudaMemcpyHostToDevice, st));
+  PP_CUDA_CHECK(cudaMemcpyAsync(d_caf, h_caf, B * s->L * 9 * cells * sizeof(float),
+                                cudaMemcpyHostToDevice, st));
+  int rc = pp_decode_batch(d_cif, d_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
+  if (rc) return rc;
+  size_t bc = B * c->ann_cap;
+  PP_D2H(ann_data, bc * s->F * 3 * sizeof(float));
+  PP_D2H(ann_scales, bc * s->F * sizeof(float));
+  PP_D2H(ann_score, bc * sizeof(double));
+  PP_D2H(ann_source, bc * sizeof(int));
+  PP_D2H(n_ann, B * sizeof(int));
+  PP_D2H(pre_data, bc * s->F * 3 * sizeof(float));
+  PP_D2H(pre_scales, bc * s->F * sizeof(float));
+  PP_D2H(pre_order, bc * s->F * 2 * sizeof(int));
+  PP_D2H(n_pre, B * sizeof(int));
+  PP_D2H(status, B * sizeof(int));
+  PP_D2H(seeds, B * c->seed_cap * 5 * sizeof(float));
+  PP_D2H(n_seeds, B * sizeof(int));
+  PP_D2H(caf_fwd, B * s->L * 9 * c->caf_cap * sizeof(float));
+  PP_D2H(caf_bwd, B * s->L * 9 * c->caf_cap * sizeof(float));
+  PP_D2H(n_caf_fwd, B * s->L * sizeof(int));
+  PP_D2H(n_caf_bwd, B * s->L * sizeof(int));
+  PP_D2H(hr, B * s->F * (size_t)hr_h(*s) * hr_w(*s) * sizeof(float));
+  PP_CUDA_CHECK(cudaStreamSynchronize(st));
+  if (h_out->status)
+    for (size_t b = 0; b < B; b++)
+      if (h_out->status[b] != 0) return PP_ERR_CAPACITY;
+  return PP_OK;
+}
+
+}  // extern "C"

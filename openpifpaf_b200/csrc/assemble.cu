@@ -1,0 +1,419 @@
+// assemble.cu -- greedy pose assembly with occupancy, on sm_100a.
+//
+// Replaces, for a whole batch, the serial part of CifCaf.__call__
+// (decoder/generator/cifcaf.py:84-108), CifCaf._grow / connection_value /
+// _grow_connection / _target_with_blend / _target_with_maxscore (:124-307),
+// caf_center_s (functional.pyx:338-359) and Occupancy (decoder/occupancy.py,
+// decoder/utils.py:61-66, functional.pyx:281-286).
+//
+// One CTA per image.  What is parallel inside an image:
+//   * "next seed that is not occupied" is a CTA-wide search over the sorted
+//     seed list -- occupancy only changes after a pose has been grown;
+//   * the occupancy map is never rasterised: Occupancy.get(f, x, y) is the
+//     number (mod 256, the reference's uint8 wrap) of Occupancy.set boxes of
+//     field f covering the cell, so each seed carries a uint8 counter that is
+//     bumped, CTA-wide, against the <= F boxes of the pose just finished;
+//   * the frontier is evaluated eagerly: when a joint is set, one WARP per
+//     outgoing edge scans the link's candidate list (lanes over candidates,
+//     per-lane top-2, butterfly merge), applies blend/max and the reverse
+//     match.  The reference evaluates lazily through a PriorityQueue whose
+//     unevaluated keys are upper bounds of the evaluated ones, so "always take
+//     the best evaluated edge whose target is still empty" visits the same
+//     edges in the same order (validated by the tests).
+//     Ties follow Python's tuple order (-score, (x, y, s, v), start, end).
+#include "common.cuh"
+#include "stages.cuh"
+
+namespace pp {
+
+constexpr int kAsmThreads = 256;
+constexpr int kAsmWarps = kAsmThreads / 32;
+constexpr int kMaxEdges = 2 * PP_MAX_L;
+
+struct Graph {
+  int F;
+  int8_t deg[PP_MAX_F];
+  int8_t nb_end[PP_MAX_F][PP_MAX_DEG];
+  int8_t nb_link[PP_MAX_F][PP_MAX_DEG];
+  int8_t nb_fwd[PP_MAX_F][PP_MAX_DEG];
+};
+
+struct CScale {
+  int has;
+  float v[PP_MAX_L];
+};
+
+// by_source tables of cifcaf.py:62-65 (dict semantics: a repeated (start, end)
+// pair overwrites the value and keeps its first position).
+int build_graph(const pp_skeleton &sk, int F, Graph *g) {
+  if (F > PP_MAX_F || sk.L > PP_MAX_L || sk.L < 0) return PP_ERR_ARG;
+  memset(g, 0, sizeof *g);
+  g->F = F;
+  for (int l = 0; l < sk.L; l++) {
+    int a = sk.joints[l][0] - 1, b = sk.joints[l][1] - 1;
+    if (a < 0 || b < 0 || a >= F || b >= F) return PP_ERR_ARG;
+    for (int dir = 0; dir < 2; dir++) {
+      int s = dir ? b : a, e = dir ? a : b, k;
+      for (k = 0; k < g->deg[s]; k++)
+        if (g->nb_end[s][k] == e) break;
+      if (k == g->deg[s]) {
+        if (k >= PP_MAX_DEG) return PP_ERR_ARG;
+        g->deg[s]++;
+      }
+      g->nb_end[s][k] = (int8_t)e;
+      g->nb_link[s][k] = (int8_t)l;
+      g->nb_fwd[s][k] = (int8_t)!dir;
+    }
+  }
+  return PP_OK;
+}
+
+struct Cand {      // (score, index) with the tie rule of the connection method
+  float s;
+  int i;
+};
+
+// blend: np.argsort ascending, take the last two => ties prefer the LARGER index
+// max:   np.argmax => ties prefer the SMALLER index
+__device__ __forceinline__ bool cand_better(Cand a, Cand b, int method) {
+  if (a.s > b.s) return true;
+  if (a.s < b.s) return false;
+  if (a.i < 0 || b.i < 0) return a.i >= 0 && b.i < 0;
+  return method == 1 ? a.i < b.i : a.i > b.i;
+}
+
+struct Xysv {
+  float x, y, s, v;
+};
+
+// _grow_connection (cifcaf.py:124-145), warp-collective; every lane returns the result.
+__device__ Xysv warp_grow_connection(float x, float y, float s, const float *__restrict__ rows,
+                                     int cap, int K, int method, int exp_mode) {
+  const int lane = lane_id();
+  const float box = __fmul_rn(2.0f, s);                           // sigma = 2.0 * xy_scale  :129
+  const float lox = __fsub_rn(x, box), hix = __fadd_rn(x, box);
+  const float loy = __fsub_rn(y, box), hiy = __fadd_rn(y, box);
+  const float sigma = __fmul_rn(0.5f, s);                         // :138
+  const float sig2 = __fmul_rn(sigma, sigma);
+  const float *cs = rows, *xs = rows + cap, *ys = rows + 2 * (size_t)cap;
+  Cand t1 = {-INFINITY, -1}, t2 = {-INFINITY, -1};
+  int cnt = 0;
+  for (int i = lane; i < K; i += 32) {
+    float cx = __ldg(xs + i), cy = __ldg(ys + i);
+    // caf_center_s: functional.pyx:346-353
+    if (cx < lox || cx > hix || cy < loy || cy > hiy) continue;
+    cnt++;
+    float dx = __fsub_rn(x, cx), dy = __fsub_rn(y, cy);
+    float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));     // :134
+    float arg = __fdiv_rn(__fmul_rn(-0.5f, __fmul_rn(d, d)), sig2);            // :139
+    float e = exp_mode ? pp_expf(arg) : expf(arg);
+    Cand c = {__fmul_rn(e, __ldg(cs + i)), i};
+    if (cand_better(c, t1, method)) { t2 = t1; t1 = c; }
+    else if (cand_better(c, t2, method)) { t2 = c; }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    Cand o1 = {__shfl_xor_sync(0xffffffffu, t1.s, off), __shfl_xor_sync(0xffffffffu, t1.i, off)};
+    Cand o2 = {__shfl_xor_sync(0xffffffffu, t2.s, off), __shfl_xor_sync(0xffffffffu, t2.i, off)};
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
+    Cand n1, n2;
+    if (cand_better(t1, o1, method)) { n1 = t1; n2 = cand_better(t2, o1, method) ? t2 : o1; }
+    else { n1 = o1; n2 = cand_better(t1, o2, method) ? t1 : o2; }
+    t1 = n1; t2 = n2;
+  }
+  Xysv out = {0.f, 0.f, 0.f, 0.f};
+  if (cnt == 0) return out;                                       // :130-131
+  const float *xt = rows + 5 * (size_t)cap, *yt = rows + 6 * (size_t)cap, *st = rows + 8 * (size_t)cap;
+  float x1 = __ldg(xt + t1.i), y1 = __ldg(yt + t1.i), s1 = __ldg(st + t1.i);
+  if (method == 1) {                                              // _target_with_maxscore :147-155
+    out.x = x1; out.y = y1; out.s = s1; out.v = t1.s;
+    return out;
+  }
+  out.x = x1; out.y = y1; out.s = s1; out.v = __fmul_rn(t1.s, 0.5f);
+  if (cnt == 1) return out;                                       // :164-170
+  if (t2.s < 0.01f || t2.s < __fmul_rn(0.5f, t1.s)) return out;   // :178-179
+  float x2 = __ldg(xt + t2.i), y2 = __ldg(yt + t2.i), s2 = __ldg(st + t2.i);
+  float ddx = __fsub_rn(x1, x2), ddy = __fsub_rn(y1, y2);
+  float d = __fsqrt_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)));   // :182
+  if (d > __fdiv_rn(s1, 2.0f)) return out;                        // :183-184
+  float den = __fadd_rn(t1.s, t2.s);
+  out.x = __fdiv_rn(__fadd_rn(__fmul_rn(t1.s, x1), __fmul_rn(t2.s, x2)), den);   // :186-191
+  out.y = __fdiv_rn(__fadd_rn(__fmul_rn(t1.s, y1), __fmul_rn(t2.s, y2)), den);
+  out.s = __fdiv_rn(__fadd_rn(__fmul_rn(t1.s, s1), __fmul_rn(t2.s, s2)), den);
+  out.v = __fmul_rn(0.5f, den);
+  return out;
+}
+
+struct CafLists {
+  const float *fwd, *bwd;   // (L,9,cap) of this image
+  const int *nfwd, *nbwd;   // (L)
+  int cap;
+};
+
+// connection_value (cifcaf.py:194-217), warp-collective.
+__device__ Xysv warp_connection_value(const float (*data)[3], const float *js, const Graph &g,
+                                      const CafLists &cf, int start, int k, bool reverse_match,
+                                      float keypoint_th, int method, int exp_mode) {
+  Xysv zero = {0.f, 0.f, 0.f, 0.f};
+  const int l = g.nb_link[start][k];
+  const bool fw = g.nb_fwd[start][k] != 0;
+  const float *rf = (fw ? cf.fwd : cf.bwd) + (size_t)l * 9 * cf.cap;
+  const float *rb = (fw ? cf.bwd : cf.fwd) + (size_t)l * 9 * cf.cap;
+  const int nf = fw ? cf.nfwd[l] : cf.nbwd[l];
+  const int nb = fw ? cf.nbwd[l] : cf.nfwd[l];
+  const float sx = data[start][0], sy = data[start][1], sv = data[start][2];
+  const float ss = js[start] > 0.0f ? js[start] : 0.0f;           // max(0.0, .)
+  Xysv nw = warp_grow_connection(sx, sy, ss, rf, cf.cap, nf, method, exp_mode);
+  float kp = __fsqrt_rn(__fmul_rn(nw.v, sv));                     // :201
+  if (kp < keypoint_th) return zero;
+  if (nw.v == 0.0f) return zero;
+  float st = nw.s > 0.0f ? nw.s : 0.0f;
+  if (reverse_match) {                                            // :208-215
+    Xysv rv = warp_grow_connection(nw.x, nw.y, st, rb, cf.cap, nb, method, exp_mode);
+    if (rv.s == 0.0f) return zero;
+    float dist = __fadd_rn(fabsf(__fsub_rn(sx, rv.x)), fabsf(__fsub_rn(sy, rv.y)));
+    if (dist > ss) return zero;
+  }
+  nw.v = kp;
+  return nw;
+}
+
+struct Pending {      // an evaluated frontier entry (-score, (x, y, s, v), start, end)
+  float key, x, y, s, v;
+  int start, end;
+};
+
+__device__ __forceinline__ bool pending_less(const Pending &a, const Pending &b) {
+  if (a.key != b.key) return a.key < b.key;
+  if (a.x != b.x) return a.x < b.x;
+  if (a.y != b.y) return a.y < b.y;
+  if (a.s != b.s) return a.s < b.s;
+  if (a.v != b.v) return a.v < b.v;
+  if (a.start != b.start) return a.start < b.start;
+  return a.end < b.end;
+}
+
+struct AsmShared {
+  float data[PP_MAX_F][3];
+  float js[PP_MAX_F];
+  Pending pend[kMaxEdges];
+  int n_pend;
+  uint32_t queued[PP_MAX_F];
+  int new_start[kMaxEdges], new_k[kMaxEdges];
+  int n_new;
+  int dec[PP_MAX_F][2];
+  int n_dec;
+  int best;
+  long long box[PP_MAX_F][4];
+  int box_valid[PP_MAX_F];
+  int found;
+  int warp_min[kAsmWarps];
+};
+
+// add_to_frontier (cifcaf.py:251-263), run by one thread.
+__device__ void queue_edges(AsmShared &sh, const Graph &g, int start) {
+  for (int k = 0; k < g.deg[start]; k++) {
+    int end = g.nb_end[start][k];
+    if (sh.data[end][2] > 0.0f) continue;
+    if (sh.queued[start] & (1u << end)) continue;
+    sh.queued[start] |= 1u << end;
+    sh.new_start[sh.n_new] = start;
+    sh.new_k[sh.n_new] = k;
+    sh.n_new++;
+  }
+}
+
+// _grow (cifcaf.py:247-307) in its eager form; CTA-collective.
+__device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const CafLists &cf,
+                     bool reverse_match, const pp_params &p) {
+  const int warp = warp_id(), lane = lane_id();
+  if (threadIdx.x == 0) {
+    sh.n_pend = 0;
+    sh.n_new = 0;
+    for (int j = 0; j < g.F; j++) sh.queued[j] = 0u;
+    for (int j = 0; j < g.F; j++) {                               // :288-291
+      if (sh.data[j][2] == 0.0f) continue;
+      queue_edges(sh, g, j);
+    }
+  }
+  __syncthreads();
+  for (;;) {
+    // evaluate the newly queued edges, one warp each
+    const int n_new = sh.n_new, base = sh.n_pend;
+    for (int e = warp; e < n_new; e += kAsmWarps) {
+      int start = sh.new_start[e], k = sh.new_k[e];
+      Xysv r = warp_connection_value(sh.data, sh.js, g, cf, start, k, reverse_match,
+                                     p.keypoint_threshold, p.connection_method, p.exp_mode);
+      if (lane == 0) {
+        Pending &q = sh.pend[base + e];
+        float score = r.v;
+        if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);   // :282-284
+        q.key = -score; q.x = r.x; q.y = r.y; q.s = r.s; q.v = r.v;
+        q.start = start; q.end = (r.v == 0.0f) ? -1 : g.nb_end[start][k];          // :277-278
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {
+      // best evaluated entry whose target is still empty (frontier_get + :297-298)
+      const int n_pend = base + n_new;
+      int best = -1;
+      for (int i = lane; i < n_pend; i += 32) {
+        const Pending &q = sh.pend[i];
+        if (q.end < 0 || sh.data[q.end][2] > 0.0f) continue;
+        if (best < 0 || pending_less(q, sh.pend[best])) best = i;
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        int o = __shfl_xor_sync(0xffffffffu, best, off);
+        if (o >= 0 && (best < 0 || pending_less(sh.pend[o], sh.pend[best]))) best = o;
+      }
+      if (lane == 0) {
+        sh.n_pend = n_pend;
+        sh.n_new = 0;
+        sh.best = best;
+        if (best >= 0) {
+          const Pending q = sh.pend[best];
+          sh.data[q.end][0] = q.x; sh.data[q.end][1] = q.y; sh.data[q.end][2] = q.v;   // :300-302
+          sh.js[q.end] = q.s;
+          sh.dec[sh.n_dec][0] = q.start; sh.dec[sh.n_dec][1] = q.end;                  // :303-304
+          sh.n_dec++;
+          sh.pend[best].end = -1;
+          queue_edges(sh, g, q.end);                                                   // :305
+        }
+      }
+    }
+    __syncthreads();
+    if (sh.best < 0) break;
+  }
+}
+
+// round(np.float32) -> Python int (half to even), clamped like the oracle.
+__device__ __forceinline__ long long py_round(float v) {
+  double r = rint((double)v);
+  if (r > 4e18) r = 4e18;
+  if (r < -4e18) r = -4e18;
+  return (long long)r;
+}
+
+// Occupancy.set box (occupancy.py:31-39 + utils.py:61-66) for a map of (oh, ow) cells.
+__device__ __forceinline__ void occupancy_box(float x, float y, float sigma, long long ow,
+                                              long long oh, long long *box) {
+  long long xi = py_round(__fdiv_rn(x, 2.0f)), yi = py_round(__fdiv_rn(y, 2.0f));
+  float shalf = __fdiv_rn(sigma, 2.0f);
+  long long si = py_round(shalf > 2.0f ? shalf : 2.0f);
+  long long minx = xi - si > 0 ? xi - si : 0;
+  long long miny = yi - si > 0 ? yi - si : 0;
+  long long t = xi + si + 1 < ow ? xi + si + 1 : ow;
+  long long maxx = minx + 1 > t ? minx + 1 : t;
+  t = yi + si + 1 < oh ? yi + si + 1 : oh;
+  long long maxy = miny + 1 > t ? miny + 1 : t;
+  if (maxx > ow) maxx = ow;      // numpy slicing clamps to the array
+  if (maxy > oh) maxy = oh;
+  box[0] = minx; box[1] = maxx; box[2] = miny; box[3] = maxy;
+}
+
+// Occupancy.get cell (occupancy.py:41-47 + functional.pyx:281-286)
+__device__ __forceinline__ void occupancy_cell(float x, float y, long long ow, long long oh,
+                                               long long *cx, long long *cy) {
+  *cx = (long long)clipf(__fdiv_rn(x, 2.0f), 0.0f, (float)(ow - 1));
+  *cy = (long long)clipf(__fdiv_rn(y, 2.0f), 0.0f, (float)(oh - 1));
+}
+
+
+__global__ void __launch_bounds__(kAsmThreads)
+assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
+  __shared__ AsmShared sh;
+  const int b = blockIdx.x;
+  const int F = g.F;
+  const float *seeds = a.seeds + (size_t)b * a.seed_cap * 5;
+  const int n_seeds = min(a.n_seeds[b], a.seed_cap);
+  uint8_t *occ = a.occ_cnt + (size_t)b * a.seed_cap;
+  CafLists cf = {a.fwd + (size_t)b * a.L * 9 * a.caf_cap, a.bwd + (size_t)b * a.L * 9 * a.caf_cap,
+                 a.nfwd + (size_t)b * a.L, a.nbwd + (size_t)b * a.L, a.caf_cap};
+  // Occupancy(cifhr.accumulated.shape, 2, min_scale=4): cifcaf.py:84, occupancy.py:21-25
+  const long long oh = (long long)((double)a.hh / 2.0), ow = (long long)((double)a.hw / 2.0);
+  float *pre_data = a.pre_data + (size_t)b * a.ann_cap * F * 3;
+  float *pre_scales = a.pre_scales + (size_t)b * a.ann_cap * F;
+  int *pre_order = a.pre_order ? a.pre_order + (size_t)b * a.ann_cap * F * 2 : nullptr;
+
+  for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) occ[i] = 0;
+  __syncthreads();
+
+  int n_ann = 0, cursor = 0;
+  for (;;) {
+    // ---- next seed whose cell is free (cifcaf.py:100-102) -------------------
+    int found = -1;
+    for (int base = cursor; base < n_seeds; base += blockDim.x) {
+      int i = base + threadIdx.x;
+      bool hit = i < n_seeds && occ[i] == 0;
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (lane_id() == 0) sh.warp_min[warp_id()] = m ? (base + warp_id() * 32 + __ffs(m) - 1) : -1;
+      __syncthreads();
+      for (int w = 0; w < kAsmWarps; w++)
+        if (sh.warp_min[w] >= 0) { found = sh.warp_min[w]; break; }
+      __syncthreads();
+      if (found >= 0) break;
+    }
+    if (found < 0) break;
+    cursor = found + 1;
+    if (n_ann >= a.ann_cap) {
+      if (threadIdx.x == 0) atomicOr(&a.status[b], PP_STATUS_ANN_OVERFLOW);
+      break;
+    }
+    // ---- new annotation from the seed (:104-105) ---------------------------
+    for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = 0.0f;
+    for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = 0.0f;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const float *sd = seeds + (size_t)found * 5;
+      int f = (int)sd[1];
+      sh.data[f][0] = sd[2]; sh.data[f][1] = sd[3]; sh.data[f][2] = sd[0];
+      sh.js[f] = sd[4];
+      sh.n_dec = 0;
+    }
+    __syncthreads();
+    grow(sh, g, cscale, cf, true, p);                             // :106
+    // ---- store + mark_occupied (:87-93, :107-108) -------------------------
+    for (int i = threadIdx.x; i < F * 3; i += blockDim.x)
+      pre_data[(size_t)n_ann * F * 3 + i] = (&sh.data[0][0])[i];
+    for (int i = threadIdx.x; i < F; i += blockDim.x) {
+      pre_scales[(size_t)n_ann * F + i] = sh.js[i];
+      if (pre_order) {
+        pre_order[((size_t)n_ann * F + i) * 2] = i < sh.n_dec ? sh.dec[i][0] : -1;
+        pre_order[((size_t)n_ann * F + i) * 2 + 1] = i < sh.n_dec ? sh.dec[i][1] : -1;
+      }
+      sh.box_valid[i] = sh.data[i][2] != 0.0f;
+      if (sh.box_valid[i]) occupancy_box(sh.data[i][0], sh.data[i][1], sh.js[i], ow, oh, sh.box[i]);
+    }
+    n_ann++;
+    __syncthreads();
+    for (int i = cursor + threadIdx.x; i < n_seeds; i += blockDim.x) {
+      const float *sd = seeds + (size_t)i * 5;
+      int f = (int)__ldg(sd + 1);
+      if (!sh.box_valid[f]) continue;
+      long long cx, cy;
+      occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
+      if (cx >= sh.box[f][0] && cx < sh.box[f][1] && cy >= sh.box[f][2] && cy < sh.box[f][3])
+        occ[i] = (uint8_t)(occ[i] + 1);                           // uint8 += 1 wraps (utils.py:66)
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) a.n_pre[b] = n_ann;
+}
+
+int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
+                    cudaStream_t st) {
+  Graph g;
+  int rc = build_graph(sk, F, &g);
+  if (rc) return rc;
+  if (p.greedy || p.force_complete) return PP_ERR_ARG;   // not in this build yet
+  CScale cs;
+  memset(&cs, 0, sizeof cs);
+  cs.has = sk.has_confidence_scales;
+  for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  assemble_kernel<<<B, kAsmThreads, 0, st>>>(args, g, cs, p);
+  PP_LAUNCH_CHECK("assemble_kernel");
+  return PP_OK;
+}
+
+}  // namespace pp

@@ -1,0 +1,107 @@
+// common.cuh -- shared device helpers for libpifpaf_b200 (sm_100a only).
+//
+// Parity rule for this library: every parity-critical float expression is a
+// sequence of single IEEE-754 binary32 operations in the reference's order.
+// The whole library is compiled with -fmad=false (no FMA contraction), and the
+// places that matter additionally spell out __fmul_rn/__fadd_rn/__fdiv_rn so the
+// intent survives a change of flags.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/pifpaf_b200.h"
+#include "../../include/pifpaf_detmath.h"
+
+#ifndef __CUDA_ARCH__
+#define PP_ARCH_OK 1
+#elif __CUDA_ARCH__ >= 1000
+#define PP_ARCH_OK 1
+#else
+#error "libpifpaf_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace pp {
+
+constexpr int kWarp = 32;
+
+// ---- error plumbing -------------------------------------------------------
+void set_cuda_error(cudaError_t e, const char *where);
+
+#define PP_CUDA_CHECK(expr)                          \
+  do {                                               \
+    cudaError_t e__ = (expr);                        \
+    if (e__ != cudaSuccess) {                        \
+      pp::set_cuda_error(e__, #expr);                \
+      return PP_ERR_CUDA;                            \
+    }                                                \
+  } while (0)
+
+#define PP_LAUNCH_CHECK(name)                        \
+  do {                                               \
+    cudaError_t e__ = cudaPeekAtLastError();         \
+    if (e__ != cudaSuccess) {                        \
+      pp::set_cuda_error(e__, name);                 \
+      return PP_ERR_CUDA;                            \
+    }                                                \
+  } while (0)
+
+inline int hr_h(const pp_shape &s) { return (s.H - 1) * s.stride + 1; }
+inline int hr_w(const pp_shape &s) { return (s.W - 1) * s.stride + 1; }
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int num_sms();
+
+// ---- exact float helpers ----------------------------------------------------
+// clip() of functional.pyx:67-68: fmax(minv, fmin(maxv, v)); NaN -> maxv.
+__device__ __forceinline__ float clipf(float v, float lo, float hi) {
+  return fmaxf(lo, fminf(hi, v));
+}
+
+// approx_exp() of functional.pyx:57-64.  The reference evaluates
+// (float)(1.0 + (double)x / 8.0); x/8 is exact and the double sum is either
+// exact or far from a float rounding boundary, so one float add is identical.
+__device__ __forceinline__ float approx_exp(float x) {
+  if (x > 2.0f || x < -2.0f) return 0.0f;
+  x = __fadd_rn(1.0f, __fmul_rn(x, 0.125f));
+  x = __fmul_rn(x, x);
+  x = __fmul_rn(x, x);
+  x = __fmul_rn(x, x);
+  return x;
+}
+
+// scalar_values() of functional.pyx:231-244 for one point.
+__device__ __forceinline__ float scalar_value_at(const float *__restrict__ field, int fh, int fw,
+                                                 float x, float y, float dflt) {
+  float maxx = (float)fw - 1.0f, maxy = (float)fh - 1.0f;
+  if (x < 0.0f || y < 0.0f || x > maxx || y > maxy) return dflt;
+  return __ldg(field + (size_t)(int)y * fw + (int)x);
+}
+
+// ---- warp / block primitives ---------------------------------------------
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ int warp_id() { return threadIdx.x >> 5; }
+
+// Exclusive prefix of a per-thread 0/1 flag over the whole CTA, in thread
+// order.  `warp_tot` is shared scratch of (blockDim.x / 32) ints.  Returns the
+// thread's offset; *total receives the CTA-wide count.  Contains two
+// __syncthreads().
+__device__ __forceinline__ int block_flag_scan(bool flag, int *warp_tot, int *total) {
+  unsigned m = __ballot_sync(0xffffffffu, flag);
+  int lane = lane_id(), w = warp_id();
+  int in_warp = __popc(m & ((1u << lane) - 1u));
+  if (lane == 0) warp_tot[w] = __popc(m);
+  __syncthreads();
+  int nw = blockDim.x >> 5;
+  int base = 0, tot = 0;
+  for (int i = 0; i < nw; i++) {
+    int t = warp_tot[i];
+    if (i < w) base += t;
+    tot += t;
+  }
+  __syncthreads();
+  *total = tot;
+  return base + in_warp;
+}
+
+}  // namespace pp

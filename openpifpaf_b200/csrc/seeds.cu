@@ -1,0 +1,187 @@
+// seeds.cu -- CifSeeds on sm_100a.
+//
+// Replaces decoder/cif_seeds.py:23-54 (CifSeeds.fill_cif / get) and the
+// scalar_values gather of functional.pyx:231-244.
+//
+//   K3 seeds_collect_kernel  one thread per CIF cell: threshold, hr gather,
+//                            v = 0.9 hr + 0.1 c, threshold, warp-aggregated
+//                            append of (v, f, x, y, s) to the image's raw list.
+//   K3b seeds_sort_kernel    one CTA per image: bitonic sort of 64-bit keys
+//                            [orderable(v):32 | f:8 | raw index:24] in shared
+//                            memory (L2-resident global scratch beyond 4 Ki seeds); keys
+//                            that tie on (v, f) are ordered by (x, y, s) read
+//                            from the raw records, which reproduces Python's
+//                            sorted(tuples, reverse=True) exactly (cif_seeds.py:54).
+//
+// This snapshot of the reference has no 3x3 max-pool seed NMS
+// (cif_seeds.py:23-50), so neither has this kernel.
+#include "common.cuh"
+#include "stages.cuh"
+
+namespace pp {
+
+constexpr int kCollectThreads = 256;
+constexpr int kSortThreads = 1024;
+constexpr int kSortSmemKeys = 4096;    // 32 KiB of dynamic shared memory; larger lists sort in L2
+
+__device__ __forceinline__ uint32_t orderable(float v) {
+  uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(kCollectThreads)
+seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr,
+                     float *__restrict__ raw, int *__restrict__ n_raw, pp_shape s, int cap, int hh,
+                     int hw, float th, float score_scale, float min_scale_over_stride,
+                     int use_min_scale, uint32_t seed_mask) {
+  const int n = s.H * s.W;
+  const int blocks_per_field = (n + kCollectThreads - 1) / kCollectThreads;
+  const int bf = blockIdx.x / blocks_per_field;
+  const int c = (blockIdx.x - bf * blocks_per_field) * kCollectThreads + threadIdx.x;
+  const int b = bf / s.F, f = bf - b * s.F;
+  if (seed_mask != 0u && !((seed_mask >> f) & 1u)) return;        // cif_seeds.py:29-30
+  const float *p = cif + (size_t)bf * 5 * n;
+  const float stride = (float)s.stride;
+  bool keep = false;
+  float v = 0.f, x = 0.f, y = 0.f, sc = 0.f;
+  if (c < n) {
+    float conf = __ldg(p + c);
+    if (conf > th) {                                              // :31
+      sc = __ldg(p + 4 * n + c);
+      if (!use_min_scale || sc > min_scale_over_stride) {         // :32-33
+        x = __fmul_rn(__ldg(p + n + c), stride);
+        y = __fmul_rn(__ldg(p + 2 * n + c), stride);
+        float hv = scalar_value_at(hr + (size_t)bf * hh * hw, hh, hw, x, y, 0.0f);   // :37
+        v = __fadd_rn(__fmul_rn(0.9f, hv), __fmul_rn(0.1f, conf));                  // :38
+        if (score_scale != 1.0f) v = __fmul_rn(v, score_scale);   // :41-42
+        keep = v > th;                                            // :43
+      }
+    }
+  }
+  // warp-aggregated slot allocation (order is irrelevant: the list is sorted next)
+  unsigned m = __ballot_sync(0xffffffffu, keep);
+  if (m == 0u) return;
+  int lane = lane_id();
+  int leader = __ffs(m) - 1;
+  int base = 0;
+  if (lane == leader) base = atomicAdd(&n_raw[b], __popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (keep) {
+    int slot = base + __popc(m & ((1u << lane) - 1u));
+    if (slot < cap) {
+      float *o = raw + ((size_t)b * cap + slot) * 5;
+      o[0] = v; o[1] = (float)f; o[2] = x; o[3] = y; o[4] = __fmul_rn(sc, stride);   // :44,47
+    }
+  }
+}
+
+// strict "a sorts before b" for descending tuple order (v, f, x, y, s)
+__device__ __forceinline__ bool seed_before(uint64_t a, uint64_t b, const float *__restrict__ raw) {
+  uint64_t ha = a >> 24, hb = b >> 24;
+  if (ha != hb) return ha > hb;
+  if (a == b) return false;
+  const float *pa = raw + (size_t)(a & 0xffffffu) * 5, *pb = raw + (size_t)(b & 0xffffffu) * 5;
+#pragma unroll
+  for (int i = 2; i < 5; i++) {
+    float xa = pa[i], xb = pb[i];
+    if (xa > xb) return true;
+    if (xa < xb) return false;
+  }
+  return false;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_raw,
+                  float *__restrict__ out_all, int *__restrict__ n_out, uint64_t *__restrict__ scratch,
+                  int cap, int scratch_stride, int *__restrict__ status) {
+  extern __shared__ uint64_t s_keys[];
+  const int b = blockIdx.x;
+  int n = n_raw[b];
+  if (n > cap) {
+    if (threadIdx.x == 0) atomicOr(&status[b], PP_STATUS_SEED_OVERFLOW);
+    n = cap;
+  }
+  const float *raw = raw_all + (size_t)b * cap * 5;
+  float *out = out_all + (size_t)b * cap * 5;
+  int npad = 1;
+  while (npad < n) npad <<= 1;
+  uint64_t *keys = (npad <= kSortSmemKeys) ? s_keys : scratch + (size_t)b * scratch_stride;
+
+  for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+    uint64_t k = 0;
+    if (i < n) {
+      const float *r = raw + (size_t)i * 5;
+      k = ((uint64_t)orderable(r[0]) << 32) | ((uint64_t)((uint32_t)r[1] & 0xffu) << 24) |
+          (uint64_t)(uint32_t)i;
+    }
+    keys[i] = k;
+  }
+  __syncthreads();
+  for (int k = 2; k <= npad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+        int l = i ^ j;
+        if (l > i) {
+          uint64_t a = keys[i], c = keys[l];
+          bool desc_block = (i & k) == 0;   // this block ends up descending
+          bool swap = desc_block ? seed_before(c, a, raw) : seed_before(a, c, raw);
+          if (swap) { keys[i] = c; keys[l] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float *r = raw + (size_t)(keys[i] & 0xffffffu) * 5;
+    float *o = out + (size_t)i * 5;
+#pragma unroll
+    for (int c = 0; c < 5; c++) o[c] = r[c];
+  }
+  if (threadIdx.x == 0) n_out[b] = n;
+}
+
+struct SeedsWs {
+  float *raw;        // (B,cap,5)
+  int *n_raw;        // (B)
+  uint64_t *scratch; // (B,pow2(cap)) only used beyond kSortSmemKeys
+  int scratch_stride;
+};
+
+static int pow2_ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c) {
+  size_t n = 0;
+  n += align_up((size_t)s.B * c.seed_cap * 5 * sizeof(float), 256);
+  n += align_up((size_t)s.B * sizeof(int), 256);
+  int p2 = pow2_ceil(c.seed_cap);
+  if (p2 > kSortSmemKeys) n += align_up((size_t)s.B * p2 * sizeof(uint64_t), 256);
+  return n;
+}
+
+int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
+                 const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
+                 cudaStream_t st) {
+  if (c.seed_cap >= (1 << 24)) return PP_ERR_ARG;
+  SeedsWs w;
+  char *q = (char *)d_ws;
+  w.raw = (float *)q; q += align_up((size_t)s.B * c.seed_cap * 5 * sizeof(float), 256);
+  w.n_raw = (int *)q; q += align_up((size_t)s.B * sizeof(int), 256);
+  w.scratch = (uint64_t *)q;
+  w.scratch_stride = pow2_ceil(c.seed_cap);
+  const int hh = hr_h(s), hw = hr_w(s), n = s.H * s.W;
+  PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
+  int blocks = s.B * s.F * ((n + kCollectThreads - 1) / kCollectThreads);
+  seeds_collect_kernel<<<blocks, kCollectThreads, 0, st>>>(
+      d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
+      p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, (uint32_t)p.reserved);
+  PP_LAUNCH_CHECK("seeds_collect_kernel");
+  // small capacities only need a small shared array
+  size_t need = (size_t)(w.scratch_stride <= kSortSmemKeys ? w.scratch_stride : kSortSmemKeys) *
+                sizeof(uint64_t);
+  seeds_sort_kernel<<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
+                                                     c.seed_cap, w.scratch_stride, d_status);
+  PP_LAUNCH_CHECK("seeds_sort_kernel");
+  return PP_OK;
+}
+
+}  // namespace pp

@@ -1,0 +1,216 @@
+"""Device-side plumbing of the decoder: buffers, parameter marshalling, calls
+into libpifpaf_b200.so.  PyTorch is used for device memory, pinned host memory
+and streams only; every computation happens in the CUDA library.
+"""
+import ctypes as C
+import dataclasses
+from typing import Optional
+
+import numpy as np
+import torch
+
+from .. import _lib
+
+
+@dataclasses.dataclass
+class DecoderParams:
+    """Python mirror of ``pp_params``; field meaning as in include/pifpaf_b200.h."""
+    cif_threshold: float = 0.1
+    seed_threshold: float = 0.2
+    seed_score_scale: float = 1.0
+    caf_threshold: float = 0.1
+    cif_floor: float = 0.1
+    keypoint_threshold: float = 0.001
+    nms_keypoint_threshold: float = 0.001
+    nms_instance_threshold: float = 0.0
+    nms_suppression: float = 0.0
+    cif_min_scale: float = 0.0
+    caf_min_distance: float = 0.0
+    caf_max_distance: Optional[float] = None
+    connection_method: str = 'blend'
+    greedy: bool = False
+    force_complete: bool = False
+    nms: bool = True
+    deterministic_exp: bool = True
+    seed_mask: Optional[list] = None
+
+    def to_c(self):
+        p = _lib.Params()
+        _lib.lib().pp_default_params(C.byref(p))
+        p.nms_instance_threshold = float(self.nms_instance_threshold)
+        p.cif_threshold = self.cif_threshold
+        p.seed_threshold = self.seed_threshold
+        p.seed_score_scale = self.seed_score_scale
+        p.caf_threshold = self.caf_threshold
+        p.cif_floor = self.cif_floor
+        # (1.0 - cif_floor) is a Python float in the reference (caf_scored.py:64)
+        p.cif_floor_compl = float(np.float32(1.0 - self.cif_floor))
+        p.keypoint_threshold = self.keypoint_threshold
+        p.nms_keypoint_threshold = self.nms_keypoint_threshold
+        p.nms_suppression = self.nms_suppression
+        p.cif_min_scale = self.cif_min_scale or 0.0
+        p.caf_min_distance = self.caf_min_distance or 0.0
+        p.caf_max_distance = self.caf_max_distance or 0.0
+        if self.connection_method not in ('blend', 'max'):
+            raise Exception('connection method not known')   # cifcaf.py:145
+        p.connection_method = 1 if self.connection_method == 'max' else 0
+        p.greedy = int(bool(self.greedy))
+        p.force_complete = int(bool(self.force_complete))
+        p.nms = int(bool(self.nms))
+        p.exp_mode = 1 if self.deterministic_exp else 0
+        mask = 0
+        if self.seed_mask is not None:
+            for i, m in enumerate(self.seed_mask):
+                if m:
+                    mask |= 1 << i
+            if mask == 0:
+                mask = 1 << 31     # "no field seeds": bit outside any valid field
+        p.reserved = mask if mask < (1 << 31) else mask - (1 << 32)
+        return p
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class BatchBuffers:
+    """Caller-owned device (and optional pinned host) buffers for one batch shape."""
+
+    def __init__(self, shape, caps, device, *, keep=('ann',), host=False):
+        B, F, L = shape.B, shape.F, shape.L
+        hh, hw = (shape.H - 1) * shape.stride + 1, (shape.W - 1) * shape.stride + 1
+        self.shape, self.caps, self.device = shape, caps, device
+        dev = dict(device=device)
+        f32, i32, f64 = torch.float32, torch.int32, torch.float64
+        t = {}
+        t['ann_data'] = torch.empty((B, caps.ann_cap, F, 3), dtype=f32, **dev)
+        t['ann_scales'] = torch.empty((B, caps.ann_cap, F), dtype=f32, **dev)
+        t['ann_score'] = torch.empty((B, caps.ann_cap), dtype=f64, **dev)
+        t['ann_source'] = torch.empty((B, caps.ann_cap), dtype=i32, **dev)
+        t['n_ann'] = torch.zeros((B,), dtype=i32, **dev)
+        t['status'] = torch.zeros((B,), dtype=i32, **dev)
+        t['pre_data'] = torch.empty((B, caps.ann_cap, F, 3), dtype=f32, **dev)
+        t['pre_scales'] = torch.empty((B, caps.ann_cap, F), dtype=f32, **dev)
+        t['pre_order'] = torch.empty((B, caps.ann_cap, F, 2), dtype=i32, **dev)
+        t['n_pre'] = torch.zeros((B,), dtype=i32, **dev)
+        if 'hr' in keep:
+            t['hr'] = torch.empty((B, F, hh, hw), dtype=f32, **dev)
+        if 'seeds' in keep:
+            t['seeds'] = torch.empty((B, caps.seed_cap, 5), dtype=f32, **dev)
+            t['n_seeds'] = torch.zeros((B,), dtype=i32, **dev)
+        if 'caf' in keep:
+            t['caf_fwd'] = torch.empty((B, L, 9, caps.caf_cap), dtype=f32, **dev)
+            t['caf_bwd'] = torch.empty((B, L, 9, caps.caf_cap), dtype=f32, **dev)
+            t['n_caf_fwd'] = torch.zeros((B, L), dtype=i32, **dev)
+            t['n_caf_bwd'] = torch.zeros((B, L), dtype=i32, **dev)
+        self.dev = t
+        self.d_out = _lib.Outputs()
+        for name, tensor in t.items():
+            setattr(self.d_out, name, tensor.data_ptr())
+        ws_bytes = _lib.lib().pp_workspace_bytes(C.byref(shape), C.byref(caps))
+        if ws_bytes == 0:
+            raise _lib.PifPafError(_lib.PP_ERR_ARG, 'bad shape/caps for workspace')
+        self.ws = torch.empty((ws_bytes,), dtype=torch.uint8, **dev)
+        self.ws_bytes = ws_bytes
+        self.host = None
+        self.h_out = None
+        self.d_cif = self.d_caf = None
+        if host:
+            self.enable_host()
+
+    HOST_COPIED = ('ann_data', 'ann_scales', 'ann_score', 'ann_source', 'n_ann', 'pre_data',
+                   'pre_order', 'n_pre', 'status')
+
+    def enable_host(self):
+        """Pinned host mirrors + device staging for pp_decode_batch_host."""
+        if self.host is not None:
+            return
+        s = self.shape
+        self.host = {n: torch.empty(self.dev[n].shape, dtype=self.dev[n].dtype, pin_memory=True)
+                     for n in self.HOST_COPIED}
+        self.h_out = _lib.Outputs()
+        for name, tensor in self.host.items():
+            setattr(self.h_out, name, tensor.data_ptr())
+        self.d_cif = torch.empty((s.B, s.F, 5, s.H, s.W), dtype=torch.float32, device=self.device)
+        self.d_caf = torch.empty((s.B, s.L, 9, s.H, s.W), dtype=torch.float32, device=self.device)
+
+
+class DeviceDecoder:
+    """Runs the CUDA decode for batches of one skeleton; caches buffers per shape."""
+
+    def __init__(self, skeleton, *, confidence_scales=None, stride=8, ann_cap=256, device=None):
+        self.skeleton = [tuple(int(j) for j in link) for link in skeleton]
+        self.c_skeleton = _lib.Skeleton.from_list(self.skeleton, confidence_scales)
+        self.stride = stride
+        self.ann_cap = ann_cap
+        self.device = device
+        self._buffers = {}
+        _lib.lib()   # fail loudly right here if the CUDA library is missing
+
+    def _device(self):
+        if self.device is None:
+            if not torch.cuda.is_available():
+                raise RuntimeError('openpifpaf_b200 needs a CUDA device (B200); there is no CPU path')
+            self.device = torch.device('cuda', torch.cuda.current_device())
+        return self.device
+
+    def buffers(self, B, F, H, W, *, keep=('ann',), host=False):
+        key = (B, F, H, W, tuple(sorted(keep)))
+        buf = self._buffers.get(key)
+        if buf is None:
+            shape = _lib.Shape(B, F, len(self.skeleton), H, W, self.stride)
+            caps = _lib.Caps()
+            _lib.check(_lib.lib().pp_default_caps(C.byref(shape), C.byref(caps)))
+            caps.ann_cap = self.ann_cap
+            buf = BatchBuffers(shape, caps, self._device(), keep=keep)
+            self._buffers[key] = buf
+        if host:
+            buf.enable_host()
+        return buf
+
+    def run_device(self, cif, caf, params: DecoderParams, *, keep=('ann',)):
+        """cif (B,F,5,H,W), caf (B,L,9,H,W): CUDA float32 tensors. Enqueues only."""
+        assert cif.is_cuda and caf.is_cuda and cif.dtype == torch.float32 and caf.dtype == torch.float32
+        cif, caf = cif.contiguous(), caf.contiguous()
+        B, F, five, H, W = cif.shape
+        assert five == 5 and caf.shape == (B, len(self.skeleton), 9, H, W), (cif.shape, caf.shape)
+        buf = self.buffers(B, F, H, W, keep=keep)
+        p = params.to_c()
+        rc = _lib.lib().pp_decode_batch(_ptr(cif), _ptr(caf), C.byref(self.c_skeleton),
+                                        C.byref(buf.d_out), _ptr(buf.ws), buf.ws_bytes,
+                                        C.byref(buf.shape), C.byref(buf.caps), C.byref(p),
+                                        _stream_ptr())
+        _lib.check(rc)
+        return buf
+
+    def run_host(self, cif, caf, params: DecoderParams, *, keep=('ann',)):
+        """cif, caf: host float32 arrays/tensors (ideally pinned). Synchronous."""
+        cif_t = torch.as_tensor(cif)
+        caf_t = torch.as_tensor(caf)
+        assert cif_t.dtype == torch.float32 and caf_t.dtype == torch.float32
+        cif_t, caf_t = cif_t.contiguous(), caf_t.contiguous()
+        B, F, five, H, W = cif_t.shape
+        assert five == 5 and caf_t.shape == (B, len(self.skeleton), 9, H, W), (cif_t.shape, caf_t.shape)
+        buf = self.buffers(B, F, H, W, keep=keep, host=True)
+        p = params.to_c()
+        with torch.cuda.device(buf.device):
+            rc = _lib.lib().pp_decode_batch_host(
+                _ptr(cif_t), _ptr(caf_t), _ptr(buf.d_cif), _ptr(buf.d_caf),
+                C.byref(self.c_skeleton), C.byref(buf.d_out), C.byref(buf.h_out), _ptr(buf.ws),
+                buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), _stream_ptr())
+        if rc == _lib.PP_ERR_CAPACITY:
+            raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
+        _lib.check(rc)
+        return buf
+
+
+def describe_status(status):
+    bad = {}
+    for b, word in enumerate(np.asarray(status).tolist()):
+        if word:
+            bad[b] = [name for bit, name in _lib.STATUS_BITS.items() if word & bit]
+    return 'capacity exceeded in images %s' % bad

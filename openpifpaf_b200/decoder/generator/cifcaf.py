@@ -1,0 +1,196 @@
+"""CifCaf: composite intensity / association fields -> person annotations.
+
+Drop-in for the reference's ``decoder/generator/cifcaf.py:24-351``: same
+constructor, class-attribute knobs (read at call time), ``__call__(fields)``
+and ``batch(model, images)``.  The reference runs CifHr, CifSeeds, CafScored,
+the seed loop with ``_grow`` + ``Occupancy`` and keypoint NMS on the CPU, one
+image per worker process; here one ``pp_decode_batch`` call does all of it for
+the whole batch on the GPU (csrc/*.cu) and only the finished annotations come
+back to the host.
+"""
+from collections import defaultdict
+import logging
+import time
+
+import numpy as np
+import torch
+
+from ...annotation import Annotation
+from .. import nms as nms_module
+from ..caf_scored import CafScored
+from ..cif_hr import CifHr
+from ..cif_seeds import CifSeeds
+from ..engine import DecoderParams, DeviceDecoder, describe_status
+from ..field_config import FieldConfig
+from ... import _lib
+from .generator import Generator
+
+LOG = logging.getLogger(__name__)
+
+
+class CifCaf(Generator):
+    """Generate CifCaf poses from fields.
+
+    :param nms: set to None to switch off non-maximum suppression.
+    """
+    connection_method = 'blend'
+    occupancy_visualizer = None
+    force_complete = False
+    greedy = False
+    keypoint_threshold = 0.0
+    deterministic_exp = True    # exp() of include/pifpaf_detmath.h (bit-reproducible)
+    max_annotations = 256       # per-image capacity of the result buffers
+
+    def __init__(self, field_config: FieldConfig, *,
+                 keypoints,
+                 skeleton,
+                 out_skeleton=None,
+                 confidence_scales=None,
+                 worker_pool=None,
+                 nms=True):
+        super().__init__(worker_pool)
+        if nms is True:
+            nms = nms_module.Keypoints()
+        self.field_config = field_config
+        self.keypoints = keypoints
+        self.skeleton = skeleton
+        self.skeleton_m1 = np.asarray(skeleton) - 1
+        self.out_skeleton = out_skeleton or skeleton
+        self.confidence_scales = confidence_scales
+        self.nms = nms
+        self.timers = defaultdict(float)
+
+        # neighbour tables in the reference's dict order (cifcaf.py:57-65)
+        self.by_target = defaultdict(dict)
+        self.by_source = defaultdict(dict)
+        for caf_i, (j1, j2) in enumerate(self.skeleton_m1.tolist()):
+            self.by_target[j2][j1] = (caf_i, True)
+            self.by_target[j1][j2] = (caf_i, False)
+            self.by_source[j1][j2] = (caf_i, True)
+            self.by_source[j2][j1] = (caf_i, False)
+        self._neighbours = {j: list(self.by_source[j].keys()) for j in range(len(keypoints))}
+        self._engine = None
+
+    def __getstate__(self):
+        state = super().__getstate__()
+        state.pop('_engine', None)
+        return state
+
+    # ------------------------------------------------------------ plumbing
+    def engine(self):
+        if getattr(self, '_engine', None) is None or self._engine.ann_cap != self.max_annotations:
+            self._engine = DeviceDecoder(
+                [tuple(link) for link in self.skeleton],
+                confidence_scales=self.confidence_scales,
+                stride=self._single_stride(),
+                ann_cap=self.max_annotations)
+        return self._engine
+
+    def _single_stride(self):
+        cfg = self.field_config
+        if not cfg.single_scale:
+            raise NotImplementedError('multi-scale field configurations are not built yet')
+        if cfg.cif_strides[0] != cfg.caf_strides[0]:
+            raise NotImplementedError('cif and caf heads must share one stride')
+        return int(cfg.cif_strides[0])
+
+    def params(self):
+        """Snapshot of the class-attribute configuration (decoder/factory.py:74-92)."""
+        cfg = self.field_config
+        if CifSeeds.threshold is None:
+            raise TypeError("'>' not supported between instances of 'float' and 'NoneType' "
+                            "(CifSeeds.threshold is not configured)")
+        kp = self.nms
+        return DecoderParams(
+            cif_threshold=CifHr.v_threshold,
+            seed_threshold=CifSeeds.threshold,
+            seed_score_scale=CifSeeds.score_scale,
+            caf_threshold=CafScored.default_score_th,
+            keypoint_threshold=self.keypoint_threshold,
+            nms_keypoint_threshold=kp.keypoint_threshold if kp is not None else 0.0,
+            nms_instance_threshold=kp.instance_threshold if kp is not None else 0.0,
+            nms_suppression=kp.suppression if kp is not None else 0.0,
+            cif_min_scale=cfg.cif_min_scales[0],
+            caf_min_distance=cfg.caf_min_distances[0],
+            caf_max_distance=cfg.caf_max_distances[0],
+            connection_method=self.connection_method,
+            greedy=self.greedy,
+            force_complete=self.force_complete,
+            nms=kp is not None,
+            deterministic_exp=self.deterministic_exp,
+            seed_mask=cfg.seed_mask,
+        )
+
+    def _annotations_from(self, n_ann, data, scales, source, pre_data, pre_order):
+        """Host arrays of one batch -> List[List[Annotation]]."""
+        out = []
+        for b, n in enumerate(n_ann.tolist()):
+            anns = []
+            for r in range(n):
+                src = int(source[b, r])
+                anns.append(Annotation.from_buffers(
+                    self.keypoints, self.out_skeleton, data[b, r], scales[b, r],
+                    pre_data=pre_data[b, src], order=pre_order[b, src], graph=self._neighbours))
+            out.append(anns)
+        return out
+
+    # -------------------------------------------------------------- decode
+    def decode_batch(self, cif, caf):
+        """Decode a batch. ``cif (B,F,5,H,W)``, ``caf (B,L,9,H,W)`` float32.
+
+        CUDA tensors are decoded in place on their device; host arrays (numpy or
+        CPU tensors, ideally pinned) go through ``pp_decode_batch_host``, which
+        includes the host->device and device->host copies.
+        """
+        start = time.perf_counter()
+        params = self.params()
+        eng = self.engine()
+        if isinstance(cif, torch.Tensor) and cif.is_cuda:
+            buf = eng.run_device(cif, caf, params)
+            n_ann = buf.dev['n_ann'].cpu().numpy()         # synchronises the stream
+            status = buf.dev['status'].cpu().numpy()
+            if status.any():
+                raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
+            nmax = int(n_ann.max(initial=0))
+            npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
+            data = buf.dev['ann_data'][:, :nmax].cpu().numpy()
+            scales = buf.dev['ann_scales'][:, :nmax].cpu().numpy()
+            source = buf.dev['ann_source'][:, :nmax].cpu().numpy()
+            pre_data = buf.dev['pre_data'][:, :npre].cpu().numpy()
+            pre_order = buf.dev['pre_order'][:, :npre].cpu().numpy()
+        else:
+            buf = eng.run_host(cif, caf, params)
+            h = buf.host
+            n_ann = h['n_ann'].numpy()
+            data, scales, source = h['ann_data'].numpy(), h['ann_scales'].numpy(), h['ann_source'].numpy()
+            pre_data, pre_order = h['pre_data'].numpy(), h['pre_order'].numpy()
+        result = self._annotations_from(n_ann, data, scales, source, pre_data, pre_order)
+        self.last_decoder_time = time.perf_counter() - start
+        return result
+
+    def decode_heads(self, heads):
+        cfg = self.field_config
+        return self.decode_batch(heads[cfg.cif_indices[0]], heads[cfg.caf_indices[0]])
+
+    def __call__(self, fields, initial_annotations=None):
+        start = time.perf_counter()
+        if initial_annotations:
+            raise NotImplementedError('initial_annotations are not built yet (SURVEY.md 8f rank 2)')
+        cfg = self.field_config
+        if cfg.cif_visualizers:
+            for vis, cif_i in zip(cfg.cif_visualizers, cfg.cif_indices):
+                vis.predicted(fields[cif_i])
+        if cfg.caf_visualizers:
+            for vis, caf_i in zip(cfg.caf_visualizers, cfg.caf_indices):
+                vis.predicted(fields[caf_i])
+        cif, caf = fields[cfg.cif_indices[0]], fields[cfg.caf_indices[0]]
+        if isinstance(cif, torch.Tensor):
+            cif, caf = cif.unsqueeze(0), caf.unsqueeze(0)
+        else:
+            cif = np.ascontiguousarray(cif, dtype=np.float32)[None]
+            caf = np.ascontiguousarray(caf, dtype=np.float32)[None]
+        annotations = self.decode_batch(cif, caf)[0]
+        LOG.debug('annotations %d, %.3fs', len(annotations), time.perf_counter() - start)
+        LOG.info('%d annotations: %s', len(annotations),
+                 [np.sum(ann.data[:, 2] > 0.1) for ann in annotations])
+        return annotations
