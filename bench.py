@@ -1,0 +1,450 @@
+#!/usr/bin/env python3
+"""bench.py -- decoded images/s of the CifCaf decode path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload NAME] [--batch B]
+
+A "step" is one pass of the hot path (CifHr -> seeds -> CafScored -> assembly
+-> keypoint NMS) over one batch of synthetic CIF/CAF fields.  One JSON line is
+printed by rank 0 (contract in DESIGN.md section "Measurement"):
+
+  value         images/s, fields already resident in HBM, pp_decode_batch
+                (7 kernels) timed with CUDA events on the launching stream;
+  e2e           images/s through the public API CifCaf.decode_batch() with
+                PINNED HOST fields: H2D of the fields, kernels, D2H of the
+                results and the construction of the Annotation objects are all
+                inside the timed region;
+  roofline      the CifHr splat kernel (the kernel that writes the hr maps)
+                against the measured HBM copy peak of MEASURED_PEAKS.json;
+  cpu_baseline  the UNMODIFIED reference decoder (oracle/_ref, its Cython
+                functional module) on this box's host cores, bounded sample;
+  --impl reference   the same reference decoder as its own arm.
+
+Under torchrun every rank decodes its own batch (image sharding, no
+collective on the data path); torch.distributed is used for the barrier and the
+max-over-ranks of the device time only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = 'decoded images/s (641px COCO-17 CIF/CAF fields, CifCaf decode)'
+UNIT = 'images/s'
+
+# name -> (image_hw, persons per image, default batch, dense skeleton)
+WORKLOADS = {
+    'coco17_641_5p': ((641, 641), 5, 64, False),
+    'crowd_1281_50p': ((1281, 1281), 50, 16, False),
+    'dense_641_5p': ((641, 641), 5, 64, True),
+}
+DEFAULT_WORKLOAD = 'coco17_641_5p'
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=('b200', 'reference'))
+    ap.add_argument('--workload', default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument('--batch', type=int, default=0, help='images per GPU per step (0 = workload default)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--cpu-workers', type=int, default=0, help='reference arm: pool size (0 = all cores)')
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------
+# workload
+
+def make_batch(workload, batch, first_seed=0):
+    """`batch` distinct synthetic images of the workload: (cif, caf, skeleton)."""
+    from openpifpaf_b200.encoder import synthetic_fields
+    from openpifpaf_b200.datasets.constants import (COCO_PERSON_SKELETON,
+                                                    DENSER_COCO_PERSON_CONNECTIONS)
+    hw, n_poses, _, dense = WORKLOADS[workload]
+    cache = '/tmp/pifpaf_bench_%s_%d_%d.npz' % (workload, batch, first_seed)
+    skeleton = list(COCO_PERSON_SKELETON)
+    if dense:
+        skeleton = skeleton + list(DENSER_COCO_PERSON_CONNECTIONS)
+    if os.path.exists(cache):
+        z = np.load(cache)
+        return z['cif'], z['caf'], skeleton
+    cifs, cafs = [], []
+    for i in range(batch):
+        cif, caf, _ = synthetic_fields(hw, n_poses, pose_seed=first_seed + i,
+                                       jitter_seed=first_seed + i + 1, dense=dense)
+        cifs.append(cif)
+        cafs.append(caf)
+    cif, caf = np.stack(cifs), np.stack(cafs)
+    try:
+        np.savez(cache + '.tmp.npz', cif=cif, caf=caf)
+        os.replace(cache + '.tmp.npz', cache)
+    except OSError:
+        pass
+    return cif, caf, skeleton
+
+
+def configure_profile(decoder):
+    """SURVEY.md 8d decoder settings (what decoder.cli + configure yield)."""
+    decoder.CifHr.v_threshold = 0.1
+    decoder.CifSeeds.threshold = 0.2
+    decoder.CifSeeds.score_scale = 1.0
+    decoder.CafScored.default_score_th = 0.1
+    decoder.CifCaf.connection_method = 'blend'
+    decoder.CifCaf.greedy = False
+    decoder.CifCaf.force_complete = False
+    decoder.CifCaf.keypoint_threshold = 0.001
+    decoder.nms.Keypoints.keypoint_threshold = 0.001
+    decoder.nms.Keypoints.instance_threshold = 0.0
+    decoder.nms.Keypoints.suppression = 0.0
+
+
+# ----------------------------------------------------------------------------
+# reference arm: the reference's own CPU decoder on the host cores
+
+def _port_decode(item):
+    from oracle import oracle as orc
+    cif, caf, skeleton = item
+    return len(orc.decode(cif, caf, skeleton, orc.Config(exp_mode=0)).data)
+
+
+class ReferenceRunner:
+    """Times Generator.batch's decode region (reference generator.py:93-98):
+    worker_pool.starmap(decoder, fields) with a multiprocessing.Pool."""
+
+    def __init__(self, workload, batch, workers):
+        from oracle import build_ref
+        self.cores = workers or os.cpu_count() or 1
+        self.cif, self.caf, self.skeleton = make_batch(workload, batch)
+        self.batch = batch
+        self.kind = 'reference' if build_ref.staged() else 'port'
+        if self.kind == 'reference':
+            ref = build_ref.import_reference()
+            configure_profile(ref.decoder)
+            from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+            self.dec = ref.decoder.CifCaf(ref.decoder.FieldConfig(), keypoints=COCO_KEYPOINTS,
+                                          skeleton=[list(l) for l in self.skeleton],
+                                          worker_pool=self.cores if self.cores > 1 else None)
+            self.fields = [[self.cif[i], self.caf[i]] for i in range(batch)]
+            self.version = 'openpifpaf %s (oracle/_ref, Cython functional)' % ref.__version__
+        else:
+            import multiprocessing
+            from oracle import oracle as orc
+            orc.build()
+            self.pool = multiprocessing.Pool(self.cores) if self.cores > 1 else None
+            self.items = [(self.cif[i], self.caf[i], self.skeleton) for i in range(batch)]
+            self.version = 'oracle/cifcaf_oracle.c (C restatement)'
+
+    def step(self):
+        if self.kind == 'reference':
+            out = self.dec.worker_pool.starmap(self.dec._mappable_annotations,
+                                               zip(self.fields, [None] * self.batch))
+            return sum(len(a) for a in out)
+        if self.pool is not None:
+            return sum(self.pool.map(_port_decode, self.items))
+        return sum(_port_decode(i) for i in self.items)
+
+    def close(self):
+        pool = getattr(self, 'pool', None) or getattr(getattr(self, 'dec', None), 'worker_pool', None)
+        if pool is not None and hasattr(pool, 'terminate'):
+            pool.terminate()
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    _, _, default_batch, _ = WORKLOADS[args.workload]
+    batch = args.batch or default_batch
+    r = ReferenceRunner(args.workload, batch, args.cpu_workers)
+    n_ann = 0
+    for _ in range(max(args.warmup, 1)):
+        n_ann = r.step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r.step()
+    dt = time.perf_counter() - t0
+    r.close()
+    value = batch * args.steps / dt
+    sample = '%d steps x %d images of %s, pool of %d processes, %s' % (
+        args.steps, batch, args.workload, r.cores, r.version)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
+        'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(args.workload, batch, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': r.cores, 'kind': r.kind,
+                         'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0, 'annotations_per_step': n_ann,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(workload, batch, n_gpus):
+    hw, n_poses, _, dense = WORKLOADS[workload]
+    return {
+        'workload': '%s: batch %d x %dx%d per GPU, %s skeleton, %d synthetic persons/image, fields '
+                    "from the repo's encoder + jitter (SURVEY 8d config 1 generator)" % (
+                        workload, batch, hw[0], hw[1], 'dense 44-link' if dense else 'COCO 17-kp/19-link',
+                        n_poses),
+        'batch_per_gpu': batch, 'global_batch': batch * n_gpus, 'image_hw': list(hw),
+        'persons_per_image': n_poses,
+        'decoder': 'cif_th 0.1, seed_th 0.2, caf_th 0.1, blend, keypoint_th 0.001, nms on, '
+                   'no force_complete',
+        'l2': 'no flush needed: one step streams the fields (%.0f MB) and writes the hr maps '
+              '(%.2f GB) per GPU, both larger than the 126 MB L2' % (
+                  batch * (17 * 5 + (44 if dense else 19) * 9) * ((hw[0] - 1) // 8 + 1) *
+                  ((hw[1] - 1) // 8 + 1) * 4 / 1e6, batch * 17 * hw[0] * hw[1] * 4 / 1e9),
+        'parallelism': 'image-sharded x%d, no collective' % n_gpus,
+    }
+
+
+# ----------------------------------------------------------------------------
+# clocks
+
+CLOCK_QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+               'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+               'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms while the timed region runs."""
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(gpu_index), '--query-gpu=' + CLOCK_QUERY,
+                 '--format=csv,noheader,nounits', '-lms', '200'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], [], set(), []
+        names = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                smax.append(float(r[2]))
+                power.append(float(r[3]))
+            except ValueError:
+                continue
+            for name, cell in zip(names, r[5:9]):
+                if cell.lower().startswith('active'):
+                    reasons.add(name)
+        return {'sm_mhz': float(np.median(sm)) if sm else None,
+                'sm_max_mhz': max(smax) if smax else None,
+                'power_w_max': max(power) if power else None,
+                'samples': len(sm), 'reasons': sorted(reasons)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        with open(path) as f:
+            return float(json.load(f)['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except (OSError, KeyError, ValueError):
+        return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+# ----------------------------------------------------------------------------
+# B200 arm
+
+def cpu_baseline_subprocess(args, batch):
+    """Runs the reference arm in a child process (before CUDA is initialised in
+    this one, so the pool's fork is clean and the cores are idle)."""
+    cmd = [sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '20',
+           '--warmup', '1', '--workload', args.workload, '--batch', str(batch)]
+    env = dict(os.environ)
+    for k in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE'):
+        env.pop(k, None)
+    try:
+        out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                             timeout=600, env=env, cwd=ROOT)
+        for line in reversed(out.stdout.strip().splitlines()):
+            if line.startswith('{'):
+                return json.loads(line)['cpu_baseline']
+        return {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'reference',
+                'sample': 'failed: ' + out.stderr.strip()[-300:]}
+    except (subprocess.TimeoutExpired, OSError, ValueError, KeyError) as e:
+        return {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'reference', 'sample': 'failed: %r' % e}
+
+
+def run_b200(args):
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    hw, _, default_batch, dense = WORKLOADS[args.workload]
+    batch = args.batch or default_batch
+
+    cpu_base = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu_base = cpu_baseline_subprocess(args, batch)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; the B200 arm has no CPU path '
+                         '(use --impl reference for the host-core baseline)')
+    torch.cuda.set_device(local_rank)
+    device = torch.device('cuda', local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=device)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([float(x)], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    from openpifpaf_b200 import _lib, decoder
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.decoder.engine import StageProfile
+    configure_profile(decoder)
+    cif, caf, skeleton = make_batch(args.workload, batch, first_seed=rank * batch)
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=skeleton)
+    eng = dec.engine()
+    params = dec.params()
+    d_cif = torch.from_numpy(cif).to(device)
+    d_caf = torch.from_numpy(caf).to(device)
+    h_cif = torch.from_numpy(cif).pin_memory()
+    h_caf = torch.from_numpy(caf).pin_memory()
+
+    # ---- device-resident throughput ("value") --------------------------------
+    for _ in range(max(args.warmup, 3)):
+        buf = eng.run_device(d_cif, d_caf, params)
+    barrier()
+    status = buf.dev['status'].cpu().numpy()
+    assert not status.any(), 'capacity overflow in warm-up: %s' % status
+    n_ann = int(buf.dev['n_ann'].sum().item())
+    prof = StageProfile(args.steps)
+    params.profile = prof.handle
+    try:
+        uuid = 'GPU-%s' % torch.cuda.get_device_properties(local_rank).uuid
+    except Exception:  # pylint: disable=broad-except
+        uuid = str(local_rank)
+    clocks = ClockSampler(uuid)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        eng.run_device(d_cif, d_caf, params)
+    ev1.record()
+    barrier()
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    stage_ms = prof.read().astype(np.float64)
+    params.profile = None
+
+    # ---- end to end through the public API, host fields ------------------------
+    for _ in range(2):
+        anns = dec.decode_batch(h_cif, h_caf)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        anns = dec.decode_batch(h_cif, h_caf)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    clock_info = clocks.stop()
+    assert sum(len(a) for a in anns) == n_ann, 'host and device paths disagree on the annotation count'
+    hbuf = eng.buffers(batch, cif.shape[1], cif.shape[3], cif.shape[4], host=True)
+    d2h = sum(t.numel() * t.element_size() for t in hbuf.host.values())
+    h2d = cif.nbytes + caf.nbytes
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the CifHr splat kernel -----------------------------------
+    peak, peak_src = measured_peak()
+    names = prof.names
+    mean_ms = stage_ms.mean(axis=0)
+    i_splat, i_compact = names.index('cifhr_splat'), names.index('cif_compact')
+    hr_bytes = batch * cif.shape[1] * hw[0] * hw[1] * 4
+    cif_bytes = cif.nbytes
+    splat_gbs = hr_bytes / (mean_ms[i_splat] * 1e-3) / 1e9
+    stage_gbs = (hr_bytes + cif_bytes) / ((mean_ms[i_splat] + mean_ms[i_compact]) * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
+            traffic = json.load(f).get('cifhr_splat_kernel', {}).get(args.workload)
+    except (OSError, ValueError):
+        pass
+    line = {
+        'metric': METRIC,
+        'value': world * batch * args.steps / (dev_ms * 1e-3),
+        'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+        'ms_per_step': dev_ms / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': workload_config(args.workload, batch, world),
+        'e2e': {'value': world * batch * args.steps / e2e_s, 'unit': UNIT,
+                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]]'},
+        'gpu_launches': _lib.lib().pp_decode_launch_count(None) * args.steps,
+        'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
+                     'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,
+                     'peak_source': peak_src, 'algorithmic_bytes_per_launch': hr_bytes,
+                     'ms_per_launch': float(mean_ms[i_splat]),
+                     'cifhr_stage': {'kernels': 'cif_compact + cifhr_splat',
+                                     'algorithmic_bytes': hr_bytes + cif_bytes,
+                                     'achieved': stage_gbs, 'frac': stage_gbs / peak}},
+        'stages_ms': {n: float(v) for n, v in zip(names, mean_ms)},
+        'annotations_per_step': n_ann * world,
+        'clocks': clock_info,
+    }
+    if cpu_base is not None:
+        line['cpu_baseline'] = cpu_base
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -88,7 +88,8 @@ typedef struct pp_params {
   int32_t force_complete;        /* CifCaf.force_complete      */
   int32_t nms;                   /* 0: CifCaf(nms=None)        */
   int32_t exp_mode;              /* 1 = deterministic pp_expf (default), 0 = CUDA expf */
-  int32_t reserved;
+  uint32_t seed_mask;            /* FieldConfig.seed_mask as bits (0 = all fields seed) */
+  struct pp_profile *profile;    /* optional per-stage CUDA-event timer (NULL = off)    */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
@@ -121,6 +122,20 @@ typedef struct pp_outputs {
   int32_t *n_pre;       /* optional (B)                                  */
   int32_t *status;      /* (B) PP_STATUS_* bits                          */
 } pp_outputs;
+
+/* Per-stage device timing.  When pp_params.profile is set, pp_decode_batch
+ * records one CUDA event before every stage and one after the last, on the
+ * stream it launches on; nothing synchronises until pp_profile_read. */
+#define PP_N_STAGES 7 /* cif_compact, cifhr_splat, seeds_collect, seeds_sort, caf_scored, assemble, nms */
+typedef struct pp_profile pp_profile;
+pp_profile *pp_profile_create(int max_steps);
+void pp_profile_destroy(pp_profile *prof);
+void pp_profile_reset(pp_profile *prof);
+/* Synchronises the recorded events; h_ms (max_steps, PP_N_STAGES) <- ms per stage. */
+int pp_profile_read(pp_profile *prof, float *h_ms, int32_t *n_steps);
+const char *pp_stage_name(int stage);
+/* Kernel launches + memsets one pp_decode_batch enqueues (constant per call). */
+int pp_decode_launch_count(const pp_params *p);
 
 const char *pp_error_string(int code);
 const char *pp_last_cuda_error(void);   /* thread-local text of the last CUDA failure */

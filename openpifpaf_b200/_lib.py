@@ -11,6 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libpifpaf_b200.so')
 
 PP_MAX_F, PP_MAX_L = 32, 64
+PP_N_STAGES = 7
 PP_OK, PP_ERR_ARG, PP_ERR_CAPACITY, PP_ERR_CUDA, PP_ERR_WORKSPACE = 0, -1, -2, -3, -4
 STATUS_BITS = {1: 'seed_cap', 2: 'caf_cap', 4: 'ann_cap', 8: 'src_cap'}
 
@@ -34,7 +35,7 @@ class Params(C.Structure):
         ('caf_min_distance', C.c_float), ('caf_max_distance', C.c_float),
         ('connection_method', C.c_int32), ('greedy', C.c_int32),
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
-        ('reserved', C.c_int32),
+        ('seed_mask', C.c_uint32), ('profile', C.c_void_p),
     ]
 
 
@@ -96,6 +97,16 @@ def lib():
     l.pp_error_string.argtypes = [i32]
     l.pp_last_cuda_error.restype = C.c_char_p
     l.pp_version.restype = C.c_char_p
+    l.pp_profile_create.restype = vp
+    l.pp_profile_create.argtypes = [i32]
+    l.pp_profile_destroy.restype = None
+    l.pp_profile_destroy.argtypes = [vp]
+    l.pp_profile_reset.restype = None
+    l.pp_profile_reset.argtypes = [vp]
+    l.pp_profile_read.argtypes = [vp, vp, vp]
+    l.pp_stage_name.restype = C.c_char_p
+    l.pp_stage_name.argtypes = [i32]
+    l.pp_decode_launch_count.argtypes = [P(Params)]
     l.pp_default_params.restype = None
     l.pp_default_params.argtypes = [P(Params)]
     l.pp_default_caps.argtypes = [P(Shape), P(Caps)]
@@ -124,6 +135,8 @@ def lib():
 
 
 EXPORTS = (
+    'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
+    'pp_stage_name', 'pp_decode_launch_count',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
     'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',

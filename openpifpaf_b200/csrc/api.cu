@@ -1,5 +1,6 @@
 // api.cu -- extern "C" surface of libpifpaf_b200.so (see include/pifpaf_b200.h).
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -24,6 +25,35 @@ int num_sms() {
     cached = n > 0 ? n : 148;
   }
   return cached;
+}
+
+}  // namespace pp
+
+// ---- per-stage timer ----------------------------------------------------------
+struct pp_profile {
+  int max_steps;
+  int step;        // completed steps
+  int open;        // a step is being recorded
+  cudaEvent_t *ev; // (max_steps, PP_N_STAGES + 1)
+};
+
+namespace pp {
+
+void prof_begin_step(pp_profile *prof) {
+  if (!prof) return;
+  prof->open = prof->step < prof->max_steps;
+}
+
+void prof_mark(pp_profile *prof, int stage, cudaStream_t st) {
+  if (!prof || !prof->open) return;
+  cudaEventRecord(prof->ev[(size_t)prof->step * (PP_N_STAGES + 1) + stage], st);
+}
+
+void prof_end_step(pp_profile *prof, cudaStream_t st) {
+  if (!prof || !prof->open) return;
+  cudaEventRecord(prof->ev[(size_t)prof->step * (PP_N_STAGES + 1) + PP_N_STAGES], st);
+  prof->step++;
+  prof->open = 0;
 }
 
 static bool shape_ok(const pp_shape *s) {
@@ -92,6 +122,55 @@ const char *pp_error_string(int code) {
 }
 
 const char *pp_last_cuda_error(void) { return g_cuda_err; }
+
+pp_profile *pp_profile_create(int max_steps) {
+  if (max_steps <= 0) return nullptr;
+  pp_profile *prof = (pp_profile *)calloc(1, sizeof(pp_profile));
+  if (!prof) return nullptr;
+  size_t n = (size_t)max_steps * (PP_N_STAGES + 1);
+  prof->ev = (cudaEvent_t *)calloc(n, sizeof(cudaEvent_t));
+  prof->max_steps = max_steps;
+  for (size_t i = 0; prof->ev && i < n; i++)
+    if (cudaEventCreate(&prof->ev[i]) != cudaSuccess) { prof->max_steps = 0; break; }
+  if (!prof->ev || prof->max_steps == 0) { pp_profile_destroy(prof); return nullptr; }
+  return prof;
+}
+
+void pp_profile_destroy(pp_profile *prof) {
+  if (!prof) return;
+  if (prof->ev) {
+    size_t n = (size_t)(prof->max_steps > 0 ? prof->max_steps : 0) * (PP_N_STAGES + 1);
+    for (size_t i = 0; i < n; i++)
+      if (prof->ev[i]) cudaEventDestroy(prof->ev[i]);
+    free(prof->ev);
+  }
+  free(prof);
+}
+
+void pp_profile_reset(pp_profile *prof) {
+  if (prof) { prof->step = 0; prof->open = 0; }
+}
+
+int pp_profile_read(pp_profile *prof, float *h_ms, int32_t *n_steps) {
+  if (!prof || !h_ms || !n_steps) return PP_ERR_ARG;
+  *n_steps = prof->step;
+  for (int s = 0; s < prof->step; s++) {
+    cudaEvent_t *e = prof->ev + (size_t)s * (PP_N_STAGES + 1);
+    PP_CUDA_CHECK(cudaEventSynchronize(e[PP_N_STAGES]));
+    for (int k = 0; k < PP_N_STAGES; k++)
+      PP_CUDA_CHECK(cudaEventElapsedTime(&h_ms[(size_t)s * PP_N_STAGES + k], e[k], e[k + 1]));
+  }
+  return PP_OK;
+}
+
+const char *pp_stage_name(int stage) {
+  static const char *names[PP_N_STAGES] = {"cif_compact", "cifhr_splat", "seeds_collect", "seeds_sort",
+                                           "caf_scored", "assemble", "nms"};
+  return (stage >= 0 && stage < PP_N_STAGES) ? names[stage] : "?";
+}
+
+/* 7 kernels + the status memset + the seed-counter memset */
+int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 2; }
 const char *pp_version(void) { return "pifpaf_b200 0.1.0 (sm_100a)"; }
 
 void pp_default_params(pp_params *p) {
@@ -254,6 +333,7 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   int *nbwd = o->n_caf_bwd ? o->n_caf_bwd : w.nbwd;
 
   PP_CUDA_CHECK(cudaMemsetAsync(o->status, 0, (size_t)s->B * sizeof(int), st));
+  prof_begin_step(p->profile);
   int rc;
   if ((rc = cifhr_launch(d_cif, hr, w.stage, *s, *c, *p, o->status, st))) return rc;
   if ((rc = seeds_launch(d_cif, hr, seeds, n_seeds, w.stage, *s, *c, *p, o->status, st))) return rc;
@@ -272,8 +352,10 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
   a.hh = hr_h(*s); a.hw = hr_w(*s);
   if ((rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
-  return nms_launch(a.pre_data, a.pre_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
-                    o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  rc = nms_launch(a.pre_data, a.pre_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+                  o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  prof_end_step(p->profile, st);
+  return rc;
 }
 
 #define PP_D2H(member, bytes)                                                                   \

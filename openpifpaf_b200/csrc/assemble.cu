@@ -411,6 +411,7 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   memset(&cs, 0, sizeof cs);
   cs.has = sk.has_confidence_scales;
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  prof_mark(p.profile, kStAssemble, st);
   assemble_kernel<<<B, kAsmThreads, 0, st>>>(args, g, cs, p);
   PP_LAUNCH_CHECK("assemble_kernel");
   return PP_OK;

@@ -116,6 +116,7 @@ int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {
   const int hh = hr_h(s), hw = hr_w(s);
   const float stride = (float)s.stride;
+  prof_mark(p.profile, kStCaf, st);
   caf_scored_kernel<<<s.B * s.L, kCafThreads, 0, st>>>(
       d_caf, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
       p.cif_floor_compl, p.caf_min_distance / stride, p.caf_min_distance != 0.0f,

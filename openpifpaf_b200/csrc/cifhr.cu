@@ -282,6 +282,7 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   const int hh = hr_h(s), hw = hr_w(s);
   const int bf = s.B * s.F;
   size_t smem = (size_t)(w.nstrips + 1) * sizeof(int);
+  prof_mark(p.profile, kStCompact, st);
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
       d_cif, w, s, c.src_cap, hh, hw, p.cif_threshold, p.cif_min_scale / (float)s.stride,
       p.cif_min_scale != 0.0f, d_status);
@@ -289,6 +290,7 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   const int n_work = bf * w.nstrips;
   int grid = num_sms() * 8;
   if (grid > n_work) grid = n_work;
+  prof_mark(p.profile, kStSplat, st);
   cifhr_splat_kernel<<<grid, kSplatThreads, 0, st>>>(d_hr, w, n_work, c.src_cap, hh, hw);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
   return PP_OK;

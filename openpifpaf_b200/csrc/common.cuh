@@ -52,6 +52,12 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 int num_sms();
 
+// ---- optional per-stage timing (pp_profile, api.cu) --------------------------
+enum Stage { kStCompact = 0, kStSplat, kStCollect, kStSort, kStCaf, kStAssemble, kStNms };
+void prof_begin_step(pp_profile *prof);
+void prof_mark(pp_profile *prof, int stage, cudaStream_t st);   // start of `stage`
+void prof_end_step(pp_profile *prof, cudaStream_t st);
+
 // ---- exact float helpers ----------------------------------------------------
 // clip() of functional.pyx:67-68: fmax(minv, fmin(maxv, v)); NaN -> maxv.
 __device__ __forceinline__ float clipf(float v, float lo, float hi) {

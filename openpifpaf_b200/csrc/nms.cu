@@ -273,6 +273,7 @@ int nms_launch(const float *in_data, const float *in_scales, const int *n_in, fl
   int threads = 32 * s.F;
   if (threads > 1024) threads = 1024;
   if (threads < 128) threads = 128;
+  prof_mark(p.profile, kStNms, st);
   nms_kernel<<<s.B, threads, 0, st>>>(a);
   PP_LAUNCH_CHECK("nms_kernel");
   return PP_OK;

@@ -169,15 +169,17 @@ int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n
   w.scratch = (uint64_t *)q;
   w.scratch_stride = pow2_ceil(c.seed_cap);
   const int hh = hr_h(s), hw = hr_w(s), n = s.H * s.W;
+  prof_mark(p.profile, kStCollect, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
   int blocks = s.B * s.F * ((n + kCollectThreads - 1) / kCollectThreads);
   seeds_collect_kernel<<<blocks, kCollectThreads, 0, st>>>(
       d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-      p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, (uint32_t)p.reserved);
+      p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, p.seed_mask);
   PP_LAUNCH_CHECK("seeds_collect_kernel");
   // small capacities only need a small shared array
   size_t need = (size_t)(w.scratch_stride <= kSortSmemKeys ? w.scratch_stride : kSortSmemKeys) *
                 sizeof(uint64_t);
+  prof_mark(p.profile, kStSort, st);
   seeds_sort_kernel<<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
                                                      c.seed_cap, w.scratch_stride, d_status);
   PP_LAUNCH_CHECK("seeds_sort_kernel");

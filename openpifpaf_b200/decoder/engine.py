@@ -33,6 +33,7 @@ class DecoderParams:
     nms: bool = True
     deterministic_exp: bool = True
     seed_mask: Optional[list] = None
+    profile: Optional[int] = None      # pp_profile* from StageProfile (bench/profiling only)
 
     def to_c(self):
         p = _lib.Params()
@@ -65,8 +66,42 @@ class DecoderParams:
                     mask |= 1 << i
             if mask == 0:
                 mask = 1 << 31     # "no field seeds": bit outside any valid field
-        p.reserved = mask if mask < (1 << 31) else mask - (1 << 32)
+        p.seed_mask = mask
+        p.profile = self.profile
         return p
+
+
+class StageProfile:
+    """Per-stage CUDA-event timer of the library (pp_profile_*)."""
+
+    def __init__(self, max_steps):
+        self.max_steps = max_steps
+        self.handle = _lib.lib().pp_profile_create(max_steps)
+        if not self.handle:
+            raise _lib.PifPafError(_lib.PP_ERR_CUDA, 'pp_profile_create failed')
+        self.names = [_lib.lib().pp_stage_name(i).decode() for i in range(_lib.PP_N_STAGES)]
+
+    def reset(self):
+        _lib.lib().pp_profile_reset(self.handle)
+
+    def read(self):
+        """Synchronises and returns ms per stage, shape (steps, PP_N_STAGES)."""
+        ms = np.zeros((self.max_steps, _lib.PP_N_STAGES), np.float32)
+        n = C.c_int32(0)
+        _lib.check(_lib.lib().pp_profile_read(self.handle, ms.ctypes.data_as(C.c_void_p),
+                                              C.byref(n)))
+        return ms[:n.value]
+
+    def close(self):
+        if self.handle:
+            _lib.lib().pp_profile_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # pylint: disable=broad-except
+            pass
 
 
 def _ptr(t):
