@@ -61,9 +61,12 @@ class Annotation:
         pre, order, graph = self._lazy
         self._lazy = None
         steps = [(int(s), int(e)) for s, e in order if s >= 0]
+        # force_complete marker (-2, n1): the first n1 steps belong to the first _grow
+        first = [int(e) for s, e in order if s == -2]
         self._decoding_order = [(s, e, np.copy(pre[s]), np.copy(pre[e])) for s, e in steps]
         if graph is not None:
-            self._frontier_order = _replay_frontier(pre, steps, graph)
+            self._frontier_order = _replay_frontier(pre, steps, graph,
+                                                    first[0] if first else None)
 
     @property
     def decoding_order(self):
@@ -162,7 +165,7 @@ class Annotation:
         return out
 
 
-def _replay_frontier(pre, steps, graph):
+def _replay_frontier(pre, steps, graph, n_first=None):
     """Recompute ``frontier_order`` (cifcaf.py:251-263) from the decoding order.
 
     The order in which (start, end) pairs were queued is a function of the seed
@@ -187,9 +190,20 @@ def _replay_frontier(pre, steps, graph):
     for j in range(n):
         if filled[j]:
             queue(j)
-    for _, end in steps:
+    for i, (_, end) in enumerate(steps):
+        if n_first is not None and i == n_first:
+            n_first = None
+            queued.clear()         # complete_annotations runs a second _grow (cifcaf.py:341)
+            for j in range(n):
+                if filled[j]:
+                    queue(j)
         filled[end] = True
         queue(end)
+    if n_first is not None and n_first == len(steps):
+        queued.clear()
+        for j in range(n):
+            if filled[j]:
+                queue(j)
     return out
 
 

@@ -73,6 +73,7 @@ struct DecodeWs {
   float *fwd, *bwd; int *nfwd, *nbwd;
   uint8_t *occ_cnt;
   float *pre_data, *pre_scales; int *pre_order; int *n_pre;
+  float *cmp_data, *cmp_scales;   // force_complete: completed annotations (NMS input)
   void *stage;               // shared by the cifhr / seeds / nms stages (used one after another)
   size_t stage_bytes;
   size_t total;
@@ -98,6 +99,8 @@ static DecodeWs layout(void *base, const pp_shape &s, const pp_caps &c, bool nee
   w.pre_scales = (float *)take(B * c.ann_cap * s.F * sizeof(float));
   w.pre_order = (int *)take(B * c.ann_cap * s.F * 2 * sizeof(int));
   w.n_pre = (int *)take(B * sizeof(int));
+  w.cmp_data = (float *)take(B * c.ann_cap * s.F * 3 * sizeof(float));
+  w.cmp_scales = (float *)take(B * c.ann_cap * s.F * sizeof(float));
   w.stage_bytes = max3(cifhr_ws_bytes(s, c), seeds_ws_bytes(s, c), nms_ws_bytes(s, c));
   w.stage = take(w.stage_bytes);
   w.total = off;
@@ -257,11 +260,11 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
                        const int32_t *d_nbwd2, const pp_skeleton *sk, const pp_outputs *d_out,
                        void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
                        const pp_params *p, void *stream) {
-  (void)d_fwd2; (void)d_nfwd2; (void)d_bwd2; (void)d_nbwd2;
   if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !d_out || !d_seeds || !d_n_seeds || !d_fwd ||
       !d_bwd || !d_nfwd || !d_nbwd || !d_ws || sk->L != s->L)
     return PP_ERR_ARG;
   if (!d_out->ann_data || !d_out->ann_scales || !d_out->n_ann || !d_out->status) return PP_ERR_ARG;
+  if (p->force_complete && (!d_fwd2 || !d_nfwd2 || !d_bwd2 || !d_nbwd2)) return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   // workspace: occ counters + pre buffers (when the caller keeps none) + nms scratch
   size_t B = s->B;
@@ -270,7 +273,7 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   size_t need_ps = align_up(B * c->ann_cap * s->F * sizeof(float), 256);
   size_t need_po = align_up(B * c->ann_cap * s->F * 2 * sizeof(int), 256);
   size_t need_np = align_up(B * sizeof(int), 256);
-  size_t need = need_occ + need_pd + need_ps + need_po + need_np + nms_ws_bytes(*s, *c);
+  size_t need = need_occ + 2 * need_pd + 2 * need_ps + need_po + need_np + nms_ws_bytes(*s, *c);
   if (ws_bytes < need) return PP_ERR_WORKSPACE;
   char *q = (char *)d_ws;
   AsmArgs a;
@@ -279,6 +282,8 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   a.pre_scales = d_out->pre_scales ? d_out->pre_scales : (float *)q; q += need_ps;
   a.pre_order = d_out->pre_order ? d_out->pre_order : (int *)q; q += need_po;
   a.n_pre = d_out->n_pre ? d_out->n_pre : (int *)q; q += need_np;
+  float *cmp_data = (float *)q; q += need_pd;
+  float *cmp_scales = (float *)q; q += need_ps;
   a.seeds = d_seeds; a.n_seeds = d_n_seeds;
   a.fwd = d_fwd; a.bwd = d_bwd; a.nfwd = d_nfwd; a.nbwd = d_nbwd;
   a.status = d_out->status;
@@ -286,6 +291,13 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   a.hh = hr_h(*s); a.hw = hr_w(*s);
   int rc = assemble_launch(a, *sk, s->B, s->F, *p, st);
   if (rc) return rc;
+  if (p->force_complete) {
+    rc = complete_launch(a, d_fwd2, d_bwd2, d_nfwd2, d_nbwd2, cmp_data, cmp_scales, *sk, s->B, s->F,
+                         *p, st);
+    if (rc) return rc;
+    return nms_launch(cmp_data, cmp_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
+                      d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p, st);
+  }
   return nms_launch(a.pre_data, a.pre_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
                     d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p, st);
 }
@@ -319,7 +331,6 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
       sk->L != s->L)
     return PP_ERR_ARG;
   if (!o->ann_data || !o->ann_scales || !o->n_ann || !o->status) return PP_ERR_ARG;
-  if (p->greedy || p->force_complete) return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const bool need_hr = o->hr == nullptr;
   DecodeWs w = layout(d_ws, *s, *c, need_hr);
@@ -352,7 +363,19 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
   a.hh = hr_h(*s); a.hw = hr_w(*s);
   if ((rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
-  rc = nms_launch(a.pre_data, a.pre_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+  const float *nms_data = a.pre_data, *nms_scales = a.pre_scales;
+  if (p->force_complete) {                                           // cifcaf.py:110-115
+    // second CafScored(score_th=0.0001) into the workspace lists (the first
+    // ones are no longer needed, or live in the caller's buffers)
+    if ((rc = caf_scored_launch(d_caf, hr, *sk, 0.0001f, w.fwd, w.nfwd, w.bwd, w.nbwd, *s, *c, *p,
+                                o->status, st)))
+      return rc;
+    if ((rc = complete_launch(a, w.fwd, w.bwd, w.nfwd, w.nbwd, w.cmp_data, w.cmp_scales, *sk, s->B,
+                              s->F, *p, st)))
+      return rc;
+    nms_data = w.cmp_data; nms_scales = w.cmp_scales;
+  }
+  rc = nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
                   o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
   prof_end_step(p->profile, st);
   return rc;

@@ -183,8 +183,17 @@ struct Pending {      // an evaluated frontier entry (-score, (x, y, s, v), star
   int start, end;
 };
 
-__device__ __forceinline__ bool pending_less(const Pending &a, const Pending &b) {
+// Heap order of the reference's frontier.  Non-greedy: evaluated entries
+// (-score, (x, y, s, v), start, end).  Greedy (cifcaf.py:280-281): an entry is
+// applied the moment it is evaluated, so only the unevaluated keys
+// (-sqrt(v_start) [* confidence_scale], None, start, end) are ever compared;
+// `key` then holds that bound.
+__device__ __forceinline__ bool pending_less(const Pending &a, const Pending &b, int greedy) {
   if (a.key != b.key) return a.key < b.key;
+  if (greedy) {
+    if (a.start != b.start) return a.start < b.start;
+    return a.end < b.end;
+  }
   if (a.x != b.x) return a.x < b.x;
   if (a.y != b.y) return a.y < b.y;
   if (a.s != b.s) return a.s < b.s;
@@ -208,6 +217,7 @@ struct AsmShared {
   int box_valid[PP_MAX_F];
   int found;
   int warp_min[kAsmWarps];
+  struct Flood { float key, sx, sy, sv, s; int end; } ff[4 * PP_MAX_L];
 };
 
 // add_to_frontier (cifcaf.py:251-263), run by one thread.
@@ -247,7 +257,8 @@ __device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const 
       if (lane == 0) {
         Pending &q = sh.pend[base + e];
         float score = r.v;
-        if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);   // :282-284
+        if (p.greedy) score = __fsqrt_rn(sh.data[start][2]);                       // :258 (the bound)
+        if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);   // :259-260, :282-284
         q.key = -score; q.x = r.x; q.y = r.y; q.s = r.s; q.v = r.v;
         q.start = start; q.end = (r.v == 0.0f) ? -1 : g.nb_end[start][k];          // :277-278
       }
@@ -260,12 +271,12 @@ __device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const 
       for (int i = lane; i < n_pend; i += 32) {
         const Pending &q = sh.pend[i];
         if (q.end < 0 || sh.data[q.end][2] > 0.0f) continue;
-        if (best < 0 || pending_less(q, sh.pend[best])) best = i;
+        if (best < 0 || pending_less(q, sh.pend[best], p.greedy)) best = i;
       }
 #pragma unroll
       for (int off = 16; off > 0; off >>= 1) {
         int o = __shfl_xor_sync(0xffffffffu, best, off);
-        if (o >= 0 && (best < 0 || pending_less(sh.pend[o], sh.pend[best]))) best = o;
+        if (o >= 0 && (best < 0 || pending_less(sh.pend[o], sh.pend[best], p.greedy))) best = o;
       }
       if (lane == 0) {
         sh.n_pend = n_pend;
@@ -401,12 +412,130 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
   if (threadIdx.x == 0) a.n_pre[b] = n_ann;
 }
 
+// ---------------------------------------------------------------------------
+// complete_annotations (cifcaf.py:333-351) + _flood_fill (:309-331).
+// Annotations are independent here, so the grid is (annotation, image).
+
+__device__ __forceinline__ bool flood_less(const AsmShared::Flood &a, const AsmShared::Flood &b) {
+  // Python tuple order of (-v, end_i, [x, y, v], s)
+  if (a.key != b.key) return a.key < b.key;
+  if (a.end != b.end) return a.end < b.end;
+  if (a.sx != b.sx) return a.sx < b.sx;
+  if (a.sy != b.sy) return a.sy < b.sy;
+  if (a.sv != b.sv) return a.sv < b.sv;
+  return a.s < b.s;
+}
+
+// one thread; `prio` is the closure quirk of cifcaf.py:317,325 (see oracle flood_fill)
+__device__ void flood_add(AsmShared &sh, const Graph &g, int &n, int start, float prio) {
+  for (int k = 0; k < g.deg[start]; k++) {
+    int end = g.nb_end[start][k];
+    if (sh.data[end][2] > 0.0f) continue;
+    if (n >= 4 * PP_MAX_L) return;     // cannot happen: <= 2 pushes per directed edge
+    AsmShared::Flood &e = sh.ff[n++];
+    e.key = -prio; e.end = end;
+    e.sx = sh.data[start][0]; e.sy = sh.data[start][1]; e.sv = sh.data[start][2];
+    e.s = sh.js[start];
+  }
+}
+
+__device__ void flood_fill(AsmShared &sh, const Graph &g) {
+  int n = 0;
+  for (int j = 0; j < g.F; j++) {
+    if (sh.data[j][2] == 0.0f) continue;
+    flood_add(sh, g, n, j, sh.data[j][2]);
+  }
+  while (n > 0) {
+    int m = 0;
+    for (int i = 1; i < n; i++)
+      if (flood_less(sh.ff[i], sh.ff[m])) m = i;
+    AsmShared::Flood e = sh.ff[m];
+    sh.ff[m] = sh.ff[--n];
+    if (sh.data[e.end][2] > 0.0f) continue;
+    sh.data[e.end][0] = e.sx; sh.data[e.end][1] = e.sy;
+    sh.data[e.end][2] = 0.00001f;
+    sh.js[e.end] = e.s;
+    flood_add(sh, g, n, e.end, e.sv);
+  }
+}
+
+__global__ void __launch_bounds__(kAsmThreads)
+complete_kernel(AsmArgs a, const float *__restrict__ fwd2, const float *__restrict__ bwd2,
+                const int *__restrict__ nfwd2, const int *__restrict__ nbwd2,
+                float *__restrict__ cmp_data, float *__restrict__ cmp_scales, Graph g, CScale cscale,
+                pp_params p) {
+  __shared__ AsmShared sh;
+  __shared__ int unfilled[PP_MAX_F];
+  const int b = blockIdx.y, an = blockIdx.x;
+  const int F = g.F;
+  if (an >= min(a.n_pre[b], a.ann_cap)) return;
+  CafLists cf = {fwd2 + (size_t)b * a.L * 9 * a.caf_cap, bwd2 + (size_t)b * a.L * 9 * a.caf_cap,
+                 nfwd2 + (size_t)b * a.L, nbwd2 + (size_t)b * a.L, a.caf_cap};
+  float *pre_data = a.pre_data + ((size_t)b * a.ann_cap + an) * F * 3;
+  float *pre_scales = a.pre_scales + ((size_t)b * a.ann_cap + an) * F;
+  int *pre_order = a.pre_order + ((size_t)b * a.ann_cap + an) * F * 2;
+  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = pre_data[i];
+  for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = pre_scales[i];
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int n1 = 0;
+    while (n1 < F && pre_order[2 * n1] >= 0) {
+      sh.dec[n1][0] = pre_order[2 * n1]; sh.dec[n1][1] = pre_order[2 * n1 + 1];
+      n1++;
+    }
+    sh.n_dec = n1;
+    sh.found = n1;     // decoding steps of the first _grow
+  }
+  for (int i = threadIdx.x; i < F; i += blockDim.x) unfilled[i] = sh.data[i][2] == 0.0f;   // :340
+  __syncthreads();
+  grow(sh, g, cscale, cf, false, p);                                // :341
+  // as-grown state (scores not yet clamped) for the host's decoding_order replay
+  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) pre_data[i] = (&sh.data[0][0])[i];
+  for (int i = threadIdx.x; i < F; i += blockDim.x) {
+    pre_scales[i] = sh.js[i];
+    int s0 = i < sh.n_dec ? sh.dec[i][0] : -1, s1 = i < sh.n_dec ? sh.dec[i][1] : -1;
+    if (i == F - 1 && sh.n_dec < F) { s0 = -2; s1 = sh.found; }   // marker: steps of the first grow
+    pre_order[2 * i] = s0; pre_order[2 * i + 1] = s1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bool any_empty = false;
+    for (int j = 0; j < F; j++) {
+      if (unfilled[j] && sh.data[j][2] > 0.0f)                     // :342-344
+        sh.data[j][2] = 0.001f < sh.data[j][2] ? 0.001f : sh.data[j][2];
+      if (sh.data[j][2] == 0.0f) any_empty = true;
+    }
+    if (any_empty) flood_fill(sh, g);                              // :347-348
+  }
+  __syncthreads();
+  float *od = cmp_data + ((size_t)b * a.ann_cap + an) * F * 3;
+  float *os = cmp_scales + ((size_t)b * a.ann_cap + an) * F;
+  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) od[i] = (&sh.data[0][0])[i];
+  for (int i = threadIdx.x; i < F; i += blockDim.x) os[i] = sh.js[i];
+}
+
+int complete_launch(const AsmArgs &args, const float *fwd2, const float *bwd2, const int *nfwd2,
+                    const int *nbwd2, float *cmp_data, float *cmp_scales, const pp_skeleton &sk,
+                    int B, int F, const pp_params &p, cudaStream_t st) {
+  Graph g;
+  int rc = build_graph(sk, F, &g);
+  if (rc) return rc;
+  CScale cs;
+  memset(&cs, 0, sizeof cs);
+  cs.has = sk.has_confidence_scales;
+  for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  dim3 grid(args.ann_cap, B);
+  complete_kernel<<<grid, kAsmThreads, 0, st>>>(args, fwd2, bwd2, nfwd2, nbwd2, cmp_data, cmp_scales,
+                                               g, cs, p);
+  PP_LAUNCH_CHECK("complete_kernel");
+  return PP_OK;
+}
+
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st) {
   Graph g;
   int rc = build_graph(sk, F, &g);
   if (rc) return rc;
-  if (p.greedy || p.force_complete) return PP_ERR_ARG;   // not in this build yet
   CScale cs;
   memset(&cs, 0, sizeof cs);
   cs.has = sk.has_confidence_scales;

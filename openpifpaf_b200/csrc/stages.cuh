@@ -30,6 +30,9 @@ struct AsmArgs {
 };
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st);
+int complete_launch(const AsmArgs &args, const float *fwd2, const float *bwd2, const int *nfwd2,
+                    const int *nbwd2, float *cmp_data, float *cmp_scales, const pp_skeleton &sk,
+                    int B, int F, const pp_params &p, cudaStream_t st);
 size_t nms_ws_bytes(const pp_shape &s, const pp_caps &c);
 size_t nms_ws_staging_offset(const pp_shape &s, const pp_caps &c);
 int nms_launch(const float *in_data, const float *in_scales, const int *n_in, float *out_data,

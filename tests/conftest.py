@@ -79,3 +79,95 @@ def configured_decoder():
      decoder.CifCaf.force_complete, decoder.CifCaf.greedy,
      decoder.CifCaf.connection_method, decoder.nms.Keypoints.keypoint_threshold,
      decoder.nms.Keypoints.instance_threshold, decoder.nms.Keypoints.suppression) = saved
+
+
+# ---------------------------------------------------------------------------
+# golden fixtures (tests/golden/*.npz, written by oracle/gen_golden.py from the reference)
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+GOLDEN_NAMES = sorted(n[:-4] for n in os.listdir(GOLDEN_DIR) if n.endswith('.npz')) \
+    if os.path.isdir(GOLDEN_DIR) else []
+
+# north_star tolerances against the reference
+TOL_XY = 1e-3       # px
+TOL_SCORE = 1e-4
+TOL_HR_REL = 1e-5
+
+
+def sha256(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+class Golden:
+    """One fixture: regenerated inputs (hash-checked) + the reference's observations."""
+
+    def __init__(self, name):
+        import ast
+        from openpifpaf_b200.datasets.constants import (COCO_PERSON_SKELETON,
+                                                        DENSER_COCO_PERSON_CONNECTIONS)
+        self.name = name
+        self.z = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+        z = self.z
+        self.dense = bool(z['dense'])
+        self.overrides = dict(ast.literal_eval(str(z['overrides'])))
+        self.cif, self.caf, _ = fields(tuple(int(v) for v in z['image_hw']), int(z['n_poses']),
+                                       pose_seed=int(z['pose_seed']),
+                                       jitter_seed=int(z['jitter_seed']), dense=self.dense)
+        assert sha256(self.cif) == str(z['cif_sha256']), 'synthetic encoder drifted (cif) for ' + name
+        assert sha256(self.caf) == str(z['caf_sha256']), 'synthetic encoder drifted (caf) for ' + name
+        self.skeleton = [tuple(l) for l in COCO_PERSON_SKELETON]
+        if self.dense:
+            self.skeleton += [tuple(l) for l in DENSER_COCO_PERSON_CONNECTIONS]
+
+    def oracle_kwargs(self):
+        """Overrides in the oracle Config's vocabulary."""
+        o = self.overrides
+        kw = {}
+        if o.get('connection_method') == 'max':
+            kw['connection_method'] = 1
+        if o.get('greedy'):
+            kw['greedy'] = 1
+        if o.get('force_complete'):
+            kw['force_complete'] = 1
+        if 'keypoint_threshold' in o:
+            kw['keypoint_th'] = o['keypoint_threshold']
+            kw['nms_keypoint_th'] = o['keypoint_threshold']
+        return kw
+
+    def engine_kwargs(self):
+        """Overrides in DecoderParams' vocabulary."""
+        o = self.overrides
+        kw = {k: o[k] for k in ('connection_method', 'greedy', 'force_complete') if k in o}
+        if 'keypoint_threshold' in o:
+            kw['keypoint_threshold'] = o['keypoint_threshold']
+            kw['nms_keypoint_threshold'] = o['keypoint_threshold']
+        return kw
+
+    def check_annotations(self, data, scales, order, key='ann', exact=False):
+        """Compare annotations with the reference's: integer outputs identical
+        (count, which joints are set, decoding order), xy / scores in tolerance."""
+        z = self.z
+        ref_data, ref_scales, ref_order = z[key + '_data'], z[key + '_scales'], z[key + '_order']
+        assert len(data) == len(ref_data), '%s: %d annotations, reference %d' % (
+            self.name, len(data), len(ref_data))
+        if len(data) == 0:
+            return
+        assert np.array_equal(data[..., 2] != 0, ref_data[..., 2] != 0), 'joint masks differ'
+        if order is not None:
+            assert np.array_equal(order, ref_order), 'decoding order differs'
+        if exact:
+            assert np.array_equal(data, ref_data) and np.array_equal(scales, ref_scales)
+            return
+        assert np.abs(data[..., :2] - ref_data[..., :2]).max() <= TOL_XY
+        assert np.abs(data[..., 2] - ref_data[..., 2]).max() <= TOL_SCORE
+        assert np.abs(scales - ref_scales).max() <= TOL_XY
+
+
+_GOLDEN_CACHE = {}
+
+
+def golden(name):
+    if name not in _GOLDEN_CACHE:
+        _GOLDEN_CACHE[name] = Golden(name)
+    return _GOLDEN_CACHE[name]

@@ -47,8 +47,15 @@ def check_image(orc, out, b, cif, caf, skeleton, **cfg_kw):
             assert np.array_equal(out['caf_bwd'][b, l, :, :nb], o.backward[l]), 'caf backward %d' % l
     npre = out['n_pre'][b]
     assert npre == len(o.pre_data)
-    assert np.array_equal(out['pre_data'][b, :npre], o.pre_data), 'grown annotations differ'
-    assert np.array_equal(out['pre_scales'][b, :npre], o.pre_joint_scales)
+    if cfg_kw.get('force_complete'):
+        # pre_* then hold the as-grown state after the completion _grow (scores not yet
+        # clamped); the joints the first _grow filled must still be the oracle's
+        m = o.pre_data[..., 2] != 0
+        assert np.array_equal(out['pre_data'][b, :npre][m], o.pre_data[m])
+        assert np.array_equal(out['pre_scales'][b, :npre][m], o.pre_joint_scales[m])
+    else:
+        assert np.array_equal(out['pre_data'][b, :npre], o.pre_data), 'grown annotations differ'
+        assert np.array_equal(out['pre_scales'][b, :npre], o.pre_joint_scales)
     n = out['n_ann'][b]
     assert n == len(o.data), (n, len(o.data))
     assert np.array_equal(out['ann_data'][b, :n], o.data), 'final annotations differ'
@@ -92,6 +99,46 @@ def test_no_nms_and_max_method(oracle, coco_skeleton, configured_decoder):
     check_image(oracle, out, 0, cif, caf, coco_skeleton, connection_method=1)
 
 
+def test_greedy_and_force_complete(oracle, coco_skeleton, configured_decoder):
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, greedy=True)
+    check_image(oracle, out, 0, cif, caf, coco_skeleton, greedy=1)
+    for kp_th in (0.0, 0.001):
+        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, force_complete=True,
+                      keypoint_threshold=kp_th, nms_keypoint_threshold=kp_th)
+        check_image(oracle, out, 0, cif, caf, coco_skeleton, force_complete=1,
+                    keypoint_th=kp_th, nms_keypoint_th=kp_th)
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, force_complete=True,
+                  keypoint_threshold=0.0, nms=False)
+    o = check_image(oracle, out, 0, cif, caf, coco_skeleton, force_complete=1, keypoint_th=0.0,
+                    do_nms=0)
+    assert np.all(o.data[..., 2] > 0), 'force_complete fills every joint (before NMS)'
+    # partial poses (people cut by the image border) exercise _flood_fill
+    cif, caf, _ = fields((161, 241), 6, pose_seed=13, jitter_seed=14)
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, force_complete=True,
+                  keypoint_threshold=0.0, nms_keypoint_threshold=0.0, greedy=True)
+    check_image(oracle, out, 0, cif, caf, coco_skeleton, force_complete=1, greedy=1,
+                keypoint_th=0.0, nms_keypoint_th=0.0)
+
+
+def test_public_api_force_complete_orders(oracle, coco_skeleton, configured_decoder):
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    decoder.CifCaf.force_complete = True
+    decoder.CifCaf.keypoint_threshold = 0.0
+    decoder.nms.Keypoints.keypoint_threshold = 0.0
+    cif, caf, _ = fields((161, 241), 6, pose_seed=13, jitter_seed=14)
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    o = oracle.decode(cif, caf, coco_skeleton,
+                      oracle.Config(exp_mode=1, force_complete=1, keypoint_th=0.0, nms_keypoint_th=0.0))
+    anns = dec([cif, caf])
+    assert len(anns) == len(o.data) >= 1
+    for ann, d, order, front in zip(anns, o.data, o.decoding_order, o.frontier_order):
+        assert np.array_equal(ann.data, d)
+        assert [(s, e) for s, e, _, _ in ann.decoding_order] == [tuple(x) for x in order.tolist()]
+        assert ann.frontier_order == [tuple(x) for x in front.tolist()]
+
+
 def test_public_api_matches_oracle(oracle, coco_skeleton, configured_decoder):
     from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
     decoder = configured_decoder
@@ -105,3 +152,125 @@ def test_public_api_matches_oracle(oracle, coco_skeleton, configured_decoder):
             assert np.array_equal(ann.joint_scales, js)
             assert [(s, e) for s, e, _, _ in ann.decoding_order] == [tuple(x) for x in order.tolist()]
             assert ann.score() == oracle.annotation_score(d)
+        for ann, front in zip(anns, o.frontier_order):
+            assert ann.frontier_order == [tuple(x) for x in front.tolist()]
+
+
+# ---------------------------------------------------------------------------
+# against the reference's golden vectors (tests/golden, oracle/gen_golden.py)
+
+from conftest import GOLDEN_NAMES, golden, sha256  # noqa: E402
+
+GPU_UNSUPPORTED = ()   # overrides the CUDA path does not implement yet
+
+
+@pytest.mark.parametrize('name', GOLDEN_NAMES)
+def test_gpu_matches_reference_golden(configured_decoder, name):
+    g = golden(name)
+    if any(g.overrides.get(k) for k in GPU_UNSUPPORTED):
+        pytest.skip('not built yet: %s' % sorted(g.overrides))
+    z = g.z
+    out = run_gpu(configured_decoder, [g.cif], [g.caf], g.skeleton, **g.engine_kwargs())
+    assert out['status'][0] == 0
+    assert sha256(out['hr'][0]) == str(z['hr_sha256']), 'hr not bit-identical to the reference'
+    n = out['n_seeds'][0]
+    assert np.array_equal(out['seeds'][0, :n], z['seeds']), 'seeds differ from the reference'
+    nf, nb = out['n_caf_fwd'][0], out['n_caf_bwd'][0]
+    assert nf.tolist() == z['caf_nf'].tolist() and nb.tolist() == z['caf_nb'].tolist()
+    for l in range(len(g.skeleton)):
+        assert sha256(out['caf_fwd'][0, l, :, :nf[l]]) == str(z['caf_f_sha256'][l])
+        assert sha256(out['caf_bwd'][0, l, :, :nb[l]]) == str(z['caf_b_sha256'][l])
+    na = out['n_ann'][0]
+    order = out['pre_order'][0][out['ann_source'][0, :na]]
+    g.check_annotations(out['ann_data'][0, :na], out['ann_scales'][0, :na], order, key='ann')
+    assert np.abs(out['ann_score'][0, :na] - z['ann_score']).max(initial=0.0) <= 1e-4
+
+
+# ---------------------------------------------------------------------------
+# full-size properties (BASELINE config sizes; no oracle needed)
+
+def test_batch64_properties(configured_decoder, coco_skeleton):
+    """Batch 64 x 641^2: decoding is per-image independent, deterministic and
+    permutation-equivariant; seeds are sorted; hr stays in [0, 1]."""
+    items = [fields((641, 641), 5, pose_seed=s, jitter_seed=s + 1) for s in range(4)]
+    idx = [i % 4 for i in range(64)]
+    cifs, cafs = [items[i][0] for i in idx], [items[i][1] for i in idx]
+    a = run_gpu(configured_decoder, cifs, cafs, coco_skeleton, keep=('ann', 'seeds', 'hr'))
+    b = run_gpu(configured_decoder, cifs, cafs, coco_skeleton, keep=('ann', 'seeds', 'hr'))
+    assert not a['status'].any()
+    for k in ('n_ann', 'n_seeds', 'n_pre'):
+        assert np.array_equal(a[k], b[k])
+    assert a['hr'].min() >= 0.0 and a['hr'].max() <= 1.0
+    for i in range(64):
+        j = idx[i]          # images j, j+4, j+8 ... are the same image
+        n, ns = a['n_ann'][i], a['n_seeds'][i]
+        assert n == a['n_ann'][j] and ns == a['n_seeds'][j] and n >= 5
+        assert np.array_equal(a['ann_data'][i, :n], a['ann_data'][j, :n])
+        assert np.array_equal(a['ann_data'][i, :n], b['ann_data'][i, :n])
+        assert np.array_equal(a['seeds'][i, :ns], a['seeds'][j, :ns])
+        v = a['seeds'][i, :ns, 0]
+        assert np.all(v[:-1] >= v[1:]) and np.all(v > 0.2)
+        assert np.all(np.diff(a['ann_score'][i, :n]) <= 0)
+    assert np.array_equal(a['hr'][0], a['hr'][60])
+    single = run_gpu(configured_decoder, cifs[1:2], cafs[1:2], coco_skeleton, keep=('ann', 'hr'))
+    n = single['n_ann'][0]
+    assert np.array_equal(single['ann_data'][0, :n], a['ann_data'][1, :n])
+    assert np.array_equal(single['hr'][0], a['hr'][1])
+
+
+def test_host_entry_equals_device_entry(configured_decoder, coco_skeleton):
+    """pp_decode_batch_host (host buffers, copies inside) == pp_decode_batch."""
+    from openpifpaf_b200.decoder.engine import DecoderParams, DeviceDecoder
+    items = [fields((321, 321), n, pose_seed=30 + n, jitter_seed=31 + n) for n in (2, 3, 5)]
+    cif = np.stack([i[0] for i in items])
+    caf = np.stack([i[1] for i in items])
+    dev = run_gpu(configured_decoder, list(cif), list(caf), coco_skeleton, keep=('ann',))
+    eng = DeviceDecoder(coco_skeleton)
+    buf = eng.run_host(torch.from_numpy(cif).pin_memory(), torch.from_numpy(caf).pin_memory(),
+                       DecoderParams())
+    for k in ('n_ann', 'ann_data', 'ann_scales', 'ann_score', 'ann_source', 'pre_order'):
+        h = buf.host[k].numpy()
+        for b in range(3):
+            n = dev['n_ann'][b]
+            if k == 'n_ann':
+                assert h[b] == n
+            elif k == 'pre_order':
+                assert np.array_equal(h[b, :dev['n_pre'][b]], dev[k][b, :dev['n_pre'][b]])
+            else:
+                assert np.array_equal(h[b, :n], dev[k][b, :n]), k
+
+
+def test_sharded_single_rank(configured_decoder, coco_skeleton):
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.decoder.sharding import ShardedDecoder
+    decoder = configured_decoder
+    items = [fields((161, 161), 1 + i % 2, pose_seed=60 + i, jitter_seed=61 + i) for i in range(5)]
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+
+    def get_fields(lo, hi):
+        return (np.stack([items[i][0] for i in range(lo, hi)]),
+                np.stack([items[i][1] for i in range(lo, hi)]))
+
+    merged = ShardedDecoder(dec.decode_batch, chunk=2).decode_all(5, get_fields)
+    assert len(merged) == 5
+    for i, anns in enumerate(merged):
+        alone = dec([items[i][0], items[i][1]])
+        assert len(anns) == len(alone)
+        for x, y in zip(anns, alone):
+            assert np.array_equal(x.data, y.data)
+
+
+def test_capacity_overflow_is_reported(configured_decoder, coco_skeleton):
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    saved = decoder.CifCaf.max_annotations
+    decoder.CifCaf.max_annotations = 2
+    try:
+        dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+        with pytest.raises(_lib.PifPafError) as e:
+            dec([cif, caf])
+        assert e.value.code == _lib.PP_ERR_CAPACITY and 'ann_cap' in str(e.value)
+    finally:
+        decoder.CifCaf.max_annotations = saved

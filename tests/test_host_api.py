@@ -1,0 +1,125 @@
+"""Host-side mirror of the reference interface: flag surface, class-attribute
+configuration, FieldConfig and Annotation behave like the reference's
+(decoder/factory.py, decoder/field_config.py, annotation.py)."""
+import argparse
+import types
+
+import numpy as np
+import pytest
+
+
+def _ref():
+    from oracle import build_ref
+    if not build_ref.staged():
+        pytest.skip('oracle/_ref not staged')
+    return build_ref.import_reference()
+
+
+def parse(decoder, argv, **cli_kw):
+    parser = argparse.ArgumentParser()
+    decoder.cli(parser, **cli_kw)
+    return parser.parse_args(argv)
+
+
+@pytest.mark.parametrize('argv,cli_kw', [
+    ([], {}),
+    (['--seed-threshold', '0.5', '--no-force-complete-pose'], {}),
+    (['--force-complete-pose', '--greedy', '--connection-method', 'max'],
+     {'force_complete_pose': False}),
+    (['--instance-threshold', '0.2', '--cif-th', '0.3', '--caf-th', '0.05', '--dense-connections'],
+     {'force_complete_pose': False, 'seed_threshold': 0.3}),
+])
+def test_cli_and_configure_match_reference(configured_decoder, argv, cli_kw):
+    ref = _ref()
+    mine = configured_decoder
+    a_ref = parse(ref.decoder, argv, **cli_kw)
+    a_mine = parse(mine, argv, **cli_kw)
+    assert vars(a_ref) == vars(a_mine)
+    saved = (ref.decoder.CifSeeds.threshold, ref.decoder.CifCaf.force_complete,
+             ref.decoder.CifCaf.keypoint_threshold, ref.decoder.CifCaf.greedy,
+             ref.decoder.CifCaf.connection_method, ref.decoder.CifHr.v_threshold,
+             ref.decoder.CafScored.default_score_th, ref.decoder.nms.Keypoints.instance_threshold,
+             ref.decoder.nms.Keypoints.keypoint_threshold)
+    try:
+        ref.decoder.configure(a_ref)
+        mine.configure(a_mine)
+        for cls, attr in (('CifHr', 'v_threshold'), ('CifSeeds', 'threshold'),
+                          ('CafScored', 'default_score_th'), ('CifCaf', 'force_complete'),
+                          ('CifCaf', 'keypoint_threshold'), ('CifCaf', 'greedy'),
+                          ('CifCaf', 'connection_method')):
+            assert getattr(getattr(mine, cls), attr) == getattr(getattr(ref.decoder, cls), attr), (cls, attr)
+        assert mine.nms.Keypoints.instance_threshold == ref.decoder.nms.Keypoints.instance_threshold
+        assert mine.nms.Keypoints.keypoint_threshold == ref.decoder.nms.Keypoints.keypoint_threshold
+    finally:
+        (ref.decoder.CifSeeds.threshold, ref.decoder.CifCaf.force_complete,
+         ref.decoder.CifCaf.keypoint_threshold, ref.decoder.CifCaf.greedy,
+         ref.decoder.CifCaf.connection_method, ref.decoder.CifHr.v_threshold,
+         ref.decoder.CafScored.default_score_th, ref.decoder.nms.Keypoints.instance_threshold,
+         ref.decoder.nms.Keypoints.keypoint_threshold) = saved
+
+
+def test_field_config_defaults_match_reference():
+    ref = _ref()
+    from openpifpaf_b200 import decoder
+    a, b = ref.decoder.FieldConfig(), decoder.FieldConfig()
+    for name in ('cif_indices', 'caf_indices', 'cif_strides', 'caf_strides', 'cif_min_scales',
+                 'caf_min_distances', 'caf_max_distances', 'seed_mask', 'confidence_scales'):
+        assert getattr(a, name) == getattr(b, name), name
+
+
+def test_annotation_matches_reference():
+    ref = _ref()
+    from openpifpaf_b200.annotation import Annotation
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, COCO_PERSON_SKELETON
+    rng = np.random.RandomState(0)
+    for _ in range(10):
+        data = np.zeros((17, 3), np.float32)
+        data[:, :2] = rng.uniform(0, 600, (17, 2))
+        data[:, 2] = rng.uniform(0, 1, 17) * (rng.uniform(0, 1, 17) > 0.3)
+        js = rng.uniform(1, 20, 17).astype(np.float32)
+        a = ref.Annotation(COCO_KEYPOINTS, COCO_PERSON_SKELETON).set(data.copy(), js.copy())
+        b = Annotation(COCO_KEYPOINTS, COCO_PERSON_SKELETON).set(data.copy(), js.copy())
+        assert a.score() == b.score()
+        assert a.scale() == b.scale()
+        assert np.array_equal(np.asarray(a.bbox()), np.asarray(b.bbox()))
+        assert a.json_data() == b.json_data()
+        a.rescale(0.5)
+        b.rescale(0.5)
+        assert np.array_equal(a.data, b.data) and np.array_equal(a.joint_scales, b.joint_scales)
+
+
+def test_factory_decode_builds_cifcaf(configured_decoder):
+    decoder = configured_decoder
+    from openpifpaf_b200.datasets.constants import (COCO_KEYPOINTS, COCO_PERSON_SKELETON,
+                                                    DENSER_COCO_PERSON_CONNECTIONS)
+
+    def head(name, **meta):
+        return types.SimpleNamespace(meta=types.SimpleNamespace(name=name, **meta),
+                                     stride=lambda basenet_stride: basenet_stride // 2)
+    before = list(COCO_PERSON_SKELETON)
+    heads = [head('cif', keypoints=COCO_KEYPOINTS),
+             head('caf', keypoints=COCO_KEYPOINTS, skeleton=COCO_PERSON_SKELETON),
+             head('caf25', keypoints=COCO_KEYPOINTS, skeleton=DENSER_COCO_PERSON_CONNECTIONS)]
+    dec = decoder.factory_decode(heads[:2], basenet_stride=16)
+    assert isinstance(dec, decoder.CifCaf)
+    assert dec.field_config.cif_strides == [8] and dec.field_config.caf_strides == [8]
+    assert list(dec.skeleton) == before
+    dense = decoder.factory_decode(heads, basenet_stride=16, dense_connections=True,
+                                   dense_coupling=0.01)
+    assert len(dense.skeleton) == 44 and dense.confidence_scales is None
+    assert dense.field_config.confidence_scales == [1.0] * 19 + [0.01] * 25
+    assert list(COCO_PERSON_SKELETON) == before, 'global skeleton must not be mutated'
+    with pytest.raises(AssertionError):
+        decoder.factory_decode(heads[:2], basenet_stride=16, caf_seeds=True)
+    with pytest.raises(Exception):
+        decoder.factory_decode([head('foo')], basenet_stride=16)
+
+
+def test_unconfigured_seed_threshold_raises(configured_decoder):
+    decoder = configured_decoder
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, COCO_PERSON_SKELETON
+    decoder.CifSeeds.threshold = None
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS,
+                         skeleton=COCO_PERSON_SKELETON)
+    with pytest.raises(TypeError):
+        dec.params()
