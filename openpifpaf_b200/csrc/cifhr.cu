@@ -5,21 +5,30 @@
 //
 // The reference walks the sources of one field sequentially and adds a clipped
 // Gaussian box per source into the hr map, clamping at 1 after every add.  All
-// increments are >= 0, so the per-step clamp equals one final clamp and only
-// the ORDER of the float adds per pixel matters (ascending source index =
-// row-major cell order).  We therefore run it as a gather:
+// increments are >= 0, so clamping at any subset of the steps gives the same
+// result and only the ORDER of the float adds per pixel matters (ascending
+// source index = row-major cell order).  We therefore run it as a gather in
+// which every pixel has exactly one owner lane:
 //
 //   K1 cif_compact_kernel   one CTA per (image, field): ordered compaction of
 //                           the cells with conf > v_threshold into a source
 //                           list {cx, cy, sigma^2, v} + integer box, plus a
 //                           per-strip source count (difference array in smem).
-//   K2 cifhr_splat_kernel   persistent CTAs over (image, field, strip of R hr
-//                           rows).  A strip is one contiguous run of floats in
-//                           HBM.  Empty strips (the vast majority) are pure
-//                           128-bit zero stores; the others filter the field's
-//                           source list into shared memory and every thread
-//                           accumulates its own 4 consecutive pixels over that
-//                           list in order, in registers, then stores once.
+//   K2 cifhr_splat_kernel   one CTA per (image, field, group of strips).  A
+//                           strip = R full hr rows = ONE contiguous run of
+//                           floats in HBM.
+//                             * empty strips (the vast majority): one TMA bulk
+//                               store (cp.async.bulk shared->global) from a
+//                               zeroed shared-memory buffer;
+//                             * other strips: the strip is assembled in a
+//                               shared-memory tile.  Warps own 128-pixel
+//                               patches (R rows x 128/R columns, 4 consecutive
+//                               pixels per lane); per 64-source chunk a 64-bit
+//                               mask per patch says which sources touch it, so
+//                               a warp only ever evaluates sources that
+//                               overlap its patch, in list order, accumulating
+//                               in registers.  The finished tile leaves with
+//                               one TMA bulk store (double-buffered).
 //
 // No atomics on hr, no read-modify-write of hr, no separate memset: every hr
 // byte is written exactly once.  Result is bit-identical to the reference.
@@ -28,9 +37,13 @@
 
 namespace pp {
 
-constexpr int kStripRows = 8;       // hr rows per strip
 constexpr int kSplatThreads = 256;
-constexpr int kChunk = 512;         // sources staged in smem at a time
+constexpr int kSplatWarps = kSplatThreads / 32;
+constexpr int kChunk = 64;            // sources per mask chunk (one bit each)
+constexpr int kGroupCap = kSplatThreads;   // sources staged per ordered-filter block
+constexpr int kGroupStrips = 9;       // strips per CTA
+constexpr int kMaxPatches = 96;       // patches per strip
+constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
 
 struct CifHrWs {
@@ -39,9 +52,17 @@ struct CifHrWs {
   int *n_src;       // (B,F)
   int *strip_cnt;   // (B,F,nstrips)
   int nstrips;
+  int rshift;       // strip rows R = 1 << rshift
 };
 
-__host__ __device__ inline int num_strips(int hh) { return (hh + kStripRows - 1) / kStripRows; }
+// rows per strip: the largest power of two <= 8 whose strip fits the smem budget
+static int strip_rshift(int hw) {
+  int r = 3;
+  while (r > 0 && ((size_t)hw << r) * sizeof(float) > (size_t)kStripBytesMax - 32) r--;
+  return r;
+}
+
+static int num_strips(int hh, int rshift) { return (hh + (1 << rshift) - 1) >> rshift; }
 
 size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   size_t bf = (size_t)s.B * s.F;
@@ -49,7 +70,7 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   n += align_up(bf * c.src_cap * sizeof(float4), 256);
   n += align_up(bf * c.src_cap * sizeof(int4), 256);
   n += align_up(bf * sizeof(int), 256);
-  n += align_up(bf * num_strips(hr_h(s)) * sizeof(int), 256);
+  n += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
   return n;
 }
 
@@ -61,7 +82,8 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
   w.src_b = (int4 *)p;   p += align_up(bf * c.src_cap * sizeof(int4), 256);
   w.n_src = (int *)p;    p += align_up(bf * sizeof(int), 256);
   w.strip_cnt = (int *)p;
-  w.nstrips = num_strips(hr_h(s));
+  w.rshift = strip_rshift(hr_w(s));
+  w.nstrips = num_strips(hr_h(s), w.rshift);
   return w;
 }
 
@@ -109,8 +131,8 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
         int maxy = (int)clipf(__fadd_rn(__fadd_rn(cy, sigma), 1.0f), (float)(miny + 1), (float)hh);
         oa[k] = make_float4(cx, cy, __fmul_rn(sigma, sigma), cv);
         ob[k] = make_int4(minx, maxx, miny, maxy);
-        atomicAdd(&sm_diff[miny / kStripRows], 1);
-        atomicAdd(&sm_diff[(maxy - 1) / kStripRows + 1], -1);
+        atomicAdd(&sm_diff[miny >> w.rshift], 1);
+        atomicAdd(&sm_diff[((maxy - 1) >> w.rshift) + 1], -1);
       }
     }
     count += total;
@@ -131,8 +153,9 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
   }
 }
 
+
 // ---------------------------------------------------------------------------
-// K2: per-strip gather.
+// K2: strips -> HBM.
 
 __device__ __forceinline__ void splat_px(float &acc, int px, int py, const float4 a, const int4 b) {
   if (px >= b.x && px < b.y && py >= b.z && py < b.w) {
@@ -159,121 +182,176 @@ __device__ __forceinline__ void splat_px(float &acc, int px, int py, const float
 
 __device__ __forceinline__ float clamp1(float v) { return (v < 1.0f) ? v : 1.0f; }  // :141
 
-__global__ void __launch_bounds__(kSplatThreads)
-cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_work, int src_cap, int hh, int hw) {
-  __shared__ float4 s_a[kChunk];
-  __shared__ int4 s_b[kChunk];
-  __shared__ int warp_tot[kSplatThreads / 32];
-  const size_t plane = (size_t)hh * hw;
+// TMA bulk copy shared -> global (no tensor map: the strip is linear memory).
+__device__ __forceinline__ void bulk_store(float *gdst, const float *ssrc, uint32_t bytes) {
+  uint32_t s = (uint32_t)__cvta_generic_to_shared(ssrc);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(gdst), "r"(s), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory");
+}
+// generic-proxy writes to smem -> visible to the async proxy (TMA)
+__device__ __forceinline__ void fence_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
 
-  for (int work = blockIdx.x; work < n_work; work += gridDim.x) {
-    const int bf = work / w.nstrips;
-    const int strip = work - bf * w.nstrips;
-    const int r0 = strip * kStripRows;
-    const int r1 = min(r0 + kStripRows, hh);
-    const size_t gp = (size_t)bf * plane;
-    const size_t gs = gp + (size_t)r0 * hw;        // first float of the strip
-    const size_t ge = gp + (size_t)r1 * hw;        // one past the last
-    const size_t ga = gs & ~(size_t)3;             // 16-byte aligned unit grid
-    const int n_units = (int)((ge - ga + 3) >> 2);
-    const int cnt = __ldg(w.strip_cnt + work);
+struct StripGeo {
+  size_t gs, ge;   // [gs, ge) floats of hr
+  size_t ga;       // gs rounded down to a 16-byte unit; smem index of float g is g - ga
+  size_t m0, m1;   // 16-byte aligned middle [m0, m1)
+  int r0, r1;
+};
 
-    if (cnt == 0) {
-      // zero fill: the dominant case.  Interior units are 128-bit stores.
-      for (int u = threadIdx.x; u < n_units; u += blockDim.x) {
-        size_t g = ga + ((size_t)u << 2);
-        if (g >= gs && g + 4 <= ge) {
-          *reinterpret_cast<float4 *>(hr + g) = make_float4(0.f, 0.f, 0.f, 0.f);
-        } else {
-          for (int i = 0; i < 4; i++)
-            if (g + i >= gs && g + i < ge) hr[g + i] = 0.f;
-        }
-      }
-      continue;
-    }
+__device__ __forceinline__ StripGeo strip_geo(size_t plane0, int strip, int rshift, int hh, int hw) {
+  StripGeo g;
+  g.r0 = strip << rshift;
+  g.r1 = min(g.r0 + (1 << rshift), hh);
+  g.gs = plane0 + (size_t)g.r0 * hw;
+  g.ge = plane0 + (size_t)g.r1 * hw;
+  g.ga = g.gs & ~(size_t)3;
+  g.m0 = (g.gs + 3) & ~(size_t)3;
+  g.m1 = g.ge & ~(size_t)3;
+  if (g.m0 > g.ge) g.m0 = g.ge;
+  if (g.m1 < g.m0) g.m1 = g.m0;
+  return g;
+}
 
-    const int nsrc = min(__ldg(w.n_src + bf), src_cap);
-    const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
-    const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
-    const bool single = nsrc <= kChunk;
-    int n_staged = 0;
-
-    for (int ubase = 0; ubase < n_units; ubase += blockDim.x) {
-      const int u = ubase + threadIdx.x;
-      const bool live = u < n_units;
-      // dead lanes shadow the last unit so that the warp extents below stay valid
-      const size_t g = ga + ((size_t)(live ? u : n_units - 1) << 2);
-      // in-plane coordinates of the unit's first float (may be < gs for the head unit)
-      long long pl = (long long)g - (long long)gp;
-      int y0 = (int)(pl / hw);
-      int x0 = (int)(pl - (long long)y0 * hw);
-      int px[4], py[4];
-#pragma unroll
-      for (int i = 0; i < 4; i++) {
-        int xx = x0 + i, yy = y0;
-        if (xx >= hw) { xx -= hw; yy += 1; }
-        px[i] = xx; py[i] = yy;
-      }
-      // warp-uniform extent of the 32 units this warp owns (<= 128 pixels)
-      int wy0 = __shfl_sync(0xffffffffu, py[0], 0);
-      int wy1 = __shfl_sync(0xffffffffu, py[3], 31);
-      int wx0 = __shfl_sync(0xffffffffu, px[0], 0);
-      int wx1 = __shfl_sync(0xffffffffu, px[3], 31);
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
-
-      for (int cbase = 0; cbase < nsrc; cbase += kChunk) {
-        if (!(single && ubase > 0)) {
-          // stage the sources of this chunk that touch rows [r0, r1), in order
-          __syncthreads();
-          n_staged = 0;
-          const int cend = min(cbase + kChunk, nsrc);
-          for (int b0 = cbase; b0 < cend; b0 += blockDim.x) {
-            int i = b0 + threadIdx.x;
-            bool keep = false;
-            int4 bb = make_int4(0, 0, 0, 0);
-            if (i < cend) {
-              bb = gb_src[i];
-              keep = bb.z < r1 && bb.w > r0;
-            }
-            int tot;
-            int off = block_flag_scan(keep, warp_tot, &tot);
-            if (keep) {
-              s_a[n_staged + off] = ga_src[i];
-              s_b[n_staged + off] = bb;
-            }
-            n_staged += tot;
-          }
-          __syncthreads();
-        }
-        if (live) {
-          for (int k = 0; k < n_staged; k++) {
-            const int4 b = s_b[k];
-            if (b.w <= wy0 || b.z > wy1) continue;                 // warp-uniform row reject
-            if (wy0 == wy1 && (b.y <= wx0 || b.x > wx1)) continue; // and column reject
-            const float4 a = s_a[k];
-#pragma unroll
-            for (int i = 0; i < 4; i++) splat_px(acc[i], px[i], py[i], a, b);
-            if ((k & 7) == 7) {
-              // saturation exit: once every pixel of the warp reached 1 nothing can change
-              bool sat = !(acc[0] < 1.f) && !(acc[1] < 1.f) && !(acc[2] < 1.f) && !(acc[3] < 1.f);
-              if (__all_sync(__activemask(), sat)) break;
-            }
-          }
-        }
-      }
-      if (live) {
-        if (g >= gs && g + 4 <= ge) {
-          *reinterpret_cast<float4 *>(hr + g) =
-              make_float4(clamp1(acc[0]), clamp1(acc[1]), clamp1(acc[2]), clamp1(acc[3]));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 4; i++)
-            if (g + i >= gs && g + i < ge) hr[g + i] = clamp1(acc[i]);
-        }
-      }
-    }
-    __syncthreads();
+// Write one finished strip from a smem buffer laid out like the strip.  Call
+// from all threads after the buffer is complete, fenced and barriered.
+__device__ __forceinline__ void emit_strip(float *__restrict__ hr, const float *buf, const StripGeo &g) {
+  const int t = threadIdx.x;
+  if (t == 0) {
+    if (g.m1 > g.m0) bulk_store(hr + g.m0, buf + (g.m0 - g.ga), (uint32_t)((g.m1 - g.m0) * sizeof(float)));
+  } else if (t >= 32 && t < 36) {          // head: < 4 floats before the aligned middle
+    size_t i = g.gs + (size_t)(t - 32);
+    if (i < g.m0) hr[i] = buf[i - g.ga];
+  } else if (t >= 36 && t < 40) {          // tail
+    size_t i = g.m1 + (size_t)(t - 36);
+    if (i < g.ge) hr[i] = buf[i - g.ga];
   }
+}
+
+__global__ void __launch_bounds__(kSplatThreads)
+cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap, int hh, int hw,
+                   int buf_floats) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float *zero = reinterpret_cast<float *>(smem_raw);
+  float *tiles = zero + buf_floats;                       // two tile buffers
+  __shared__ float4 s_a[kGroupCap];
+  __shared__ int4 s_b[kGroupCap];
+  __shared__ unsigned long long s_mask[kMaxPatches];
+  __shared__ int warp_tot[kSplatWarps];
+  __shared__ int s_cnt[kGroupStrips];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bf = blockIdx.x / n_groups;
+  const int grp = blockIdx.x - bf * n_groups;
+  const int strip0 = grp * kGroupStrips;
+  const int nloc = min(kGroupStrips, w.nstrips - strip0);
+  const int rshift = w.rshift;
+  const int cshift = 7 - rshift;                          // patch = (1 << rshift) rows x (1 << cshift) cols
+  const size_t plane0 = (size_t)bf * hh * hw;
+
+  if (tid < kGroupStrips) s_cnt[tid] = tid < nloc ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + tid) : 0;
+  for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
+    reinterpret_cast<float4 *>(zero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_async_smem();
+  __syncthreads();
+
+  // ---- empty strips: pure TMA zero stores ------------------------------------
+  int n_busy = 0;
+  for (int k = 0; k < nloc; k++) {
+    if (s_cnt[k] != 0) { n_busy++; continue; }
+    emit_strip(hr, zero, strip_geo(plane0, strip0 + k, rshift, hh, hw));
+  }
+  if (n_busy == 0) {
+    if (tid == 0) bulk_wait_read<0>();
+    return;
+  }
+
+  // ---- strips with sources ------------------------------------------------------
+  const int nsrc = min(__ldg(w.n_src + bf), src_cap);
+  const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
+  const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
+  const int n_patches = (hw + (1 << cshift) - 1) >> cshift;
+  const int row = lane >> (5 - rshift);                   // lane's row inside the patch
+  const int cg = lane & ((1 << (5 - rshift)) - 1);        // lane's 4-pixel column group
+  int n_tiles = 0;
+
+  for (int k = 0; k < nloc; k++) {
+    if (s_cnt[k] == 0) continue;
+    const StripGeo g = strip_geo(plane0, strip0 + k, rshift, hh, hw);
+    float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
+    // the bulk store that last read this buffer (two tiles ago) must have drained
+    if (n_tiles >= 2 && tid == 0) bulk_wait_read<1>();
+    __syncthreads();
+    for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
+      reinterpret_cast<float4 *>(tile)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int py = g.r0 + row;
+    const int tile_row = (int)(g.gs - g.ga) + row * hw;
+
+    for (int base = 0; base < nsrc; base += kSplatThreads) {
+      // ordered filter of this block of sources by the strip's rows
+      const int i = base + tid;
+      bool keep = false;
+      int4 bb = make_int4(0, 0, 0, 0);
+      if (i < nsrc) {
+        bb = gb_src[i];
+        keep = bb.z < g.r1 && bb.w > g.r0;
+      }
+      int n_staged;
+      const int off = block_flag_scan(keep, warp_tot, &n_staged);   // two barriers
+      if (keep) { s_a[off] = ga_src[i]; s_b[off] = bb; }
+      if (n_staged == 0) continue;
+
+      for (int c0 = 0; c0 < n_staged; c0 += kChunk) {
+        const int nchunk = min(kChunk, n_staged - c0);
+        for (int p = tid; p < n_patches; p += kSplatThreads) s_mask[p] = 0ull;
+        __syncthreads();                                   // staged list + cleared masks visible
+        if (tid < nchunk) {
+          const int4 b = s_b[c0 + tid];
+          const int p0 = b.x >> cshift, p1 = (b.y - 1) >> cshift;
+          for (int p = p0; p <= p1; p++) atomicOr(&s_mask[p], 1ull << tid);
+        }
+        __syncthreads();
+        for (int p = warp; p < n_patches; p += kSplatWarps) {
+          unsigned long long m = s_mask[p];
+          if (m == 0ull) continue;
+          const int px0 = (p << cshift) + (cg << 2);
+          const bool ok = py < g.r1;
+          float acc[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) acc[j] = (ok && px0 + j < hw) ? tile[tile_row + px0 + j] : 0.f;
+          int seen = 0;
+          while (m) {
+            const int s = __ffsll((long long)m) - 1;
+            m &= m - 1ull;
+            const float4 a = s_a[c0 + s];
+            const int4 b = s_b[c0 + s];
+#pragma unroll
+            for (int j = 0; j < 4; j++) splat_px(acc[j], px0 + j, py, a, b);
+            if ((++seen & 7) == 0) {
+              // once every pixel of the patch reached 1 nothing can change any more
+              bool sat = !(acc[0] < 1.f) && !(acc[1] < 1.f) && !(acc[2] < 1.f) && !(acc[3] < 1.f);
+              if (__all_sync(0xffffffffu, sat)) break;
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if (ok && px0 + j < hw) tile[tile_row + px0 + j] = clamp1(acc[j]);
+        }
+        __syncthreads();                                   // patches done before masks are cleared again
+      }
+    }
+    fence_async_smem();
+    __syncthreads();
+    emit_strip(hr, tile, g);
+    n_tiles++;
+  }
+  if (tid == 0) bulk_wait_read<0>();
 }
 
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
@@ -281,17 +359,24 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   CifHrWs w = carve(d_ws, s, c);
   const int hh = hr_h(s), hw = hr_w(s);
   const int bf = s.B * s.F;
+  if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
+  if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
   size_t smem = (size_t)(w.nstrips + 1) * sizeof(int);
   prof_mark(p.profile, kStCompact, st);
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
       d_cif, w, s, c.src_cap, hh, hw, p.cif_threshold, p.cif_min_scale / (float)s.stride,
       p.cif_min_scale != 0.0f, d_status);
   PP_LAUNCH_CHECK("cif_compact_kernel");
-  const int n_work = bf * w.nstrips;
-  int grid = num_sms() * 8;
-  if (grid > n_work) grid = n_work;
+  // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
+  const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
+  const size_t dyn = (size_t)3 * buf_floats * sizeof(float);
+  // per device and cheap: set on every launch rather than caching per process
+  PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_splat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     3 * kStripBytesMax));
+  const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
   prof_mark(p.profile, kStSplat, st);
-  cifhr_splat_kernel<<<grid, kSplatThreads, 0, st>>>(d_hr, w, n_work, c.src_cap, hh, hw);
+  cifhr_splat_kernel<<<bf * n_groups, kSplatThreads, dyn, st>>>(d_hr, w, n_groups, c.src_cap, hh, hw,
+                                                               buf_floats);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
   return PP_OK;
 }
