@@ -21,9 +21,9 @@
 //                               store (cp.async.bulk shared->global) from a
 //                               zeroed shared-memory buffer;
 //                             * other strips: the strip is assembled in a
-//                               shared-memory tile.  Warps own 128-pixel
-//                               patches (R rows x 128/R columns, 4 consecutive
-//                               pixels per lane); per 64-source chunk a 64-bit
+//                               shared-memory tile.  Warps own 32-pixel
+//                               patches (R rows x 32/R columns, one pixel per
+//                               lane); per 64-source chunk a 64-bit
 //                               mask per patch says which sources touch it, so
 //                               a warp only ever evaluates sources that
 //                               overlap its patch, in list order, accumulating
@@ -32,6 +32,8 @@
 //
 // No atomics on hr, no read-modify-write of hr, no separate memset: every hr
 // byte is written exactly once.  Result is bit-identical to the reference.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "stages.cuh"
 
@@ -41,8 +43,13 @@ constexpr int kSplatThreads = 256;
 constexpr int kSplatWarps = kSplatThreads / 32;
 constexpr int kChunk = 64;            // sources per mask chunk (one bit each)
 constexpr int kGroupCap = kSplatThreads;   // sources staged per ordered-filter block
-constexpr int kGroupStrips = 9;       // strips per CTA
-constexpr int kMaxPatches = 96;       // patches per strip
+constexpr int kGroupStripsMax = 32;
+static int group_strips() {           // strips per CTA
+  if (const char *e = getenv("PP_CIFHR_GROUP")) { int g = atoi(e); if (g >= 1 && g <= kGroupStripsMax) return g; }
+  return 9;
+}
+constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see strip_rshift)
+constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored from (4 KiB pieces)
 constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
 
@@ -58,6 +65,7 @@ struct CifHrWs {
 // rows per strip: the largest power of two <= 8 whose strip fits the smem budget
 static int strip_rshift(int hw) {
   int r = 3;
+  if (const char *e = getenv("PP_CIFHR_RSHIFT")) r = atoi(e) & 3;   // tuning experiments only
   while (r > 0 && ((size_t)hw << r) * sizeof(float) > (size_t)kStripBytesMax - 32) r--;
   return r;
 }
@@ -234,17 +242,34 @@ __device__ __forceinline__ void emit_strip(float *__restrict__ hr, const float *
   }
 }
 
+// An empty strip: zeros, in pieces of the small zero buffer.
+__device__ __forceinline__ void emit_zero_strip(float *__restrict__ hr, const float *zero, const StripGeo &g) {
+  const int t = threadIdx.x;
+  if (t == 0) {
+    for (size_t o = g.m0; o < g.m1; o += kZeroFloats) {
+      size_t n = g.m1 - o < (size_t)kZeroFloats ? g.m1 - o : (size_t)kZeroFloats;
+      bulk_store(hr + o, zero, (uint32_t)(n * sizeof(float)));
+    }
+  } else if (t >= 32 && t < 36) {
+    size_t i = g.gs + (size_t)(t - 32);
+    if (i < g.m0) hr[i] = 0.f;
+  } else if (t >= 36 && t < 40) {
+    size_t i = g.m1 + (size_t)(t - 36);
+    if (i < g.ge) hr[i] = 0.f;
+  }
+}
+
 __global__ void __launch_bounds__(kSplatThreads)
-cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap, int hh, int hw,
-                   int buf_floats) {
+cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int kGroupStrips, int src_cap,
+                   int hh, int hw, int buf_floats) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float *zero = reinterpret_cast<float *>(smem_raw);
-  float *tiles = zero + buf_floats;                       // two tile buffers
+  float *tiles = zero + kZeroFloats;                      // two tile buffers
   __shared__ float4 s_a[kGroupCap];
   __shared__ int4 s_b[kGroupCap];
   __shared__ unsigned long long s_mask[kMaxPatches];
   __shared__ int warp_tot[kSplatWarps];
-  __shared__ int s_cnt[kGroupStrips];
+  __shared__ int s_cnt[kGroupStripsMax];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bf = blockIdx.x / n_groups;
@@ -252,11 +277,11 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap,
   const int strip0 = grp * kGroupStrips;
   const int nloc = min(kGroupStrips, w.nstrips - strip0);
   const int rshift = w.rshift;
-  const int cshift = 7 - rshift;                          // patch = (1 << rshift) rows x (1 << cshift) cols
+  const int cshift = 5 - rshift;                          // patch = (1 << rshift) rows x (1 << cshift) cols, 1 px per lane
   const size_t plane0 = (size_t)bf * hh * hw;
 
   if (tid < kGroupStrips) s_cnt[tid] = tid < nloc ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + tid) : 0;
-  for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
+  for (int i = tid; i < (kZeroFloats >> 2); i += kSplatThreads)
     reinterpret_cast<float4 *>(zero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_async_smem();
   __syncthreads();
@@ -265,7 +290,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap,
   int n_busy = 0;
   for (int k = 0; k < nloc; k++) {
     if (s_cnt[k] != 0) { n_busy++; continue; }
-    emit_strip(hr, zero, strip_geo(plane0, strip0 + k, rshift, hh, hw));
+    emit_zero_strip(hr, zero, strip_geo(plane0, strip0 + k, rshift, hh, hw));
   }
   if (n_busy == 0) {
     if (tid == 0) bulk_wait_read<0>();
@@ -278,7 +303,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap,
   const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
   const int n_patches = (hw + (1 << cshift) - 1) >> cshift;
   const int row = lane >> (5 - rshift);                   // lane's row inside the patch
-  const int cg = lane & ((1 << (5 - rshift)) - 1);        // lane's 4-pixel column group
+  const int cg = lane & ((1 << (5 - rshift)) - 1);        // lane's column inside the patch
   int n_tiles = 0;
 
   for (int k = 0; k < nloc; k++) {
@@ -320,28 +345,20 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int src_cap,
         for (int p = warp; p < n_patches; p += kSplatWarps) {
           unsigned long long m = s_mask[p];
           if (m == 0ull) continue;
-          const int px0 = (p << cshift) + (cg << 2);
-          const bool ok = py < g.r1;
-          float acc[4];
-#pragma unroll
-          for (int j = 0; j < 4; j++) acc[j] = (ok && px0 + j < hw) ? tile[tile_row + px0 + j] : 0.f;
+          const int px = (p << cshift) + cg;
+          const bool ok = py < g.r1 && px < hw;
+          float acc = ok ? tile[tile_row + px] : 0.f;
           int seen = 0;
           while (m) {
             const int s = __ffsll((long long)m) - 1;
             m &= m - 1ull;
-            const float4 a = s_a[c0 + s];
-            const int4 b = s_b[c0 + s];
-#pragma unroll
-            for (int j = 0; j < 4; j++) splat_px(acc[j], px0 + j, py, a, b);
+            splat_px(acc, px, py, s_a[c0 + s], s_b[c0 + s]);
             if ((++seen & 7) == 0) {
               // once every pixel of the patch reached 1 nothing can change any more
-              bool sat = !(acc[0] < 1.f) && !(acc[1] < 1.f) && !(acc[2] < 1.f) && !(acc[3] < 1.f);
-              if (__all_sync(0xffffffffu, sat)) break;
+              if (__all_sync(0xffffffffu, !(acc < 1.f))) break;
             }
           }
-#pragma unroll
-          for (int j = 0; j < 4; j++)
-            if (ok && px0 + j < hw) tile[tile_row + px0 + j] = clamp1(acc[j]);
+          if (ok) tile[tile_row + px] = clamp1(acc);
         }
         __syncthreads();                                   // patches done before masks are cleared again
       }
@@ -369,14 +386,15 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   PP_LAUNCH_CHECK("cif_compact_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
-  const size_t dyn = (size_t)3 * buf_floats * sizeof(float);
+  const size_t dyn = ((size_t)kZeroFloats + 2 * (size_t)buf_floats) * sizeof(float);
   // per device and cheap: set on every launch rather than caching per process
   PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_splat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     3 * kStripBytesMax));
+                                     2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
+  const int kGroupStrips = group_strips();
   const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
   prof_mark(p.profile, kStSplat, st);
-  cifhr_splat_kernel<<<bf * n_groups, kSplatThreads, dyn, st>>>(d_hr, w, n_groups, c.src_cap, hh, hw,
-                                                               buf_floats);
+  cifhr_splat_kernel<<<bf * n_groups, kSplatThreads, dyn, st>>>(d_hr, w, n_groups, kGroupStrips, c.src_cap,
+                                                               hh, hw, buf_floats);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
   return PP_OK;
 }
