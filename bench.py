@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument('--workload', default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument('--batch', type=int, default=0, help='images per GPU per step (0 = workload default)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--host-chunk', type=int, default=0, help='e2e: images per pipeline chunk (0 = decoder default)')
     ap.add_argument('--cpu-workers', type=int, default=0, help='reference arm: pool size (0 = all cores)')
     return ap.parse_args()
 
@@ -342,6 +343,8 @@ def run_b200(args):
     configure_profile(decoder)
     cif, caf, skeleton = make_batch(args.workload, batch, first_seed=rank * batch)
     dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=skeleton)
+    if args.host_chunk:
+        decoder.CifCaf.host_chunk = args.host_chunk
     eng = dec.engine()
     params = dec.params()
     d_cif = torch.from_numpy(cif).to(device)
@@ -389,6 +392,19 @@ def run_b200(args):
     d2h = sum(t.numel() * t.element_size() for t in hbuf.host.values())
     h2d = cif.nbytes + caf.nbytes
 
+    # pure host->device copy of one step's fields: the PCIe floor under e2e
+    for _ in range(2):
+        d_cif.copy_(h_cif, non_blocking=True)
+        d_caf.copy_(h_caf, non_blocking=True)
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(5):
+        d_cif.copy_(h_cif, non_blocking=True)
+        d_caf.copy_(h_caf, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_ms = ev0.elapsed_time(ev1) / 5
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -418,7 +434,10 @@ def run_b200(args):
         'config': workload_config(args.workload, batch, world),
         'e2e': {'value': world * batch * args.steps / e2e_s, 'unit': UNIT,
                 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]]'},
+                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]]',
+                'host_chunk': decoder.CifCaf.host_chunk, 'ms_per_step': 1e3 * e2e_s / args.steps,
+                'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
+                'pcie_floor_frac': h2d_ms / (1e3 * e2e_s / args.steps)},
         'gpu_launches': _lib.lib().pp_decode_launch_count(None) * args.steps,
         'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
                      'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,

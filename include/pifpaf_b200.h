@@ -200,6 +200,24 @@ int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, f
                          void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
                          const pp_params *p, void *stream);
 
+/* Pipelined variant of pp_decode_batch_host for pinned host buffers: the batch
+ * is cut into chunks of `chunk_images`; the host->device copy of chunk c+1 and
+ * the device->host copy of chunk c-1 (two internal streams of the pipeline
+ * object) overlap the kernels of chunk c (on `stream`).  Only enqueues;
+ * pp_pipeline_wait(pipe, c) blocks until chunk c's results are in h_out (so the
+ * caller can consume chunk c while later chunks are in flight) and returns
+ * PP_ERR_CAPACITY if one of its images overflowed; c = -1 waits for all. */
+typedef struct pp_pipeline pp_pipeline;
+pp_pipeline *pp_pipeline_create(int max_chunks);
+void pp_pipeline_destroy(pp_pipeline *pipe);
+int pp_decode_batch_host_async(pp_pipeline *pipe, const float *h_cif, const float *h_caf,
+                               float *d_cif, float *d_caf, const pp_skeleton *sk,
+                               const pp_outputs *d_out, const pp_outputs *h_out, void *d_ws,
+                               size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                               const pp_params *p, int chunk_images, void *stream);
+int pp_pipeline_wait(pp_pipeline *pipe, int chunk);
+int pp_pipeline_chunks(const pp_pipeline *pipe);
+
 /* ---- parity shim: the reference's live functional.pyx primitives ---------
  * Same names / argument meaning as functional.pyx, on device buffers. */
 

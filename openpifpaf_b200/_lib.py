@@ -124,6 +124,14 @@ def lib():
                                   P(Params), vp]
     l.pp_decode_batch_host.argtypes = [vp, vp, vp, vp, P(Skeleton), P(Outputs), P(Outputs), vp, sz,
                                        P(Shape), P(Caps), P(Params), vp]
+    l.pp_pipeline_create.restype = vp
+    l.pp_pipeline_create.argtypes = [i32]
+    l.pp_pipeline_destroy.restype = None
+    l.pp_pipeline_destroy.argtypes = [vp]
+    l.pp_pipeline_wait.argtypes = [vp, i32]
+    l.pp_pipeline_chunks.argtypes = [vp]
+    l.pp_decode_batch_host_async.argtypes = [vp, vp, vp, vp, vp, P(Skeleton), P(Outputs), P(Outputs),
+                                             vp, sz, P(Shape), P(Caps), P(Params), i32, vp]
     l.pp_scalar_square_add_gauss_with_max.argtypes = [vp, i32, i32, vp, vp, vp, vp, i32, f32, f32, vp]
     l.pp_scalar_values.argtypes = [vp, i32, i32, vp, vp, i32, f32, vp, vp]
     l.pp_caf_center_s.argtypes = [vp, i32, f32, f32, f32, vp, vp, vp]
@@ -140,7 +148,8 @@ EXPORTS = (
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
     'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
-    'pp_decode_batch_host', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
+    'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
+    'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
     'pp_caf_center_s', 'pp_scalar_nonzero_clipped_with_reduction', 'pp_scalar_square_add_single',
 )
 

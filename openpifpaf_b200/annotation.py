@@ -14,12 +14,18 @@ import numpy as np
 NOTSET = '__notset__'
 
 
+_WEIGHTS = {}
+
+
 def _score_weights(n, suppress_last=False):
-    w = np.ones((n,))
-    if suppress_last:
-        w[-1] = 0.0
-    w[:3] = 3.0
-    return w / np.sum(w)
+    key = (n, suppress_last)
+    if key not in _WEIGHTS:
+        w = np.ones((n,))
+        if suppress_last:
+            w[-1] = 0.0
+        w[:3] = 3.0
+        _WEIGHTS[key] = w / np.sum(w)
+    return _WEIGHTS[key].copy()
 
 
 class Annotation:
@@ -53,6 +59,24 @@ class Annotation:
         ann.joint_scales = np.array(joint_scales, dtype=np.float32)
         if order is not None:
             ann._lazy = (np.array(pre_data, dtype=np.float32), np.array(order), graph)
+        return ann
+
+    @classmethod
+    def wrap(cls, keypoints, skeleton, data, joint_scales, lazy):
+        """Fast path of ``from_buffers``: adopts the given arrays (no copies, no zero fill).
+        ``data`` / ``joint_scales`` must be arrays this annotation may own and mutate."""
+        ann = cls.__new__(cls)
+        ann.keypoints = keypoints
+        ann.skeleton = skeleton
+        ann.category_id = 1
+        ann.suppress_score_index = None
+        ann.data = data
+        ann.joint_scales = joint_scales
+        ann.fixed_score = NOTSET
+        ann._decoding_order = []
+        ann._frontier_order = []
+        ann._lazy = lazy
+        ann.score_weights = _score_weights(len(keypoints))
         return ann
 
     def _materialise(self):

@@ -381,9 +381,54 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   return rc;
 }
 
-#define PP_D2H(member, bytes)                                                                   \
-  if (h_out->member && d_out->member)                                                           \
-  PP_CUDA_CHECK(cudaMemcpyAsync(h_out->member, d_out->member, (bytes), cudaMemcpyDeviceToHost, st))
+// ---- host entries ------------------------------------------------------------
+
+struct OutField { size_t offset; size_t bytes_per_image; };
+
+// byte size of one image's slice of every pp_outputs member, in declaration order
+static void output_strides(const pp_shape &s, const pp_caps &c, size_t out[17]) {
+  const size_t F = s.F, L = s.L, A = c.ann_cap;
+  const size_t f = sizeof(float), i = sizeof(int32_t);
+  out[0] = F * hr_h(s) * hr_w(s) * f;   // hr
+  out[1] = (size_t)c.seed_cap * 5 * f;  // seeds
+  out[2] = i;                           // n_seeds
+  out[3] = L * 9 * c.caf_cap * f;       // caf_fwd
+  out[4] = L * 9 * c.caf_cap * f;       // caf_bwd
+  out[5] = L * i;                       // n_caf_fwd
+  out[6] = L * i;                       // n_caf_bwd
+  out[7] = A * F * 3 * f;               // ann_data
+  out[8] = A * F * f;                   // ann_scales
+  out[9] = A * sizeof(double);          // ann_score
+  out[10] = A * i;                      // ann_source
+  out[11] = i;                          // n_ann
+  out[12] = A * F * 3 * f;              // pre_data
+  out[13] = A * F * f;                  // pre_scales
+  out[14] = A * F * 2 * i;              // pre_order
+  out[15] = i;                          // n_pre
+  out[16] = i;                          // status
+}
+
+static_assert(sizeof(pp_outputs) == 17 * sizeof(void *), "pp_outputs member table out of date");
+
+// the outputs of images [b0, ...) as their own pp_outputs
+static pp_outputs slice_outputs(const pp_outputs &o, const size_t strides[17], size_t b0) {
+  pp_outputs r = o;
+  char **src = (char **)&r;
+  for (int k = 0; k < 17; k++)
+    if (src[k]) src[k] += b0 * strides[k];
+  return r;
+}
+
+static int copy_outputs_to_host(const pp_outputs &d, const pp_outputs &h, const size_t strides[17],
+                                size_t b0, size_t nb, cudaStream_t st) {
+  char *const *dp = (char *const *)&d;
+  char *const *hp = (char *const *)&h;
+  for (int k = 0; k < 17; k++)
+    if (dp[k] && hp[k])
+      PP_CUDA_CHECK(cudaMemcpyAsync(hp[k] + b0 * strides[k], dp[k] + b0 * strides[k], nb * strides[k],
+                                    cudaMemcpyDeviceToHost, st));
+  return PP_OK;
+}
 
 int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, float *d_caf,
                          const pp_skeleton *sk, const pp_outputs *d_out, const pp_outputs *h_out,
@@ -399,28 +444,125 @@ int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, f
                                 cudaMemcpyHostToDevice, st));
   int rc = pp_decode_batch(d_cif, d_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
   if (rc) return rc;
-  size_t bc = B * c->ann_cap;
-  PP_D2H(ann_data, bc * s->F * 3 * sizeof(float));
-  PP_D2H(ann_scales, bc * s->F * sizeof(float));
-  PP_D2H(ann_score, bc * sizeof(double));
-  PP_D2H(ann_source, bc * sizeof(int));
-  PP_D2H(n_ann, B * sizeof(int));
-  PP_D2H(pre_data, bc * s->F * 3 * sizeof(float));
-  PP_D2H(pre_scales, bc * s->F * sizeof(float));
-  PP_D2H(pre_order, bc * s->F * 2 * sizeof(int));
-  PP_D2H(n_pre, B * sizeof(int));
-  PP_D2H(status, B * sizeof(int));
-  PP_D2H(seeds, B * c->seed_cap * 5 * sizeof(float));
-  PP_D2H(n_seeds, B * sizeof(int));
-  PP_D2H(caf_fwd, B * s->L * 9 * c->caf_cap * sizeof(float));
-  PP_D2H(caf_bwd, B * s->L * 9 * c->caf_cap * sizeof(float));
-  PP_D2H(n_caf_fwd, B * s->L * sizeof(int));
-  PP_D2H(n_caf_bwd, B * s->L * sizeof(int));
-  PP_D2H(hr, B * s->F * (size_t)hr_h(*s) * hr_w(*s) * sizeof(float));
+  size_t strides[17];
+  output_strides(*s, *c, strides);
+  if ((rc = copy_outputs_to_host(*d_out, *h_out, strides, 0, B, st))) return rc;
   PP_CUDA_CHECK(cudaStreamSynchronize(st));
   if (h_out->status)
     for (size_t b = 0; b < B; b++)
       if (h_out->status[b] != 0) return PP_ERR_CAPACITY;
+  return PP_OK;
+}
+
+}  // extern "C"
+
+struct pp_pipeline {
+  int max_chunks, n_chunks, chunk_images, B;
+  cudaStream_t s_in, s_out;
+  cudaEvent_t ev_start;
+  cudaEvent_t *ev_in, *ev_done, *ev_out;   // (max_chunks) each
+  const int32_t *h_status;
+};
+
+extern "C" {
+
+pp_pipeline *pp_pipeline_create(int max_chunks) {
+  if (max_chunks <= 0) return nullptr;
+  pp_pipeline *q = (pp_pipeline *)calloc(1, sizeof(pp_pipeline));
+  if (!q) return nullptr;
+  q->max_chunks = max_chunks;
+  q->ev_in = (cudaEvent_t *)calloc(3 * (size_t)max_chunks, sizeof(cudaEvent_t));
+  bool ok = q->ev_in != nullptr;
+  if (ok) {
+    q->ev_done = q->ev_in + max_chunks;
+    q->ev_out = q->ev_done + max_chunks;
+    ok = cudaStreamCreateWithFlags(&q->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaStreamCreateWithFlags(&q->s_out, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&q->ev_start, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < 3 * max_chunks; i++)
+      ok = cudaEventCreateWithFlags(&q->ev_in[i], cudaEventDisableTiming) == cudaSuccess;
+  }
+  if (!ok) { pp_pipeline_destroy(q); return nullptr; }
+  return q;
+}
+
+void pp_pipeline_destroy(pp_pipeline *q) {
+  if (!q) return;
+  if (q->ev_in) {
+    for (int i = 0; i < 3 * q->max_chunks; i++)
+      if (q->ev_in[i]) cudaEventDestroy(q->ev_in[i]);
+    free(q->ev_in);
+  }
+  if (q->ev_start) cudaEventDestroy(q->ev_start);
+  if (q->s_in) cudaStreamDestroy(q->s_in);
+  if (q->s_out) cudaStreamDestroy(q->s_out);
+  free(q);
+}
+
+int pp_pipeline_chunks(const pp_pipeline *q) { return q ? q->n_chunks : 0; }
+
+int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *h_caf, float *d_cif,
+                               float *d_caf, const pp_skeleton *sk, const pp_outputs *d_out,
+                               const pp_outputs *h_out, void *d_ws, size_t ws_bytes,
+                               const pp_shape *s, const pp_caps *c, const pp_params *p,
+                               int chunk_images, void *stream) {
+  if (!q || !shape_ok(s) || !caps_ok(s, c) || !h_cif || !h_caf || !d_cif || !d_caf || !d_out ||
+      !h_out || !p || !sk)
+    return PP_ERR_ARG;
+  if (chunk_images <= 0 || chunk_images > s->B) chunk_images = s->B;
+  const int n_chunks = (s->B + chunk_images - 1) / chunk_images;
+  if (n_chunks > q->max_chunks) return PP_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  q->n_chunks = n_chunks; q->chunk_images = chunk_images; q->B = s->B;
+  q->h_status = h_out->status;
+  const size_t cells = (size_t)s->H * s->W;
+  const size_t cif_img = (size_t)s->F * 5 * cells, caf_img = (size_t)s->L * 9 * cells;
+  size_t strides[17];
+  output_strides(*s, *c, strides);
+
+  // the copy-in stream starts after whatever is already queued on `stream`
+  PP_CUDA_CHECK(cudaEventRecord(q->ev_start, st));
+  PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_in, q->ev_start, 0));
+  for (int k = 0; k < n_chunks; k++) {
+    const size_t b0 = (size_t)k * chunk_images;
+    const size_t nb = (size_t)s->B - b0 < (size_t)chunk_images ? (size_t)s->B - b0 : (size_t)chunk_images;
+    PP_CUDA_CHECK(cudaMemcpyAsync(d_cif + b0 * cif_img, h_cif + b0 * cif_img, nb * cif_img * sizeof(float),
+                                  cudaMemcpyHostToDevice, q->s_in));
+    PP_CUDA_CHECK(cudaMemcpyAsync(d_caf + b0 * caf_img, h_caf + b0 * caf_img, nb * caf_img * sizeof(float),
+                                  cudaMemcpyHostToDevice, q->s_in));
+    PP_CUDA_CHECK(cudaEventRecord(q->ev_in[k], q->s_in));
+  }
+  for (int k = 0; k < n_chunks; k++) {
+    const size_t b0 = (size_t)k * chunk_images;
+    const size_t nb = (size_t)s->B - b0 < (size_t)chunk_images ? (size_t)s->B - b0 : (size_t)chunk_images;
+    pp_shape sub = *s;
+    sub.B = (int32_t)nb;
+    const pp_outputs d_sub = slice_outputs(*d_out, strides, b0);
+    PP_CUDA_CHECK(cudaStreamWaitEvent(st, q->ev_in[k], 0));
+    // kernels of successive chunks are serial on `stream`, so they share one workspace
+    int rc = pp_decode_batch(d_cif + b0 * cif_img, d_caf + b0 * caf_img, sk, &d_sub, d_ws, ws_bytes,
+                             &sub, c, p, stream);
+    if (rc) return rc;
+    PP_CUDA_CHECK(cudaEventRecord(q->ev_done[k], st));
+    PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_out, q->ev_done[k], 0));
+    if ((rc = copy_outputs_to_host(*d_out, *h_out, strides, b0, nb, q->s_out))) return rc;
+    PP_CUDA_CHECK(cudaEventRecord(q->ev_out[k], q->s_out));
+  }
+  // later work on `stream` is ordered after the last copy-out
+  PP_CUDA_CHECK(cudaStreamWaitEvent(st, q->ev_out[n_chunks - 1], 0));
+  return PP_OK;
+}
+
+int pp_pipeline_wait(pp_pipeline *q, int chunk) {
+  if (!q || chunk >= q->n_chunks) return PP_ERR_ARG;
+  const int k0 = chunk < 0 ? 0 : chunk, k1 = chunk < 0 ? q->n_chunks : chunk + 1;
+  for (int k = k0; k < k1; k++) PP_CUDA_CHECK(cudaEventSynchronize(q->ev_out[k]));
+  if (q->h_status) {
+    const int b0 = k0 * q->chunk_images;
+    const int b1 = k1 * q->chunk_images < q->B ? k1 * q->chunk_images : q->B;
+    for (int b = b0; b < b1; b++)
+      if (q->h_status[b] != 0) return PP_ERR_CAPACITY;
+  }
   return PP_OK;
 }
 

@@ -184,6 +184,7 @@ class DeviceDecoder:
         self.ann_cap = ann_cap
         self.device = device
         self._buffers = {}
+        self._pipeline = None
         _lib.lib()   # fail loudly right here if the CUDA library is missing
 
     def _device(self):
@@ -241,6 +242,58 @@ class DeviceDecoder:
             raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
         _lib.check(rc)
         return buf
+
+    def run_host_chunked(self, cif, caf, params, chunk, *, keep=('ann',)):
+        """Generator: enqueue the pipelined host decode, then yield ``(buf, b0, b1)`` as each
+        chunk's results land in the pinned host mirrors (later chunks still in flight)."""
+        cif_t = torch.as_tensor(cif)
+        caf_t = torch.as_tensor(caf)
+        assert cif_t.dtype == torch.float32 and caf_t.dtype == torch.float32
+        cif_t, caf_t = cif_t.contiguous(), caf_t.contiguous()
+        B, F, five, H, W = cif_t.shape
+        assert five == 5 and caf_t.shape == (B, len(self.skeleton), 9, H, W), (cif_t.shape, caf_t.shape)
+        buf = self.buffers(B, F, H, W, keep=keep, host=True)
+        if self._pipeline is None:
+            self._pipeline = HostPipeline()
+        chunk = max(1, min(int(chunk), B))
+        if (B + chunk - 1) // chunk > HostPipeline.MAX_CHUNKS:
+            chunk = (B + HostPipeline.MAX_CHUNKS - 1) // HostPipeline.MAX_CHUNKS
+        p = params.to_c()
+        lib = _lib.lib()
+        with torch.cuda.device(buf.device):
+            _lib.check(lib.pp_decode_batch_host_async(
+                self._pipeline.handle, _ptr(cif_t), _ptr(caf_t), _ptr(buf.d_cif), _ptr(buf.d_caf),
+                C.byref(self.c_skeleton), C.byref(buf.d_out), C.byref(buf.h_out), _ptr(buf.ws),
+                buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), chunk, _stream_ptr()))
+            for k in range(lib.pp_pipeline_chunks(self._pipeline.handle)):
+                rc = lib.pp_pipeline_wait(self._pipeline.handle, k)
+                if rc == _lib.PP_ERR_CAPACITY:
+                    lib.pp_pipeline_wait(self._pipeline.handle, -1)
+                    raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
+                _lib.check(rc)
+                yield buf, k * chunk, min((k + 1) * chunk, B)
+
+
+class HostPipeline:
+    """pp_pipeline handle: chunked H2D / kernels / D2H overlap for host inputs."""
+    MAX_CHUNKS = 64
+
+    def __init__(self):
+        self.handle = _lib.lib().pp_pipeline_create(self.MAX_CHUNKS)
+        if not self.handle:
+            raise _lib.PifPafError(_lib.PP_ERR_CUDA, 'pp_pipeline_create failed')
+
+    def close(self):
+        if self.handle:
+            _lib.lib().pp_pipeline_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # pylint: disable=broad-except
+            pass
+
 
 
 def describe_status(status):

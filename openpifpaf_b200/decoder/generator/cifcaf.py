@@ -40,6 +40,7 @@ class CifCaf(Generator):
     keypoint_threshold = 0.0
     deterministic_exp = True    # exp() of include/pifpaf_detmath.h (bit-reproducible)
     max_annotations = 256       # per-image capacity of the result buffers
+    host_chunk = 16             # images per pipeline chunk when the fields come from the host
 
     def __init__(self, field_config: FieldConfig, *,
                  keypoints,
@@ -121,17 +122,23 @@ class CifCaf(Generator):
             seed_mask=cfg.seed_mask,
         )
 
-    def _annotations_from(self, n_ann, data, scales, source, pre_data, pre_order):
-        """Host arrays of one batch -> List[List[Annotation]]."""
+    def _annotations_from(self, n_ann, data, scales, source, pre_data, pre_order, b0=0, b1=None):
+        """Host arrays of one batch (images b0..b1) -> List[List[Annotation]].
+
+        The rows are copied out of the (reused, pinned) result buffers once per image;
+        each Annotation owns views of those private copies."""
         out = []
-        for b, n in enumerate(n_ann.tolist()):
-            anns = []
-            for r in range(n):
-                src = int(source[b, r])
-                anns.append(Annotation.from_buffers(
-                    self.keypoints, self.out_skeleton, data[b, r], scales[b, r],
-                    pre_data=pre_data[b, src], order=pre_order[b, src], graph=self._neighbours))
-            out.append(anns)
+        b1 = len(n_ann) if b1 is None else b1
+        kps, skel, graph = self.keypoints, self.out_skeleton, self._neighbours
+        for b, n in zip(range(b0, b1), n_ann[b0:b1].tolist()):
+            if n == 0:
+                out.append([])
+                continue
+            src = source[b, :n]
+            d, sc = data[b, :n].copy(), scales[b, :n].copy()
+            pre, order = pre_data[b][src], pre_order[b][src]     # fancy index = copies
+            out.append([Annotation.wrap(kps, skel, d[r], sc[r], (pre[r], order[r], graph))
+                        for r in range(n)])
         return out
 
     # -------------------------------------------------------------- decode
@@ -159,11 +166,16 @@ class CifCaf(Generator):
             pre_data = buf.dev['pre_data'][:, :npre].cpu().numpy()
             pre_order = buf.dev['pre_order'][:, :npre].cpu().numpy()
         else:
-            buf = eng.run_host(cif, caf, params)
-            h = buf.host
-            n_ann = h['n_ann'].numpy()
-            data, scales, source = h['ann_data'].numpy(), h['ann_scales'].numpy(), h['ann_source'].numpy()
-            pre_data, pre_order = h['pre_data'].numpy(), h['pre_order'].numpy()
+            # pipelined: annotations of chunk k are built while chunk k+1.. are still
+            # being copied / decoded (engine.run_host_chunked)
+            result = []
+            for buf, b0, b1 in eng.run_host_chunked(cif, caf, params, self.host_chunk):
+                h = buf.host
+                result.extend(self._annotations_from(
+                    h['n_ann'].numpy(), h['ann_data'].numpy(), h['ann_scales'].numpy(),
+                    h['ann_source'].numpy(), h['pre_data'].numpy(), h['pre_order'].numpy(), b0, b1))
+            self.last_decoder_time = time.perf_counter() - start
+            return result
         result = self._annotations_from(n_ann, data, scales, source, pre_data, pre_order)
         self.last_decoder_time = time.perf_counter() - start
         return result

@@ -275,3 +275,30 @@ def test_capacity_overflow_is_reported(configured_decoder, coco_skeleton):
         assert e.value.code == _lib.PP_ERR_CAPACITY and 'ann_cap' in str(e.value)
     finally:
         decoder.CifCaf.max_annotations = saved
+
+
+def test_pipelined_host_decode_matches_device(configured_decoder, coco_skeleton):
+    """decode_batch on host arrays (chunked H2D/compute/D2H pipeline, ragged last chunk)
+    returns exactly what decode_batch on CUDA tensors returns."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    items = [fields((161, 161), 1 + i % 3, pose_seed=70 + i, jitter_seed=71 + i) for i in range(7)]
+    cif = np.stack([i[0] for i in items])
+    caf = np.stack([i[1] for i in items])
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    want = dec.decode_batch(torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda())
+    saved = decoder.CifCaf.host_chunk
+    try:
+        for chunk in (1, 3, 7, 100):
+            decoder.CifCaf.host_chunk = chunk
+            for host in ((cif, caf), (torch.from_numpy(cif).pin_memory(), torch.from_numpy(caf).pin_memory())):
+                got = dec.decode_batch(*host)
+                assert [len(a) for a in got] == [len(a) for a in want]
+                for ga, wa in zip(got, want):
+                    for x, y in zip(ga, wa):
+                        assert np.array_equal(x.data, y.data)
+                        assert np.array_equal(x.joint_scales, y.joint_scales)
+                        assert [(s, e) for s, e, _, _ in x.decoding_order] == \
+                            [(s, e) for s, e, _, _ in y.decoding_order]
+    finally:
+        decoder.CifCaf.host_chunk = saved
