@@ -276,7 +276,7 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   size_t need = need_occ + 2 * need_pd + 2 * need_ps + need_po + need_np + nms_ws_bytes(*s, *c);
   if (ws_bytes < need) return PP_ERR_WORKSPACE;
   char *q = (char *)d_ws;
-  AsmArgs a;
+  AsmArgs a = {};
   a.occ_cnt = (uint8_t *)q; q += need_occ;
   a.pre_data = d_out->pre_data ? d_out->pre_data : (float *)q; q += need_pd;
   a.pre_scales = d_out->pre_scales ? d_out->pre_scales : (float *)q; q += need_ps;
@@ -351,7 +351,7 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   if ((rc = caf_scored_launch(d_caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, *s, *c, *p,
                               o->status, st)))
     return rc;
-  AsmArgs a;
+  AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
   a.fwd = fwd; a.bwd = bwd; a.nfwd = nfwd; a.nbwd = nbwd;
   a.occ_cnt = w.occ_cnt;

@@ -21,6 +21,8 @@
 //     the best evaluated edge whose target is still empty" visits the same
 //     edges in the same order (validated by the tests).
 //     Ties follow Python's tuple order (-score, (x, y, s, v), start, end).
+#include <cuda_pipeline.h>
+
 #include "common.cuh"
 #include "stages.cuh"
 
@@ -29,6 +31,7 @@ namespace pp {
 constexpr int kAsmThreads = 256;
 constexpr int kAsmWarps = kAsmThreads / 32;
 constexpr int kMaxEdges = 2 * PP_MAX_L;
+constexpr int kStageBytes = 88 * 1024;   // dynamic smem for the staged candidate lists (2 CTAs / SM)
 
 struct Graph {
   int F;
@@ -86,45 +89,99 @@ struct Xysv {
   float x, y, s, v;
 };
 
-// _grow_connection (cifcaf.py:124-145), warp-collective; every lane returns the result.
-__device__ Xysv warp_grow_connection(float x, float y, float s, const float *__restrict__ rows,
-                                     int cap, int K, int method, int exp_mode) {
+constexpr int kScratch = 128;     // in-box candidate indices per warp and pass
+
+// _grow_connection (cifcaf.py:124-145), warp-collective; every lane returns the
+// result.  `base` points at the score row of one directed candidate list whose
+// six live rows (score, source x/y, target x/y/scale) are `stride` floats apart:
+// rows 0,1,2,3,4,5 of the packed shared-memory copy, or rows 0,1,2,5,6,8 of the
+// (9, caf_cap) CafScored block in global memory.
+//
+// Two passes keep the serial chain of the one active warp short: (1) a tight
+// loop tests the caf_center_s box and compacts the indices of the candidates
+// inside it into `scratch`; (2) each lane scores ONE of them (sqrt, divide,
+// exp), so the expensive chain runs once, not once per 32 candidates.
+// Not inlined: the forward and the reverse match share one copy of the code.
+__device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, const float *base,
+                                                  int stride, int packed, int K, int *scratch,
+                                                  int method, int exp_mode) {
   const int lane = lane_id();
+  const unsigned full = 0xffffffffu;
   const float box = __fmul_rn(2.0f, s);                           // sigma = 2.0 * xy_scale  :129
   const float lox = __fsub_rn(x, box), hix = __fadd_rn(x, box);
   const float loy = __fsub_rn(y, box), hiy = __fadd_rn(y, box);
   const float sigma = __fmul_rn(0.5f, s);                         // :138
   const float sig2 = __fmul_rn(sigma, sigma);
-  const float *cs = rows, *xs = rows + cap, *ys = rows + 2 * (size_t)cap;
+  const float *cs = base, *xs = base + stride, *ys = base + 2 * (size_t)stride;
   Cand t1 = {-INFINITY, -1}, t2 = {-INFINITY, -1};
   int cnt = 0;
-  for (int i = lane; i < K; i += 32) {
-    float cx = __ldg(xs + i), cy = __ldg(ys + i);
-    // caf_center_s: functional.pyx:346-353
-    if (cx < lox || cx > hix || cy < loy || cy > hiy) continue;
-    cnt++;
-    float dx = __fsub_rn(x, cx), dy = __fsub_rn(y, cy);
-    float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));     // :134
-    float arg = __fdiv_rn(__fmul_rn(-0.5f, __fmul_rn(d, d)), sig2);            // :139
-    float e = exp_mode ? pp_expf(arg) : expf(arg);
-    Cand c = {__fmul_rn(e, __ldg(cs + i)), i};
-    if (cand_better(c, t1, method)) { t2 = t1; t1 = c; }
-    else if (cand_better(c, t2, method)) { t2 = c; }
-  }
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    Cand o1 = {__shfl_xor_sync(0xffffffffu, t1.s, off), __shfl_xor_sync(0xffffffffu, t1.i, off)};
-    Cand o2 = {__shfl_xor_sync(0xffffffffu, t2.s, off), __shfl_xor_sync(0xffffffffu, t2.i, off)};
-    cnt += __shfl_xor_sync(0xffffffffu, cnt, off);
-    Cand n1, n2;
-    if (cand_better(t1, o1, method)) { n1 = t1; n2 = cand_better(t2, o1, method) ? t2 : o1; }
-    else { n1 = o1; n2 = cand_better(t1, o2, method) ? t1 : o2; }
-    t1 = n1; t2 = n2;
+  for (int seg = 0; seg < K;) {
+    // pass 1: caf_center_s (functional.pyx:346-353), order preserved
+    int n = 0;
+    for (; seg < K && n <= kScratch - 32; seg += 32) {
+      const int i = seg + lane;
+      bool in = false;
+      if (i < K) {
+        const float cx = xs[i], cy = ys[i];
+        in = !(cx < lox || cx > hix || cy < loy || cy > hiy);
+      }
+      const unsigned m = __ballot_sync(full, in);
+      if (in) scratch[n + __popc(m & ((1u << lane) - 1u))] = i;
+      n += __popc(m);
+    }
+    __syncwarp();
+    cnt += n;
+    // pass 2: score the candidates inside the box
+    for (int t = lane; t < n; t += 32) {
+      const int i = scratch[t];
+      const float dx = __fsub_rn(x, xs[i]), dy = __fsub_rn(y, ys[i]);
+      const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));   // :134
+      const float arg = __fdiv_rn(__fmul_rn(-0.5f, __fmul_rn(d, d)), sig2);          // :139
+      const float e = exp_mode ? pp_expf(arg) : expf(arg);
+      const Cand c = {__fmul_rn(e, cs[i]), i};
+      if (cand_better(c, t1, method)) { t2 = t1; t1 = c; }
+      else if (cand_better(c, t2, method)) { t2 = c; }
+    }
+    __syncwarp();
   }
   Xysv out = {0.f, 0.f, 0.f, 0.f};
   if (cnt == 0) return out;                                       // :130-131
-  const float *xt = rows + 5 * (size_t)cap, *yt = rows + 6 * (size_t)cap, *st = rows + 8 * (size_t)cap;
-  float x1 = __ldg(xt + t1.i), y1 = __ldg(yt + t1.i), s1 = __ldg(st + t1.i);
+  // warp-wide top-2.  Scores are products of exp() and a confidence above the
+  // threshold, i.e. non-negative and ordered like their bit patterns, so two
+  // integer warp reductions per rank do it; anything else (NaN from a zero
+  // scale, negative thresholds) takes the generic butterfly below.
+  const unsigned b1 = __float_as_uint(t1.s), b2 = __float_as_uint(t2.s);
+  const bool plain = (t1.i < 0 || b1 <= 0x7f800000u) && (t2.i < 0 || b2 <= 0x7f800000u);
+  if (__all_sync(full, plain)) {
+    const unsigned k1 = t1.i >= 0 ? b1 + 1u : 0u;
+    const unsigned m1 = __reduce_max_sync(full, k1);
+    // ties: blend keeps the larger index (argsort), max the smaller (argmax)
+    const int w1 = method == 1 ? __reduce_min_sync(full, k1 == m1 ? t1.i : 0x7fffffff)
+                               : __reduce_max_sync(full, k1 == m1 ? t1.i : -1);
+    const Cand o = (t1.i == w1) ? t2 : t1;
+    const unsigned k2 = o.i >= 0 ? __float_as_uint(o.s) + 1u : 0u;
+    const unsigned m2 = __reduce_max_sync(full, k2);
+    int w2 = -1;
+    if (m2 != 0u)
+      w2 = method == 1 ? __reduce_min_sync(full, k2 == m2 ? o.i : 0x7fffffff)
+                       : __reduce_max_sync(full, k2 == m2 ? o.i : -1);
+    t1.s = __uint_as_float(m1 - 1u); t1.i = w1;
+    t2.s = m2 ? __uint_as_float(m2 - 1u) : -INFINITY; t2.i = w2;
+  } else {
+#pragma unroll 1
+    for (int off = 16; off > 0; off >>= 1) {
+      Cand o1 = {__shfl_xor_sync(full, t1.s, off), __shfl_xor_sync(full, t1.i, off)};
+      Cand o2 = {__shfl_xor_sync(full, t2.s, off), __shfl_xor_sync(full, t2.i, off)};
+      Cand n1, n2;
+      if (cand_better(t1, o1, method)) { n1 = t1; n2 = cand_better(t2, o1, method) ? t2 : o1; }
+      else { n1 = o1; n2 = cand_better(t1, o2, method) ? t1 : o2; }
+      t1 = n1; t2 = n2;
+    }
+  }
+  const int r3 = packed ? 3 : 5, r4 = packed ? 4 : 6, r5 = packed ? 5 : 8;
+  const float *xt = base + (size_t)r3 * stride, *yt = base + (size_t)r4 * stride;
+  const float *st = base + (size_t)r5 * stride;
+  float x1 = xt[t1.i], y1 = yt[t1.i], s1 = st[t1.i];
   if (method == 1) {                                              // _target_with_maxscore :147-155
     out.x = x1; out.y = y1; out.s = s1; out.v = t1.s;
     return out;
@@ -132,7 +189,7 @@ __device__ Xysv warp_grow_connection(float x, float y, float s, const float *__r
   out.x = x1; out.y = y1; out.s = s1; out.v = __fmul_rn(t1.s, 0.5f);
   if (cnt == 1) return out;                                       // :164-170
   if (t2.s < 0.01f || t2.s < __fmul_rn(0.5f, t1.s)) return out;   // :178-179
-  float x2 = __ldg(xt + t2.i), y2 = __ldg(yt + t2.i), s2 = __ldg(st + t2.i);
+  float x2 = xt[t2.i], y2 = yt[t2.i], s2 = st[t2.i];
   float ddx = __fsub_rn(x1, x2), ddy = __fsub_rn(y1, y2);
   float d = __fsqrt_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)));   // :182
   if (d > __fdiv_rn(s1, 2.0f)) return out;                        // :183-184
@@ -146,30 +203,39 @@ __device__ Xysv warp_grow_connection(float x, float y, float s, const float *__r
 
 struct CafLists {
   const float *fwd, *bwd;   // (L,9,cap) of this image
-  const int *nfwd, *nbwd;   // (L)
   int cap;
+  const int *n;             // (2L) list lengths in shared memory: [2l] forward, [2l+1] backward
+  const float *stage;       // shared-memory copy of the six live rows of every list, or nullptr
+  const int *stage_off;     // (2L) float offset of each list inside `stage`
 };
+
+// grow_connection on the directed list (l, fw)
+__device__ __forceinline__ Xysv scan_list(const CafLists &cf, int l, bool fw, float x, float y, float s,
+                                          int *scratch, int method, int exp_mode) {
+  const int i = 2 * l + (fw ? 0 : 1);
+  const int K = cf.n[i];
+  if (cf.stage) return warp_grow_connection(x, y, s, cf.stage + cf.stage_off[i], K, 1, K, scratch,
+                                            method, exp_mode);
+  return warp_grow_connection(x, y, s, (fw ? cf.fwd : cf.bwd) + (size_t)l * 9 * cf.cap, cf.cap, 0, K,
+                              scratch, method, exp_mode);
+}
 
 // connection_value (cifcaf.py:194-217), warp-collective.
 __device__ Xysv warp_connection_value(const float (*data)[3], const float *js, const Graph &g,
                                       const CafLists &cf, int start, int k, bool reverse_match,
-                                      float keypoint_th, int method, int exp_mode) {
+                                      float keypoint_th, int method, int exp_mode, int *scratch) {
   Xysv zero = {0.f, 0.f, 0.f, 0.f};
   const int l = g.nb_link[start][k];
   const bool fw = g.nb_fwd[start][k] != 0;
-  const float *rf = (fw ? cf.fwd : cf.bwd) + (size_t)l * 9 * cf.cap;
-  const float *rb = (fw ? cf.bwd : cf.fwd) + (size_t)l * 9 * cf.cap;
-  const int nf = fw ? cf.nfwd[l] : cf.nbwd[l];
-  const int nb = fw ? cf.nbwd[l] : cf.nfwd[l];
   const float sx = data[start][0], sy = data[start][1], sv = data[start][2];
   const float ss = js[start] > 0.0f ? js[start] : 0.0f;           // max(0.0, .)
-  Xysv nw = warp_grow_connection(sx, sy, ss, rf, cf.cap, nf, method, exp_mode);
+  Xysv nw = scan_list(cf, l, fw, sx, sy, ss, scratch, method, exp_mode);
   float kp = __fsqrt_rn(__fmul_rn(nw.v, sv));                     // :201
   if (kp < keypoint_th) return zero;
   if (nw.v == 0.0f) return zero;
   float st = nw.s > 0.0f ? nw.s : 0.0f;
   if (reverse_match) {                                            // :208-215
-    Xysv rv = warp_grow_connection(nw.x, nw.y, st, rb, cf.cap, nb, method, exp_mode);
+    Xysv rv = scan_list(cf, l, !fw, nw.x, nw.y, st, scratch, method, exp_mode);
     if (rv.s == 0.0f) return zero;
     float dist = __fadd_rn(fabsf(__fsub_rn(sx, rv.x)), fabsf(__fsub_rn(sy, rv.y)));
     if (dist > ss) return zero;
@@ -178,34 +244,32 @@ __device__ Xysv warp_connection_value(const float (*data)[3], const float *js, c
   return nw;
 }
 
-struct Pending {      // an evaluated frontier entry (-score, (x, y, s, v), start, end)
-  float key, x, y, s, v;
-  int start, end;
-};
-
-// Heap order of the reference's frontier.  Non-greedy: evaluated entries
-// (-score, (x, y, s, v), start, end).  Greedy (cifcaf.py:280-281): an entry is
-// applied the moment it is evaluated, so only the unevaluated keys
-// (-sqrt(v_start) [* confidence_scale], None, start, end) are ever compared;
-// `key` then holds that bound.
-__device__ __forceinline__ bool pending_less(const Pending &a, const Pending &b, int greedy) {
-  if (a.key != b.key) return a.key < b.key;
-  if (greedy) {
-    if (a.start != b.start) return a.start < b.start;
-    return a.end < b.end;
-  }
-  if (a.x != b.x) return a.x < b.x;
-  if (a.y != b.y) return a.y < b.y;
-  if (a.s != b.s) return a.s < b.s;
-  if (a.v != b.v) return a.v < b.v;
-  if (a.start != b.start) return a.start < b.start;
-  return a.end < b.end;
-}
+// Phase timing for tuning (build with PP_EXTRA_NVCC=-DPP_ASM_TIMING): thread 0
+// accumulates clock64 deltas per phase into g_asm_cycles; read them with
+// pp_debug_asm_cycles.  Compiled out otherwise.
+#ifdef PP_ASM_TIMING
+__device__ unsigned long long g_asm_cycles[8];
+#define PP_TICK(slot)                                                              \
+  do {                                                                             \
+    if (threadIdx.x == 0) {                                                        \
+      long long now_ = clock64();                                                  \
+      atomicAdd(&g_asm_cycles[slot], (unsigned long long)(now_ - sh.tick));        \
+      sh.tick = now_;                                                              \
+    }                                                                              \
+  } while (0)
+#else
+#define PP_TICK(slot) do { } while (0)
+#endif
 
 struct AsmShared {
+#ifdef PP_ASM_TIMING
+  long long tick;
+#endif
   float data[PP_MAX_F][3];
   float js[PP_MAX_F];
-  Pending pend[kMaxEdges];
+  // evaluated frontier entries (-score, (x, y, s, v), start, end), one array per member
+  float p_key[kMaxEdges], p_x[kMaxEdges], p_y[kMaxEdges], p_s[kMaxEdges], p_v[kMaxEdges];
+  int p_start[kMaxEdges], p_end[kMaxEdges];
   int n_pend;
   uint32_t queued[PP_MAX_F];
   int new_start[kMaxEdges], new_k[kMaxEdges];
@@ -218,7 +282,69 @@ struct AsmShared {
   int found;
   int warp_min[kAsmWarps];
   struct Flood { float key, sx, sy, sv, s; int end; } ff[4 * PP_MAX_L];
+  int list_n[2 * PP_MAX_L];      // candidate-list lengths, [2l] forward / [2l+1] backward
+  int list_off[2 * PP_MAX_L];    // float offsets into the staged copy
+  int stage_total;               // entries over all lists
+  int scratch[kAsmWarps][kScratch];
 };
+
+// Heap order of the reference's frontier.  Non-greedy: evaluated entries
+// (-score, (x, y, s, v), start, end).  Greedy (cifcaf.py:280-281): an entry is
+// applied the moment it is evaluated, so only the unevaluated keys
+// (-sqrt(v_start) [* confidence_scale], None, start, end) are ever compared;
+// `key` then holds that bound.
+__device__ __forceinline__ bool pending_less(const AsmShared &sh, int a, int b, int greedy) {
+  if (sh.p_key[a] != sh.p_key[b]) return sh.p_key[a] < sh.p_key[b];
+  if (!greedy) {
+    if (sh.p_x[a] != sh.p_x[b]) return sh.p_x[a] < sh.p_x[b];
+    if (sh.p_y[a] != sh.p_y[b]) return sh.p_y[a] < sh.p_y[b];
+    if (sh.p_s[a] != sh.p_s[b]) return sh.p_s[a] < sh.p_s[b];
+    if (sh.p_v[a] != sh.p_v[b]) return sh.p_v[a] < sh.p_v[b];
+  }
+  if (sh.p_start[a] != sh.p_start[b]) return sh.p_start[a] < sh.p_start[b];
+  return sh.p_end[a] < sh.p_end[b];
+}
+
+// ascending float order as ascending unsigned order (NaN excluded by the caller)
+__device__ __forceinline__ uint32_t float_orderable(float v) {
+  uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// Load the list lengths of one image into shared memory and, when everything
+// fits into `stage_floats` of dynamic shared memory, copy the six live rows of
+// all 2L candidate lists there with cp.async (all copies in flight at once).
+// CTA-collective.  Returns the CafLists the growth code reads through.
+__device__ CafLists load_lists(AsmShared &sh, const float *fwd, const float *bwd, const int *nfwd,
+                               const int *nbwd, int L, int cap, float *stage, int stage_floats) {
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 2 * L; i += blockDim.x)
+    sh.list_n[i] = (i & 1) ? nbwd[i >> 1] : nfwd[i >> 1];
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int i = 0; i < 2 * L; i++) { sh.list_off[i] = 6 * run; run += sh.list_n[i]; }
+    sh.stage_total = run;
+  }
+  __syncthreads();
+  CafLists cf = {fwd, bwd, cap, sh.list_n, nullptr, sh.list_off};
+  if (stage == nullptr || 6 * sh.stage_total > stage_floats) return cf;
+  const int warp = warp_id(), lane = lane_id(), nw = blockDim.x >> 5;
+  // one warp per (list, row); rows 0,1,2,5,6,8 of the (9, cap) block
+  for (int pr = warp; pr < 12 * L; pr += nw) {
+    const int i = pr / 6, r = pr - 6 * i;
+    const int row = r < 3 ? r : (r == 5 ? 8 : r + 2);
+    const int K = sh.list_n[i];
+    const float *src = ((i & 1) ? bwd : fwd) + ((size_t)(i >> 1) * 9 + row) * cap;
+    float *dst = stage + sh.list_off[i] + r * K;
+    for (int k = lane; k < K; k += 32) __pipeline_memcpy_async(dst + k, src + k, sizeof(float));
+  }
+  __pipeline_commit();
+  __pipeline_wait_prior(0);
+  __syncthreads();
+  cf.stage = stage;
+  return cf;
+}
 
 // add_to_frontier (cifcaf.py:251-263), run by one thread.
 __device__ void queue_edges(AsmShared &sh, const Graph &g, int start) {
@@ -233,10 +359,33 @@ __device__ void queue_edges(AsmShared &sh, const Graph &g, int start) {
   }
 }
 
+// the same for one start joint, by a whole warp (lane = neighbour slot); sets n_new
+__device__ __forceinline__ void queue_edges_warp(AsmShared &sh, const Graph &g, int start) {
+  const int lane = lane_id();
+  bool ok = false;
+  int end = 0;
+  if (lane < g.deg[start]) {
+    end = g.nb_end[start][lane];
+    ok = !(sh.data[end][2] > 0.0f) && !(sh.queued[start] & (1u << end));
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, ok);
+  const unsigned bits = __reduce_or_sync(0xffffffffu, ok ? (1u << end) : 0u);
+  if (ok) {
+    const int pos = __popc(m & ((1u << lane) - 1u));
+    sh.new_start[pos] = start;
+    sh.new_k[pos] = lane;
+  }
+  if (lane == 0) {
+    sh.queued[start] |= bits;
+    sh.n_new = __popc(m);
+  }
+}
+
 // _grow (cifcaf.py:247-307) in its eager form; CTA-collective.
 __device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const CafLists &cf,
                      bool reverse_match, const pp_params &p) {
   const int warp = warp_id(), lane = lane_id();
+  const unsigned full = 0xffffffffu;
   if (threadIdx.x == 0) {
     sh.n_pend = 0;
     sh.n_new = 0;
@@ -247,53 +396,82 @@ __device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const 
     }
   }
   __syncthreads();
+  PP_TICK(7);
   for (;;) {
     // evaluate the newly queued edges, one warp each
     const int n_new = sh.n_new, base = sh.n_pend;
     for (int e = warp; e < n_new; e += kAsmWarps) {
       int start = sh.new_start[e], k = sh.new_k[e];
       Xysv r = warp_connection_value(sh.data, sh.js, g, cf, start, k, reverse_match,
-                                     p.keypoint_threshold, p.connection_method, p.exp_mode);
+                                     p.keypoint_threshold, p.connection_method, p.exp_mode,
+                                     sh.scratch[warp]);
       if (lane == 0) {
-        Pending &q = sh.pend[base + e];
+        const int q = base + e;
         float score = r.v;
         if (p.greedy) score = __fsqrt_rn(sh.data[start][2]);                       // :258 (the bound)
         if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);   // :259-260, :282-284
-        q.key = -score; q.x = r.x; q.y = r.y; q.s = r.s; q.v = r.v;
-        q.start = start; q.end = (r.v == 0.0f) ? -1 : g.nb_end[start][k];          // :277-278
+        sh.p_key[q] = -score; sh.p_x[q] = r.x; sh.p_y[q] = r.y; sh.p_s[q] = r.s; sh.p_v[q] = r.v;
+        sh.p_start[q] = start;
+        sh.p_end[q] = (r.v == 0.0f) ? -1 : g.nb_end[start][k];                     // :277-278
       }
     }
     __syncthreads();
+    PP_TICK(3);
     if (warp == 0) {
       // best evaluated entry whose target is still empty (frontier_get + :297-298)
       const int n_pend = base + n_new;
       int best = -1;
+      uint32_t bu = 0xffffffffu;
+      bool odd = false;                      // NaN key: leave the integer fast path
       for (int i = lane; i < n_pend; i += 32) {
-        const Pending &q = sh.pend[i];
-        if (q.end < 0 || sh.data[q.end][2] > 0.0f) continue;
-        if (best < 0 || pending_less(q, sh.pend[best], p.greedy)) best = i;
+        const int end = sh.p_end[i];
+        if (end < 0 || sh.data[end][2] > 0.0f) continue;
+        const float key = sh.p_key[i];
+        if (key != key) odd = true;
+        const uint32_t u = float_orderable(key);
+        if (best < 0 || u < bu || (u == bu && pending_less(sh, i, best, p.greedy))) { best = i; bu = u; }
       }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        int o = __shfl_xor_sync(0xffffffffu, best, off);
-        if (o >= 0 && (best < 0 || pending_less(sh.pend[o], sh.pend[best], p.greedy))) best = o;
+      const unsigned have = __ballot_sync(full, best >= 0);
+      if (have == 0u) {
+        best = -1;
+      } else if (!__any_sync(full, odd)) {
+        // primary key by one integer reduction; full tuple order only among exact ties
+        const uint32_t m = __reduce_min_sync(full, best >= 0 ? bu : 0xffffffffu);
+        unsigned tie = __ballot_sync(full, best >= 0 && bu == m);
+        int w = __shfl_sync(full, best, __ffs(tie) - 1);
+        for (tie &= tie - 1u; tie; tie &= tie - 1u) {
+          const int o = __shfl_sync(full, best, __ffs(tie) - 1);
+          if (pending_less(sh, o, w, p.greedy)) w = o;
+        }
+        best = w;
+      } else {
+#pragma unroll 1
+        for (int off = 16; off > 0; off >>= 1) {
+          int o = __shfl_xor_sync(full, best, off);
+          if (o >= 0 && (best < 0 || pending_less(sh, o, best, p.greedy))) best = o;
+        }
       }
       if (lane == 0) {
         sh.n_pend = n_pend;
         sh.n_new = 0;
         sh.best = best;
-        if (best >= 0) {
-          const Pending q = sh.pend[best];
-          sh.data[q.end][0] = q.x; sh.data[q.end][1] = q.y; sh.data[q.end][2] = q.v;   // :300-302
-          sh.js[q.end] = q.s;
-          sh.dec[sh.n_dec][0] = q.start; sh.dec[sh.n_dec][1] = q.end;                  // :303-304
+      }
+      if (best >= 0) {
+        const int end = sh.p_end[best];
+        if (lane == 0) {
+          sh.data[end][0] = sh.p_x[best]; sh.data[end][1] = sh.p_y[best];          // :300-302
+          sh.data[end][2] = sh.p_v[best];
+          sh.js[end] = sh.p_s[best];
+          sh.dec[sh.n_dec][0] = sh.p_start[best]; sh.dec[sh.n_dec][1] = end;       // :303-304
           sh.n_dec++;
-          sh.pend[best].end = -1;
-          queue_edges(sh, g, q.end);                                                   // :305
+          sh.p_end[best] = -1;
         }
+        __syncwarp();
+        queue_edges_warp(sh, g, end);                                              // :305
       }
     }
     __syncthreads();
+    PP_TICK(4);
     if (sh.best < 0) break;
   }
 }
@@ -339,8 +517,13 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
   const float *seeds = a.seeds + (size_t)b * a.seed_cap * 5;
   const int n_seeds = min(a.n_seeds[b], a.seed_cap);
   uint8_t *occ = a.occ_cnt + (size_t)b * a.seed_cap;
-  CafLists cf = {a.fwd + (size_t)b * a.L * 9 * a.caf_cap, a.bwd + (size_t)b * a.L * 9 * a.caf_cap,
-                 a.nfwd + (size_t)b * a.L, a.nbwd + (size_t)b * a.L, a.caf_cap};
+  extern __shared__ __align__(16) float stage_buf[];
+#ifdef PP_ASM_TIMING
+  if (threadIdx.x == 0) sh.tick = clock64();
+#endif
+  const CafLists cf = load_lists(sh, a.fwd + (size_t)b * a.L * 9 * a.caf_cap,
+                                 a.bwd + (size_t)b * a.L * 9 * a.caf_cap, a.nfwd + (size_t)b * a.L,
+                                 a.nbwd + (size_t)b * a.L, a.L, a.caf_cap, stage_buf, a.stage_floats);
   // Occupancy(cifhr.accumulated.shape, 2, min_scale=4): cifcaf.py:84, occupancy.py:21-25
   const long long oh = (long long)((double)a.hh / 2.0), ow = (long long)((double)a.hw / 2.0);
   float *pre_data = a.pre_data + (size_t)b * a.ann_cap * F * 3;
@@ -351,6 +534,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
   __syncthreads();
 
   int n_ann = 0, cursor = 0;
+  PP_TICK(0);
   for (;;) {
     // ---- next seed whose cell is free (cifcaf.py:100-102) -------------------
     int found = -1;
@@ -365,6 +549,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
       __syncthreads();
       if (found >= 0) break;
     }
+    PP_TICK(1);
     if (found < 0) break;
     cursor = found + 1;
     if (n_ann >= a.ann_cap) {
@@ -383,6 +568,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
       sh.n_dec = 0;
     }
     __syncthreads();
+    PP_TICK(2);
     grow(sh, g, cscale, cf, true, p);                             // :106
     // ---- store + mark_occupied (:87-93, :107-108) -------------------------
     for (int i = threadIdx.x; i < F * 3; i += blockDim.x)
@@ -398,6 +584,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
     }
     n_ann++;
     __syncthreads();
+    PP_TICK(5);
     for (int i = cursor + threadIdx.x; i < n_seeds; i += blockDim.x) {
       const float *sd = seeds + (size_t)i * 5;
       int f = (int)__ldg(sd + 1);
@@ -408,6 +595,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
         occ[i] = (uint8_t)(occ[i] + 1);                           // uint8 += 1 wraps (utils.py:66)
     }
     __syncthreads();
+    PP_TICK(6);
   }
   if (threadIdx.x == 0) a.n_pre[b] = n_ann;
 }
@@ -469,8 +657,10 @@ complete_kernel(AsmArgs a, const float *__restrict__ fwd2, const float *__restri
   const int b = blockIdx.y, an = blockIdx.x;
   const int F = g.F;
   if (an >= min(a.n_pre[b], a.ann_cap)) return;
-  CafLists cf = {fwd2 + (size_t)b * a.L * 9 * a.caf_cap, bwd2 + (size_t)b * a.L * 9 * a.caf_cap,
-                 nfwd2 + (size_t)b * a.L, nbwd2 + (size_t)b * a.L, a.caf_cap};
+  // the score_th = 1e-4 lists hold nearly every cell: read them in place
+  const CafLists cf = load_lists(sh, fwd2 + (size_t)b * a.L * 9 * a.caf_cap,
+                                 bwd2 + (size_t)b * a.L * 9 * a.caf_cap, nfwd2 + (size_t)b * a.L,
+                                 nbwd2 + (size_t)b * a.L, a.L, a.caf_cap, nullptr, 0);
   float *pre_data = a.pre_data + ((size_t)b * a.ann_cap + an) * F * 3;
   float *pre_scales = a.pre_scales + ((size_t)b * a.ann_cap + an) * F;
   int *pre_order = a.pre_order + ((size_t)b * a.ann_cap + an) * F * 2;
@@ -540,10 +730,25 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   memset(&cs, 0, sizeof cs);
   cs.has = sk.has_confidence_scales;
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  AsmArgs a2 = args;
+  a2.stage_floats = kStageBytes / (int)sizeof(float);
+  PP_CUDA_CHECK(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kStageBytes));
   prof_mark(p.profile, kStAssemble, st);
-  assemble_kernel<<<B, kAsmThreads, 0, st>>>(args, g, cs, p);
+  assemble_kernel<<<B, kAsmThreads, kStageBytes, st>>>(a2, g, cs, p);
   PP_LAUNCH_CHECK("assemble_kernel");
   return PP_OK;
 }
 
 }  // namespace pp
+
+#ifdef PP_ASM_TIMING
+extern "C" int pp_debug_asm_cycles(unsigned long long *out8, int reset) {
+  if (cudaMemcpyFromSymbol(out8, pp::g_asm_cycles, 8 * sizeof(unsigned long long)) != cudaSuccess) return -3;
+  if (reset) {
+    unsigned long long z[8] = {0};
+    cudaMemcpyToSymbol(pp::g_asm_cycles, z, sizeof z);
+  }
+  return 0;
+}
+#endif

@@ -27,6 +27,7 @@ struct AsmArgs {
   int *status;
   int seed_cap, caf_cap, ann_cap, L;
   int hh, hw;
+  int stage_floats;   // set by assemble_launch
 };
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st);

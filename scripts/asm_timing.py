@@ -1,0 +1,25 @@
+"""Per-phase cycles of assemble_kernel (library built with PP_EXTRA_NVCC=-DPP_ASM_TIMING)."""
+import ctypes as C, sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import bench
+from openpifpaf_b200 import _lib, decoder
+from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+bench.configure_profile(decoder)
+cif, caf, skel = bench.make_batch('coco17_641_5p', 64)
+dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=skel)
+eng, params = dec.engine(), dec.params()
+d_cif, d_caf = torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda()
+for _ in range(3): eng.run_device(d_cif, d_caf, params)
+torch.cuda.synchronize()
+out = (C.c_ulonglong * 8)()
+_lib.lib().pp_debug_asm_cycles(out, 1)
+N = 10
+for _ in range(N): eng.run_device(d_cif, d_caf, params)
+torch.cuda.synchronize()
+_lib.lib().pp_debug_asm_cycles(out, 1)
+names = ['setup', 'seed_search', 'init_ann', 'grow_eval', 'grow_select', 'store_boxes', 'occ_update', 'grow_init']
+tot = sum(out)
+for n, v in zip(names, out):
+    print('%-12s %8.1f us/image  %5.1f%%' % (n, v / N / 64 / 1965.0, 100.0 * v / tot))
+print('total %.1f us/image' % (tot / N / 64 / 1965.0))
