@@ -31,7 +31,8 @@ namespace pp {
 constexpr int kAsmThreads = 256;
 constexpr int kAsmWarps = kAsmThreads / 32;
 constexpr int kMaxEdges = 2 * PP_MAX_L;
-constexpr int kStageBytes = 88 * 1024;   // dynamic smem for the staged candidate lists (2 CTAs / SM)
+constexpr int kStageBytes = 80 * 1024;        // staged candidate lists, 2 CTAs / SM (batches > #SMs)
+constexpr int kStageBytesSolo = 192 * 1024;   // ... 1 CTA / SM
 
 struct Graph {
   int F;
@@ -89,7 +90,7 @@ struct Xysv {
   float x, y, s, v;
 };
 
-constexpr int kScratch = 128;     // in-box candidate indices per warp and pass
+constexpr int kScratch = 256;     // in-box candidate indices per warp and pass
 
 // _grow_connection (cifcaf.py:124-145), warp-collective; every lane returns the
 // result.  `base` points at the score row of one directed candidate list whose
@@ -116,18 +117,24 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
   Cand t1 = {-INFINITY, -1}, t2 = {-INFINITY, -1};
   int cnt = 0;
   for (int seg = 0; seg < K;) {
-    // pass 1: caf_center_s (functional.pyx:346-353), order preserved
+    // pass 1: caf_center_s (functional.pyx:346-353), order preserved.  Four
+    // independent 32-candidate groups per trip keep four loads in flight when
+    // the list is read from global memory.
     int n = 0;
-    for (; seg < K && n <= kScratch - 32; seg += 32) {
-      const int i = seg + lane;
-      bool in = false;
-      if (i < K) {
-        const float cx = xs[i], cy = ys[i];
-        in = !(cx < lox || cx > hix || cy < loy || cy > hiy);
+    for (; seg < K && n <= kScratch - 128; seg += 128) {
+      bool in[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int i = seg + 32 * j + lane;
+        const float cx = i < K ? xs[i] : 0.f, cy = i < K ? ys[i] : 0.f;
+        in[j] = i < K && !(cx < lox || cx > hix || cy < loy || cy > hiy);
       }
-      const unsigned m = __ballot_sync(full, in);
-      if (in) scratch[n + __popc(m & ((1u << lane) - 1u))] = i;
-      n += __popc(m);
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const unsigned m = __ballot_sync(full, in[j]);
+        if (in[j]) scratch[n + __popc(m & ((1u << lane) - 1u))] = seg + 32 * j + lane;
+        n += __popc(m);
+      }
     }
     __syncwarp();
     cnt += n;
@@ -731,11 +738,13 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   cs.has = sk.has_confidence_scales;
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
   AsmArgs a2 = args;
-  a2.stage_floats = kStageBytes / (int)sizeof(float);
+  // one image per SM is the common case: give the lists (almost) the whole shared memory
+  const int stage_bytes = B <= num_sms() ? kStageBytesSolo : kStageBytes;
+  a2.stage_floats = stage_bytes / (int)sizeof(float);
   PP_CUDA_CHECK(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kStageBytes));
+                                     kStageBytesSolo));
   prof_mark(p.profile, kStAssemble, st);
-  assemble_kernel<<<B, kAsmThreads, kStageBytes, st>>>(a2, g, cs, p);
+  assemble_kernel<<<B, kAsmThreads, stage_bytes, st>>>(a2, g, cs, p);
   PP_LAUNCH_CHECK("assemble_kernel");
   return PP_OK;
 }
