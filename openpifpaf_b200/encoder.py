@@ -272,3 +272,40 @@ def synthetic_fields(image_hw=(641, 641), n_poses=5, *, pose_seed=0, jitter_seed
     cif, caf = enc(poses)
     cif, caf = jitter(cif, caf, np.random.RandomState(jitter_seed))
     return cif, caf, poses
+
+
+def random_init_like_fields(field_hw, seed=0, n_links=19, n_keypoints=17, scale_sigma=3.0,
+                            n_nonfinite=0):
+    """Fields with the statistics of a randomly initialised head:
+    sigmoid confidences with ~25 % of the cells above 0.1, regressions a few cells off
+    their cell, and ``exp()`` scales with a heavy tail (sigmas from 1e-4 to 1e4 cells, so
+    some sources cover the whole hr map and many fall outside it).  ``n_nonfinite`` cells
+    additionally get NaN / inf coordinates or scales (SURVEY appendix B edge cases).
+
+    Workload tooling for parity tests and stress runs; not on the decode path.
+    """
+    H, W = field_hw
+    rng = np.random.RandomState(seed)
+    yy, xx = np.mgrid[0:H, 0:W].astype(np.float32)
+
+    def block(n, pairs):
+        f = np.zeros((n, 1 + 4 * pairs, H, W), np.float32)
+        f[:, 0] = 1.0 / (1.0 + np.exp(-rng.normal(-1.0, 1.5, (n, H, W))))
+        for p in range(pairs):
+            a = 1 + 4 * p
+            f[:, a] = xx + rng.normal(0, 3, (n, H, W))
+            f[:, a + 1] = yy + rng.normal(0, 3, (n, H, W))
+            f[:, a + 2] = rng.normal(0, 1, (n, H, W))
+            f[:, a + 3] = np.exp(rng.normal(0, scale_sigma, (n, H, W)))
+        return f
+
+    cif = block(n_keypoints, 1)
+    caf = block(n_links, 2)
+    specials = (np.nan, np.inf, -np.inf, 1e30, -1e30)
+    for k in range(n_nonfinite):
+        for f, chans in ((cif, (1, 2, 4)), (caf, (1, 2, 4, 5, 6, 8))):
+            i = rng.randint(f.shape[0])
+            y, x = rng.randint(H), rng.randint(W)
+            f[i, chans[rng.randint(len(chans))], y, x] = specials[k % len(specials)]
+            f[i, 0, y, x] = max(f[i, 0, y, x], 0.5)        # make sure the cell is active
+    return cif.astype(np.float32), caf.astype(np.float32)

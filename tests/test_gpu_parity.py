@@ -302,3 +302,32 @@ def test_pipelined_host_decode_matches_device(configured_decoder, coco_skeleton)
                             [(s, e) for s, e, _, _ in y.decoding_order]
     finally:
         decoder.CifCaf.host_chunk = saved
+
+
+@pytest.mark.parametrize('seed', [0, 1, 2])
+def test_random_init_like_fields_bit_exact(oracle, coco_skeleton, configured_decoder, seed):
+    """Config-2 statistics: whole-map sources, out-of-bounds sources, saturated hr,
+    hundreds of seeds and ~100 annotations per small image."""
+    from openpifpaf_b200.encoder import random_init_like_fields
+    cif, caf = random_init_like_fields((13, 17), seed)
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton)
+    o = check_image(oracle, out, 0, cif, caf, coco_skeleton)
+    assert len(o.data) >= 20
+
+
+def test_nonfinite_sources_stage_outputs_gpu(oracle, coco_skeleton, configured_decoder):
+    from openpifpaf_b200.encoder import random_init_like_fields
+    for seed in range(4):
+        cif, caf = random_init_like_fields((11, 14), seed, n_nonfinite=5)
+        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, nms=False)
+        o_hr = oracle.cifhr(cif)
+        assert np.array_equal(out['hr'][0], o_hr, equal_nan=True)
+        o_seeds = oracle.seeds(cif, o_hr)
+        n = out['n_seeds'][0]
+        assert n == len(o_seeds)
+        assert np.array_equal(out['seeds'][0, :n], o_seeds, equal_nan=True)
+        f, b = oracle.caf_scored(caf, o_hr, coco_skeleton)
+        for l in range(len(coco_skeleton)):
+            nf, nb = out['n_caf_fwd'][0, l], out['n_caf_bwd'][0, l]
+            assert np.array_equal(out['caf_fwd'][0, l, :, :nf], f[l], equal_nan=True)
+            assert np.array_equal(out['caf_bwd'][0, l, :, :nb], b[l], equal_nan=True)

@@ -131,3 +131,60 @@ def test_primitive_occupancy(ref, oracle):
         oracle.lib().orc_occupancy_set(vp(m2), C.c_long(60), C.c_long(80), C.c_float(40.0),
                                        C.c_float(40.0), C.c_float(4.0))
     assert m2.max() == 0
+
+
+@pytest.mark.parametrize('seed', [0, 1, 2])
+def test_random_init_like_fields(ref, oracle, coco_skeleton, seed):
+    """Config-2 statistics (heavy-tailed exp() scales: whole-map and out-of-bounds sources,
+    hundreds of overlapping seeds): the restatement still tracks the reference."""
+    import warnings
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.encoder import random_init_like_fields
+    dec = ref.decoder
+    configure(dec)
+    cif, caf = random_init_like_fields((13, 17), seed)
+    cfg = dec.FieldConfig()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        hr = dec.CifHr(cfg).fill([cif.copy(), caf.copy()]).accumulated
+        seeds = dec.CifSeeds(hr, cfg).fill([cif, caf]).get()
+        d = dec.CifCaf(cfg, keypoints=COCO_KEYPOINTS, skeleton=[list(l) for l in coco_skeleton])
+        try:
+            anns = d([cif.copy(), caf.copy()])
+        except TypeError:
+            pytest.skip('the reference raises on an exact frontier tie for this input')
+    o = oracle.decode(cif, caf, coco_skeleton, oracle.Config(exp_mode=1))
+    assert np.array_equal(hr, o.hr)
+    assert np.array_equal(np.array([list(s) for s in seeds], np.float32).reshape(-1, 5), o.seeds)
+    assert len(anns) == len(o.data) >= 20
+    for a, data, js in zip(anns, o.data, o.joint_scales):
+        assert np.array_equal(a.data[:, 2] != 0, data[:, 2] != 0)
+        assert np.abs(a.data[:, :2] - data[:, :2]).max() <= TOL_XY
+        assert np.abs(a.data[:, 2] - data[:, 2]).max() <= TOL_SCORE
+
+
+def test_nonfinite_sources_stage_outputs(ref, oracle, coco_skeleton):
+    """NaN / inf / 1e30 coordinates and scales (appendix B): CifHr, seeds and CafScored of
+    the restatement equal the reference's.  (Assembly on such inputs is not pinned: the
+    reference itself raises ValueError / OverflowError on part of them.)"""
+    import warnings
+    from openpifpaf_b200.encoder import random_init_like_fields
+    dec = ref.decoder
+    configure(dec)
+    for seed in range(4):
+        cif, caf = random_init_like_fields((11, 14), seed, n_nonfinite=5)
+        cfg = dec.FieldConfig()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            hr = dec.CifHr(cfg).fill([cif.copy(), caf.copy()]).accumulated
+            seeds = dec.CifSeeds(hr, cfg).fill([cif, caf]).get()
+            sc = dec.CafScored(hr, cfg, [list(l) for l in coco_skeleton]).fill([cif, caf])
+        o_hr = oracle.cifhr(cif)
+        assert np.array_equal(hr, o_hr, equal_nan=True)
+        o_seeds = oracle.seeds(cif, o_hr)
+        assert np.array_equal(np.array([list(s) for s in seeds], np.float32).reshape(-1, 5), o_seeds,
+                              equal_nan=True)
+        f, b = oracle.caf_scored(caf, o_hr, coco_skeleton)
+        for l in range(len(coco_skeleton)):
+            assert np.array_equal(sc.forward[l], f[l], equal_nan=True)
+            assert np.array_equal(sc.backward[l], b[l], equal_nan=True)
