@@ -172,8 +172,8 @@ const char *pp_stage_name(int stage) {
   return (stage >= 0 && stage < PP_N_STAGES) ? names[stage] : "?";
 }
 
-/* 7 kernels + the status memset + the seed-counter memset */
-int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 2; }
+/* 7 kernels + the status, CifHr-cursor and seed-counter memsets */
+int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 3; }
 const char *pp_version(void) { return "pifpaf_b200 0.1.0 (sm_100a)"; }
 
 void pp_default_params(pp_params *p) {

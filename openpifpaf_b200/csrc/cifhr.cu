@@ -14,21 +14,26 @@
 //                           the cells with conf > v_threshold into a source
 //                           list {cx, cy, sigma^2, v} + integer box, plus a
 //                           per-strip source count (difference array in smem).
-//   K2 cifhr_splat_kernel   one CTA per (image, field, group of strips).  A
-//                           strip = R full hr rows = ONE contiguous run of
-//                           floats in HBM.
-//                             * empty strips (the vast majority): one TMA bulk
-//                               store (cp.async.bulk shared->global) from a
-//                               zeroed shared-memory buffer;
-//                             * other strips: the strip is assembled in a
-//                               shared-memory tile.  Warps own 32-pixel
-//                               patches (R rows x 32/R columns, one pixel per
-//                               lane); per 64-source chunk a 64-bit
-//                               mask per patch says which sources touch it, so
-//                               a warp only ever evaluates sources that
-//                               overlap its patch, in list order, accumulating
-//                               in registers.  The finished tile leaves with
-//                               one TMA bulk store (double-buffered).
+//   K2 cifhr_splat_kernel   persistent, warp-specialised CTAs (one producer
+//                           warp + eight consumer warps).  A strip = R full hr
+//                           rows = ONE contiguous run of floats in HBM.
+//                             * the producer warp walks strip groups from a
+//                               global cursor and writes every EMPTY strip (the
+//                               vast majority) with TMA bulk stores
+//                               (cp.async.bulk shared->global) from a zeroed
+//                               shared-memory buffer; it never waits on the
+//                               consumers, so the HBM write stream never stalls
+//                               behind splat arithmetic;
+//                             * the consumer warps take the strips that have
+//                               sources from a compact list K1 built.  The
+//                               strip is assembled in a shared-memory tile:
+//                               warps own 32-pixel patches (R rows x 32/R
+//                               columns, one pixel per lane); per 64-source
+//                               chunk a 64-bit mask per patch says which
+//                               sources touch it, so a warp only evaluates
+//                               sources that overlap its patch, in list order,
+//                               accumulating in a register.  The finished tile
+//                               leaves with one TMA bulk store (double-buffered).
 //
 // No atomics on hr, no read-modify-write of hr, no separate memset: every hr
 // byte is written exactly once.  Result is bit-identical to the reference.
@@ -39,14 +44,15 @@
 
 namespace pp {
 
-constexpr int kSplatThreads = 256;
+constexpr int kSplatThreads = 256;             // consumer threads
 constexpr int kSplatWarps = kSplatThreads / 32;
+constexpr int kSplatBlock = kSplatThreads + 32; // + the producer warp
 constexpr int kChunk = 64;            // sources per mask chunk (one bit each)
 constexpr int kGroupCap = kSplatThreads;   // sources staged per ordered-filter block
 constexpr int kGroupStripsMax = 32;
 static int group_strips() {           // strips per CTA
   if (const char *e = getenv("PP_CIFHR_GROUP")) { int g = atoi(e); if (g >= 1 && g <= kGroupStripsMax) return g; }
-  return 9;
+  return 3;
 }
 constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see strip_rshift)
 constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored from (4 KiB pieces)
@@ -58,6 +64,8 @@ struct CifHrWs {
   int4 *src_b;      // (B,F,src_cap) minx, maxx, miny, maxy
   int *n_src;       // (B,F)
   int *strip_cnt;   // (B,F,nstrips)
+  int *busy_list;   // (B*F*nstrips) ids (bf * nstrips + strip) of the strips with sources, any order
+  int *cursors;     // [0] number of busy strips, [1] producer group cursor, [2] consumer strip cursor
   int nstrips;
   int rshift;       // strip rows R = 1 << rshift
 };
@@ -78,7 +86,8 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   n += align_up(bf * c.src_cap * sizeof(float4), 256);
   n += align_up(bf * c.src_cap * sizeof(int4), 256);
   n += align_up(bf * sizeof(int), 256);
-  n += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
+  n += 2 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
+  n += 256;
   return n;
 }
 
@@ -89,7 +98,9 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
   w.src_a = (float4 *)p; p += align_up(bf * c.src_cap * sizeof(float4), 256);
   w.src_b = (int4 *)p;   p += align_up(bf * c.src_cap * sizeof(int4), 256);
   w.n_src = (int *)p;    p += align_up(bf * sizeof(int), 256);
-  w.strip_cnt = (int *)p;
+  w.strip_cnt = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
+  w.busy_list = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
+  w.cursors = (int *)p;
   w.rshift = strip_rshift(hr_w(s));
   w.nstrips = num_strips(hr_h(s), w.rshift);
   return w;
@@ -154,9 +165,17 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
     w.n_src[bf] = count;
     int run = 0;
     int *sc = w.strip_cnt + (size_t)bf * w.nstrips;
+    int n_busy = 0;
     for (int i = 0; i < w.nstrips; i++) {
       run += sm_diff[i];
       sc[i] = run;
+      n_busy += run != 0;
+    }
+    // strips with sources go to the consumers' work list (order is irrelevant)
+    if (n_busy) {
+      int at = atomicAdd(&w.cursors[0], n_busy);
+      for (int i = 0; i < w.nstrips; i++)
+        if (sc[i] != 0) w.busy_list[at++] = bf * w.nstrips + i;
     }
   }
 }
@@ -227,8 +246,8 @@ __device__ __forceinline__ StripGeo strip_geo(size_t plane0, int strip, int rshi
   return g;
 }
 
-// Write one finished strip from a smem buffer laid out like the strip.  Call
-// from all threads after the buffer is complete, fenced and barriered.
+// Write one finished strip from a smem buffer laid out like the strip.  Called
+// by the 256 consumer threads after the buffer is complete, fenced and barriered.
 __device__ __forceinline__ void emit_strip(float *__restrict__ hr, const float *buf, const StripGeo &g) {
   const int t = threadIdx.x;
   if (t == 0) {
@@ -242,79 +261,113 @@ __device__ __forceinline__ void emit_strip(float *__restrict__ hr, const float *
   }
 }
 
-// An empty strip: zeros, in pieces of the small zero buffer.
-__device__ __forceinline__ void emit_zero_strip(float *__restrict__ hr, const float *zero, const StripGeo &g) {
-  const int t = threadIdx.x;
-  if (t == 0) {
+// An empty strip: zeros, in pieces of the small zero buffer.  One warp.
+__device__ __forceinline__ void emit_zero_strip(float *__restrict__ hr, const float *zero, const StripGeo &g,
+                                                int lane) {
+  if (lane == 0) {
     for (size_t o = g.m0; o < g.m1; o += kZeroFloats) {
       size_t n = g.m1 - o < (size_t)kZeroFloats ? g.m1 - o : (size_t)kZeroFloats;
       bulk_store(hr + o, zero, (uint32_t)(n * sizeof(float)));
     }
-  } else if (t >= 32 && t < 36) {
-    size_t i = g.gs + (size_t)(t - 32);
+  } else if (lane >= 1 && lane < 5) {
+    size_t i = g.gs + (size_t)(lane - 1);
     if (i < g.m0) hr[i] = 0.f;
-  } else if (t >= 36 && t < 40) {
-    size_t i = g.m1 + (size_t)(t - 36);
+  } else if (lane >= 5 && lane < 9) {
+    size_t i = g.m1 + (size_t)(lane - 5);
     if (i < g.ge) hr[i] = 0.f;
   }
 }
 
-__global__ void __launch_bounds__(kSplatThreads)
-cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int kGroupStrips, int src_cap,
+// barrier of the consumer warps only (the producer warp never joins it)
+__device__ __forceinline__ void consumer_sync() {
+  asm volatile("bar.sync 1, %0;" :: "n"(kSplatThreads) : "memory");
+}
+
+// block_flag_scan for the consumer warps
+__device__ __forceinline__ int consumer_flag_scan(bool flag, int *warp_tot, int *total) {
+  unsigned m = __ballot_sync(0xffffffffu, flag);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int in_warp = __popc(m & ((1u << lane) - 1u));
+  if (lane == 0) warp_tot[w] = __popc(m);
+  consumer_sync();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int i = 0; i < kSplatWarps; i++) {
+    int t = warp_tot[i];
+    if (i < w) base += t;
+    tot += t;
+  }
+  consumer_sync();
+  *total = tot;
+  return base + in_warp;
+}
+
+__global__ void __launch_bounds__(kSplatBlock)
+cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
                    int hh, int hw, int buf_floats) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float *zero = reinterpret_cast<float *>(smem_raw);
   float *tiles = zero + kZeroFloats;                      // two tile buffers
   __shared__ float4 s_a[kGroupCap];
   __shared__ int4 s_b[kGroupCap];
-  __shared__ unsigned long long s_mask[kMaxPatches];
+  __shared__ uint32_t s_mask[2][kMaxPatches];             // bit s of word s/32: source s touches the patch
   __shared__ int warp_tot[kSplatWarps];
-  __shared__ int s_cnt[kGroupStripsMax];
+  __shared__ int s_item;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int bf = blockIdx.x / n_groups;
-  const int grp = blockIdx.x - bf * n_groups;
-  const int strip0 = grp * kGroupStrips;
-  const int nloc = min(kGroupStrips, w.nstrips - strip0);
   const int rshift = w.rshift;
-  const int cshift = 5 - rshift;                          // patch = (1 << rshift) rows x (1 << cshift) cols, 1 px per lane
-  const size_t plane0 = (size_t)bf * hh * hw;
+  const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
 
-  if (tid < kGroupStrips) s_cnt[tid] = tid < nloc ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + tid) : 0;
-  for (int i = tid; i < (kZeroFloats >> 2); i += kSplatThreads)
+  for (int i = tid; i < (kZeroFloats >> 2); i += kSplatBlock)
     reinterpret_cast<float4 *>(zero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   fence_async_smem();
   __syncthreads();
 
-  // ---- empty strips: pure TMA zero stores ------------------------------------
-  int n_busy = 0;
-  for (int k = 0; k < nloc; k++) {
-    if (s_cnt[k] != 0) { n_busy++; continue; }
-    emit_zero_strip(hr, zero, strip_geo(plane0, strip0 + k, rshift, hh, hw));
-  }
-  if (n_busy == 0) {
-    if (tid == 0) bulk_wait_read<0>();
+  if (warp == kSplatWarps) {
+    // ---- producer warp: every empty strip, as TMA zero stores ---------------------
+    const int total = n_planes * n_groups;
+    for (;;) {
+      int item = 0;
+      if (lane == 0) item = atomicAdd(&w.cursors[1], 1);
+      item = __shfl_sync(0xffffffffu, item, 0);
+      if (item >= total) break;
+      const int bf = item / n_groups;
+      const int strip0 = (item - bf * n_groups) * kGroupStrips;
+      const int nloc = min(kGroupStrips, w.nstrips - strip0);
+      const size_t plane0 = (size_t)bf * hh * hw;
+      const int cnt = lane < nloc ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + lane) : 1;
+      unsigned empty = __ballot_sync(0xffffffffu, cnt == 0);
+      for (; empty; empty &= empty - 1u)
+        emit_zero_strip(hr, zero, strip_geo(plane0, strip0 + __ffs(empty) - 1, rshift, hh, hw), lane);
+    }
+    if (lane == 0) bulk_wait_read<0>();     // smem must outlive the reads of the async proxy
     return;
   }
 
-  // ---- strips with sources ------------------------------------------------------
-  const int nsrc = min(__ldg(w.n_src + bf), src_cap);
-  const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
-  const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
+  // ---- consumer warps: the strips that have sources ------------------------------------
+  const int n_busy = __ldg(w.cursors);
+  const int cshift = 5 - rshift;            // patch = (1 << rshift) rows x (1 << cshift) cols, 1 px per lane
   const int n_patches = (hw + (1 << cshift) - 1) >> cshift;
   const int row = lane >> (5 - rshift);                   // lane's row inside the patch
   const int cg = lane & ((1 << (5 - rshift)) - 1);        // lane's column inside the patch
   int n_tiles = 0;
 
-  for (int k = 0; k < nloc; k++) {
-    if (s_cnt[k] == 0) continue;
-    const StripGeo g = strip_geo(plane0, strip0 + k, rshift, hh, hw);
-    float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
-    // the bulk store that last read this buffer (two tiles ago) must have drained
+  for (;;) {
+    if (tid == 0) s_item = atomicAdd(&w.cursors[2], 1);
+    // the bulk store that last read the tile buffer about to be reused (two tiles ago) must have drained
     if (n_tiles >= 2 && tid == 0) bulk_wait_read<1>();
-    __syncthreads();
+    consumer_sync();
+    const int item = s_item;
+    if (item >= n_busy) break;
+    const int id = __ldg(w.busy_list + item);
+    const int bf = id / w.nstrips;
+    const StripGeo g = strip_geo((size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
+    float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
     for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
       reinterpret_cast<float4 *>(tile)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int nsrc = min(__ldg(w.n_src + bf), src_cap);
+    const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
+    const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
     const int py = g.r0 + row;
     const int tile_row = (int)(g.gs - g.ga) + row * hw;
 
@@ -328,22 +381,24 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int kGroupSt
         keep = bb.z < g.r1 && bb.w > g.r0;
       }
       int n_staged;
-      const int off = block_flag_scan(keep, warp_tot, &n_staged);   // two barriers
+      const int off = consumer_flag_scan(keep, warp_tot, &n_staged);   // two barriers
       if (keep) { s_a[off] = ga_src[i]; s_b[off] = bb; }
       if (n_staged == 0) continue;
 
       for (int c0 = 0; c0 < n_staged; c0 += kChunk) {
         const int nchunk = min(kChunk, n_staged - c0);
-        for (int p = tid; p < n_patches; p += kSplatThreads) s_mask[p] = 0ull;
-        __syncthreads();                                   // staged list + cleared masks visible
+        for (int p = tid; p < 2 * kMaxPatches; p += kSplatThreads) (&s_mask[0][0])[p] = 0u;
+        consumer_sync();                                   // staged list + cleared masks visible
         if (tid < nchunk) {
           const int4 b = s_b[c0 + tid];
           const int p0 = b.x >> cshift, p1 = (b.y - 1) >> cshift;
-          for (int p = p0; p <= p1; p++) atomicOr(&s_mask[p], 1ull << tid);
+          uint32_t *word = s_mask[tid >> 5];
+          const uint32_t bit = 1u << (tid & 31);
+          for (int p = p0; p <= p1; p++) atomicOr(&word[p], bit);
         }
-        __syncthreads();
+        consumer_sync();
         for (int p = warp; p < n_patches; p += kSplatWarps) {
-          unsigned long long m = s_mask[p];
+          unsigned long long m = (unsigned long long)s_mask[0][p] | ((unsigned long long)s_mask[1][p] << 32);
           if (m == 0ull) continue;
           const int px = (p << cshift) + cg;
           const bool ok = py < g.r1 && px < hw;
@@ -360,11 +415,11 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_groups, int kGroupSt
           }
           if (ok) tile[tile_row + px] = clamp1(acc);
         }
-        __syncthreads();                                   // patches done before masks are cleared again
+        consumer_sync();                                   // patches done before masks are cleared again
       }
     }
     fence_async_smem();
-    __syncthreads();
+    consumer_sync();
     emit_strip(hr, tile, g);
     n_tiles++;
   }
@@ -380,6 +435,7 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
   size_t smem = (size_t)(w.nstrips + 1) * sizeof(int);
   prof_mark(p.profile, kStCompact, st);
+  PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
       d_cif, w, s, c.src_cap, hh, hw, p.cif_threshold, p.cif_min_scale / (float)s.stride,
       p.cif_min_scale != 0.0f, d_status);
@@ -392,9 +448,14 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
                                      2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
   const int kGroupStrips = group_strips();
   const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
+  // persistent grid: as many CTAs as fit (shared memory allows 4 per SM at 641 px)
+  int per_sm = 4;
+  if (const char *e = getenv("PP_CIFHR_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
+  int grid = num_sms() * per_sm;
+  if (grid > bf * n_groups) grid = bf * n_groups;
   prof_mark(p.profile, kStSplat, st);
-  cifhr_splat_kernel<<<bf * n_groups, kSplatThreads, dyn, st>>>(d_hr, w, n_groups, kGroupStrips, c.src_cap,
-                                                               hh, hw, buf_floats);
+  cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
+                                                    buf_floats);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
   return PP_OK;
 }

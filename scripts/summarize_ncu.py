@@ -25,16 +25,17 @@ def launches(tag, out):
         return
     rows = list(csv.reader(l for l in open(path) if l.startswith('"')))
     h = rows[0]
-    ki, vi = h.index('Kernel Name'), h.index('Metric Value')
+    ki, vi, gi = h.index('Kernel Name'), h.index('Metric Value'), h.index('Grid Size')
     agg = collections.OrderedDict()
-    for r in rows[1:]:
-        agg.setdefault(r[ki], []).append(float(r[vi].replace(',', '')))
+    for r in rows[1:]:     # the same kernel at another grid size is another workload (e2e chunks)
+        agg.setdefault(r[ki].split('(')[0] + ' grid ' + r[gi].replace(' ', ''), []).append(
+            float(r[vi].replace(',', '')))
     tot = sum(sum(v) for v in agg.values())
     out.write('## Launch list (ncu --metrics gpu__time_duration.sum --clock-control none; '
               'cold-cache, serialised: compare shares)\n\n')
     out.write('| kernel | launches | mean us | share |\n|---|---|---|---|\n')
     for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
-        out.write('| `%s` | %d | %.1f | %.3f |\n' % (k.split('(')[0], len(v), sum(v) / len(v) / 1e3,
+        out.write('| `%s` | %d | %.1f | %.3f |\n' % (k, len(v), sum(v) / len(v) / 1e3,
                                                     sum(v) / tot))
     out.write('\n')
 
