@@ -67,6 +67,15 @@ typedef struct pp_caps {
   int32_t src_cap;  /* CifHr sources per field    (worst case H*W)   */
 } pp_caps;
 
+/* initial_annotations of CifCaf.__call__ (cifcaf.py:67-71,95-98): annotations that
+ * are grown and marked occupied before the seeds are visited.  Device pointers. */
+typedef struct pp_initial {
+  const float *data;    /* (B, cap, F, 3) x, y, v */
+  const float *scales;  /* (B, cap, F) joint_scales */
+  const int32_t *n;     /* (B) annotations per image */
+  int32_t cap;
+} pp_initial;
+
 /* Decoder knobs; same meaning and defaults-by-configuration as the reference's
  * class attributes (decoder/factory.py:74-92). */
 typedef struct pp_params {
@@ -90,6 +99,7 @@ typedef struct pp_params {
   int32_t exp_mode;              /* 1 = deterministic pp_expf (default), 0 = CUDA expf */
   uint32_t seed_mask;            /* FieldConfig.seed_mask as bits (0 = all fields seed) */
   struct pp_profile *profile;    /* optional per-stage CUDA-event timer (NULL = off)    */
+  const pp_initial *initial;     /* optional initial annotations (NULL = none)          */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's

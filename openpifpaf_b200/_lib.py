@@ -24,6 +24,10 @@ class Caps(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ('seed_cap', 'caf_cap', 'ann_cap', 'src_cap')]
 
 
+class Initial(C.Structure):
+    _fields_ = [('data', C.c_void_p), ('scales', C.c_void_p), ('n', C.c_void_p), ('cap', C.c_int32)]
+
+
 class Params(C.Structure):
     _fields_ = [
         ('nms_instance_threshold', C.c_double),
@@ -35,7 +39,7 @@ class Params(C.Structure):
         ('caf_min_distance', C.c_float), ('caf_max_distance', C.c_float),
         ('connection_method', C.c_int32), ('greedy', C.c_int32),
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
-        ('seed_mask', C.c_uint32), ('profile', C.c_void_p),
+        ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
     ]
 
 

@@ -289,6 +289,11 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   a.status = d_out->status;
   a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
   a.hh = hr_h(*s); a.hw = hr_w(*s);
+  if (p->initial) {
+    if (!p->initial->data || !p->initial->scales || !p->initial->n || p->initial->cap <= 0) return PP_ERR_ARG;
+    a.init_data = p->initial->data; a.init_scales = p->initial->scales;
+    a.init_n = p->initial->n; a.init_cap = p->initial->cap;
+  }
   int rc = assemble_launch(a, *sk, s->B, s->F, *p, st);
   if (rc) return rc;
   if (p->force_complete) {
@@ -362,6 +367,11 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   a.status = o->status;
   a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
   a.hh = hr_h(*s); a.hw = hr_w(*s);
+  if (p->initial) {
+    if (!p->initial->data || !p->initial->scales || !p->initial->n || p->initial->cap <= 0) return PP_ERR_ARG;
+    a.init_data = p->initial->data; a.init_scales = p->initial->scales;
+    a.init_n = p->initial->n; a.init_cap = p->initial->cap;
+  }
   if ((rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
   const float *nms_data = a.pre_data, *nms_scales = a.pre_scales;
   if (p->force_complete) {                                           // cifcaf.py:110-115
@@ -540,8 +550,17 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
     const pp_outputs d_sub = slice_outputs(*d_out, strides, b0);
     PP_CUDA_CHECK(cudaStreamWaitEvent(st, q->ev_in[k], 0));
     // kernels of successive chunks are serial on `stream`, so they share one workspace
+    pp_params p_sub = *p;
+    pp_initial ini_sub;
+    if (p->initial) {          // the chunk's slice of the initial annotations
+      ini_sub = *p->initial;
+      ini_sub.data += b0 * (size_t)ini_sub.cap * s->F * 3;
+      ini_sub.scales += b0 * (size_t)ini_sub.cap * s->F;
+      ini_sub.n += b0;
+      p_sub.initial = &ini_sub;
+    }
     int rc = pp_decode_batch(d_cif + b0 * cif_img, d_caf + b0 * caf_img, sk, &d_sub, d_ws, ws_bytes,
-                             &sub, c, p, stream);
+                             &sub, c, &p_sub, stream);
     if (rc) return rc;
     PP_CUDA_CHECK(cudaEventRecord(q->ev_done[k], st));
     PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_out, q->ev_done[k], 0));

@@ -540,12 +540,15 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
   for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) occ[i] = 0;
   __syncthreads();
 
-  int n_ann = 0, cursor = 0;
+  // initial_annotations (cifcaf.py:95-98) are grown first, then the seeds
+  const int n_init = a.init_n ? min(a.init_n[b], a.init_cap) : 0;
+  int n_ann = 0, cursor = 0, ia = 0;
   PP_TICK(0);
   for (;;) {
+    const bool from_init = ia < n_init;
     // ---- next seed whose cell is free (cifcaf.py:100-102) -------------------
     int found = -1;
-    for (int base = cursor; base < n_seeds; base += blockDim.x) {
+    for (int base = cursor; !from_init && base < n_seeds; base += blockDim.x) {
       int i = base + threadIdx.x;
       bool hit = i < n_seeds && occ[i] == 0;
       unsigned m = __ballot_sync(0xffffffffu, hit);
@@ -557,17 +560,28 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
       if (found >= 0) break;
     }
     PP_TICK(1);
-    if (found < 0) break;
-    cursor = found + 1;
+    if (!from_init) {
+      if (found < 0) break;
+      cursor = found + 1;
+    }
     if (n_ann >= a.ann_cap) {
       if (threadIdx.x == 0) atomicOr(&a.status[b], PP_STATUS_ANN_OVERFLOW);
       break;
     }
-    // ---- new annotation from the seed (:104-105) ---------------------------
-    for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = 0.0f;
-    for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = 0.0f;
+    // ---- new annotation from the seed (:104-105), or the next initial annotation ----
+    if (from_init) {
+      const float *idata = a.init_data + ((size_t)b * a.init_cap + ia) * F * 3;
+      const float *iscales = a.init_scales + ((size_t)b * a.init_cap + ia) * F;
+      for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = idata[i];
+      for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = iscales[i];
+      if (threadIdx.x == 0) sh.n_dec = 0;
+      ia++;
+    } else {
+      for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = 0.0f;
+      for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = 0.0f;
+    }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (!from_init && threadIdx.x == 0) {
       const float *sd = seeds + (size_t)found * 5;
       int f = (int)sd[1];
       sh.data[f][0] = sd[2]; sh.data[f][1] = sd[3]; sh.data[f][2] = sd[0];

@@ -28,6 +28,9 @@ struct AsmArgs {
   int seed_cap, caf_cap, ann_cap, L;
   int hh, hw;
   int stage_floats;   // set by assemble_launch
+  const float *init_data, *init_scales;   // initial annotations (optional)
+  const int *init_n;
+  int init_cap;
 };
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st);

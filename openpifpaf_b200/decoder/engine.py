@@ -34,6 +34,8 @@ class DecoderParams:
     deterministic_exp: bool = True
     seed_mask: Optional[list] = None
     profile: Optional[int] = None      # pp_profile* from StageProfile (bench/profiling only)
+    # initial annotations: (data (B, cap, F, 3), scales (B, cap, F), n (B,) int32) CUDA tensors
+    initial: Optional[tuple] = None
 
     def to_c(self):
         p = _lib.Params()
@@ -68,6 +70,14 @@ class DecoderParams:
                 mask = 1 << 31     # "no field seeds": bit outside any valid field
         p.seed_mask = mask
         p.profile = self.profile
+        if self.initial is not None:
+            data, scales, n = self.initial
+            assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()
+            assert scales.is_cuda and scales.dtype == torch.float32 and scales.is_contiguous()
+            assert n.is_cuda and n.dtype == torch.int32
+            ini = _lib.Initial(data.data_ptr(), scales.data_ptr(), n.data_ptr(), data.shape[1])
+            p._initial_struct = ini          # keep the struct alive as long as the params
+            p.initial = C.pointer(ini)
         return p
 
 

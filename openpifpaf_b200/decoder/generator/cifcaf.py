@@ -142,8 +142,26 @@ class CifCaf(Generator):
         return out
 
     # -------------------------------------------------------------- decode
-    def decode_batch(self, cif, caf):
+    def _initial_tensors(self, initial, device):
+        """List (per image) of lists of Annotation -> padded CUDA tensors for pp_initial."""
+        F = len(self.keypoints)
+        cap = max(1, max(len(anns) for anns in initial))
+        data = np.zeros((len(initial), cap, F, 3), np.float32)
+        scales = np.zeros((len(initial), cap, F), np.float32)
+        n = np.zeros((len(initial),), np.int32)
+        for b, anns in enumerate(initial):
+            n[b] = len(anns)
+            for i, ann in enumerate(anns):
+                data[b, i] = ann.data
+                scales[b, i] = ann.joint_scales
+        return (torch.from_numpy(data).to(device), torch.from_numpy(scales).to(device),
+                torch.from_numpy(n).to(device))
+
+    def decode_batch(self, cif, caf, initial_annotations=None):
         """Decode a batch. ``cif (B,F,5,H,W)``, ``caf (B,L,9,H,W)`` float32.
+        ``initial_annotations``: optional list (per image) of lists of Annotation that are
+        grown and marked occupied before the seeds (cifcaf.py:95-98); like the reference,
+        those objects are updated in place and returned in the result lists.
 
         CUDA tensors are decoded in place on their device; host arrays (numpy or
         CPU tensors, ideally pinned) go through ``pp_decode_batch_host``, which
@@ -152,6 +170,15 @@ class CifCaf(Generator):
         start = time.perf_counter()
         params = self.params()
         eng = self.engine()
+        has_initial = bool(initial_annotations) and any(len(a) for a in initial_annotations)
+        if has_initial and not (isinstance(cif, torch.Tensor) and cif.is_cuda):
+            device = eng._device()           # the pipelined host path carries no initial annotations
+            cif = torch.as_tensor(np.ascontiguousarray(cif) if not isinstance(cif, torch.Tensor)
+                                  else cif).to(device)
+            caf = torch.as_tensor(np.ascontiguousarray(caf) if not isinstance(caf, torch.Tensor)
+                                  else caf).to(device)
+        if has_initial:
+            params.initial = self._initial_tensors(initial_annotations, cif.device)
         if isinstance(cif, torch.Tensor) and cif.is_cuda:
             buf = eng.run_device(cif, caf, params)
             n_ann = buf.dev['n_ann'].cpu().numpy()         # synchronises the stream
@@ -177,8 +204,24 @@ class CifCaf(Generator):
             self.last_decoder_time = time.perf_counter() - start
             return result
         result = self._annotations_from(n_ann, data, scales, source, pre_data, pre_order)
+        if has_initial:
+            self._adopt_initial(result, source, initial_annotations)
         self.last_decoder_time = time.perf_counter() - start
         return result
+
+    @staticmethod
+    def _adopt_initial(result, source, initial):
+        """The reference mutates and returns the caller's initial Annotation objects."""
+        for b, anns in enumerate(result):
+            for r, ann in enumerate(anns):
+                src = int(source[b, r])
+                if src < len(initial[b]):
+                    orig = initial[b][src]
+                    orig.data = ann.data
+                    orig.joint_scales = ann.joint_scales
+                    orig.decoding_order = list(orig.decoding_order) + list(ann.decoding_order)
+                    orig.frontier_order = list(orig.frontier_order) + list(ann.frontier_order)
+                    anns[r] = orig
 
     def decode_heads(self, heads):
         cfg = self.field_config
@@ -186,8 +229,6 @@ class CifCaf(Generator):
 
     def __call__(self, fields, initial_annotations=None):
         start = time.perf_counter()
-        if initial_annotations:
-            raise NotImplementedError('initial_annotations are not built yet (SURVEY.md 8f rank 2)')
         cfg = self.field_config
         if cfg.cif_visualizers:
             for vis, cif_i in zip(cfg.cif_visualizers, cfg.cif_indices):
@@ -201,7 +242,8 @@ class CifCaf(Generator):
         else:
             cif = np.ascontiguousarray(cif, dtype=np.float32)[None]
             caf = np.ascontiguousarray(caf, dtype=np.float32)[None]
-        annotations = self.decode_batch(cif, caf)[0]
+        annotations = self.decode_batch(
+            cif, caf, [list(initial_annotations)] if initial_annotations else None)[0]
         LOG.debug('annotations %d, %.3fs', len(annotations), time.perf_counter() - start)
         LOG.info('%d annotations: %s', len(annotations),
                  [np.sum(ann.data[:, 2] > 0.1) for ann in annotations])

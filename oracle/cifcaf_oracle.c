@@ -720,7 +720,8 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
                float *fwd, int *nfwd, float *bwd, int *nbwd, long caf_cap,
                int ann_cap, float *ann_data, float *ann_js, int *ann_ndec, int *ann_dec,
                int *ann_nfront, int *ann_front,
-               int *pre_n, float *pre_data, float *pre_js, int *tie_flag) {
+               int *pre_n, float *pre_data, float *pre_js, int *tie_flag,
+               int init_n, const float *init_data, const float *init_js) {
   orc_graph g;
   int rc = graph_init(&g, F, L, skeleton);
   if (rc) return rc;
@@ -742,7 +743,23 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
   float *scores = (float *)malloc(sizeof(float) * (size_t)(caf_cap + 1));
   int n = 0, tie = 0;
   rc = ORC_OK;
-  for (long si = 0; si < ns; si++) {                                            /* :100-108 */
+  for (int ia = 0; ia < init_n && rc == ORC_OK; ia++) {                         /* :95-98 */
+    if (n >= ann_cap) { rc = ORC_ERR_CAPACITY; break; }
+    orc_ann *an = &anns[n];
+    memset(an, 0, sizeof *an);
+    an->F = F;
+    for (int j = 0; j < F; j++) {
+      for (int c = 0; c < 3; c++) an->data[j][c] = init_data[((size_t)ia * F + j) * 3 + c];
+      an->js[j] = init_js[(size_t)ia * F + j];
+    }
+    if (grow(an, &g, &cf, cfg, conf_scales, 1, fr, idx, scores) == ORC_ERR_TIE) tie = 1;
+    n++;
+    for (int j = 0; j < F; j++) {
+      if (an->data[j][2] == 0.0f) continue;
+      occ_set(&occ, j, an->data[j][0], an->data[j][1], an->js[j]);
+    }
+  }
+  for (long si = 0; si < ns && rc == ORC_OK; si++) {                            /* :100-108 */
     const float *sd = seeds + 5 * si;
     int f = (int)sd[1];
     if (occ_get(&occ, f, sd[2], sd[3])) continue;

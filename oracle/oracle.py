@@ -133,7 +133,7 @@ class Decoded:
                  'frontier_order', 'pre_data', 'pre_joint_scales', 'tie')
 
 
-def decode(cif, caf, skeleton, cfg=None, *, confidence_scales=None, ann_cap=None):
+def decode(cif, caf, skeleton, cfg=None, *, confidence_scales=None, ann_cap=None, initial=None):
     """Full CifCaf decode of one image. Returns a ``Decoded``."""
     cfg = cfg or Config()
     cif, caf = _f32(cif), _f32(caf)
@@ -163,13 +163,18 @@ def decode(cif, caf, skeleton, cfg=None, *, confidence_scales=None, ann_cap=None
     cs = None
     if confidence_scales is not None:
         cs = _f32(confidence_scales)
+    init_n, init_data, init_js = 0, None, None
+    if initial is not None:          # (data (n, F, 3), joint_scales (n, F))
+        init_data, init_js = _f32(initial[0]), _f32(initial[1])
+        init_n = len(init_data)
     vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
     n = lib().orc_decode(vp(cif), vp(caf), F, L, H, W, vp(skel),
                          vp(cs) if cs is not None else None, C.byref(cfg),
                          vp(hr), vp(seeds_), C.c_long(seed_cap), C.byref(n_seeds),
                          vp(fwd), vp(nf), vp(bwd), vp(nb), C.c_long(caf_cap),
                          ann_cap, vp(data), vp(js), vp(ndec), vp(dec), vp(nfront), vp(front),
-                         C.byref(pre_n), vp(pre_data), vp(pre_js), C.byref(tie))
+                         C.byref(pre_n), vp(pre_data), vp(pre_js), C.byref(tie),
+                         init_n, vp(init_data) if init_n else None, vp(init_js) if init_n else None)
     if n < 0:
         raise RuntimeError('oracle decode failed with code %d' % n)
     out = Decoded()

@@ -331,3 +331,31 @@ def test_nonfinite_sources_stage_outputs_gpu(oracle, coco_skeleton, configured_d
             nf, nb = out['n_caf_fwd'][0, l], out['n_caf_bwd'][0, l]
             assert np.array_equal(out['caf_fwd'][0, l, :, :nf], f[l], equal_nan=True)
             assert np.array_equal(out['caf_bwd'][0, l, :, :nb], b[l], equal_nan=True)
+
+
+def test_initial_annotations(oracle, coco_skeleton, configured_decoder):
+    """CifCaf.__call__(fields, initial_annotations): grown first, marked occupied, returned
+    as the same (mutated) objects -- cifcaf.py:67-71,95-98."""
+    from openpifpaf_b200.annotation import Annotation
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    cif, caf, poses = fields((321, 481), 6, pose_seed=3, jitter_seed=4)
+    poses = np.asarray(poses)
+    init_data = np.zeros((2, 17, 3), np.float32)
+    init_js = np.zeros((2, 17), np.float32)
+    init_data[0, 0] = (poses[0][0][0], poses[0][0][1], 0.9)
+    init_js[0, 0] = 4.0
+    for j in (5, 6, 11):
+        init_data[1, j] = (poses[2][j][0], poses[2][j][1], 0.8)
+        init_js[1, j] = 6.0
+    o = oracle.decode(cif, caf, coco_skeleton, oracle.Config(exp_mode=1), initial=(init_data, init_js))
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    for to_field in (lambda a: a, lambda a: torch.from_numpy(a).cuda()):
+        initial = [Annotation(COCO_KEYPOINTS, coco_skeleton).set(init_data[i].copy(), init_js[i].copy())
+                   for i in range(2)]
+        anns = dec([to_field(cif), to_field(caf)], initial_annotations=initial)
+        assert len(anns) == len(o.data)
+        for ann, d, js in zip(anns, o.data, o.joint_scales):
+            assert np.array_equal(ann.data, d) and np.array_equal(ann.joint_scales, js)
+        assert sum(any(a is i for a in anns) for i in initial) == 2, 'initial objects are returned'
+        assert all(np.count_nonzero(i.data[:, 2]) >= 10 for i in initial), 'and were grown'

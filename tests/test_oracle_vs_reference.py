@@ -188,3 +188,29 @@ def test_nonfinite_sources_stage_outputs(ref, oracle, coco_skeleton):
         for l in range(len(coco_skeleton)):
             assert np.array_equal(sc.forward[l], f[l], equal_nan=True)
             assert np.array_equal(sc.backward[l], b[l], equal_nan=True)
+
+
+def test_initial_annotations(ref, oracle, coco_skeleton):
+    """cifcaf.py:67-71,95-98: initial annotations are grown and marked occupied before the seeds."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    dec = ref.decoder
+    configure(dec)
+    cif, caf, poses = fields((321, 481), 6, pose_seed=3, jitter_seed=4)
+    poses = np.asarray(poses)
+    init_data = np.zeros((2, 17, 3), np.float32)
+    init_js = np.zeros((2, 17), np.float32)
+    init_data[0, 0] = (poses[0][0][0], poses[0][0][1], 0.9)
+    init_js[0, 0] = 4.0
+    for j in (5, 6, 11):
+        init_data[1, j] = (poses[2][j][0], poses[2][j][1], 0.8)
+        init_js[1, j] = 6.0
+    initial = [ref.Annotation(COCO_KEYPOINTS, coco_skeleton).set(init_data[i].copy(), init_js[i].copy())
+               for i in range(2)]
+    d = dec.CifCaf(dec.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=[list(l) for l in coco_skeleton])
+    anns = d([cif.copy(), caf.copy()], initial_annotations=initial)
+    o = oracle.decode(cif, caf, coco_skeleton, oracle.Config(exp_mode=1), initial=(init_data, init_js))
+    assert len(anns) == len(o.data)
+    for a, data in zip(anns, o.data):
+        assert np.array_equal(a.data[:, 2] != 0, data[:, 2] != 0)
+        assert np.abs(a.data[:, :2] - data[:, :2]).max() <= TOL_XY
+        assert np.abs(a.data[:, 2] - data[:, 2]).max() <= TOL_SCORE
