@@ -71,7 +71,8 @@ struct DecodeWs {
   float *hr;                 // (B,F,Hh,Wh)      when the caller passes none
   float *seeds; int *n_seeds;
   float *fwd, *bwd; int *nfwd, *nbwd;
-  uint8_t *occ_cnt;
+  float *bin_rows; int *bin_start;   // spatially binned copy of the lists for the assembly
+  uint8_t *occ_cnt; int2 *occ_rec;
   float *pre_data, *pre_scales; int *pre_order; int *n_pre;
   float *cmp_data, *cmp_scales;   // force_complete: completed annotations (NMS input)
   void *stage;               // shared by the cifhr / seeds / nms stages (used one after another)
@@ -94,7 +95,10 @@ static DecodeWs layout(void *base, const pp_shape &s, const pp_caps &c, bool nee
   w.bwd = (float *)take(B * s.L * 9 * c.caf_cap * sizeof(float));
   w.nfwd = (int *)take(B * s.L * sizeof(int));
   w.nbwd = (int *)take(B * s.L * sizeof(int));
+  w.bin_rows = (float *)take(binned_rows_bytes(s, c));
+  w.bin_start = (int *)take(binned_start_bytes(s));
   w.occ_cnt = (uint8_t *)take(B * c.seed_cap);
+  w.occ_rec = (int2 *)take(B * c.seed_cap * sizeof(int2));
   w.pre_data = (float *)take(B * c.ann_cap * s.F * 3 * sizeof(float));
   w.pre_scales = (float *)take(B * c.ann_cap * s.F * sizeof(float));
   w.pre_order = (int *)take(B * c.ann_cap * s.F * 2 * sizeof(int));
@@ -172,8 +176,8 @@ const char *pp_stage_name(int stage) {
   return (stage >= 0 && stage < PP_N_STAGES) ? names[stage] : "?";
 }
 
-/* 7 kernels + the status, CifHr-cursor and seed-counter memsets */
-int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 3; }
+/* 7 stage kernels + the candidate binning kernel + the status, CifHr-cursor and seed-counter memsets */
+int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 4; }
 const char *pp_version(void) { return "pifpaf_b200 0.1.0 (sm_100a)"; }
 
 void pp_default_params(pp_params *p) {
@@ -269,23 +273,32 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   // workspace: occ counters + pre buffers (when the caller keeps none) + nms scratch
   size_t B = s->B;
   size_t need_occ = align_up(B * c->seed_cap, 256);
+  size_t need_rec = align_up(B * c->seed_cap * sizeof(int2), 256);
   size_t need_pd = align_up(B * c->ann_cap * s->F * 3 * sizeof(float), 256);
   size_t need_ps = align_up(B * c->ann_cap * s->F * sizeof(float), 256);
   size_t need_po = align_up(B * c->ann_cap * s->F * 2 * sizeof(int), 256);
   size_t need_np = align_up(B * sizeof(int), 256);
-  size_t need = need_occ + 2 * need_pd + 2 * need_ps + need_po + need_np + nms_ws_bytes(*s, *c);
+  size_t need_br = align_up(binned_rows_bytes(*s, *c), 256);
+  size_t need_bs = align_up(binned_start_bytes(*s), 256);
+  size_t need = need_occ + need_rec + 2 * need_pd + 2 * need_ps + need_po + need_np + need_br + need_bs +
+                nms_ws_bytes(*s, *c);
   if (ws_bytes < need) return PP_ERR_WORKSPACE;
   char *q = (char *)d_ws;
   AsmArgs a = {};
   a.occ_cnt = (uint8_t *)q; q += need_occ;
+  a.occ_rec = (int2 *)q; q += need_rec;
   a.pre_data = d_out->pre_data ? d_out->pre_data : (float *)q; q += need_pd;
   a.pre_scales = d_out->pre_scales ? d_out->pre_scales : (float *)q; q += need_ps;
   a.pre_order = d_out->pre_order ? d_out->pre_order : (int *)q; q += need_po;
   a.n_pre = d_out->n_pre ? d_out->n_pre : (int *)q; q += need_np;
   float *cmp_data = (float *)q; q += need_pd;
   float *cmp_scales = (float *)q; q += need_ps;
+  float *bin_rows = (float *)q; q += need_br;
+  int *bin_start = (int *)q; q += need_bs;
   a.seeds = d_seeds; a.n_seeds = d_n_seeds;
-  a.fwd = d_fwd; a.bwd = d_bwd; a.nfwd = d_nfwd; a.nbwd = d_nbwd;
+  int rcb = caf_bin_launch(d_fwd, d_nfwd, d_bwd, d_nbwd, bin_rows, bin_start, *s, *c, st);
+  if (rcb) return rcb;
+  a.rows = bin_rows; a.start = bin_start; a.geo = bin_geo(*s); a.nfwd = d_nfwd; a.nbwd = d_nbwd;
   a.status = d_out->status;
   a.seed_cap = c->seed_cap; a.caf_cap = c->caf_cap; a.ann_cap = c->ann_cap; a.L = s->L;
   a.hh = hr_h(*s); a.hw = hr_w(*s);
@@ -297,7 +310,9 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
   int rc = assemble_launch(a, *sk, s->B, s->F, *p, st);
   if (rc) return rc;
   if (p->force_complete) {
-    rc = complete_launch(a, d_fwd2, d_bwd2, d_nfwd2, d_nbwd2, cmp_data, cmp_scales, *sk, s->B, s->F,
+    // the first lists' binned copy is no longer needed: reuse it for the completion lists
+    if ((rc = caf_bin_launch(d_fwd2, d_nfwd2, d_bwd2, d_nbwd2, bin_rows, bin_start, *s, *c, st))) return rc;
+    rc = complete_launch(a, bin_rows, bin_start, d_nfwd2, d_nbwd2, cmp_data, cmp_scales, *sk, s->B, s->F,
                          *p, st);
     if (rc) return rc;
     return nms_launch(cmp_data, cmp_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
@@ -358,8 +373,9 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
     return rc;
   AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
-  a.fwd = fwd; a.bwd = bwd; a.nfwd = nfwd; a.nbwd = nbwd;
-  a.occ_cnt = w.occ_cnt;
+  if ((rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st))) return rc;
+  a.rows = w.bin_rows; a.start = w.bin_start; a.geo = bin_geo(*s); a.nfwd = nfwd; a.nbwd = nbwd;
+  a.occ_cnt = w.occ_cnt; a.occ_rec = w.occ_rec;
   a.pre_data = o->pre_data ? o->pre_data : w.pre_data;
   a.pre_scales = o->pre_scales ? o->pre_scales : w.pre_scales;
   a.pre_order = o->pre_order ? o->pre_order : w.pre_order;
@@ -380,8 +396,10 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
     if ((rc = caf_scored_launch(d_caf, hr, *sk, 0.0001f, w.fwd, w.nfwd, w.bwd, w.nbwd, *s, *c, *p,
                                 o->status, st)))
       return rc;
-    if ((rc = complete_launch(a, w.fwd, w.bwd, w.nfwd, w.nbwd, w.cmp_data, w.cmp_scales, *sk, s->B,
-                              s->F, *p, st)))
+    if ((rc = caf_bin_launch(w.fwd, w.nfwd, w.bwd, w.nbwd, w.bin_rows, w.bin_start, *s, *c, st)))
+      return rc;
+    if ((rc = complete_launch(a, w.bin_rows, w.bin_start, w.nfwd, w.nbwd, w.cmp_data, w.cmp_scales,
+                              *sk, s->B, s->F, *p, st)))
       return rc;
     nms_data = w.cmp_data; nms_scales = w.cmp_scales;
   }

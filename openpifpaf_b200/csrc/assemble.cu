@@ -90,22 +90,30 @@ struct Xysv {
   float x, y, s, v;
 };
 
-constexpr int kScratch = 256;     // in-box candidate indices per warp and pass
+constexpr int kScratch = 256;     // in-box candidate positions per warp and pass
+constexpr int kDirectScan = 192;  // lists up to this long are scanned whole (no bin lookup)
+
+struct Cand2 {     // a candidate with its column in the binned store
+  float s;
+  int i;           // original list index (tie rule)
+  int pos;
+};
 
 // _grow_connection (cifcaf.py:124-145), warp-collective; every lane returns the
-// result.  `base` points at the score row of one directed candidate list whose
-// six live rows (score, source x/y, target x/y/scale) are `stride` floats apart:
-// rows 0,1,2,3,4,5 of the packed shared-memory copy, or rows 0,1,2,5,6,8 of the
-// (9, caf_cap) CafScored block in global memory.
+// result.  `base` points at the score row of one directed candidate list in the
+// binned store (rows score, source x/y, target x/y/scale, original index;
+// `stride` floats apart; K columns sorted by spatial bin, bin b occupying
+// columns [start[b], start[b+1])) -- either the shared-memory copy or global.
 //
-// Two passes keep the serial chain of the one active warp short: (1) a tight
-// loop tests the caf_center_s box and compacts the indices of the candidates
-// inside it into `scratch`; (2) each lane scores ONE of them (sqrt, divide,
-// exp), so the expensive chain runs once, not once per 32 candidates.
-// Not inlined: the forward and the reverse match share one copy of the code.
+// Three steps keep the serial chain of the one active warp short: (0) only the
+// bin rows that intersect the caf_center_s box are visited; (1) a tight loop
+// tests the box exactly (functional.pyx:346-353) and compacts the columns of
+// the candidates inside it into `scratch`; (2) each lane scores ONE of them
+// (sqrt, divide, exp), so the expensive chain runs once, not once per 32
+// candidates.  Not inlined: the forward and the reverse match share one copy.
 __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, const float *base,
-                                                  int stride, int packed, int K, int *scratch,
-                                                  int method, int exp_mode) {
+                                                  int stride, int K, const int *start, BinGeo geo,
+                                                  int *scratch, int method, int exp_mode) {
   const int lane = lane_id();
   const unsigned full = 0xffffffffu;
   const float box = __fmul_rn(2.0f, s);                           // sigma = 2.0 * xy_scale  :129
@@ -114,20 +122,53 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
   const float sigma = __fmul_rn(0.5f, s);                         // :138
   const float sig2 = __fmul_rn(sigma, sigma);
   const float *cs = base, *xs = base + stride, *ys = base + 2 * (size_t)stride;
-  Cand t1 = {-INFINITY, -1}, t2 = {-INFINITY, -1};
+  const int *oi = reinterpret_cast<const int *>(base + 6 * (size_t)stride);
+  Xysv out = {0.f, 0.f, 0.f, 0.f};
+  if (K == 0) return out;
+
+  // step 0: column ranges to visit, one per lane (lane 31 = the NaN bin)
+  int r_lo = 0, r_hi = 0, n_ranges = 1;
+  const bool nanbox = lox != lox || hix != hix || loy != loy || hiy != hiy;
+  bool whole = K <= kDirectScan || nanbox;
+  if (!whole) {
+    const float inv = 1.0f / (float)(1 << geo.bshift);
+    const int bx0 = (int)fminf(fmaxf(__fmul_rn(lox, inv), 0.0f), (float)(geo.nbx - 1));
+    const int bx1 = (int)fminf(fmaxf(__fmul_rn(hix, inv), 0.0f), (float)(geo.nbx - 1));
+    const int by0 = (int)fminf(fmaxf(__fmul_rn(loy, inv), 0.0f), (float)(geo.nby - 1));
+    const int by1 = (int)fminf(fmaxf(__fmul_rn(hiy, inv), 0.0f), (float)(geo.nby - 1));
+    n_ranges = by1 - by0 + 2;
+    if (n_ranges > 32) {
+      whole = true;
+    } else {
+      if (lane < n_ranges - 1) {
+        r_lo = start[(by0 + lane) * geo.nbx + bx0];
+        r_hi = start[(by0 + lane) * geo.nbx + bx1 + 1];
+      } else if (lane == n_ranges - 1) {
+        r_lo = start[geo.nb - 1];
+        r_hi = K;
+      }
+    }
+  }
+  if (whole) { n_ranges = 1; r_lo = 0; r_hi = K; }
+
+  Cand2 t1 = {-INFINITY, -1, 0}, t2 = {-INFINITY, -1, 0};
   int cnt = 0;
-  for (int seg = 0; seg < K;) {
-    // pass 1: caf_center_s (functional.pyx:346-353), order preserved.  Four
-    // independent 32-candidate groups per trip keep four loads in flight when
-    // the list is read from global memory.
+  int rr = 0;
+  int seg = __shfl_sync(full, r_lo, 0), seg_end = __shfl_sync(full, r_hi, 0);
+  while (rr < n_ranges) {
+    // step 1: exact box test, compaction of the columns inside it
     int n = 0;
-    for (; seg < K && n <= kScratch - 128; seg += 128) {
+    while (rr < n_ranges && n <= kScratch - 128) {
+      if (seg >= seg_end) {
+        if (++rr < n_ranges) { seg = __shfl_sync(full, r_lo, rr); seg_end = __shfl_sync(full, r_hi, rr); }
+        continue;
+      }
       bool in[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         const int i = seg + 32 * j + lane;
-        const float cx = i < K ? xs[i] : 0.f, cy = i < K ? ys[i] : 0.f;
-        in[j] = i < K && !(cx < lox || cx > hix || cy < loy || cy > hiy);
+        const float cx = i < seg_end ? xs[i] : 0.f, cy = i < seg_end ? ys[i] : 0.f;
+        in[j] = i < seg_end && !(cx < lox || cx > hix || cy < loy || cy > hiy);
       }
 #pragma unroll
       for (int j = 0; j < 4; j++) {
@@ -135,23 +176,24 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
         if (in[j]) scratch[n + __popc(m & ((1u << lane) - 1u))] = seg + 32 * j + lane;
         n += __popc(m);
       }
+      seg += 128;
     }
     __syncwarp();
     cnt += n;
-    // pass 2: score the candidates inside the box
+    // step 2: score the candidates inside the box
     for (int t = lane; t < n; t += 32) {
-      const int i = scratch[t];
-      const float dx = __fsub_rn(x, xs[i]), dy = __fsub_rn(y, ys[i]);
+      const int pos = scratch[t];
+      const float dx = __fsub_rn(x, xs[pos]), dy = __fsub_rn(y, ys[pos]);
       const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));   // :134
       const float arg = __fdiv_rn(__fmul_rn(-0.5f, __fmul_rn(d, d)), sig2);          // :139
       const float e = exp_mode ? pp_expf(arg) : expf(arg);
-      const Cand c = {__fmul_rn(e, cs[i]), i};
-      if (cand_better(c, t1, method)) { t2 = t1; t1 = c; }
-      else if (cand_better(c, t2, method)) { t2 = c; }
+      const Cand2 c = {__fmul_rn(e, cs[pos]), oi[pos], pos};
+      const Cand ck = {c.s, c.i}, k1 = {t1.s, t1.i}, k2 = {t2.s, t2.i};
+      if (cand_better(ck, k1, method)) { t2 = t1; t1 = c; }
+      else if (cand_better(ck, k2, method)) { t2 = c; }
     }
     __syncwarp();
   }
-  Xysv out = {0.f, 0.f, 0.f, 0.f};
   if (cnt == 0) return out;                                       // :130-131
   // warp-wide top-2.  Scores are products of exp() and a confidence above the
   // threshold, i.e. non-negative and ordered like their bit patterns, so two
@@ -165,30 +207,36 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
     // ties: blend keeps the larger index (argsort), max the smaller (argmax)
     const int w1 = method == 1 ? __reduce_min_sync(full, k1 == m1 ? t1.i : 0x7fffffff)
                                : __reduce_max_sync(full, k1 == m1 ? t1.i : -1);
-    const Cand o = (t1.i == w1) ? t2 : t1;
+    const bool mine = t1.i == w1;
+    const int p1 = __shfl_sync(full, t1.pos, __ffs(__ballot_sync(full, mine)) - 1);
+    const Cand2 o = mine ? t2 : t1;
     const unsigned k2 = o.i >= 0 ? __float_as_uint(o.s) + 1u : 0u;
     const unsigned m2 = __reduce_max_sync(full, k2);
-    int w2 = -1;
-    if (m2 != 0u)
+    int w2 = -1, p2 = 0;
+    if (m2 != 0u) {
       w2 = method == 1 ? __reduce_min_sync(full, k2 == m2 ? o.i : 0x7fffffff)
                        : __reduce_max_sync(full, k2 == m2 ? o.i : -1);
-    t1.s = __uint_as_float(m1 - 1u); t1.i = w1;
-    t2.s = m2 ? __uint_as_float(m2 - 1u) : -INFINITY; t2.i = w2;
+      p2 = __shfl_sync(full, o.pos, __ffs(__ballot_sync(full, o.i == w2)) - 1);
+    }
+    t1.s = __uint_as_float(m1 - 1u); t1.i = w1; t1.pos = p1;
+    t2.s = m2 ? __uint_as_float(m2 - 1u) : -INFINITY; t2.i = w2; t2.pos = p2;
   } else {
 #pragma unroll 1
     for (int off = 16; off > 0; off >>= 1) {
-      Cand o1 = {__shfl_xor_sync(full, t1.s, off), __shfl_xor_sync(full, t1.i, off)};
-      Cand o2 = {__shfl_xor_sync(full, t2.s, off), __shfl_xor_sync(full, t2.i, off)};
-      Cand n1, n2;
-      if (cand_better(t1, o1, method)) { n1 = t1; n2 = cand_better(t2, o1, method) ? t2 : o1; }
-      else { n1 = o1; n2 = cand_better(t1, o2, method) ? t1 : o2; }
+      Cand2 o1 = {__shfl_xor_sync(full, t1.s, off), __shfl_xor_sync(full, t1.i, off),
+                  __shfl_xor_sync(full, t1.pos, off)};
+      Cand2 o2 = {__shfl_xor_sync(full, t2.s, off), __shfl_xor_sync(full, t2.i, off),
+                  __shfl_xor_sync(full, t2.pos, off)};
+      const Cand a1 = {t1.s, t1.i}, a2 = {t2.s, t2.i}, c1 = {o1.s, o1.i}, c2 = {o2.s, o2.i};
+      Cand2 n1, n2;
+      if (cand_better(a1, c1, method)) { n1 = t1; n2 = cand_better(a2, c1, method) ? t2 : o1; }
+      else { n1 = o1; n2 = cand_better(a1, c2, method) ? t1 : o2; }
       t1 = n1; t2 = n2;
     }
   }
-  const int r3 = packed ? 3 : 5, r4 = packed ? 4 : 6, r5 = packed ? 5 : 8;
-  const float *xt = base + (size_t)r3 * stride, *yt = base + (size_t)r4 * stride;
-  const float *st = base + (size_t)r5 * stride;
-  float x1 = xt[t1.i], y1 = yt[t1.i], s1 = st[t1.i];
+  const float *xt = base + 3 * (size_t)stride, *yt = base + 4 * (size_t)stride;
+  const float *st = base + 5 * (size_t)stride;
+  float x1 = xt[t1.pos], y1 = yt[t1.pos], s1 = st[t1.pos];
   if (method == 1) {                                              // _target_with_maxscore :147-155
     out.x = x1; out.y = y1; out.s = s1; out.v = t1.s;
     return out;
@@ -196,7 +244,7 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
   out.x = x1; out.y = y1; out.s = s1; out.v = __fmul_rn(t1.s, 0.5f);
   if (cnt == 1) return out;                                       // :164-170
   if (t2.s < 0.01f || t2.s < __fmul_rn(0.5f, t1.s)) return out;   // :178-179
-  float x2 = xt[t2.i], y2 = yt[t2.i], s2 = st[t2.i];
+  float x2 = xt[t2.pos], y2 = yt[t2.pos], s2 = st[t2.pos];
   float ddx = __fsub_rn(x1, x2), ddy = __fsub_rn(y1, y2);
   float d = __fsqrt_rn(__fadd_rn(__fmul_rn(ddx, ddx), __fmul_rn(ddy, ddy)));   // :182
   if (d > __fdiv_rn(s1, 2.0f)) return out;                        // :183-184
@@ -209,10 +257,12 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
 }
 
 struct CafLists {
-  const float *fwd, *bwd;   // (L,9,cap) of this image
+  const float *rows;        // (L, 2, kBinRows, cap) binned store of this image
+  const int *start;         // (L, 2, nb + 1)
+  BinGeo geo;
   int cap;
   const int *n;             // (2L) list lengths in shared memory: [2l] forward, [2l+1] backward
-  const float *stage;       // shared-memory copy of the six live rows of every list, or nullptr
+  const float *stage;       // shared-memory copy of the rows of every list (packed), or nullptr
   const int *stage_off;     // (2L) float offset of each list inside `stage`
 };
 
@@ -221,10 +271,11 @@ __device__ __forceinline__ Xysv scan_list(const CafLists &cf, int l, bool fw, fl
                                           int *scratch, int method, int exp_mode) {
   const int i = 2 * l + (fw ? 0 : 1);
   const int K = cf.n[i];
-  if (cf.stage) return warp_grow_connection(x, y, s, cf.stage + cf.stage_off[i], K, 1, K, scratch,
-                                            method, exp_mode);
-  return warp_grow_connection(x, y, s, (fw ? cf.fwd : cf.bwd) + (size_t)l * 9 * cf.cap, cf.cap, 0, K,
-                              scratch, method, exp_mode);
+  const int *start = cf.start + (size_t)i * (cf.geo.nb + 1);
+  if (cf.stage) return warp_grow_connection(x, y, s, cf.stage + cf.stage_off[i], K, K, start, cf.geo,
+                                            scratch, method, exp_mode);
+  return warp_grow_connection(x, y, s, cf.rows + (size_t)i * kBinRows * cf.cap, cf.cap, K, start,
+                              cf.geo, scratch, method, exp_mode);
 }
 
 // connection_value (cifcaf.py:194-217), warp-collective.
@@ -319,30 +370,29 @@ __device__ __forceinline__ uint32_t float_orderable(float v) {
 }
 
 // Load the list lengths of one image into shared memory and, when everything
-// fits into `stage_floats` of dynamic shared memory, copy the six live rows of
-// all 2L candidate lists there with cp.async (all copies in flight at once).
+// fits into `stage_floats` of dynamic shared memory, copy the rows of all 2L
+// binned lists there with cp.async (all copies in flight at once).
 // CTA-collective.  Returns the CafLists the growth code reads through.
-__device__ CafLists load_lists(AsmShared &sh, const float *fwd, const float *bwd, const int *nfwd,
-                               const int *nbwd, int L, int cap, float *stage, int stage_floats) {
+__device__ CafLists load_lists(AsmShared &sh, const float *rows, const int *start, BinGeo geo,
+                               const int *nfwd, const int *nbwd, int L, int cap, float *stage,
+                               int stage_floats) {
   const int tid = threadIdx.x;
   for (int i = tid; i < 2 * L; i += blockDim.x)
-    sh.list_n[i] = (i & 1) ? nbwd[i >> 1] : nfwd[i >> 1];
+    sh.list_n[i] = min((i & 1) ? nbwd[i >> 1] : nfwd[i >> 1], cap);
   __syncthreads();
   if (tid == 0) {
     int run = 0;
-    for (int i = 0; i < 2 * L; i++) { sh.list_off[i] = 6 * run; run += sh.list_n[i]; }
+    for (int i = 0; i < 2 * L; i++) { sh.list_off[i] = kBinRows * run; run += sh.list_n[i]; }
     sh.stage_total = run;
   }
   __syncthreads();
-  CafLists cf = {fwd, bwd, cap, sh.list_n, nullptr, sh.list_off};
-  if (stage == nullptr || 6 * sh.stage_total > stage_floats) return cf;
+  CafLists cf = {rows, start, geo, cap, sh.list_n, nullptr, sh.list_off};
+  if (stage == nullptr || kBinRows * sh.stage_total > stage_floats) return cf;
   const int warp = warp_id(), lane = lane_id(), nw = blockDim.x >> 5;
-  // one warp per (list, row); rows 0,1,2,5,6,8 of the (9, cap) block
-  for (int pr = warp; pr < 12 * L; pr += nw) {
-    const int i = pr / 6, r = pr - 6 * i;
-    const int row = r < 3 ? r : (r == 5 ? 8 : r + 2);
+  for (int pr = warp; pr < 2 * kBinRows * L; pr += nw) {      // one warp per (list, row)
+    const int i = pr / kBinRows, r = pr - kBinRows * i;
     const int K = sh.list_n[i];
-    const float *src = ((i & 1) ? bwd : fwd) + ((size_t)(i >> 1) * 9 + row) * cap;
+    const float *src = rows + ((size_t)i * kBinRows + r) * cap;
     float *dst = stage + sh.list_off[i] + r * K;
     for (int k = lane; k < K; k += 32) __pipeline_memcpy_async(dst + k, src + k, sizeof(float));
   }
@@ -528,16 +578,25 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
 #ifdef PP_ASM_TIMING
   if (threadIdx.x == 0) sh.tick = clock64();
 #endif
-  const CafLists cf = load_lists(sh, a.fwd + (size_t)b * a.L * 9 * a.caf_cap,
-                                 a.bwd + (size_t)b * a.L * 9 * a.caf_cap, a.nfwd + (size_t)b * a.L,
-                                 a.nbwd + (size_t)b * a.L, a.L, a.caf_cap, stage_buf, a.stage_floats);
+  const CafLists cf = load_lists(sh, a.rows + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
+                                 a.start + (size_t)b * a.L * 2 * (a.geo.nb + 1), a.geo,
+                                 a.nfwd + (size_t)b * a.L, a.nbwd + (size_t)b * a.L, a.L, a.caf_cap,
+                                 stage_buf, a.stage_floats);
   // Occupancy(cifhr.accumulated.shape, 2, min_scale=4): cifcaf.py:84, occupancy.py:21-25
   const long long oh = (long long)((double)a.hh / 2.0), ow = (long long)((double)a.hw / 2.0);
   float *pre_data = a.pre_data + (size_t)b * a.ann_cap * F * 3;
   float *pre_scales = a.pre_scales + (size_t)b * a.ann_cap * F;
   int *pre_order = a.pre_order ? a.pre_order + (size_t)b * a.ann_cap * F * 2 : nullptr;
 
-  for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) occ[i] = 0;
+  // every seed's Occupancy.get cell is fixed: compute it once (occupancy.py:41-47)
+  int2 *rec = a.occ_rec + (size_t)b * a.seed_cap;
+  for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) {
+    const float *sd = seeds + (size_t)i * 5;
+    long long cx, cy;
+    occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
+    rec[i] = make_int2((int)cx, (int)cy | ((int)__ldg(sd + 1) << 24));
+    occ[i] = 0;
+  }
   __syncthreads();
 
   // initial_annotations (cifcaf.py:95-98) are grown first, then the seeds
@@ -606,14 +665,27 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
     n_ann++;
     __syncthreads();
     PP_TICK(5);
-    for (int i = cursor + threadIdx.x; i < n_seeds; i += blockDim.x) {
-      const float *sd = seeds + (size_t)i * 5;
-      int f = (int)__ldg(sd + 1);
-      if (!sh.box_valid[f]) continue;
-      long long cx, cy;
-      occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
-      if (cx >= sh.box[f][0] && cx < sh.box[f][1] && cy >= sh.box[f][2] && cy < sh.box[f][3])
-        occ[i] = (uint8_t)(occ[i] + 1);                           // uint8 += 1 wraps (utils.py:66)
+    // Occupancy.set of the pose's joints, seen from the seeds: four seeds per thread and
+    // trip so that four loads are in flight
+    for (int i0 = cursor + threadIdx.x; i0 < n_seeds; i0 += 4 * blockDim.x) {
+      int2 r[4];
+      uint8_t c[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int i = i0 + j * blockDim.x;
+        r[j] = i < n_seeds ? rec[i] : make_int2(0, 0);
+        c[j] = i < n_seeds ? occ[i] : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int i = i0 + j * blockDim.x;
+        if (i >= n_seeds) continue;
+        const int f = r[j].y >> 24;
+        if (!sh.box_valid[f]) continue;
+        const long long cx = r[j].x, cy = r[j].y & 0xffffff;
+        if (cx >= sh.box[f][0] && cx < sh.box[f][1] && cy >= sh.box[f][2] && cy < sh.box[f][3])
+          occ[i] = (uint8_t)(c[j] + 1);                           // uint8 += 1 wraps (utils.py:66)
+      }
     }
     __syncthreads();
     PP_TICK(6);
@@ -669,7 +741,7 @@ __device__ void flood_fill(AsmShared &sh, const Graph &g) {
 }
 
 __global__ void __launch_bounds__(kAsmThreads)
-complete_kernel(AsmArgs a, const float *__restrict__ fwd2, const float *__restrict__ bwd2,
+complete_kernel(AsmArgs a, const float *__restrict__ rows2, const int *__restrict__ start2,
                 const int *__restrict__ nfwd2, const int *__restrict__ nbwd2,
                 float *__restrict__ cmp_data, float *__restrict__ cmp_scales, Graph g, CScale cscale,
                 pp_params p) {
@@ -679,9 +751,10 @@ complete_kernel(AsmArgs a, const float *__restrict__ fwd2, const float *__restri
   const int F = g.F;
   if (an >= min(a.n_pre[b], a.ann_cap)) return;
   // the score_th = 1e-4 lists hold nearly every cell: read them in place
-  const CafLists cf = load_lists(sh, fwd2 + (size_t)b * a.L * 9 * a.caf_cap,
-                                 bwd2 + (size_t)b * a.L * 9 * a.caf_cap, nfwd2 + (size_t)b * a.L,
-                                 nbwd2 + (size_t)b * a.L, a.L, a.caf_cap, nullptr, 0);
+  const CafLists cf = load_lists(sh, rows2 + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
+                                 start2 + (size_t)b * a.L * 2 * (a.geo.nb + 1), a.geo,
+                                 nfwd2 + (size_t)b * a.L, nbwd2 + (size_t)b * a.L, a.L, a.caf_cap,
+                                 nullptr, 0);
   float *pre_data = a.pre_data + ((size_t)b * a.ann_cap + an) * F * 3;
   float *pre_scales = a.pre_scales + ((size_t)b * a.ann_cap + an) * F;
   int *pre_order = a.pre_order + ((size_t)b * a.ann_cap + an) * F * 2;
@@ -725,7 +798,7 @@ complete_kernel(AsmArgs a, const float *__restrict__ fwd2, const float *__restri
   for (int i = threadIdx.x; i < F; i += blockDim.x) os[i] = sh.js[i];
 }
 
-int complete_launch(const AsmArgs &args, const float *fwd2, const float *bwd2, const int *nfwd2,
+int complete_launch(const AsmArgs &args, const float *rows2, const int *start2, const int *nfwd2,
                     const int *nbwd2, float *cmp_data, float *cmp_scales, const pp_skeleton &sk,
                     int B, int F, const pp_params &p, cudaStream_t st) {
   Graph g;
@@ -736,7 +809,7 @@ int complete_launch(const AsmArgs &args, const float *fwd2, const float *bwd2, c
   cs.has = sk.has_confidence_scales;
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
   dim3 grid(args.ann_cap, B);
-  complete_kernel<<<grid, kAsmThreads, 0, st>>>(args, fwd2, bwd2, nfwd2, nbwd2, cmp_data, cmp_scales,
+  complete_kernel<<<grid, kAsmThreads, 0, st>>>(args, rows2, start2, nfwd2, nbwd2, cmp_data, cmp_scales,
                                                g, cs, p);
   PP_LAUNCH_CHECK("complete_kernel");
   return PP_OK;

@@ -111,6 +111,107 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
   }
 }
 
+// ---------------------------------------------------------------------------
+// Spatial binning of the candidate lists for the assembly scans.
+//
+// _grow_connection only wants the candidates whose source end lies in a box
+// around the joint (caf_center_s, functional.pyx:346-353); crowded scenes have
+// >1000 candidates per link.  One CTA per (image, link, direction) counting-sorts
+// the list by the bin of (x_source, y_source).  Order inside a bin is arbitrary:
+// the assembly breaks score ties on the ORIGINAL list index, which is kept as
+// the seventh row, so results do not depend on it.
+
+BinGeo bin_geo(const pp_shape &s) {
+  BinGeo g;
+  g.bshift = 5;
+  for (;;) {
+    g.nbx = (hr_w(s) >> g.bshift) + 1;
+    g.nby = (hr_h(s) >> g.bshift) + 1;
+    if ((long long)g.nbx * g.nby + 1 <= kMaxBins) break;
+    g.bshift++;
+  }
+  g.nb = g.nbx * g.nby + 1;
+  return g;
+}
+
+size_t binned_rows_bytes(const pp_shape &s, const pp_caps &c) {
+  return (size_t)s.B * s.L * 2 * kBinRows * c.caf_cap * sizeof(float);
+}
+size_t binned_start_bytes(const pp_shape &s) {
+  return (size_t)s.B * s.L * 2 * (bin_geo(s).nb + 1) * sizeof(int);
+}
+
+__device__ __forceinline__ int bin_coord(float v, float inv, int n) {
+  return (int)fminf(fmaxf(__fmul_rn(v, inv), 0.0f), (float)(n - 1));   // monotonic, clamped
+}
+
+__device__ __forceinline__ int bin_of(float x, float y, const BinGeo &g, float inv) {
+  if (x != x || y != y) return g.nb - 1;          // NaN passes every box test: "always" bin
+  return bin_coord(y, inv, g.nby) * g.nbx + bin_coord(x, inv, g.nbx);
+}
+
+__global__ void __launch_bounds__(kCafThreads)
+caf_bin_kernel(const float *__restrict__ fwd, const int *__restrict__ nfwd,
+               const float *__restrict__ bwd, const int *__restrict__ nbwd, float *__restrict__ rows,
+               int *__restrict__ start, int cap, BinGeo g) {
+  __shared__ int hist[kMaxBins];
+  __shared__ int warp_sum[kCafThreads / 32];
+  const int bl = blockIdx.x >> 1, dir = blockIdx.x & 1;
+  const int K = min(dir ? nbwd[bl] : nfwd[bl], cap);
+  const float *src = (dir ? bwd : fwd) + (size_t)bl * 9 * cap;
+  float *dst = rows + (size_t)blockIdx.x * kBinRows * cap;
+  int *st = start + (size_t)blockIdx.x * (g.nb + 1);
+  const float inv = 1.0f / (float)(1 << g.bshift);
+  const int tid = threadIdx.x;
+  for (int i = tid; i < g.nb; i += kCafThreads) hist[i] = 0;
+  __syncthreads();
+  for (int k = tid; k < K; k += kCafThreads)
+    atomicAdd(&hist[bin_of(src[(size_t)cap + k], src[2 * (size_t)cap + k], g, inv)], 1);
+  __syncthreads();
+  // exclusive scan of hist[0..nb): each thread owns a run of consecutive bins
+  const int per = (g.nb + kCafThreads - 1) / kCafThreads;
+  const int b0 = tid * per, b1 = min(b0 + per, g.nb);
+  int local = 0;
+  for (int i = b0; i < b1; i++) local += hist[i];
+  int incl = local;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    int v = __shfl_up_sync(0xffffffffu, incl, off);
+    if ((tid & 31) >= off) incl += v;
+  }
+  if ((tid & 31) == 31) warp_sum[tid >> 5] = incl;
+  __syncthreads();
+  int base = incl - local;
+  for (int w = 0; w < (tid >> 5); w++) base += warp_sum[w];
+  for (int i = b0; i < b1; i++) {
+    int h = hist[i];
+    hist[i] = base;      // becomes the running insert cursor of the bin
+    st[i] = base;
+    base += h;
+  }
+  if (tid == 0) st[g.nb] = K;
+  __syncthreads();
+  for (int k = tid; k < K; k += kCafThreads) {
+    const float xs = src[(size_t)cap + k], ys = src[2 * (size_t)cap + k];
+    const int pos = atomicAdd(&hist[bin_of(xs, ys, g, inv)], 1);
+    dst[pos] = src[k];
+    dst[(size_t)cap + pos] = xs;
+    dst[2 * (size_t)cap + pos] = ys;
+    dst[3 * (size_t)cap + pos] = src[5 * (size_t)cap + k];
+    dst[4 * (size_t)cap + pos] = src[6 * (size_t)cap + k];
+    dst[5 * (size_t)cap + pos] = src[8 * (size_t)cap + k];
+    dst[6 * (size_t)cap + pos] = __int_as_float(k);
+  }
+}
+
+int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, const int *d_nbwd,
+                   float *d_rows, int *d_start, const pp_shape &s, const pp_caps &c, cudaStream_t st) {
+  caf_bin_kernel<<<s.B * s.L * 2, kCafThreads, 0, st>>>(d_fwd, d_nfwd, d_bwd, d_nbwd, d_rows, d_start,
+                                                       c.caf_cap, bin_geo(s));
+  PP_LAUNCH_CHECK("caf_bin_kernel");
+  return PP_OK;
+}
+
 int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                       float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {

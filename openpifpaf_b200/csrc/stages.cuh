@@ -14,12 +14,32 @@ int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n
 int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                       float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st);
+// Candidate lists re-ordered by spatial bin of their source end, for the assembly
+// scans (caf_scored.cu: caf_bin_kernel).  Per (image, link, direction): seven rows
+// (score, source x/y, target x/y/scale, original list index) of `cap` columns, and
+// the start column of every bin (bins row-major, plus one last bin for NaN sources).
+struct BinGeo {
+  int bshift;      // bin edge = 1 << bshift hr pixels
+  int nbx, nby;
+  int nb;          // nbx * nby + 1
+};
+constexpr int kBinRows = 7;
+constexpr int kMaxBins = 2048;
+BinGeo bin_geo(const pp_shape &s);
+size_t binned_rows_bytes(const pp_shape &s, const pp_caps &c);    // one (fwd + bwd) store
+size_t binned_start_bytes(const pp_shape &s);
+int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, const int *d_nbwd,
+                   float *d_rows, int *d_start, const pp_shape &s, const pp_caps &c, cudaStream_t st);
+
 struct AsmArgs {
   const float *seeds;
   const int *n_seeds;
-  const float *fwd, *bwd;
+  const float *rows;        // (B, L, 2, kBinRows, caf_cap) binned candidate store
+  const int *start;         // (B, L, 2, nb + 1)
+  BinGeo geo;
   const int *nfwd, *nbwd;
-  uint8_t *occ_cnt;
+  uint8_t *occ_cnt;         // (B, seed_cap) Occupancy.get() counters, one per seed
+  int2 *occ_rec;            // (B, seed_cap) the seed's occupancy cell: x = cell x, y = cell y | field << 24
   float *pre_data;
   float *pre_scales;
   int *pre_order;
@@ -34,7 +54,7 @@ struct AsmArgs {
 };
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st);
-int complete_launch(const AsmArgs &args, const float *fwd2, const float *bwd2, const int *nfwd2,
+int complete_launch(const AsmArgs &args, const float *rows2, const int *start2, const int *nfwd2,
                     const int *nbwd2, float *cmp_data, float *cmp_scales, const pp_skeleton &sk,
                     int B, int F, const pp_params &p, cudaStream_t st);
 size_t nms_ws_bytes(const pp_shape &s, const pp_caps &c);

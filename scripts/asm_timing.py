@@ -6,7 +6,9 @@ import bench
 from openpifpaf_b200 import _lib, decoder
 from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
 bench.configure_profile(decoder)
-cif, caf, skel = bench.make_batch('coco17_641_5p', 64)
+WL = sys.argv[1] if len(sys.argv) > 1 else 'coco17_641_5p'
+NB = bench.WORKLOADS[WL][2]
+cif, caf, skel = bench.make_batch(WL, NB)
 dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=skel)
 eng, params = dec.engine(), dec.params()
 d_cif, d_caf = torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda()
@@ -21,5 +23,5 @@ _lib.lib().pp_debug_asm_cycles(out, 1)
 names = ['setup', 'seed_search', 'init_ann', 'grow_eval', 'grow_select', 'store_boxes', 'occ_update', 'grow_init']
 tot = sum(out)
 for n, v in zip(names, out):
-    print('%-12s %8.1f us/image  %5.1f%%' % (n, v / N / 64 / 1965.0, 100.0 * v / tot))
-print('total %.1f us/image' % (tot / N / 64 / 1965.0))
+    print('%-12s %8.1f us/image  %5.1f%%' % (n, v / N / NB / 1965.0, 100.0 * v / tot))
+print('total %.1f us/image' % (tot / N / NB / 1965.0))
