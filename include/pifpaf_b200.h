@@ -76,6 +76,27 @@ typedef struct pp_initial {
   int32_t cap;
 } pp_initial;
 
+/* Per-image preprocessing record for annotations_inverse (transforms/preprocess.py:35-82):
+ * the decoded coordinates are mapped back to the original image.  The host fills this from
+ * the reference's meta dict; trigonometry is done on the host (math.cos / math.sin of
+ * -meta['rotation']['angle'] degrees, then rounded to float32 like numpy does for a Python
+ * scalar against a float32 array). */
+typedef struct pp_image_meta {
+  double offset_x, offset_y;  /* meta['offset']                                  */
+  double scale_x, scale_y;    /* meta['scale']                                   */
+  double flip_w1;             /* meta['width_height'][0] - 1 (used when hflip)   */
+  float rot_cos, rot_sin;     /* of -angle                                       */
+  float rot_cx, rot_cy;       /* (rotation width - 1) / 2, (height - 1) / 2      */
+  int32_t rotate;             /* angle != 0                                      */
+  int32_t hflip;              /* meta['hflip']                                   */
+} pp_image_meta;
+
+typedef struct pp_inverse {
+  const pp_image_meta *meta;    /* (B) device array                                            */
+  const int32_t *hflip_target;  /* (F) device: row j moves to row hflip_target[j] when hflip;
+                                   a permutation (meta['horizontal_swap']), or NULL = no swap */
+} pp_inverse;
+
 /* Decoder knobs; same meaning and defaults-by-configuration as the reference's
  * class attributes (decoder/factory.py:74-92). */
 typedef struct pp_params {
@@ -100,6 +121,7 @@ typedef struct pp_params {
   uint32_t seed_mask;            /* FieldConfig.seed_mask as bits (0 = all fields seed) */
   struct pp_profile *profile;    /* optional per-stage CUDA-event timer (NULL = off)    */
   const pp_initial *initial;     /* optional initial annotations (NULL = none)          */
+  const pp_inverse *inverse;     /* optional annotations_inverse after the NMS (NULL = none) */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
@@ -191,6 +213,31 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
 int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
                     int32_t *d_source, void *d_ws, size_t ws_bytes, const pp_shape *s,
                     const pp_caps *c, const pp_params *p, void *stream);
+
+/* Inference epilogue of a fused head network + field collection, one pass:
+ * PixelShuffle(2) and crop (quad = 1), sigmoid on confidences, exp on scales,
+ * absolute coordinates (regression + cell index) and the decoder's channel order.
+ * Replaces the tail of CompositeFieldFused.forward (network/heads.py:406-448) and
+ * CifCafCollector.forward (network/heads.py:65-88).
+ *   d_x   (B, n_fields * (1 + 4 * n_vectors) * (quad ? 4 : 1), h, w) raw convolution output
+ *   d_out (B, n_fields, 1 + 4 * n_vectors, H, W), H = quad ? 2h-1 : h, W likewise
+ * n_vectors = 1 gives a cif field, 2 a caf field. */
+int pp_head_epilogue(const float *d_x, float *d_out, int32_t B, int32_t n_fields, int32_t n_vectors,
+                     int32_t h, int32_t w, int32_t quad, void *stream);
+
+/* sizeof of the ABI structs, for bindings to check their mirrors:
+ * which = 0 pp_params, 1 pp_image_meta, 2 pp_outputs, 3 pp_skeleton, 4 pp_shape, 5 pp_caps. */
+int32_t pp_sizeof(int32_t which);
+
+/* Preprocess.annotations_inverse (transforms/preprocess.py:35-82) for a whole batch, in place on
+ * the decoder's result buffers: rotation (float32), offset and scale (float64, rounded to
+ * float32 after each step, as numpy's in-place operators do), joint_scales / scale_x, hflip with
+ * the horizontal keypoint swap.  d_pre_data (may be NULL) holds the as-grown rows that
+ * decoding_order is rebuilt from; like the reference's decoding_order entries they get offset
+ * and scale only. */
+int pp_annotations_inverse(float *d_ann_data, float *d_ann_scales, const int32_t *d_n_ann,
+                           float *d_pre_data, const int32_t *d_n_pre, const pp_inverse *inv,
+                           int32_t B, int32_t F, int32_t ann_cap, void *stream);
 
 /* ---- fused drivers ------------------------------------------------------- */
 

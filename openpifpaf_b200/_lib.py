@@ -28,6 +28,18 @@ class Initial(C.Structure):
     _fields_ = [('data', C.c_void_p), ('scales', C.c_void_p), ('n', C.c_void_p), ('cap', C.c_int32)]
 
 
+class ImageMeta(C.Structure):
+    _fields_ = [('offset_x', C.c_double), ('offset_y', C.c_double),
+                ('scale_x', C.c_double), ('scale_y', C.c_double), ('flip_w1', C.c_double),
+                ('rot_cos', C.c_float), ('rot_sin', C.c_float),
+                ('rot_cx', C.c_float), ('rot_cy', C.c_float),
+                ('rotate', C.c_int32), ('hflip', C.c_int32)]
+
+
+class Inverse(C.Structure):
+    _fields_ = [('meta', C.c_void_p), ('hflip_target', C.c_void_p)]
+
+
 class Params(C.Structure):
     _fields_ = [
         ('nms_instance_threshold', C.c_double),
@@ -40,6 +52,7 @@ class Params(C.Structure):
         ('connection_method', C.c_int32), ('greedy', C.c_int32),
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
         ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
+        ('inverse', C.POINTER(Inverse)),
     ]
 
 
@@ -117,6 +130,10 @@ def lib():
     l.pp_coco_skeleton.argtypes = [P(Skeleton)]
     l.pp_workspace_bytes.restype = sz
     l.pp_workspace_bytes.argtypes = [P(Shape), P(Caps)]
+    l.pp_sizeof.argtypes = [i32]
+    l.pp_sizeof.restype = i32
+    l.pp_annotations_inverse.argtypes = [vp, vp, vp, vp, vp, C.POINTER(Inverse), i32, i32, i32, vp]
+    l.pp_head_epilogue.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, vp]
     l.pp_cifhr_accumulate.argtypes = [vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp, vp]
     l.pp_cif_seeds.argtypes = [vp, vp, vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp, vp]
     l.pp_caf_scored.argtypes = [vp, vp, P(Skeleton), f32, vp, vp, vp, vp, P(Shape), P(Caps),
@@ -142,6 +159,10 @@ def lib():
     l.pp_scalar_nonzero_clipped_with_reduction.argtypes = [vp, i32, i32, f32, f32, f32, vp, vp]
     l.pp_scalar_square_add_single.argtypes = [vp, i32, i32, C.c_longlong, C.c_longlong,
                                               C.c_longlong, i32, vp]
+    for which, mirror in enumerate((Params, ImageMeta, Outputs, Skeleton, Shape, Caps)):
+        if l.pp_sizeof(which) != C.sizeof(mirror):
+            raise ImportError('ctypes mirror %s (%d bytes) does not match the library (%d): rebuild' % (
+                mirror.__name__, C.sizeof(mirror), l.pp_sizeof(which)))
     _lib = l
     return l
 
@@ -150,7 +171,7 @@ EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
     'pp_stage_name', 'pp_decode_launch_count',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
-    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_cifhr_accumulate', 'pp_cif_seeds',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
     'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',

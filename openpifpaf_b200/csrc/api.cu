@@ -226,6 +226,32 @@ size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c) {
   return layout(nullptr, *s, *c, true).total;
 }
 
+int32_t pp_sizeof(int32_t which) {
+  switch (which) {
+    case 0: return (int32_t)sizeof(pp_params);
+    case 1: return (int32_t)sizeof(pp_image_meta);
+    case 2: return (int32_t)sizeof(pp_outputs);
+    case 3: return (int32_t)sizeof(pp_skeleton);
+    case 4: return (int32_t)sizeof(pp_shape);
+    case 5: return (int32_t)sizeof(pp_caps);
+    default: return -1;
+  }
+}
+
+int pp_annotations_inverse(float *d_ann_data, float *d_ann_scales, const int32_t *d_n_ann,
+                           float *d_pre_data, const int32_t *d_n_pre, const pp_inverse *inv,
+                           int32_t B, int32_t F, int32_t ann_cap, void *stream) {
+  if (!d_ann_data || !d_ann_scales || !d_n_ann || !inv || (d_pre_data && !d_n_pre)) return PP_ERR_ARG;
+  return annotations_inverse_launch(d_ann_data, d_ann_scales, d_n_ann, d_pre_data, d_n_pre, *inv, B, F,
+                                    ann_cap, (cudaStream_t)stream);
+}
+
+int pp_head_epilogue(const float *d_x, float *d_out, int32_t B, int32_t n_fields, int32_t n_vectors,
+                     int32_t h, int32_t w, int32_t quad, void *stream) {
+  if (!d_x || !d_out) return PP_ERR_ARG;
+  return head_epilogue_launch(d_x, d_out, B, n_fields, n_vectors, h, w, quad != 0, (cudaStream_t)stream);
+}
+
 int pp_cifhr_accumulate(const float *d_cif, float *d_hr, void *d_ws, size_t ws_bytes,
                         const pp_shape *s, const pp_caps *c, const pp_params *p,
                         int32_t *d_status, void *stream) {
@@ -405,6 +431,9 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   }
   rc = nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
                   o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  if (!rc && p->inverse)      // optional Preprocess.annotations_inverse on the results (inside the nms stage time)
+    rc = annotations_inverse_launch(o->ann_data, o->ann_scales, o->n_ann, a.pre_data, a.n_pre, *p->inverse,
+                                    s->B, s->F, c->ann_cap, st);
   prof_end_step(p->profile, st);
   return rc;
 }
@@ -576,6 +605,12 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
       ini_sub.scales += b0 * (size_t)ini_sub.cap * s->F;
       ini_sub.n += b0;
       p_sub.initial = &ini_sub;
+    }
+    pp_inverse inv_sub;
+    if (p->inverse) {          // and of the per-image preprocessing records
+      inv_sub = *p->inverse;
+      inv_sub.meta += b0;
+      p_sub.inverse = &inv_sub;
     }
     int rc = pp_decode_batch(d_cif + b0 * cif_img, d_caf + b0 * caf_img, sk, &d_sub, d_ws, ws_bytes,
                              &sub, c, &p_sub, stream);

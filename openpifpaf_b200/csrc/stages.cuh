@@ -63,5 +63,10 @@ int nms_launch(const float *in_data, const float *in_scales, const int *n_in, fl
                float *out_scales, double *out_score, int *out_source, int *n_out, void *d_ws,
                const pp_shape &s, const pp_caps &c, const pp_params &p, cudaStream_t st);
 
+int annotations_inverse_launch(float *ann_data, float *ann_scales, const int *n_ann, float *pre_data,
+                               const int *n_pre, const pp_inverse &inv, int B, int F, int ann_cap,
+                               cudaStream_t st);
+int head_epilogue_launch(const float *d_x, float *d_out, int B, int nf, int nv, int h, int w, int quad,
+                         cudaStream_t st);
 
 }  // namespace pp

@@ -69,3 +69,11 @@ COCO_UPRIGHT_POSE = np.array([
     (-1.4, 2.0, 2.0), (1.4, 2.1, 2.0),
     (-1.4, 0.0, 2.0), (1.4, 0.1, 2.0),
 ])
+
+# left <-> right keypoint names under a horizontal flip (reference datasets/constants.py:86-103)
+HFLIP = {}
+for _name in COCO_KEYPOINTS:
+    if _name.startswith('left_'):
+        HFLIP[_name] = 'right_' + _name[len('left_'):]
+    elif _name.startswith('right_'):
+        HFLIP[_name] = 'left_' + _name[len('right_'):]

@@ -36,6 +36,9 @@ class DecoderParams:
     profile: Optional[int] = None      # pp_profile* from StageProfile (bench/profiling only)
     # initial annotations: (data (B, cap, F, 3), scales (B, cap, F), n (B,) int32) CUDA tensors
     initial: Optional[tuple] = None
+    # annotations_inverse: (meta (B, sizeof pp_image_meta) uint8 CUDA tensor, hflip_target (F,) int32
+    # CUDA tensor or None), see transforms.preprocess.pack_metas
+    inverse: Optional[tuple] = None
 
     def to_c(self):
         p = _lib.Params()
@@ -78,6 +81,14 @@ class DecoderParams:
             ini = _lib.Initial(data.data_ptr(), scales.data_ptr(), n.data_ptr(), data.shape[1])
             p._initial_struct = ini          # keep the struct alive as long as the params
             p.initial = C.pointer(ini)
+        if self.inverse is not None:
+            meta, target = self.inverse
+            assert meta.is_cuda and meta.dtype == torch.uint8 and meta.is_contiguous()
+            assert meta.shape[1] == C.sizeof(_lib.ImageMeta)
+            assert target is None or (target.is_cuda and target.dtype == torch.int32)
+            inv = _lib.Inverse(meta.data_ptr(), target.data_ptr() if target is not None else None)
+            p._inverse_struct = inv
+            p.inverse = C.pointer(inv)
         return p
 
 

@@ -40,7 +40,8 @@ class CifCaf(Generator):
     keypoint_threshold = 0.0
     deterministic_exp = True    # exp() of include/pifpaf_detmath.h (bit-reproducible)
     max_annotations = 256       # per-image capacity of the result buffers
-    host_chunk = 16             # images per pipeline chunk when the fields come from the host
+    host_chunk = 16               # images per pipeline chunk when the fields come from the host
+    head_collector = None         # network.CifCafCollector when the model emits raw head outputs
 
     def __init__(self, field_config: FieldConfig, *,
                  keypoints,
@@ -157,11 +158,14 @@ class CifCaf(Generator):
         return (torch.from_numpy(data).to(device), torch.from_numpy(scales).to(device),
                 torch.from_numpy(n).to(device))
 
-    def decode_batch(self, cif, caf, initial_annotations=None):
+    def decode_batch(self, cif, caf, initial_annotations=None, metas=None):
         """Decode a batch. ``cif (B,F,5,H,W)``, ``caf (B,L,9,H,W)`` float32.
         ``initial_annotations``: optional list (per image) of lists of Annotation that are
         grown and marked occupied before the seeds (cifcaf.py:95-98); like the reference,
         those objects are updated in place and returned in the result lists.
+        ``metas``: optional list (per image) of the reference's preprocessing meta dicts;
+        when given, ``Preprocess.annotations_inverse`` (transforms/preprocess.py:35-82) is
+        applied on the device and the annotations come back in original-image coordinates.
 
         CUDA tensors are decoded in place on their device; host arrays (numpy or
         CPU tensors, ideally pinned) go through ``pp_decode_batch_host``, which
@@ -179,6 +183,13 @@ class CifCaf(Generator):
                                   else caf).to(device)
         if has_initial:
             params.initial = self._initial_tensors(initial_annotations, cif.device)
+        if metas is not None:
+            from ...transforms.preprocess import hflip_target, pack_metas
+            if len(metas) != len(cif):
+                raise ValueError('one meta dict per image')
+            device = cif.device if isinstance(cif, torch.Tensor) and cif.is_cuda else eng._device()
+            params.inverse = (pack_metas(metas, device),
+                              hflip_target(metas, len(self.keypoints), device))
         if isinstance(cif, torch.Tensor) and cif.is_cuda:
             buf = eng.run_device(cif, caf, params)
             n_ann = buf.dev['n_ann'].cpu().numpy()         # synchronises the stream
@@ -224,8 +235,14 @@ class CifCaf(Generator):
                     anns[r] = orig
 
     def decode_heads(self, heads):
+        """Head tensors of a batch -> annotations.  With ``head_collector`` set (a
+        ``network.CifCafCollector``) the heads are the raw convolution outputs of the fused head
+        networks and the epilogue (heads.py:65-88,406-448) runs on the device first."""
         cfg = self.field_config
-        return self.decode_batch(heads[cfg.cif_indices[0]], heads[cfg.caf_indices[0]])
+        cif, caf = heads[cfg.cif_indices[0]], heads[cfg.caf_indices[0]]
+        if self.head_collector is not None:
+            cif, caf = self.head_collector(cif, caf)
+        return self.decode_batch(cif, caf)
 
     def __call__(self, fields, initial_annotations=None):
         start = time.perf_counter()

@@ -85,8 +85,22 @@ def configured_decoder():
 # golden fixtures (tests/golden/*.npz, written by oracle/gen_golden.py from the reference)
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
-GOLDEN_NAMES = sorted(n[:-4] for n in os.listdir(GOLDEN_DIR) if n.endswith('.npz')) \
+_ALL_GOLDEN = sorted(n[:-4] for n in os.listdir(GOLDEN_DIR) if n.endswith('.npz')) \
     if os.path.isdir(GOLDEN_DIR) else []
+GOLDEN_NAMES = [n for n in _ALL_GOLDEN if not n.startswith(('head_', 'inverse_'))]   # decoder cases
+HEAD_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('head_')]       # head epilogue cases
+TOL_HEAD_REL = 2e-6  # sigmoid / exp of the head epilogue against torch's CPU kernels
+
+
+def head_golden(name):
+    """(x_cif, x_caf, cif, caf) of a head-epilogue fixture; raw inputs regenerated and hash-checked."""
+    import hashlib
+    from oracle.gen_golden_heads import raw_head_outputs
+    g = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    x_cif, x_caf = raw_head_outputs(int(g['batch']), int(g['h']), int(g['w']), int(g['seed']))
+    assert hashlib.sha256(x_cif.tobytes()).hexdigest() == str(g['x_cif_sha256'])
+    assert hashlib.sha256(x_caf.tobytes()).hexdigest() == str(g['x_caf_sha256'])
+    return x_cif, x_caf, g['cif'], g['caf']
 
 # north_star tolerances against the reference
 TOL_XY = 1e-3       # px
@@ -171,3 +185,27 @@ def golden(name):
     if name not in _GOLDEN_CACHE:
         _GOLDEN_CACHE[name] = Golden(name)
     return _GOLDEN_CACHE[name]
+
+
+def inverse_inputs():
+    """Annotations of the golden case mid_321x481_8p as packed arrays + the flip permutation:
+    (data, joint_scales, decoding (s, e) lists, decoding xy rows, hflip target)."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, HFLIP
+    g = np.load(os.path.join(GOLDEN_DIR, 'mid_321x481_8p.npz'))
+    data, js = g['ann_data'], g['ann_scales']
+    orders = [[(int(s), int(e)) for s, e in o if s >= 0] for o in g['ann_order']]
+    dxy = np.array([d[j][:2] for d, o in zip(data, orders) for s, e in o for j in (s, e)], np.float32)
+    target = np.array([COCO_KEYPOINTS.index(HFLIP.get(k, k)) for k in COCO_KEYPOINTS], np.int32)
+    return data, js, orders, dxy, target
+
+
+class HorizontalSwap:
+    """Stand-in for the reference's hflip._HorizontalSwap (rows move to their mirrored joint)."""
+
+    def __init__(self, target):
+        self.target = np.asarray(target)
+
+    def __call__(self, keypoints):
+        out = np.zeros(keypoints.shape)
+        out[self.target] = keypoints
+        return out

@@ -9,7 +9,7 @@ for bit is numpy's SIMD float32 exp, cifcaf.py:139).
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_NAMES, golden, sha256
+from conftest import GOLDEN_NAMES, HEAD_GOLDEN_NAMES, TOL_HEAD_REL, golden, head_golden, sha256
 
 
 def pad_order(orders, F):
@@ -53,3 +53,32 @@ def test_oracle_matches_reference_golden(oracle, name, exp_mode):
 def test_golden_covers_the_configs():
     assert {'c1_641_5p', 'crowd_1281_50p', 'dense_321_4p', 'empty_161', 'mid_force_complete',
             'mid_greedy', 'mid_max'} <= set(GOLDEN_NAMES)
+
+
+@pytest.mark.parametrize('name', HEAD_GOLDEN_NAMES)
+def test_head_oracle_matches_reference_golden(name):
+    """oracle/head_oracle.py against the reference's CompositeFieldFused (eval) + CifCafCollector."""
+    from oracle.head_oracle import head_epilogue
+    x_cif, x_caf, cif, caf = head_golden(name)
+    for x, want, nf, nv in ((x_cif, cif, 17, 1), (x_caf, caf, 19, 2)):
+        got = head_epilogue(x, nf, nv, quad=1)
+        assert got.shape == want.shape
+        exact = [c for c in range(want.shape[2]) if c % 4 in (1, 2, 3)]      # x, y, logb rows: adds / copies
+        assert np.array_equal(got[:, :, exact], want[:, :, exact])
+        np.testing.assert_allclose(got, want, rtol=TOL_HEAD_REL, atol=0)
+
+
+@pytest.mark.parametrize('kind', ['plain', 'scaled', 'flipped', 'rotated'])
+def test_inverse_oracle_matches_reference_golden(kind):
+    """oracle/inverse_oracle.py against the reference's Preprocess.annotations_inverse outputs."""
+    from conftest import GOLDEN_DIR, HorizontalSwap, inverse_inputs
+    from oracle.gen_golden_inverse import make_meta
+    from oracle.inverse_oracle import annotations_inverse
+    import os
+    g = np.load(os.path.join(GOLDEN_DIR, 'inverse_mid.npz'))
+    data, js, _, dxy, target = inverse_inputs()
+    meta = make_meta(kind, HorizontalSwap(target))
+    got = annotations_inverse(data, js, dxy, meta, target if meta['hflip'] else None)
+    assert np.array_equal(got[0], g[kind + '_data'])
+    assert np.array_equal(got[1], g[kind + '_scales'])
+    assert np.array_equal(got[2], g[kind + '_dxy'])

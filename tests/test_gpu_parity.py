@@ -359,3 +359,172 @@ def test_initial_annotations(oracle, coco_skeleton, configured_decoder):
             assert np.array_equal(ann.data, d) and np.array_equal(ann.joint_scales, js)
         assert sum(any(a is i for a in anns) for i in initial) == 2, 'initial objects are returned'
         assert all(np.count_nonzero(i.data[:, 2]) >= 10 for i in initial), 'and were grown'
+
+
+def test_head_epilogue_matches_oracle_and_golden():
+    """pp_head_epilogue (csrc/head.cu) against oracle/head_oracle.py and the reference's own
+    head modules (tests/golden/head_*.npz): regression / logb rows bit-exact, sigmoid / exp rows
+    within TOL_HEAD_REL; quad = 0 and ragged sizes included."""
+    from conftest import HEAD_GOLDEN_NAMES, TOL_HEAD_REL, head_golden
+    from oracle.head_oracle import head_epilogue
+    from openpifpaf_b200.network import FusedHeadEpilogue
+    assert HEAD_GOLDEN_NAMES
+    for name in HEAD_GOLDEN_NAMES:
+        x_cif, x_caf, cif, caf = head_golden(name)
+        for x, want, nf, nv in ((x_cif, cif, 17, 1), (x_caf, caf, 19, 2)):
+            got = FusedHeadEpilogue(nf, nv)(torch.from_numpy(x).cuda()).cpu().numpy()
+            exact = [c for c in range(want.shape[2]) if c % 4 in (1, 2, 3)]
+            assert np.array_equal(got[:, :, exact], want[:, :, exact])
+            np.testing.assert_allclose(got, want, rtol=TOL_HEAD_REL, atol=0)
+    rng = np.random.RandomState(5)
+    for B, nf, nv, h, w, quad in ((2, 17, 1, 41, 41, 1), (1, 19, 2, 33, 47, 1), (3, 5, 2, 7, 3, 0),
+                                  (1, 1, 1, 1, 1, 1)):
+        x = rng.normal(0, 3, (B, nf * (1 + 4 * nv) * (4 if quad else 1), h, w)).astype(np.float32)
+        x.flat[::97] = 100.0         # saturating sigmoid, overflowing exp
+        x.flat[5::131] = -100.0
+        want = head_epilogue(x, nf, nv, quad)
+        got = FusedHeadEpilogue(nf, nv, quad)(torch.from_numpy(x).cuda()).cpu().numpy()
+        exact = [c for c in range(want.shape[2]) if c % 4 in (1, 2, 3)]
+        assert np.array_equal(got[:, :, exact], want[:, :, exact])
+        np.testing.assert_allclose(got, want, rtol=TOL_HEAD_REL, atol=1e-45)
+
+
+def test_head_epilogue_feeds_the_decoder(oracle, coco_skeleton, configured_decoder):
+    """Raw head tensors -> pp_head_epilogue -> CifCaf.decode_batch, all on the device, equals the
+    oracle decode of the oracle's epilogue."""
+    from oracle.head_oracle import head_epilogue
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.network import FusedHeadEpilogue
+    decoder = configured_decoder
+    cif, caf, _ = fields((161, 161), 2, pose_seed=5, jitter_seed=6)
+    H = cif.shape[-1]
+    h = (H + 1) // 2
+
+    def invert(field, nv):       # raw convolution output that the epilogue maps back onto `field`
+        nf = field.shape[0]
+        f = field.astype(np.float64).copy()
+        rows, cols = np.mgrid[0:H, 0:H]
+        chans = [np.log(np.clip(f[:, 0], 1e-6, 1 - 1e-6) / (1 - np.clip(f[:, 0], 1e-6, 1 - 1e-6)))]
+        regs, logb, scale = [], [], []
+        for v in range(nv):
+            regs += [f[:, 1 + 4 * v] - cols, f[:, 2 + 4 * v] - rows]
+            logb.append(f[:, 3 + 4 * v])
+            scale.append(np.log(np.maximum(f[:, 4 + 4 * v], 1e-6)))
+        flat = np.concatenate([chans[0],
+                               np.stack(regs, 1).reshape(nf * nv * 2, H, H),
+                               np.stack(logb, 1).reshape(nf * nv, H, H),
+                               np.stack(scale, 1).reshape(nf * nv, H, H)]).astype(np.float32)
+        padded = np.zeros((flat.shape[0], 2 * h, 2 * h), np.float32)
+        padded[:, :H, :H] = flat
+        return padded.reshape(-1, h, 2, h, 2).transpose(0, 2, 4, 1, 3).reshape(1, -1, h, h)
+
+    x_cif, x_caf = invert(cif, 1), invert(caf, 2)
+    o_cif, o_caf = head_epilogue(x_cif, 17, 1)[0], head_epilogue(x_caf, 19, 2)[0]
+    d_cif = FusedHeadEpilogue(17, 1)(torch.from_numpy(x_cif).cuda())
+    d_caf = FusedHeadEpilogue(19, 2)(torch.from_numpy(x_caf).cuda())
+    o = oracle.decode(d_cif[0].cpu().numpy(), d_caf[0].cpu().numpy(), coco_skeleton, oracle.Config(exp_mode=1))
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    anns = dec.decode_batch(d_cif, d_caf)[0]
+    assert len(anns) == len(o.data) >= 1
+    for ann, d in zip(anns, o.data):
+        assert np.array_equal(ann.data, d)
+    np.testing.assert_allclose(d_cif[0].cpu().numpy(), o_cif, rtol=2e-6, atol=0)
+    np.testing.assert_allclose(d_caf[0].cpu().numpy(), o_caf, rtol=2e-6, atol=0)
+
+
+@pytest.mark.parametrize('kind', ['plain', 'scaled', 'flipped', 'rotated'])
+def test_annotations_inverse_matches_oracle_and_golden(kind):
+    """Preprocess.annotations_inverse (pp_annotations_inverse) is bit-identical to the numpy
+    oracle and to the reference's outputs in tests/golden/inverse_mid.npz."""
+    import os
+    from conftest import GOLDEN_DIR, HorizontalSwap, inverse_inputs
+    from oracle.gen_golden_inverse import make_meta
+    from oracle.inverse_oracle import annotations_inverse
+    from openpifpaf_b200.annotation import Annotation
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, COCO_PERSON_SKELETON
+    from openpifpaf_b200.transforms import Preprocess
+    g = np.load(os.path.join(GOLDEN_DIR, 'inverse_mid.npz'))
+    data, js, orders, dxy, target = inverse_inputs()
+    meta = make_meta(kind, HorizontalSwap(target))
+    anns = []
+    for d, s, o in zip(data, js, orders):
+        a = Annotation(COCO_KEYPOINTS, COCO_PERSON_SKELETON).set(d.copy(), s.copy())
+        a.decoding_order = [(s_, e_, d[s_].copy(), d[e_].copy()) for s_, e_ in o]
+        anns.append(a)
+    res = Preprocess.annotations_inverse(anns, meta)
+    want = annotations_inverse(data, js, dxy, meta, target if meta['hflip'] else None)
+    got_data = np.stack([a.data for a in res])
+    got_js = np.stack([a.joint_scales for a in res])
+    got_dxy = np.array([c[:2] for a in res for _, __, c1, c2 in a.decoding_order for c in (c1, c2)],
+                       np.float32)
+    for got, w, key in ((got_data, want[0], 'data'), (got_js, want[1], 'scales'), (got_dxy, want[2], 'dxy')):
+        assert np.array_equal(got, w), key
+        assert np.array_equal(got, g['%s_%s' % (kind, key)]), key
+    assert np.array_equal(anns[0].data, data[0]), 'inputs are left untouched'
+    assert [(s, e) for s, e, _, __ in res[0].decoding_order] == orders[0]
+
+
+def test_decode_batch_with_metas(oracle, coco_skeleton, configured_decoder):
+    """decode_batch(..., metas=[...]) == annotations_inverse(oracle decode), per image with its own
+    meta, on the device path and on the pipelined host path."""
+    from conftest import HorizontalSwap, inverse_inputs
+    from oracle.gen_golden_inverse import META_KINDS, make_meta
+    from oracle.inverse_oracle import annotations_inverse
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    target = inverse_inputs()[4]
+    swap = HorizontalSwap(target)
+    B = 6
+    batch = [fields((161, 241), 1 + b % 3, pose_seed=40 + b, jitter_seed=50 + b)[:2] for b in range(B)]
+    cif = np.stack([c for c, _ in batch])
+    caf = np.stack([c for _, c in batch])
+    metas = [make_meta(META_KINDS[b % 4], swap) for b in range(B)]
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.host_chunk = 4
+    plain = dec.decode_batch(torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda())
+    for to_field in (lambda a: torch.from_numpy(a).cuda(), lambda a: a):
+        result = dec.decode_batch(to_field(cif), to_field(caf), metas=metas)
+        assert len(result) == B
+        for b in range(B):
+            o = oracle.decode(cif[b], caf[b], coco_skeleton, oracle.Config(exp_mode=1))
+            assert len(result[b]) == len(plain[b]) == len(o.data) >= 1
+            assert np.array_equal(np.stack([a.data for a in plain[b]]), o.data)
+            # coordinates stored in decoding_order, as decoded (parity of those: test_batch_*)
+            dxy = np.array([c[:2] for a in plain[b] for _, __, c1, c2 in a.decoding_order
+                            for c in (c1, c2)], np.float32).reshape(-1, 2)
+            want = annotations_inverse(o.data, o.joint_scales, dxy, metas[b],
+                                       target if metas[b]['hflip'] else None)
+            assert np.array_equal(np.stack([a.data for a in result[b]]), want[0])
+            assert np.array_equal(np.stack([a.joint_scales for a in result[b]]), want[1])
+            got_dxy = np.array([c[:2] for a in result[b] for _, __, c1, c2 in a.decoding_order
+                                for c in (c1, c2)], np.float32).reshape(-1, 2)
+            assert np.array_equal(got_dxy, want[2])
+
+
+def test_generator_batch_with_raw_heads(oracle, coco_skeleton, configured_decoder):
+    """Generator.batch with a model that emits raw fused-head outputs: head_collector runs the
+    epilogue on the device and the decode equals decoding the collected fields directly."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.network import CifCafCollector, FusedHeadEpilogue
+    decoder = configured_decoder
+
+    class Meta:
+        n_confidences = 1
+
+        def __init__(self, n_fields, n_vectors):
+            self.n_fields, self.n_vectors, self.n_scales = n_fields, n_vectors, n_vectors
+
+    rng = np.random.RandomState(11)
+    x_cif = torch.from_numpy(rng.normal(-2.0, 1.5, (3, 17 * 5 * 4, 11, 13)).astype(np.float32)).cuda()
+    x_caf = torch.from_numpy(rng.normal(-2.0, 1.5, (3, 19 * 9 * 4, 11, 13)).astype(np.float32)).cuda()
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.head_collector = CifCafCollector(Meta(17, 1), Meta(19, 2))
+    got = dec.batch(lambda images: (x_cif, x_caf), torch.zeros(3, 3, 8, 8), device='cuda')
+    cif, caf = FusedHeadEpilogue(17, 1)(x_cif), FusedHeadEpilogue(19, 2)(x_caf)
+    dec.head_collector = None
+    want = dec.decode_batch(cif, caf)
+    assert len(got) == len(want) == 3
+    for g, w in zip(got, want):
+        assert len(g) == len(w)
+        for a, b in zip(g, w):
+            assert np.array_equal(a.data, b.data)

@@ -123,3 +123,26 @@ def test_unconfigured_seed_threshold_raises(configured_decoder):
                          skeleton=COCO_PERSON_SKELETON)
     with pytest.raises(TypeError):
         dec.params()
+
+
+def test_json_data_batch_equals_per_annotation():
+    """json_data_batch == [a.json_data() ...] exactly (keypoints, bbox, score), including empty
+    annotations, fixed scores and ids."""
+    from openpifpaf_b200.annotation import Annotation, json_data_batch
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, COCO_PERSON_SKELETON
+    rng = np.random.RandomState(3)
+    anns = []
+    for i in range(40):
+        a = Annotation(COCO_KEYPOINTS, COCO_PERSON_SKELETON)
+        data = rng.uniform(0, 640, (17, 3)).astype(np.float32)
+        data[:, 2] = rng.uniform(0, 1, 17).astype(np.float32) * (rng.uniform(size=17) > 0.3)
+        if i == 5:
+            data[:, 2] = 0.0
+        a.set(data, rng.uniform(0.5, 9, 17).astype(np.float32))
+        if i == 7:
+            a.fixed_score = 0.25
+        if i == 9:
+            a.id_ = 4
+        anns.append(a)
+    assert json_data_batch(anns) == [a.json_data() for a in anns]
+    assert json_data_batch([]) == []

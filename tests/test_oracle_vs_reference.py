@@ -214,3 +214,73 @@ def test_initial_annotations(ref, oracle, coco_skeleton):
         assert np.array_equal(a.data[:, 2] != 0, data[:, 2] != 0)
         assert np.abs(a.data[:, :2] - data[:, :2]).max() <= TOL_XY
         assert np.abs(a.data[:, 2] - data[:, 2]).max() <= TOL_SCORE
+
+
+@pytest.mark.parametrize('batch,h,w,seed', [(1, 4, 6, 31), (3, 11, 9, 32)])
+def test_head_epilogue(ref, batch, h, w, seed):
+    """oracle/head_oracle.py == CompositeFieldFused.forward (eval) + CifCafCollector.forward
+    (network/heads.py:406-448, 65-88) on seeded raw convolution outputs, and the decoder accepts
+    the collected layout."""
+    from oracle.gen_golden_heads import raw_head_outputs, reference_fields
+    from oracle.head_oracle import head_epilogue
+    import openpifpaf.network.heads  # noqa: F401
+    x_cif, x_caf = raw_head_outputs(batch, h, w, seed)
+    cif, caf = reference_fields(ref, x_cif, x_caf)
+    for x, want, nf, nv in ((x_cif, cif, 17, 1), (x_caf, caf, 19, 2)):
+        got = head_epilogue(x, nf, nv, quad=1)
+        assert got.shape == want.shape == (batch, nf, 1 + 4 * nv, 2 * h - 1, 2 * w - 1)
+        np.testing.assert_allclose(got, want, rtol=2e-6, atol=0)
+
+
+def _metas(ref):
+    """Meta dicts as the reference's transforms build them (transforms/*.py)."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, HFLIP
+    import openpifpaf.transforms.hflip as ref_hflip
+    swap = ref_hflip._HorizontalSwap(COCO_KEYPOINTS, HFLIP)    # pylint: disable=protected-access
+    plain = {'offset': np.array((0.0, 0.0)), 'scale': np.array((1.0, 1.0)), 'hflip': False,
+             'width_height': np.array((640, 480)), 'rotation': {'angle': 0.0, 'width': None, 'height': None}}
+    scaled = dict(plain, offset=np.array((-12.0, 31.5)), scale=np.array((0.8013, 0.7977)))
+    flipped = dict(scaled, hflip=True, horizontal_swap=swap)
+    rotated = dict(flipped, rotation={'angle': 17.5, 'width': 513, 'height': 385})
+    return {'plain': plain, 'scaled': scaled, 'flipped': flipped, 'rotated': rotated}
+
+
+@pytest.mark.parametrize('kind', ['plain', 'scaled', 'flipped', 'rotated'])
+def test_annotations_inverse(ref, oracle, coco_skeleton, kind):
+    """oracle/inverse_oracle.py == Preprocess.annotations_inverse (transforms/preprocess.py:35-82)
+    on decoded annotations, bit for bit (data, joint_scales, decoding_order coordinates)."""
+    from oracle.inverse_oracle import annotations_inverse
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.transforms.preprocess import hflip_target
+    import openpifpaf.transforms  # noqa: F401
+    meta = _metas(ref)[kind]
+    dec = ref.decoder
+    configure(dec)
+    cif, caf, _ = fields((321, 481), 5, pose_seed=3, jitter_seed=4)
+    anns = dec.CifCaf(dec.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)([cif, caf])
+    assert len(anns) >= 3
+    data = np.stack([a.data for a in anns])
+    js = np.stack([a.joint_scales for a in anns])
+    dxy = np.array([c[:2] for a in anns for _, __, c1, c2 in a.decoding_order for c in (c1, c2)], np.float32)
+    target = None
+    if meta['hflip']:
+        target = hflip_target([meta], 17, 'cpu').numpy()
+    got_data, got_js, got_dxy = annotations_inverse(data, js, dxy, meta, target)
+    want = ref.transforms.Preprocess.annotations_inverse(anns, meta)
+    assert np.array_equal(got_data, np.stack([a.data for a in want]))
+    assert np.array_equal(got_js, np.stack([a.joint_scales for a in want]))
+    want_dxy = np.array([c[:2] for a in want for _, __, c1, c2 in a.decoding_order for c in (c1, c2)],
+                        np.float32)
+    assert np.array_equal(got_dxy, want_dxy)
+
+
+def test_json_data_batch(ref, coco_skeleton):
+    """annotation.json_data_batch == the reference's Annotation.json_data per annotation."""
+    from openpifpaf_b200.annotation import Annotation, json_data_batch
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    dec = ref.decoder
+    configure(dec)
+    cif, caf, _ = fields((321, 481), 6, pose_seed=3, jitter_seed=4)
+    anns = dec.CifCaf(dec.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)([cif, caf])
+    ours = [Annotation(COCO_KEYPOINTS, coco_skeleton).set(a.data.copy(), a.joint_scales.copy()) for a in anns]
+    assert json_data_batch(ours) == [a.json_data() for a in anns]
