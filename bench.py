@@ -9,7 +9,7 @@ A "step" is one pass of the hot path (CifHr -> seeds -> CafScored -> assembly
 printed by rank 0 (contract in DESIGN.md section "Measurement"):
 
   value         images/s, fields already resident in HBM, pp_decode_batch
-                (7 kernels) timed with CUDA events on the launching stream;
+                (8 kernels) timed with CUDA events on the launching stream;
   e2e           images/s through the public API CifCaf.decode_batch() with
                 PINNED HOST fields: H2D of the fields, kernels, D2H of the
                 results and the construction of the Annotation objects are all
@@ -423,6 +423,8 @@ def run_b200(args):
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
             traffic = json.load(f).get('cifhr_splat_kernel', {}).get(args.workload)
+        if batch != default_batch:
+            traffic = None       # the captured launch was at the workload's default batch
     except (OSError, ValueError):
         pass
     line = {

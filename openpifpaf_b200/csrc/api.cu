@@ -177,7 +177,14 @@ const char *pp_stage_name(int stage) {
 }
 
 /* 7 stage kernels + the candidate binning kernel + the status, CifHr-cursor and seed-counter memsets */
-int pp_decode_launch_count(const pp_params *p) { (void)p; return PP_N_STAGES + 4; }
+int pp_decode_launch_count(const pp_params *p) {
+  // 8 kernels (compact, splat, seeds collect, seeds sort, CafScored, candidate binning, assembly, NMS)
+  // + 3 memsets (status, work cursors, raw seed counts)
+  int n = PP_N_STAGES + 4;
+  if (p && p->force_complete) n += 3;   // second CafScored, its binning, complete_kernel
+  if (p && p->inverse) n += 1;          // annotations_inverse_kernel
+  return n;
+}
 const char *pp_version(void) { return "pifpaf_b200 0.1.0 (sm_100a)"; }
 
 void pp_default_params(pp_params *p) {
