@@ -225,8 +225,61 @@ int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, do
 int pp_head_epilogue(const float *d_x, float *d_out, int32_t B, int32_t n_fields, int32_t n_vectors,
                      int32_t h, int32_t w, int32_t quad, void *stream);
 
+/* ---- CifDet (detection decoder), generator/cifdet.py:17-52 ---------------------------------
+ * Fields are (B, C, 7, H, W) float32 with channels [v, x, y, _, w, h, _] in field units, C
+ * categories (<= PP_MAX_CATEGORIES).  pp_shape.F carries C, pp_shape.L is ignored. */
+#define PP_MAX_CATEGORIES 256
+
+typedef struct pp_det_params {
+  float cif_threshold;            /* CifHr.v_threshold                 cif_hr.py:16   */
+  float seed_threshold;           /* CifSeeds.threshold                cif_seeds.py:14 */
+  float seed_score_scale;         /* CifSeeds.score_scale              cif_seeds.py:15 */
+  float cif_min_scale;            /* FieldConfig.cif_min_scales[0]                     */
+  float nms_suppression;          /* nms.Detection.suppression         nms.py:61 (0.1) */
+  float nms_suppression_soft;     /* nms.Detection.suppression_soft    nms.py:62 (0.3) */
+  float nms_instance_threshold;   /* nms.Detection.instance_threshold  nms.py:63 (0.1) */
+  float nms_iou_threshold;        /* nms.Detection.iou_threshold       nms.py:64 (0.7) */
+  float nms_iou_threshold_soft;   /* nms.Detection.iou_threshold_soft  nms.py:65 (0.5) */
+  int32_t nms;                    /* 0: skip nms.Detection                            */
+} pp_det_params;
+
+/* Device result buffers of one batch of detections.  Optional members may be NULL. */
+typedef struct pp_det_outputs {
+  float *hr;            /* optional (B,C,Hh,Wh) CifDetHr.accumulated                   */
+  float *seeds;         /* optional (B,seed_cap,6): v, f, x, y, w, h sorted descending */
+  int32_t *n_seeds;     /* optional (B)                                                */
+  int32_t *pre_field;   /* optional (B,ann_cap) detections before the NMS, seed order  */
+  float *pre_score;     /* optional (B,ann_cap)                                        */
+  float *pre_box;       /* optional (B,ann_cap,4) x, y, w, h; 16-byte aligned          */
+  int32_t *n_pre;       /* optional (B)                                                */
+  int32_t *det_field;   /* (B,ann_cap) AnnotationDet.field_i, score order              */
+  float *det_score;     /* (B,ann_cap) AnnotationDet.score                             */
+  float *det_box;       /* (B,ann_cap,4) AnnotationDet.bbox x, y, w, h; 16-byte aligned */
+  int32_t *det_source;  /* optional (B,ann_cap) index into the pre list                */
+  int32_t *n_det;       /* (B)                                                         */
+  int32_t *status;      /* (B) PP_STATUS_* bits                                        */
+} pp_det_outputs;
+
+void pp_det_default_params(pp_det_params *p);
+size_t pp_cifdet_workspace_bytes(const pp_shape *s, const pp_caps *c);
+/* CifDet.__call__ for a batch: CifDetHr (cif_hr.py:84-100) -> CifDetSeeds (cif_seeds.py:67-90)
+ * -> seed loop with Occupancy(shape, 2, min_scale=2.0) (cifdet.py:34-44) -> nms.Detection
+ * (nms.py:60-102).  Asynchronous on `stream`. */
+int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *d_out, void *d_ws,
+                           size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                           const pp_det_params *p, void *stream);
+
+/* nms.Detection.annotations (nms.py:79-102) on its own: B lists of `cap` detections in any
+ * order (d_box 16-byte aligned); results in score order.  Scratch: pp_detection_nms_workspace_bytes. */
+size_t pp_detection_nms_workspace_bytes(int32_t B, int32_t cap);
+int pp_detection_nms(const int32_t *d_field, const float *d_score, const float *d_box,
+                     const int32_t *d_n, int32_t *d_out_field, float *d_out_score, float *d_out_box,
+                     int32_t *d_out_source /* optional: input index per result */, int32_t *d_out_n, void *d_ws, size_t ws_bytes, int32_t B, int32_t cap,
+                     const pp_det_params *p, void *stream);
+
 /* sizeof of the ABI structs, for bindings to check their mirrors:
- * which = 0 pp_params, 1 pp_image_meta, 2 pp_outputs, 3 pp_skeleton, 4 pp_shape, 5 pp_caps. */
+ * which = 0 pp_params, 1 pp_image_meta, 2 pp_outputs, 3 pp_skeleton, 4 pp_shape, 5 pp_caps,
+ * 6 pp_det_params, 7 pp_det_outputs. */
 int32_t pp_sizeof(int32_t which);
 
 /* Preprocess.annotations_inverse (transforms/preprocess.py:35-82) for a whole batch, in place on

@@ -40,6 +40,20 @@ class Inverse(C.Structure):
     _fields_ = [('meta', C.c_void_p), ('hflip_target', C.c_void_p)]
 
 
+class DetParams(C.Structure):
+    _fields_ = [('cif_threshold', C.c_float), ('seed_threshold', C.c_float),
+                ('seed_score_scale', C.c_float), ('cif_min_scale', C.c_float),
+                ('nms_suppression', C.c_float), ('nms_suppression_soft', C.c_float),
+                ('nms_instance_threshold', C.c_float), ('nms_iou_threshold', C.c_float),
+                ('nms_iou_threshold_soft', C.c_float), ('nms', C.c_int32)]
+
+
+class DetOutputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        'hr', 'seeds', 'n_seeds', 'pre_field', 'pre_score', 'pre_box', 'n_pre',
+        'det_field', 'det_score', 'det_box', 'det_source', 'n_det', 'status')]
+
+
 class Params(C.Structure):
     _fields_ = [
         ('nms_instance_threshold', C.c_double),
@@ -130,6 +144,14 @@ def lib():
     l.pp_coco_skeleton.argtypes = [P(Skeleton)]
     l.pp_workspace_bytes.restype = sz
     l.pp_workspace_bytes.argtypes = [P(Shape), P(Caps)]
+    l.pp_det_default_params.argtypes = [P(DetParams)]
+    l.pp_det_default_params.restype = None
+    l.pp_cifdet_workspace_bytes.argtypes = [P(Shape), P(Caps)]
+    l.pp_cifdet_workspace_bytes.restype = sz
+    l.pp_cifdet_decode_batch.argtypes = [vp, P(DetOutputs), vp, sz, P(Shape), P(Caps), P(DetParams), vp]
+    l.pp_detection_nms_workspace_bytes.argtypes = [i32, i32]
+    l.pp_detection_nms_workspace_bytes.restype = sz
+    l.pp_detection_nms.argtypes = [vp] * 10 + [sz, i32, i32, P(DetParams), vp]
     l.pp_sizeof.argtypes = [i32]
     l.pp_sizeof.restype = i32
     l.pp_annotations_inverse.argtypes = [vp, vp, vp, vp, vp, C.POINTER(Inverse), i32, i32, i32, vp]
@@ -159,7 +181,8 @@ def lib():
     l.pp_scalar_nonzero_clipped_with_reduction.argtypes = [vp, i32, i32, f32, f32, f32, vp, vp]
     l.pp_scalar_square_add_single.argtypes = [vp, i32, i32, C.c_longlong, C.c_longlong,
                                               C.c_longlong, i32, vp]
-    for which, mirror in enumerate((Params, ImageMeta, Outputs, Skeleton, Shape, Caps)):
+    for which, mirror in enumerate((Params, ImageMeta, Outputs, Skeleton, Shape, Caps, DetParams,
+                                    DetOutputs)):
         if l.pp_sizeof(which) != C.sizeof(mirror):
             raise ImportError('ctypes mirror %s (%d bytes) does not match the library (%d): rebuild' % (
                 mirror.__name__, C.sizeof(mirror), l.pp_sizeof(which)))
@@ -171,7 +194,8 @@ EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
     'pp_stage_name', 'pp_decode_launch_count',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
-    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
+    'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
     'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',

@@ -206,7 +206,9 @@ void pp_default_params(pp_params *p) {
 }
 
 int pp_default_caps(const pp_shape *s, pp_caps *c) {
-  if (!shape_ok(s) || !c) return PP_ERR_ARG;
+  // F up to PP_MAX_CATEGORIES so that the detection path can use the same defaults
+  if (!s || !c || s->B <= 0 || s->F <= 0 || s->F > PP_MAX_CATEGORIES || s->H <= 0 || s->W <= 0 || s->stride <= 0)
+    return PP_ERR_ARG;
   long long cells = (long long)s->H * s->W;
   long long seeds = cells * s->F;
   if (seeds >= (1 << 24)) seeds = (1 << 24) - 1;
@@ -241,6 +243,8 @@ int32_t pp_sizeof(int32_t which) {
     case 3: return (int32_t)sizeof(pp_skeleton);
     case 4: return (int32_t)sizeof(pp_shape);
     case 5: return (int32_t)sizeof(pp_caps);
+    case 6: return (int32_t)sizeof(pp_det_params);
+    case 7: return (int32_t)sizeof(pp_det_outputs);
     default: return -1;
   }
 }
@@ -443,6 +447,112 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
                                     s->B, s->F, c->ann_cap, st);
   prof_end_step(p->profile, st);
   return rc;
+}
+
+// ---- CifDet ------------------------------------------------------------------
+void pp_det_default_params(pp_det_params *p) {
+  if (!p) return;
+  memset(p, 0, sizeof *p);
+  p->cif_threshold = 0.1f;
+  p->seed_threshold = 0.2f;
+  p->seed_score_scale = 1.0f;
+  p->cif_min_scale = 0.0f;
+  p->nms_suppression = 0.1f;
+  p->nms_suppression_soft = 0.3f;
+  p->nms_instance_threshold = 0.1f;
+  p->nms_iou_threshold = 0.7f;
+  p->nms_iou_threshold_soft = 0.5f;
+  p->nms = 1;
+}
+
+static bool det_shape_ok(const pp_shape *s) {
+  return s && s->B > 0 && s->F > 0 && s->F <= PP_MAX_CATEGORIES && s->H > 0 && s->W > 0 && s->stride > 0;
+}
+
+struct DetWs {
+  float *hr; float *seeds; int *n_seeds;
+  int *pre_field; float *pre_score; float *pre_box; int *n_pre;
+  uint8_t *occ_cnt; int2 *occ_rec; float *work_score;
+  void *stage;
+  size_t total;
+};
+
+static DetWs det_layout(void *base, const pp_shape &s, const pp_caps &c) {
+  DetWs w;
+  char *p = (char *)base;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { void *r = p ? p + off : nullptr; off += align_up(bytes, 256); return r; };
+  const size_t B = s.B, A = c.ann_cap;
+  w.hr = (float *)take(B * s.F * hr_h(s) * hr_w(s) * sizeof(float));
+  w.seeds = (float *)take(B * c.seed_cap * 6 * sizeof(float));
+  w.n_seeds = (int *)take(B * sizeof(int));
+  w.pre_field = (int *)take(B * A * sizeof(int));
+  w.pre_score = (float *)take(B * A * sizeof(float));
+  w.pre_box = (float *)take(B * A * 4 * sizeof(float));
+  w.n_pre = (int *)take(B * sizeof(int));
+  w.occ_cnt = (uint8_t *)take(B * c.seed_cap);
+  w.occ_rec = (int2 *)take(B * c.seed_cap * sizeof(int2));
+  w.work_score = (float *)take(B * A * sizeof(float));
+  size_t st = cifhr_ws_bytes(s, c), st2 = seeds_ws_bytes(s, c, 1);
+  w.stage = take(st > st2 ? st : st2);
+  w.total = off;
+  return w;
+}
+
+size_t pp_cifdet_workspace_bytes(const pp_shape *s, const pp_caps *c) {
+  if (!det_shape_ok(s) || !caps_ok(s, c)) return 0;
+  return det_layout(nullptr, *s, *c).total;
+}
+
+int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *o, void *d_ws, size_t ws_bytes,
+                           const pp_shape *s, const pp_caps *c, const pp_det_params *p, void *stream) {
+  if (!det_shape_ok(s) || !caps_ok(s, c) || !p || !o || !d_field || !d_ws || !o->det_field ||
+      !o->det_score || !o->det_box || !o->n_det || !o->status)
+    return PP_ERR_ARG;
+  DetWs w = det_layout(d_ws, *s, *c);
+  if (ws_bytes < w.total) return PP_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  pp_params q;
+  pp_default_params(&q);
+  q.cif_threshold = p->cif_threshold;
+  q.seed_threshold = p->seed_threshold;
+  q.seed_score_scale = p->seed_score_scale;
+  q.cif_min_scale = p->cif_min_scale;
+  PP_CUDA_CHECK(cudaMemsetAsync(o->status, 0, (size_t)s->B * sizeof(int), st));
+  float *hr = o->hr ? o->hr : w.hr;
+  int rc = cifhr_launch(d_field, hr, w.stage, *s, *c, q, o->status, st, 1);
+  if (rc) return rc;
+  float *seeds = o->seeds ? o->seeds : w.seeds;
+  int *n_seeds = o->n_seeds ? o->n_seeds : w.n_seeds;
+  if ((rc = seeds_launch(d_field, hr, seeds, n_seeds, w.stage, *s, *c, q, o->status, st, 1))) return rc;
+  DetArgs a;
+  a.seeds = seeds; a.n_seeds = n_seeds;
+  a.occ_cnt = w.occ_cnt; a.occ_rec = w.occ_rec;
+  a.pre_field = o->pre_field ? o->pre_field : w.pre_field;
+  a.pre_score = o->pre_score ? o->pre_score : w.pre_score;
+  a.pre_box = o->pre_box ? o->pre_box : w.pre_box;
+  a.n_pre = o->n_pre ? o->n_pre : w.n_pre;
+  a.det_field = o->det_field; a.det_score = o->det_score; a.det_box = o->det_box; a.n_det = o->n_det;
+  a.det_source = o->det_source;
+  a.status = o->status;
+  a.seed_cap = c->seed_cap; a.ann_cap = c->ann_cap; a.hh = hr_h(*s); a.hw = hr_w(*s); a.C = s->F;
+  return det_assemble_launch(a, s->B, *p, w.work_score, st);
+}
+
+size_t pp_detection_nms_workspace_bytes(int32_t B, int32_t cap) {
+  return (B > 0 && cap > 0) ? det_nms_ws_bytes(B, cap) : 0;
+}
+
+int pp_detection_nms(const int32_t *d_field, const float *d_score, const float *d_box,
+                     const int32_t *d_n, int32_t *d_out_field, float *d_out_score, float *d_out_box,
+                     int32_t *d_out_source, int32_t *d_out_n, void *d_ws, size_t ws_bytes, int32_t B, int32_t cap,
+                     const pp_det_params *p, void *stream) {
+  if (!d_field || !d_score || !d_box || !d_n || !d_out_field || !d_out_score || !d_out_box || !d_out_n ||
+      !d_ws || !p || B <= 0 || cap <= 0)
+    return PP_ERR_ARG;
+  if (ws_bytes < det_nms_ws_bytes(B, cap)) return PP_ERR_WORKSPACE;
+  return det_nms_launch(d_field, d_score, d_box, d_n, d_out_field, d_out_score, d_out_box, d_out_source, d_out_n, d_ws,
+                        B, cap, *p, (cudaStream_t)stream);
 }
 
 // ---- host entries ------------------------------------------------------------

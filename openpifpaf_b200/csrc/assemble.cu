@@ -25,6 +25,7 @@
 
 #include "common.cuh"
 #include "stages.cuh"
+#include "occupancy.cuh"
 
 namespace pp {
 
@@ -532,39 +533,6 @@ __device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const 
     if (sh.best < 0) break;
   }
 }
-
-// round(np.float32) -> Python int (half to even), clamped like the oracle.
-__device__ __forceinline__ long long py_round(float v) {
-  double r = rint((double)v);
-  if (r > 4e18) r = 4e18;
-  if (r < -4e18) r = -4e18;
-  return (long long)r;
-}
-
-// Occupancy.set box (occupancy.py:31-39 + utils.py:61-66) for a map of (oh, ow) cells.
-__device__ __forceinline__ void occupancy_box(float x, float y, float sigma, long long ow,
-                                              long long oh, long long *box) {
-  long long xi = py_round(__fdiv_rn(x, 2.0f)), yi = py_round(__fdiv_rn(y, 2.0f));
-  float shalf = __fdiv_rn(sigma, 2.0f);
-  long long si = py_round(shalf > 2.0f ? shalf : 2.0f);
-  long long minx = xi - si > 0 ? xi - si : 0;
-  long long miny = yi - si > 0 ? yi - si : 0;
-  long long t = xi + si + 1 < ow ? xi + si + 1 : ow;
-  long long maxx = minx + 1 > t ? minx + 1 : t;
-  t = yi + si + 1 < oh ? yi + si + 1 : oh;
-  long long maxy = miny + 1 > t ? miny + 1 : t;
-  if (maxx > ow) maxx = ow;      // numpy slicing clamps to the array
-  if (maxy > oh) maxy = oh;
-  box[0] = minx; box[1] = maxx; box[2] = miny; box[3] = maxy;
-}
-
-// Occupancy.get cell (occupancy.py:41-47 + functional.pyx:281-286)
-__device__ __forceinline__ void occupancy_cell(float x, float y, long long ow, long long oh,
-                                               long long *cx, long long *cy) {
-  *cx = (long long)clipf(__fdiv_rn(x, 2.0f), 0.0f, (float)(ow - 1));
-  *cy = (long long)clipf(__fdiv_rn(y, 2.0f), 0.0f, (float)(oh - 1));
-}
-
 
 __global__ void __launch_bounds__(kAsmThreads)
 assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {

@@ -110,13 +110,13 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
 // K1: ordered compaction of CIF sources per (image, field).
 __global__ void __launch_bounds__(kCompactThreads)
 cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src_cap, int hh, int hw,
-                   float v_th, float min_scale_over_stride, int use_min_scale,
+                   float v_th, float min_scale_over_stride, int use_min_scale, int det,
                    int *__restrict__ status) {
   extern __shared__ int sm_diff[];   // nstrips + 1 difference array
   __shared__ int warp_tot[kCompactThreads / 32];
   const int bf = blockIdx.x;
   const int n = s.H * s.W;
-  const float *p = cif + (size_t)bf * 5 * n;
+  const float *p = cif + (size_t)bf * (det ? 7 : 5) * n;    // CifDet fields: [v, x, y, _, w, h, _]
   const float stride = (float)s.stride;
   for (int i = threadIdx.x; i <= w.nstrips; i += blockDim.x) sm_diff[i] = 0;
   __syncthreads();
@@ -132,6 +132,7 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
       conf = __ldg(p + c);
       flag = conf > v_th;                                         // cif_hr.py:27
       if (flag && use_min_scale) flag = __ldg(p + 4 * n + c) > min_scale_over_stride;  // :28-29
+      if (flag && use_min_scale && det) flag = __ldg(p + 5 * n + c) > min_scale_over_stride;  // :87-89
     }
     int total;
     int off = block_flag_scan(flag, warp_tot, &total);
@@ -140,7 +141,14 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
       if (k < src_cap) {
         float cx = __fmul_rn(__ldg(p + n + c), stride);           // :32
         float cy = __fmul_rn(__ldg(p + 2 * n + c), stride);       // :33
-        float sg = __fmul_rn(__fmul_rn(0.5f, __ldg(p + 4 * n + c)), stride);
+        float sg;
+        if (det) {      // CifDetHr: sigma = max(1, 0.1 * min(w, h) * stride), cif_hr.py:91-94
+          const float bw = __ldg(p + 4 * n + c), bh = __ldg(p + 5 * n + c);
+          const float m = (bw != bw) ? bw : ((bh != bh) ? bh : fminf(bw, bh));   // np.minimum keeps NaN
+          sg = __fmul_rn(__fmul_rn(0.1f, m), stride);
+        } else {
+          sg = __fmul_rn(__fmul_rn(0.5f, __ldg(p + 4 * n + c)), stride);
+        }
         float sigma = (sg != sg) ? sg : fmaxf(1.0f, sg);          // np.maximum(1.0, .) :34
         float cv = __fdiv_rn(conf, 16.0f);                        // v / neighbors / len_cifs :40
         // functional.pyx:122-125 with truncate = 1.0
@@ -427,7 +435,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
 }
 
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
-                 const pp_params &p, int *d_status, cudaStream_t st) {
+                 const pp_params &p, int *d_status, cudaStream_t st, int det) {
   CifHrWs w = carve(d_ws, s, c);
   const int hh = hr_h(s), hw = hr_w(s);
   const int bf = s.B * s.F;
@@ -438,7 +446,7 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
       d_cif, w, s, c.src_cap, hh, hw, p.cif_threshold, p.cif_min_scale / (float)s.stride,
-      p.cif_min_scale != 0.0f, d_status);
+      p.cif_min_scale != 0.0f, det, d_status);
   PP_LAUNCH_CHECK("cif_compact_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));

@@ -29,6 +29,9 @@ __device__ __forceinline__ uint32_t orderable(float v) {
   return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
 }
 
+// REC = floats per seed record: 5 (v, f, x, y, s) for poses, 6 (v, f, x, y, w, h) for CifDet
+// (cif_seeds.py:67-90; fields have 7 channels [v, x, y, _, w, h, _])
+template <int REC>
 __global__ void __launch_bounds__(kCollectThreads)
 seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr,
                      float *__restrict__ raw, int *__restrict__ n_raw, pp_shape s, int cap, int hh,
@@ -40,15 +43,17 @@ seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr
   const int c = (blockIdx.x - bf * blocks_per_field) * kCollectThreads + threadIdx.x;
   const int b = bf / s.F, f = bf - b * s.F;
   if (seed_mask != 0u && !((seed_mask >> f) & 1u)) return;        // cif_seeds.py:29-30
-  const float *p = cif + (size_t)bf * 5 * n;
+  const float *p = cif + (size_t)bf * (REC == 6 ? 7 : 5) * n;
   const float stride = (float)s.stride;
   bool keep = false;
-  float v = 0.f, x = 0.f, y = 0.f, sc = 0.f;
+  float v = 0.f, x = 0.f, y = 0.f, sc = 0.f, sc2 = 0.f;
   if (c < n) {
     float conf = __ldg(p + c);
     if (conf > th) {                                              // :31
       sc = __ldg(p + 4 * n + c);
-      if (!use_min_scale || sc > min_scale_over_stride) {         // :32-33
+      if (REC == 6) sc2 = __ldg(p + 5 * n + c);
+      if (!use_min_scale || (sc > min_scale_over_stride &&
+                             (REC == 5 || sc2 > min_scale_over_stride))) {   // :32-33, :75-77
         x = __fmul_rn(__ldg(p + n + c), stride);
         y = __fmul_rn(__ldg(p + 2 * n + c), stride);
         float hv = scalar_value_at(hr + (size_t)bf * hh * hw, hh, hw, x, y, 0.0f);   // :37
@@ -69,20 +74,22 @@ seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr
   if (keep) {
     int slot = base + __popc(m & ((1u << lane) - 1u));
     if (slot < cap) {
-      float *o = raw + ((size_t)b * cap + slot) * 5;
+      float *o = raw + ((size_t)b * cap + slot) * REC;
       o[0] = v; o[1] = (float)f; o[2] = x; o[3] = y; o[4] = __fmul_rn(sc, stride);   // :44,47
+      if (REC == 6) o[5] = __fmul_rn(sc2, stride);                                   // :84
     }
   }
 }
 
-// strict "a sorts before b" for descending tuple order (v, f, x, y, s)
+// strict "a sorts before b" for descending tuple order (v, f, x, y, s) / (v, f, x, y, w, h)
+template <int REC>
 __device__ __forceinline__ bool seed_before(uint64_t a, uint64_t b, const float *__restrict__ raw) {
   uint64_t ha = a >> 24, hb = b >> 24;
   if (ha != hb) return ha > hb;
   if (a == b) return false;
-  const float *pa = raw + (size_t)(a & 0xffffffu) * 5, *pb = raw + (size_t)(b & 0xffffffu) * 5;
+  const float *pa = raw + (size_t)(a & 0xffffffu) * REC, *pb = raw + (size_t)(b & 0xffffffu) * REC;
 #pragma unroll
-  for (int i = 2; i < 5; i++) {
+  for (int i = 2; i < REC; i++) {
     float xa = pa[i], xb = pb[i];
     if (xa > xb) return true;
     if (xa < xb) return false;
@@ -90,6 +97,7 @@ __device__ __forceinline__ bool seed_before(uint64_t a, uint64_t b, const float 
   return false;
 }
 
+template <int REC>
 __global__ void __launch_bounds__(kSortThreads)
 seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_raw,
                   float *__restrict__ out_all, int *__restrict__ n_out, uint64_t *__restrict__ scratch,
@@ -101,8 +109,8 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
     if (threadIdx.x == 0) atomicOr(&status[b], PP_STATUS_SEED_OVERFLOW);
     n = cap;
   }
-  const float *raw = raw_all + (size_t)b * cap * 5;
-  float *out = out_all + (size_t)b * cap * 5;
+  const float *raw = raw_all + (size_t)b * cap * REC;
+  float *out = out_all + (size_t)b * cap * REC;
   int npad = 1;
   while (npad < n) npad <<= 1;
   uint64_t *keys = (npad <= kSortSmemKeys) ? s_keys : scratch + (size_t)b * scratch_stride;
@@ -110,7 +118,7 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
   for (int i = threadIdx.x; i < npad; i += blockDim.x) {
     uint64_t k = 0;
     if (i < n) {
-      const float *r = raw + (size_t)i * 5;
+      const float *r = raw + (size_t)i * REC;
       k = ((uint64_t)orderable(r[0]) << 32) | ((uint64_t)((uint32_t)r[1] & 0xffu) << 24) |
           (uint64_t)(uint32_t)i;
     }
@@ -124,7 +132,7 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
         if (l > i) {
           uint64_t a = keys[i], c = keys[l];
           bool desc_block = (i & k) == 0;   // this block ends up descending
-          bool swap = desc_block ? seed_before(c, a, raw) : seed_before(a, c, raw);
+          bool swap = desc_block ? seed_before<REC>(c, a, raw) : seed_before<REC>(a, c, raw);
           if (swap) { keys[i] = c; keys[l] = a; }
         }
       }
@@ -132,10 +140,10 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
     }
   }
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const float *r = raw + (size_t)(keys[i] & 0xffffffu) * 5;
-    float *o = out + (size_t)i * 5;
+    const float *r = raw + (size_t)(keys[i] & 0xffffffu) * REC;
+    float *o = out + (size_t)i * REC;
 #pragma unroll
-    for (int c = 0; c < 5; c++) o[c] = r[c];
+    for (int c = 0; c < REC; c++) o[c] = r[c];
   }
   if (threadIdx.x == 0) n_out[b] = n;
 }
@@ -149,9 +157,9 @@ struct SeedsWs {
 
 static int pow2_ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
-size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c) {
+size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det) {
   size_t n = 0;
-  n += align_up((size_t)s.B * c.seed_cap * 5 * sizeof(float), 256);
+  n += align_up((size_t)s.B * c.seed_cap * (det ? 6 : 5) * sizeof(float), 256);
   n += align_up((size_t)s.B * sizeof(int), 256);
   int p2 = pow2_ceil(c.seed_cap);
   if (p2 > kSortSmemKeys) n += align_up((size_t)s.B * p2 * sizeof(uint64_t), 256);
@@ -160,11 +168,11 @@ size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c) {
 
 int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
                  const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
-                 cudaStream_t st) {
-  if (c.seed_cap >= (1 << 24)) return PP_ERR_ARG;
+                 cudaStream_t st, int det) {
+  if (c.seed_cap >= (1 << 24) || s.F > 256) return PP_ERR_ARG;    // key layout: f:8 | index:24
   SeedsWs w;
   char *q = (char *)d_ws;
-  w.raw = (float *)q; q += align_up((size_t)s.B * c.seed_cap * 5 * sizeof(float), 256);
+  w.raw = (float *)q; q += align_up((size_t)s.B * c.seed_cap * (det ? 6 : 5) * sizeof(float), 256);
   w.n_raw = (int *)q; q += align_up((size_t)s.B * sizeof(int), 256);
   w.scratch = (uint64_t *)q;
   w.scratch_stride = pow2_ceil(c.seed_cap);
@@ -172,16 +180,25 @@ int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n
   prof_mark(p.profile, kStCollect, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
   int blocks = s.B * s.F * ((n + kCollectThreads - 1) / kCollectThreads);
-  seeds_collect_kernel<<<blocks, kCollectThreads, 0, st>>>(
-      d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-      p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, p.seed_mask);
+  if (det)
+    seeds_collect_kernel<6><<<blocks, kCollectThreads, 0, st>>>(
+        d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
+        p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, 0u);
+  else
+    seeds_collect_kernel<5><<<blocks, kCollectThreads, 0, st>>>(
+        d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
+        p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, p.seed_mask);
   PP_LAUNCH_CHECK("seeds_collect_kernel");
   // small capacities only need a small shared array
   size_t need = (size_t)(w.scratch_stride <= kSortSmemKeys ? w.scratch_stride : kSortSmemKeys) *
                 sizeof(uint64_t);
   prof_mark(p.profile, kStSort, st);
-  seeds_sort_kernel<<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
-                                                     c.seed_cap, w.scratch_stride, d_status);
+  if (det)
+    seeds_sort_kernel<6><<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
+                                                          c.seed_cap, w.scratch_stride, d_status);
+  else
+    seeds_sort_kernel<5><<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
+                                                          c.seed_cap, w.scratch_stride, d_status);
   PP_LAUNCH_CHECK("seeds_sort_kernel");
   return PP_OK;
 }

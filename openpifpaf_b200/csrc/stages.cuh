@@ -5,12 +5,34 @@
 namespace pp {
 
 size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c);
+// det = 1: CifDet fields (B,C,7,H,W) [v, x, y, _, w, h, _]; sigma / seed records follow
+// CifDetHr / CifDetSeeds (cif_hr.py:84-100, cif_seeds.py:67-90); seeds are 6 floats (v, f, x, y, w, h)
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
-                 const pp_params &p, int *d_status, cudaStream_t st);
-size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c);
+                 const pp_params &p, int *d_status, cudaStream_t st, int det = 0);
+size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det = 0);
 int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
                  const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
-                 cudaStream_t st);
+                 cudaStream_t st, int det = 0);
+
+// CifDet: seed loop with occupancy + nms.Detection (det.cu)
+struct DetArgs {
+  const float *seeds;      // (B, seed_cap, 6) sorted
+  const int *n_seeds;
+  uint8_t *occ_cnt;        // (B, seed_cap)
+  int2 *occ_rec;           // (B, seed_cap)
+  int *pre_field; float *pre_score; float *pre_box; int *n_pre;      // before the NMS, seed order
+  int *det_field; float *det_score; float *det_box; int *n_det;      // after nms.Detection
+  int *det_source;         // optional: index into the pre list
+  int *status;
+  int seed_cap, ann_cap, hh, hw, C;
+};
+size_t det_nms_ws_bytes(int B, int cap);
+int det_nms_launch(const int *in_field, const float *in_score, const float *in_box, const int *n_in,
+                   int *det_field, float *det_score, float *det_box, int *det_source, int *n_det,
+                   void *d_ws, int B, int cap, const pp_det_params &p, cudaStream_t st);
+int det_assemble_launch(const DetArgs &a, int B, const pp_det_params &p, float *work_score,
+                        cudaStream_t st);
+
 int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                       float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st);

@@ -7,6 +7,7 @@ from .engine import DecoderParams, DeviceDecoder
 from .factory import cli, configure, factory_decode, factory_from_args
 from .field_config import FieldConfig
 from .generator.cifcaf import CifCaf
+from .generator.cifdet import CifDet, CifDetHr, CifDetSeeds
 from .generator.generator import Generator
 from . import nms
 from .occupancy import Occupancy

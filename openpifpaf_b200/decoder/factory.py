@@ -21,6 +21,7 @@ from .cif_hr import CifHr
 from .cif_seeds import CifSeeds
 from .field_config import FieldConfig
 from .generator.cifcaf import CifCaf
+from .generator.cifdet import CifDet
 
 LOG = logging.getLogger(__name__)
 
@@ -125,8 +126,9 @@ def factory_decode(head_nets, *,
     head_names = tuple(hn.meta.name for hn in head_nets)
     LOG.debug('head names = %s', head_names)
 
-    if hasattr(head_nets[0].meta, 'categories'):
-        raise NotImplementedError('CifDet decoding is outside the CifCaf hot path (SURVEY.md 8f)')
+    if hasattr(head_nets[0].meta, 'categories'):          # DetectionMeta, factory.py:138-149
+        field_config = FieldConfig()       # the reference keeps the default stride 8 here
+        return CifDet(field_config, head_nets[0].meta.categories, worker_pool=worker_pool)
 
     if len(head_nets) >= 2 and _is_intensity(head_nets[0].meta) \
        and _is_association(head_nets[1].meta):

@@ -309,3 +309,46 @@ def random_init_like_fields(field_hw, seed=0, n_links=19, n_keypoints=17, scale_
             f[i, chans[rng.randint(len(chans))], y, x] = specials[k % len(specials)]
             f[i, 0, y, x] = max(f[i, 0, y, x], 0.5)        # make sure the cell is active
     return cif.astype(np.float32), caf.astype(np.float32)
+
+
+def synthetic_det_fields(image_hw=(641, 641), n_boxes=8, *, box_seed=0, jitter_seed=1,
+                         n_categories=5, stride=8, duplicates=True):
+    """Synthetic CifDet head output ``(C, 7, H, W)``, channels ``[v, x, y, _, w, h, _]`` in
+    field units (the layout ``CifDet`` reads, generator/cifdet.py + cif_hr.py:84-100).
+
+    Every box lights up the cells around its centre (confidence falling off with distance,
+    regressions pointing at the centre, jittered sizes); with ``duplicates`` some boxes get a
+    shifted twin of the same category so that the IoU soft-NMS has work to do.  Returns
+    ``(field, boxes)`` with ``boxes`` rows ``(category, cx, cy, w, h)`` in pixels.
+    """
+    H, W = (image_hw[0] - 1) // stride + 1, (image_hw[1] - 1) // stride + 1
+    rng = np.random.RandomState(box_seed)
+    boxes = []
+    for _ in range(n_boxes):
+        w, h = rng.uniform(40, 0.45 * image_hw[1]), rng.uniform(40, 0.45 * image_hw[0])
+        cx, cy = rng.uniform(0.5 * w, image_hw[1] - 0.5 * w), rng.uniform(0.5 * h, image_hw[0] - 0.5 * h)
+        cat = rng.randint(n_categories)
+        boxes.append((cat, cx, cy, w, h))
+        if duplicates and rng.uniform() < 0.5:
+            shift = rng.choice([0.08, 0.2, 0.5])
+            boxes.append((cat, cx + shift * w, cy, w * rng.uniform(0.9, 1.1), h))
+    jr = np.random.RandomState(jitter_seed)
+    field = np.zeros((n_categories, 7, H, W), np.float32)
+    field[:, 0] = jr.uniform(0.0, 0.05, (n_categories, H, W))
+    field[:, 4:6] = 1.0
+    ys, xs = np.mgrid[0:H, 0:W].astype(np.float32)
+    for cat, cx, cy, w, h in boxes:
+        fx, fy = cx / stride, cy / stride
+        d2 = (xs - fx) ** 2 + (ys - fy) ** 2
+        near = d2 < 2.5 ** 2
+        peak = jr.uniform(0.55, 0.95)
+        conf = (peak * np.exp(-0.5 * d2 / 1.2 ** 2) * jr.uniform(0.9, 1.0, d2.shape)).astype(np.float32)
+        upd = near & (conf > field[cat, 0])
+        field[cat, 0][upd] = conf[upd]
+        field[cat, 1][upd] = (fx + jr.normal(0, 0.05, d2.shape))[upd]
+        field[cat, 2][upd] = (fy + jr.normal(0, 0.05, d2.shape))[upd]
+        field[cat, 3][upd] = jr.uniform(-1, 1, d2.shape)[upd]
+        field[cat, 4][upd] = (w / stride * jr.uniform(0.95, 1.05, d2.shape))[upd]
+        field[cat, 5][upd] = (h / stride * jr.uniform(0.95, 1.05, d2.shape))[upd]
+        field[cat, 6][upd] = jr.uniform(-1, 1, d2.shape)[upd]
+    return field, np.array(boxes, np.float64)

@@ -490,10 +490,11 @@ static int grow(orc_ann *ann, const orc_graph *g, const orc_cafs *cf, const orc_
 /* ------------------------------------------------------------------------- */
 /* Occupancy -- occupancy.py:10-47, utils.py:61-66, functional.pyx:281-286    */
 
-typedef struct { unsigned char *m; long F, H, W; } orc_occ;
+typedef struct { unsigned char *m; long F, H, W; float min_scale_reduced; } orc_occ;
 
 static int occ_init(orc_occ *o, long F, long shape_h, long shape_w) {
   o->F = F;
+  o->min_scale_reduced = 2.0f;                          /* CifCaf: Occupancy(shape, 2, min_scale=4) cifcaf.py:84 */
   o->H = (long)((double)shape_h / 2.0);                 /* int(shape[1] / reduction) */
   o->W = (long)((double)shape_w / 2.0);
   if (o->H < 0 || o->W < 0) return ORC_ERR_ARG;
@@ -512,7 +513,7 @@ static void occ_set(orc_occ *o, int f, float x, float y, float sigma) {   /* occ
   if (f >= o->F) return;
   long long xi = py_round_f(x / 2.0f), yi = py_round_f(y / 2.0f);
   float sh = sigma / 2.0f;
-  long long si = py_round_f(sh > 2.0f ? sh : 2.0f);     /* max(min_scale_reduced, sigma / r) */
+  long long si = py_round_f(sh > o->min_scale_reduced ? sh : o->min_scale_reduced); /* max(min_scale_reduced, sigma / r) */
   long long minx = xi - si > 0 ? xi - si : 0;
   long long miny = yi - si > 0 ? yi - si : 0;
   long long t = xi + si + 1 < o->W ? xi + si + 1 : o->W;
@@ -816,6 +817,203 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
 /* Per-primitive entry points with the reference's own names, for known-answer */
 /* tests against the compiled functional.pyx.                                 */
 
+/* ------------------------------------------------------------------------- */
+/* CifDet: generator/cifdet.py:26-52 with CifDetHr (cif_hr.py:84-100),      */
+/* CifDetSeeds (cif_seeds.py:67-90) and nms.Detection (nms.py:60-102).                    */
+/* field: (C,7,H,W) channels [v, x, y, _, w, h, _].                                       */
+
+typedef struct {
+  float cif_th;            /* CifHr.v_threshold        */
+  float seed_th;           /* CifSeeds.threshold       */
+  float seed_score_scale;  /* CifSeeds.score_scale     */
+  float cif_min_scale;     /* FieldConfig.cif_min_scales[0] */
+  float suppression;       /* nms.Detection.suppression       0.1 */
+  float suppression_soft;  /* nms.Detection.suppression_soft  0.3 */
+  float instance_th;       /* nms.Detection.instance_threshold 0.1 */
+  float iou_th;            /* nms.Detection.iou_threshold     0.7 */
+  float iou_th_soft;       /* nms.Detection.iou_threshold_soft 0.5 */
+  int do_nms;
+  int stride;
+} orc_det_config;
+
+int orc_cifdet_hr(const float *cif, int C_, int H, int W, const orc_det_config *cfg, float *hr) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  long n = (long)H * W;
+  float *buf = (float *)malloc(sizeof(float) * 4 * (size_t)n);
+  if (!buf) return ORC_ERR_ARG;
+  float *sx = buf, *sy = buf + n, *ss = buf + 2 * n, *sv = buf + 3 * n;
+  float stride = (float)cfg->stride;
+  memset(hr, 0, sizeof(float) * (size_t)C_ * hh * hw);
+  for (int f = 0; f < C_; f++) {
+    const float *p = cif + (size_t)f * 7 * n;
+    long k = 0;
+    for (long c = 0; c < n; c++) {
+      if (!(p[c] > cfg->cif_th)) continue;                          /* cif_hr.py:86 */
+      if (cfg->cif_min_scale != 0.0f) {                             /* :87-89 */
+        float lim = cfg->cif_min_scale / stride;
+        if (!(p[4 * n + c] > lim) || !(p[5 * n + c] > lim)) continue;
+      }
+      float w = p[4 * n + c], h = p[5 * n + c];
+      sx[k] = p[n + c] * stride;                                    /* :92 */
+      sy[k] = p[2 * n + c] * stride;                                /* :93 */
+      float m = (w != w) ? w : ((h != h) ? h : (w < h ? w : h));    /* np.minimum propagates NaN */
+      float sg = 0.1f * m;
+      sg = sg * stride;
+      ss[k] = (sg != sg) ? sg : (1.0f > sg ? 1.0f : sg);            /* np.maximum :94 */
+      sv[k] = p[c] / 16.0f / 1.0f;                                  /* :100 */
+      k++;
+    }
+    splat_gauss_with_max(hr + (size_t)f * hh * hw, hh, hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
+  }
+  free(buf);
+  return ORC_OK;
+}
+
+static int det_seed_cmp_desc(const void *a, const void *b) {
+  const float *p = (const float *)a, *q = (const float *)b;
+  for (int i = 0; i < 6; i++) {
+    if (p[i] > q[i]) return -1;
+    if (p[i] < q[i]) return 1;
+  }
+  return 0;
+}
+
+/* out: cap x 6 floats (v, f, x, y, w, h) sorted like sorted(seeds, reverse=True) */
+long orc_cifdet_seeds(const float *cif, int C_, int H, int W, const float *hr,
+                      const orc_det_config *cfg, float *out, long cap) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  long n = (long)H * W, k = 0;
+  float stride = (float)cfg->stride;
+  for (int f = 0; f < C_; f++) {
+    const float *p = cif + (size_t)f * 7 * n;
+    for (long c = 0; c < n; c++) {
+      float conf = p[c];
+      if (!(conf > cfg->seed_th)) continue;                            /* cif_seeds.py:74 */
+      if (cfg->cif_min_scale != 0.0f) {                                /* :75-77 */
+        float lim = cfg->cif_min_scale / stride;
+        if (!(p[4 * n + c] > lim) || !(p[5 * n + c] > lim)) continue;
+      }
+      float x = p[n + c] * stride, y = p[2 * n + c] * stride;
+      float hv = scalar_value_at(hr + (size_t)f * hh * hw, hh, hw, x, y, 0.0f); /* :79 */
+      float a = 0.9f * hv, b = 0.1f * conf;
+      float v = a + b;                                                 /* :80 */
+      if (cfg->seed_score_scale != 1.0f) v = v * cfg->seed_score_scale; /* :81-82 */
+      if (!(v > cfg->seed_th)) continue;                               /* :83 */
+      if (k >= cap) return ORC_ERR_CAPACITY;
+      float *o = out + 6 * k++;
+      o[0] = v; o[1] = (float)f; o[2] = x; o[3] = y;
+      o[4] = p[4 * n + c] * stride; o[5] = p[5 * n + c] * stride;      /* :84 */
+    }
+  }
+  qsort(out, (size_t)k, 6 * sizeof(float), det_seed_cmp_desc);
+  return k;
+}
+
+/* nms.Detection.bbox_iou for one pair, float32 -- nms.py:67-77 */
+static float det_iou(const float *a, const float *b) {
+  float x1 = a[0] > b[0] ? a[0] : b[0];
+  float y1 = a[1] > b[1] ? a[1] : b[1];
+  float ax2 = a[0] + a[2], bx2 = b[0] + b[2];
+  float ay2 = a[1] + a[3], by2 = b[1] + b[3];
+  float x2 = ax2 < bx2 ? ax2 : bx2;
+  float y2 = ay2 < by2 ? ay2 : by2;
+  if (a[0] != a[0] || b[0] != b[0]) x1 = a[0] + b[0];        /* np.maximum / np.minimum propagate NaN */
+  if (a[1] != a[1] || b[1] != b[1]) y1 = a[1] + b[1];
+  if (ax2 != ax2 || bx2 != bx2) x2 = ax2 + bx2;
+  if (ay2 != ay2 || by2 != by2) y2 = ay2 + by2;
+  float dx = x2 - x1, dy = y2 - y1;
+  float mx = (dx != dx) ? dx : (0.0f > dx ? 0.0f : dx);
+  float my = (dy != dy) ? dy : (0.0f > dy ? 0.0f : dy);
+  float inter = mx * my;
+  float area_a = a[2] * a[3], area_b = b[2] * b[3];
+  float den = area_a + area_b;
+  den = den - inter;
+  den = den + 1e-5f;
+  return inter / den;
+}
+
+/* Stable sort of indices by descending score (sorted(key=-score)). */
+static void det_sort(int *order, const float *score, int n) {
+  for (int i = 1; i < n; i++) {
+    int o = order[i], j = i;
+    while (j > 0 && -score[order[j - 1]] > -score[o]) { order[j] = order[j - 1]; j--; }
+    order[j] = o;
+  }
+}
+
+/* Whole CifDet decode of one image.  pre_*: annotations before nms (seed order);
+ * det_*: after nms.Detection.  Returns the number of final detections or < 0. */
+int orc_cifdet_decode(const float *cif, int C_, int H, int W, const orc_det_config *cfg,
+                      float *hr, float *seeds, long seed_cap, long *n_seeds_out,
+                      int ann_cap, int *pre_field, float *pre_score, float *pre_box, int *n_pre_out,
+                      int *det_field, float *det_score, float *det_box) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  int rc = orc_cifdet_hr(cif, C_, H, W, cfg, hr);
+  if (rc) return rc;
+  long ns = orc_cifdet_seeds(cif, C_, H, W, hr, cfg, seeds, seed_cap);
+  if (ns < 0) return (int)ns;
+  *n_seeds_out = ns;
+  orc_occ occ;
+  if ((rc = occ_init(&occ, C_, hh, hw))) return rc;
+  occ.min_scale_reduced = 1.0f;                      /* Occupancy(shape, 2, min_scale=2.0) cifdet.py:36 */
+  int n = 0;
+  for (long i = 0; i < ns; i++) {                    /* cifdet.py:39-44 */
+    const float *sd = seeds + 6 * i;
+    int f = (int)sd[1];
+    float x = sd[2], y = sd[3], w = sd[4], h = sd[5];
+    if (occ_get(&occ, f, x, y)) continue;
+    if (n >= ann_cap) { free(occ.m); return ORC_ERR_CAPACITY; }
+    pre_field[n] = f; pre_score[n] = sd[0];
+    pre_box[4 * n] = x - w / 2.0f; pre_box[4 * n + 1] = y - h / 2.0f;
+    pre_box[4 * n + 2] = w; pre_box[4 * n + 3] = h;
+    n++;
+    float m = (h < w) ? h : w;                       /* Python min(w, h) */
+    occ_set(&occ, f, x, y, 0.1f * m);
+  }
+  free(occ.m);
+  *n_pre_out = n;
+  if (!cfg->do_nms) {
+    for (int i = 0; i < n; i++) {
+      det_field[i] = pre_field[i]; det_score[i] = pre_score[i];
+      memcpy(det_box + 4 * i, pre_box + 4 * i, 4 * sizeof(float));
+    }
+    return n;
+  }
+  /* nms.Detection.annotations -- nms.py:79-102 */
+  int *order = (int *)malloc(sizeof(int) * (size_t)(n + 1));
+  float *score = (float *)malloc(sizeof(float) * (size_t)(n + 1));
+  int m = 0;
+  for (int i = 0; i < n; i++)
+    if (pre_score[i] >= cfg->instance_th) order[m++] = i;            /* :82 */
+  for (int i = 0; i < n; i++) score[i] = pre_score[i];
+  det_sort(order, score, m);                                         /* :85 */
+  for (int i = 1; i < m; i++) {                                      /* :88-96 */
+    float max_iou = -1.0f;
+    int any_nan = 0;
+    for (int j = 0; j < i; j++) {
+      if (!(score[order[j]] >= cfg->instance_th)) continue;
+      float iou = det_iou(pre_box + 4 * order[i], pre_box + 4 * order[j]);
+      if (iou != iou) any_nan = 1;
+      if (iou > max_iou) max_iou = iou;
+    }
+    if (any_nan) continue;                                           /* np.max -> NaN, both tests false */
+    if (max_iou > cfg->iou_th) score[order[i]] = score[order[i]] * cfg->suppression;
+    else if (max_iou > cfg->iou_th_soft) score[order[i]] = score[order[i]] * cfg->suppression_soft;
+  }
+  int k = 0;
+  for (int i = 0; i < m; i++)
+    if (score[order[i]] >= cfg->instance_th) order[k++] = order[i];  /* :98 */
+  det_sort(order, score, k);                                         /* :99 */
+  for (int i = 0; i < k; i++) {
+    det_field[i] = pre_field[order[i]]; det_score[i] = score[order[i]];
+    memcpy(det_box + 4 * i, pre_box + 4 * order[i], 4 * sizeof(float));
+  }
+  free(order); free(score);
+  return k;
+}
+
+int orc_det_config_size(void) { return (int)sizeof(orc_det_config); }
+
 void orc_scalar_square_add_gauss_with_max(float *field, long fh, long fw, const float *x,
                                           const float *y, const float *sigma, const float *v,
                                           long n, float truncate, float max_value) {
@@ -853,7 +1051,7 @@ int orc_occupancy_get(const unsigned char *field, long fh, long fw, float x, flo
 }
 
 void orc_occupancy_set(unsigned char *field, long fh, long fw, float x, float y, float sigma) {
-  orc_occ o = {field, 1, fh, fw};
+  orc_occ o = {field, 1, fh, fw, 2.0f};
   occ_set(&o, 0, x, y, sigma);
 }
 

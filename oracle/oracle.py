@@ -45,6 +45,28 @@ class Config(C.Structure):
             setattr(self, k, v)
 
 
+class DetConfig(C.Structure):
+    """Mirror of ``orc_det_config``; defaults = the reference's class attributes with the
+    thresholds the test suite configures (CifHr.v_threshold 0.1, CifSeeds.threshold 0.2)."""
+    _fields_ = [
+        ('cif_th', C.c_float), ('seed_th', C.c_float), ('seed_score_scale', C.c_float),
+        ('cif_min_scale', C.c_float), ('suppression', C.c_float), ('suppression_soft', C.c_float),
+        ('instance_th', C.c_float), ('iou_th', C.c_float), ('iou_th_soft', C.c_float),
+        ('do_nms', C.c_int), ('stride', C.c_int),
+    ]
+
+    def __init__(self, **kw):
+        super().__init__()
+        base = dict(cif_th=0.1, seed_th=0.2, seed_score_scale=1.0, cif_min_scale=0.0,
+                    suppression=0.1, suppression_soft=0.3, instance_th=0.1, iou_th=0.7,
+                    iou_th_soft=0.5, do_nms=1, stride=8)
+        base.update(kw)
+        for k, v in base.items():
+            if not any(k == name for name, _ in self._fields_):
+                raise TypeError('unknown oracle option %r' % k)
+            setattr(self, k, v)
+
+
 def build(force=False):
     src = os.path.join(HERE, 'cifcaf_oracle.c')
     hdr = os.path.join(HERE, '..', 'include', 'pifpaf_detmath.h')
@@ -66,6 +88,7 @@ def lib():
         build()
         _lib = C.CDLL(LIB_PATH)
         assert _lib.orc_config_size() == C.sizeof(Config), 'orc_config layout mismatch'
+        assert _lib.orc_det_config_size() == C.sizeof(DetConfig), 'orc_det_config layout mismatch'
         _lib.orc_seeds.restype = C.c_long
         _lib.orc_caf_center_s.restype = C.c_long
         _lib.orc_annotation_score.restype = C.c_double
@@ -199,3 +222,40 @@ def annotation_score(data):
 
 def detexp(x):
     return lib().orc_detexp(C.c_float(float(x)))
+
+
+class Detected:
+    """Everything the oracle observed for one image of the CifDet path."""
+    __slots__ = ('hr', 'seeds', 'pre_field', 'pre_score', 'pre_box', 'field', 'score', 'box')
+
+
+def cifdet_decode(field, cfg=None, *, ann_cap=4096):
+    """CifDet decode of one image: ``field (C, 7, H, W)`` -> ``Detected``."""
+    cfg = cfg or DetConfig()
+    field = _f32(field)
+    Cn, seven, H, W = field.shape
+    assert seven == 7
+    hr = np.empty((Cn, (H - 1) * cfg.stride + 1, (W - 1) * cfg.stride + 1), np.float32)
+    seed_cap = Cn * H * W
+    seeds_ = np.empty((seed_cap, 6), np.float32)
+    n_seeds, n_pre = C.c_long(0), C.c_int(0)
+    pre_field = np.zeros(ann_cap, np.int32)
+    pre_score = np.zeros(ann_cap, np.float32)
+    pre_box = np.zeros((ann_cap, 4), np.float32)
+    det_field = np.zeros(ann_cap, np.int32)
+    det_score = np.zeros(ann_cap, np.float32)
+    det_box = np.zeros((ann_cap, 4), np.float32)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    n = lib().orc_cifdet_decode(vp(field), Cn, H, W, C.byref(cfg), vp(hr), vp(seeds_),
+                                C.c_long(seed_cap), C.byref(n_seeds), ann_cap, vp(pre_field),
+                                vp(pre_score), vp(pre_box), C.byref(n_pre), vp(det_field),
+                                vp(det_score), vp(det_box))
+    if n < 0:
+        raise RuntimeError('oracle cifdet decode failed with code %d' % n)
+    out = Detected()
+    out.hr = hr
+    out.seeds = seeds_[:n_seeds.value].copy()
+    out.pre_field, out.pre_score = pre_field[:n_pre.value].copy(), pre_score[:n_pre.value].copy()
+    out.pre_box = pre_box[:n_pre.value].copy()
+    out.field, out.score, out.box = det_field[:n].copy(), det_score[:n].copy(), det_box[:n].copy()
+    return out

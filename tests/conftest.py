@@ -87,7 +87,8 @@ def configured_decoder():
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
 _ALL_GOLDEN = sorted(n[:-4] for n in os.listdir(GOLDEN_DIR) if n.endswith('.npz')) \
     if os.path.isdir(GOLDEN_DIR) else []
-GOLDEN_NAMES = [n for n in _ALL_GOLDEN if not n.startswith(('head_', 'inverse_'))]   # decoder cases
+GOLDEN_NAMES = [n for n in _ALL_GOLDEN if not n.startswith(('head_', 'inverse_', 'det_'))]   # pose decoder cases
+DET_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('det_')]            # CifDet cases
 HEAD_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('head_')]       # head epilogue cases
 TOL_HEAD_REL = 2e-6  # sigmoid / exp of the head epilogue against torch's CPU kernels
 
@@ -209,3 +210,15 @@ class HorizontalSwap:
         out = np.zeros(keypoints.shape)
         out[self.target] = keypoints
         return out
+
+
+def det_golden(name):
+    """(field, golden npz) of a CifDet fixture; the field is regenerated and hash-checked."""
+    import hashlib
+    from openpifpaf_b200.encoder import synthetic_det_fields
+    g = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    field, _ = synthetic_det_fields(tuple(int(v) for v in g['image_hw']), int(g['n_boxes']),
+                                    box_seed=int(g['box_seed']), jitter_seed=int(g['jitter_seed']),
+                                    n_categories=int(g['n_categories']))
+    assert hashlib.sha256(field.tobytes()).hexdigest() == str(g['field_sha256'])
+    return field, g

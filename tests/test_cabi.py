@@ -100,8 +100,11 @@ def test_argument_validation_returns_codes(lib):
                                C.byref(c), C.byref(p), None) == _lib.PP_ERR_ARG
     assert lib.pp_cifhr_accumulate(None, None, None, 0, C.byref(s), C.byref(c), C.byref(p),
                                    None, None) == _lib.PP_ERR_ARG
-    too_many = _lib.Shape(1, 33, 19, 11, 11, 8)
-    assert lib.pp_default_caps(C.byref(too_many), C.byref(c)) == _lib.PP_ERR_ARG
+    too_many = _lib.Shape(1, 33, 19, 11, 11, 8)      # > PP_MAX_F keypoint types: pose entries refuse,
+    assert lib.pp_default_caps(C.byref(too_many), C.byref(c)) == _lib.PP_OK    # detection may have 256
+    assert lib.pp_workspace_bytes(C.byref(too_many), C.byref(c)) == 0
+    assert lib.pp_cifdet_workspace_bytes(C.byref(too_many), C.byref(c)) > 0
+    assert lib.pp_default_caps(C.byref(_lib.Shape(1, 257, 0, 11, 11, 8)), C.byref(c)) == _lib.PP_ERR_ARG
 
 
 def test_no_cpu_fallback_in_product():

@@ -82,3 +82,22 @@ def test_inverse_oracle_matches_reference_golden(kind):
     assert np.array_equal(got[0], g[kind + '_data'])
     assert np.array_equal(got[1], g[kind + '_scales'])
     assert np.array_equal(got[2], g[kind + '_dxy'])
+
+
+from conftest import DET_GOLDEN_NAMES, det_golden  # noqa: E402
+
+
+@pytest.mark.parametrize('name', DET_GOLDEN_NAMES)
+def test_det_oracle_matches_reference_golden(oracle, name):
+    """orc_cifdet_decode against the reference's CifDet outputs: everything bit-identical."""
+    field, g = det_golden(name)
+    o = oracle.cifdet_decode(field, oracle.DetConfig(cif_min_scale=float(g['cif_min_scale'])))
+    assert sha256(o.hr) == str(g['hr_sha256'])
+    assert np.array_equal(o.seeds, g['seeds'])
+    assert np.array_equal(o.field, g['det_field'])
+    assert np.array_equal(o.score, g['det_score'])
+    assert np.array_equal(o.box, g['det_box'])
+
+
+def test_det_golden_covers_the_cases():
+    assert len(DET_GOLDEN_NAMES) >= 5

@@ -528,3 +528,93 @@ def test_generator_batch_with_raw_heads(oracle, coco_skeleton, configured_decode
         assert len(g) == len(w)
         for a, b in zip(g, w):
             assert np.array_equal(a.data, b.data)
+
+
+@pytest.fixture
+def configured_det():
+    """openpifpaf_b200.decoder with the detection thresholds of the golden cases."""
+    import openpifpaf_b200.decoder as decoder
+    saved = (decoder.CifHr.v_threshold, decoder.CifSeeds.threshold, decoder.CifSeeds.score_scale)
+    decoder.CifHr.v_threshold, decoder.CifSeeds.threshold, decoder.CifSeeds.score_scale = 0.1, 0.2, 1.0
+    yield decoder
+    decoder.CifHr.v_threshold, decoder.CifSeeds.threshold, decoder.CifSeeds.score_scale = saved
+
+
+def _det_case_names():
+    from conftest import DET_GOLDEN_NAMES
+    return DET_GOLDEN_NAMES
+
+
+@pytest.mark.parametrize('name', _det_case_names())
+def test_cifdet_matches_oracle_and_golden(oracle, configured_det, name):
+    """pp_cifdet_decode_batch: hr, seeds, detections before and after nms.Detection bit-identical
+    to the oracle, and the final detections to the reference's golden outputs."""
+    from conftest import det_golden
+    from openpifpaf_b200.decoder.generator.cifdet import run_cifdet
+    field, g = det_golden(name)
+    min_scale = float(g['cif_min_scale'])
+    o = oracle.cifdet_decode(field, oracle.DetConfig(cif_min_scale=min_scale))
+    t = run_cifdet(field[None], 8, min_scale=min_scale,
+                   want=('hr', 'seeds', 'n_seeds', 'pre_field', 'pre_score', 'pre_box', 'n_pre'))
+    assert np.array_equal(t['hr'][0].cpu().numpy(), o.hr)
+    ns = int(t['n_seeds'][0])
+    assert np.array_equal(t['seeds'][0, :ns].cpu().numpy(), o.seeds)
+    npre = int(t['n_pre'][0])
+    assert npre == len(o.pre_field)
+    assert np.array_equal(t['pre_field'][0, :npre].cpu().numpy(), o.pre_field)
+    assert np.array_equal(t['pre_score'][0, :npre].cpu().numpy(), o.pre_score)
+    assert np.array_equal(t['pre_box'][0, :npre].cpu().numpy(), o.pre_box)
+    n = int(t['n_det'][0])
+    for got, want, gold in ((t['det_field'], o.field, g['det_field']), (t['det_score'], o.score, g['det_score']),
+                            (t['det_box'], o.box, g['det_box'])):
+        got = got[0, :n].cpu().numpy()
+        assert np.array_equal(got, want) and np.array_equal(got, gold)
+
+
+def test_cifdet_public_api_batch_and_standalone_nms(oracle, configured_det):
+    """CifDet.__call__ / decode_batch (AnnotationDet objects) on a ragged batch, batch-composition
+    invariance, and nms.Detection.annotations on shuffled detections."""
+    from openpifpaf_b200.annotation import AnnotationDet
+    from openpifpaf_b200.encoder import synthetic_det_fields
+    decoder = configured_det
+    cats = ['c%d' % i for i in range(6)]
+    dec = decoder.CifDet(decoder.FieldConfig(), cats)
+    batch = [synthetic_det_fields((321, 321), 3 + 4 * b, box_seed=60 + b, jitter_seed=70 + b,
+                                  n_categories=6)[0] for b in range(5)]
+    oracles = [oracle.cifdet_decode(f) for f in batch]
+    result = dec.decode_batch(torch.from_numpy(np.stack(batch)).cuda())
+    single = dec([batch[3]])
+    assert len(result) == 5
+    for anns, o in zip(result, oracles):
+        assert len(anns) == len(o.field) >= 2
+        assert [a.field_i for a in anns] == o.field.tolist()
+        assert np.array_equal(np.array([a.score for a in anns], np.float32), o.score)
+        assert np.array_equal(np.stack([a.bbox for a in anns]), o.box)
+        assert anns[0].json_data()['category'] == cats[anns[0].field_i]
+    assert [a.field_i for a in single] == [a.field_i for a in result[3]]
+    assert np.array_equal(np.stack([a.bbox for a in single]), np.stack([a.bbox for a in result[3]]))
+    # standalone NMS: the pre-NMS detections in a shuffled order give the same survivors
+    o = oracles[4]
+    perm = np.random.RandomState(1).permutation(len(o.pre_field))
+    anns = [AnnotationDet(cats).set(int(o.pre_field[i]), o.pre_score[i], o.pre_box[i].copy()) for i in perm]
+    kept = decoder.nms.Detection().annotations(anns)
+    assert len(kept) == len(o.field)
+    assert np.array_equal(np.array([a.score for a in kept], np.float32), o.score)
+    assert np.array_equal(np.stack([a.bbox for a in kept]), o.box)
+    assert all(any(k is a for a in anns) for k in kept), 'the same objects come back'
+
+
+def test_cifdet_many_categories_and_capacity(oracle, configured_det):
+    """91 categories (COCO detection) decode; a too-small result capacity is reported."""
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.decoder.generator.cifdet import run_cifdet
+    from openpifpaf_b200.encoder import synthetic_det_fields
+    field, _ = synthetic_det_fields((321, 481), 14, box_seed=81, jitter_seed=82, n_categories=91)
+    o = oracle.cifdet_decode(field)
+    t = run_cifdet(field[None], 8)
+    n = int(t['n_det'][0])
+    assert n == len(o.field) >= 5
+    assert np.array_equal(t['det_field'][0, :n].cpu().numpy(), o.field)
+    assert np.array_equal(t['det_score'][0, :n].cpu().numpy(), o.score)
+    with pytest.raises(_lib.PifPafError):
+        run_cifdet(field[None], 8, ann_cap=3)

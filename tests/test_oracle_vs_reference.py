@@ -284,3 +284,21 @@ def test_json_data_batch(ref, coco_skeleton):
     anns = dec.CifCaf(dec.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)([cif, caf])
     ours = [Annotation(COCO_KEYPOINTS, coco_skeleton).set(a.data.copy(), a.joint_scales.copy()) for a in anns]
     assert json_data_batch(ours) == [a.json_data() for a in anns]
+
+
+@pytest.mark.parametrize('hw,nb,seed,ncat,min_scale', [((241, 321), 6, 31, 4, 0.0), ((481, 481), 25, 32, 8, 0.0),
+                                                       ((321, 321), 10, 33, 91, 48.0)])
+def test_cifdet_decode(ref, oracle, hw, nb, seed, ncat, min_scale):
+    """orc_cifdet_decode == CifDetHr / CifDetSeeds / CifDet / nms.Detection of the running reference
+    (cif_hr.py:84-100, cif_seeds.py:67-90, cifdet.py:26-52, nms.py:60-102), bit for bit."""
+    from oracle.gen_golden_det import run_reference
+    from openpifpaf_b200.encoder import synthetic_det_fields
+    field, _ = synthetic_det_fields(hw, nb, box_seed=seed, jitter_seed=seed + 100, n_categories=ncat)
+    hr, seeds, anns = run_reference(ref, field, min_scale)
+    o = oracle.cifdet_decode(field, oracle.DetConfig(cif_min_scale=min_scale))
+    assert np.array_equal(o.hr, hr)
+    assert np.array_equal(o.seeds, seeds)
+    assert len(anns) == len(o.field) and (nb == 0 or len(anns) >= 2)
+    assert np.array_equal(o.field, np.array([a.field_i for a in anns], np.int32))
+    assert np.array_equal(o.score, np.array([a.score for a in anns], np.float32))
+    assert np.array_equal(o.box, np.array([a.bbox for a in anns], np.float32).reshape(-1, 4))
