@@ -225,6 +225,30 @@ int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, do
 int pp_head_epilogue(const float *d_x, float *d_out, int32_t B, int32_t n_fields, int32_t n_vectors,
                      int32_t h, int32_t w, int32_t quad, void *stream);
 
+/* ---- multi-scale FieldConfig (decoder/factory.py:153-180, field_config.py) ---------------------
+ * One field set per entry of FieldConfig.cif_indices / caf_indices: its own resolution, stride and
+ * filters.  Set 0 defines the shape of the hr map (cif_hr.py:44-51). */
+#define PP_MAX_SETS 16
+typedef struct pp_field_set {
+  const float *cif;        /* device (B,F,5,H,W) */
+  const float *caf;        /* device (B,L,9,H,W) */
+  int32_t H, W, stride;    /* FieldConfig.cif_strides[k] (= caf_strides[k]) */
+  float cif_min_scale;     /* FieldConfig.cif_min_scales[k]                 */
+  float caf_min_distance;  /* FieldConfig.caf_min_distances[k]              */
+  float caf_max_distance;  /* FieldConfig.caf_max_distances[k]; 0 = None    */
+} pp_field_set;
+
+/* pp_decode_batch over several field sets: CifHr maps merged with np.maximum (cif_hr.py:59-78;
+ * hflip_pairs != 0: sets (k, k + n/2) are accumulated together with v / neighbors / 2, the
+ * reference's 10-head case), seeds of all sets in one sorted list (cif_seeds.py:56-65), candidate
+ * lists concatenated in set order (caf_scored.py:89-98).  `s` carries B, F, L and the H, W, stride
+ * of set 0; capacities must cover the sums over the sets (seed_cap, caf_cap) and the largest
+ * group (src_cap). */
+int pp_decode_batch_multiscale(const pp_field_set *sets, int32_t n_sets, int32_t hflip_pairs,
+                               const pp_skeleton *sk, const pp_outputs *d_out, void *d_ws,
+                               size_t ws_bytes, const pp_shape *s, const pp_caps *c,
+                               const pp_params *p, void *stream);
+
 /* ---- CifDet (detection decoder), generator/cifdet.py:17-52 ---------------------------------
  * Fields are (B, C, 7, H, W) float32 with channels [v, x, y, _, w, h, _] in field units, C
  * categories (<= PP_MAX_CATEGORIES).  pp_shape.F carries C, pp_shape.L is ignored. */

@@ -40,6 +40,12 @@ class Inverse(C.Structure):
     _fields_ = [('meta', C.c_void_p), ('hflip_target', C.c_void_p)]
 
 
+class FieldSet(C.Structure):
+    _fields_ = [('cif', C.c_void_p), ('caf', C.c_void_p), ('H', C.c_int32), ('W', C.c_int32),
+                ('stride', C.c_int32), ('cif_min_scale', C.c_float), ('caf_min_distance', C.c_float),
+                ('caf_max_distance', C.c_float)]
+
+
 class DetParams(C.Structure):
     _fields_ = [('cif_threshold', C.c_float), ('seed_threshold', C.c_float),
                 ('seed_score_scale', C.c_float), ('cif_min_scale', C.c_float),
@@ -152,6 +158,8 @@ def lib():
     l.pp_detection_nms_workspace_bytes.argtypes = [i32, i32]
     l.pp_detection_nms_workspace_bytes.restype = sz
     l.pp_detection_nms.argtypes = [vp] * 10 + [sz, i32, i32, P(DetParams), vp]
+    l.pp_decode_batch_multiscale.argtypes = [P(FieldSet), i32, i32, P(Skeleton), P(Outputs), vp, sz,
+                                             P(Shape), P(Caps), P(Params), vp]
     l.pp_sizeof.argtypes = [i32]
     l.pp_sizeof.restype = i32
     l.pp_annotations_inverse.argtypes = [vp, vp, vp, vp, vp, C.POINTER(Inverse), i32, i32, i32, vp]
@@ -194,7 +202,7 @@ EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
     'pp_stage_name', 'pp_decode_launch_count',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
-    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',

@@ -381,13 +381,20 @@ int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, do
                     d_ws, *s, *c, *p, st);
 }
 
-int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *sk,
-                    const pp_outputs *o, void *d_ws, size_t ws_bytes, const pp_shape *s,
-                    const pp_caps *c, const pp_params *p, void *stream) {
-  if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !o || !d_cif || !d_caf || !d_ws ||
-      sk->L != s->L)
+// One decode over n_sets field sets (multi-scale FieldConfig, decoder/factory.py:153-180); the plain
+// single-scale decode is the case n_sets = 1.
+static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, const pp_skeleton *sk,
+                       const pp_outputs *o, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                       const pp_caps *c, const pp_params *p, void *stream) {
+  if (!shape_ok(s) || !caps_ok(s, c) || !p || !sk || !o || !sets || n_sets < 1 || n_sets > PP_MAX_SETS ||
+      !d_ws || sk->L != s->L)
     return PP_ERR_ARG;
   if (!o->ann_data || !o->ann_scales || !o->n_ann || !o->status) return PP_ERR_ARG;
+  if (hflip_pairs && (n_sets & 1)) return PP_ERR_ARG;
+  for (int k = 0; k < n_sets; k++)
+    if (!sets[k].cif || !sets[k].caf || sets[k].H <= 0 || sets[k].W <= 0 || sets[k].stride <= 0)
+      return PP_ERR_ARG;
+  if (sets[0].H != s->H || sets[0].W != s->W || sets[0].stride != s->stride) return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const bool need_hr = o->hr == nullptr;
   DecodeWs w = layout(d_ws, *s, *c, need_hr);
@@ -399,15 +406,38 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   float *bwd = o->caf_bwd ? o->caf_bwd : w.bwd;
   int *nfwd = o->n_caf_fwd ? o->n_caf_fwd : w.nfwd;
   int *nbwd = o->n_caf_bwd ? o->n_caf_bwd : w.nbwd;
+  auto set_shape = [&](int k) {
+    pp_shape q = *s;
+    q.H = sets[k].H; q.W = sets[k].W; q.stride = sets[k].stride;
+    return q;
+  };
 
   PP_CUDA_CHECK(cudaMemsetAsync(o->status, 0, (size_t)s->B * sizeof(int), st));
   prof_begin_step(p->profile);
   int rc;
-  if ((rc = cifhr_launch(d_cif, hr, w.stage, *s, *c, *p, o->status, st))) return rc;
-  if ((rc = seeds_launch(d_cif, hr, seeds, n_seeds, w.stage, *s, *c, *p, o->status, st))) return rc;
-  if ((rc = caf_scored_launch(d_caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, *s, *c, *p,
-                              o->status, st)))
-    return rc;
+  // CifHr.fill (cif_hr.py:66-78): one map per group, merged with np.maximum; with 10 heads the
+  // groups are the hflip pairs (i, i + 5), each accumulated with v / neighbors / 2
+  const int n_groups = hflip_pairs ? n_sets / 2 : n_sets;
+  for (int g = 0; g < n_groups; g++) {
+    const pp_shape q = set_shape(g);
+    const float *second = hflip_pairs ? sets[g + n_groups].cif : nullptr;
+    if (second && (sets[g + n_groups].H != q.H || sets[g + n_groups].W != q.W)) return PP_ERR_ARG;
+    if ((rc = cifhr_launch_ex(sets[g].cif, second, hr, w.stage, q, *s, *c, *p, sets[g].cif_min_scale,
+                              o->status, st, 0, g > 0)))
+      return rc;
+  }
+  // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
+  for (int k = 0; k < n_sets; k++)
+    if ((rc = seeds_collect_launch(sets[k].cif, hr, w.stage, set_shape(k), *s, *c, *p, sets[k].cif_min_scale,
+                                   k == 0, st, 0)))
+      return rc;
+  if ((rc = seeds_sort_launch(seeds, n_seeds, w.stage, s->B, *c, *p, o->status, st, 0))) return rc;
+  // CafScored.fill (caf_scored.py:89-98): lists concatenated over the heads
+  for (int k = 0; k < n_sets; k++)
+    if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, set_shape(k),
+                                   *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
+                                   o->status, st)))
+      return rc;
   AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
   if ((rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st))) return rc;
@@ -430,9 +460,11 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
   if (p->force_complete) {                                           // cifcaf.py:110-115
     // second CafScored(score_th=0.0001) into the workspace lists (the first
     // ones are no longer needed, or live in the caller's buffers)
-    if ((rc = caf_scored_launch(d_caf, hr, *sk, 0.0001f, w.fwd, w.nfwd, w.bwd, w.nbwd, *s, *c, *p,
-                                o->status, st)))
-      return rc;
+    for (int k = 0; k < n_sets; k++)
+      if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, 0.0001f, w.fwd, w.nfwd, w.bwd, w.nbwd, set_shape(k),
+                                     *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
+                                     o->status, st)))
+        return rc;
     if ((rc = caf_bin_launch(w.fwd, w.nfwd, w.bwd, w.nbwd, w.bin_rows, w.bin_start, *s, *c, st)))
       return rc;
     if ((rc = complete_launch(a, w.bin_rows, w.bin_start, w.nfwd, w.nbwd, w.cmp_data, w.cmp_scales,
@@ -447,6 +479,21 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
                                     s->B, s->F, c->ann_cap, st);
   prof_end_step(p->profile, st);
   return rc;
+}
+
+int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *sk,
+                    const pp_outputs *o, void *d_ws, size_t ws_bytes, const pp_shape *s,
+                    const pp_caps *c, const pp_params *p, void *stream) {
+  if (!s || !p) return PP_ERR_ARG;
+  pp_field_set one = {d_cif, d_caf, s->H, s->W, s->stride, p->cif_min_scale, p->caf_min_distance,
+                      p->caf_max_distance};
+  return decode_core(&one, 1, 0, sk, o, d_ws, ws_bytes, s, c, p, stream);
+}
+
+int pp_decode_batch_multiscale(const pp_field_set *sets, int32_t n_sets, int32_t hflip_pairs,
+                               const pp_skeleton *sk, const pp_outputs *o, void *d_ws, size_t ws_bytes,
+                               const pp_shape *s, const pp_caps *c, const pp_params *p, void *stream) {
+  return decode_core(sets, n_sets, hflip_pairs, sk, o, d_ws, ws_bytes, s, c, p, stream);
 }
 
 // ---- CifDet ------------------------------------------------------------------

@@ -23,7 +23,7 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
                   float *__restrict__ fwd, int *__restrict__ nfwd, float *__restrict__ bwd,
                   int *__restrict__ nbwd, pp_shape s, int cap, int hh, int hw, float th,
                   float cif_floor, float cif_floor_compl, float min_dist, int use_min, float max_dist,
-                  int use_max, int *__restrict__ status) {
+                  int use_max, int append, int *__restrict__ status) {
   __shared__ int wtot_f[kCafThreads / 32], wtot_b[kCafThreads / 32];
   const int bl = blockIdx.x;
   const int b = bl / s.L, l = bl - b * s.L;
@@ -35,7 +35,8 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
   float *fo = fwd + (size_t)bl * 9 * cap;
   float *bo = bwd + (size_t)bl * 9 * cap;
   const int lane = lane_id(), w = warp_id(), nw = blockDim.x >> 5;
-  int cnt_f = 0, cnt_b = 0;
+  // append: a later field set of a multi-scale configuration continues the lists (caf_scored.py:70,81)
+  int cnt_f = append ? nfwd[bl] : 0, cnt_b = append ? nbwd[bl] : 0;
 
   for (int base = 0; base < n; base += blockDim.x) {
     const int c = base + threadIdx.x;
@@ -212,18 +213,26 @@ int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, co
   return PP_OK;
 }
 
-int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
-                      float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
-                      const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {
-  const int hh = hr_h(s), hw = hr_w(s);
+int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
+                         float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
+                         const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_distance,
+                         float max_distance, int append, int *d_status, cudaStream_t st) {
+  const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const float stride = (float)s.stride;
   prof_mark(p.profile, kStCaf, st);
   caf_scored_kernel<<<s.B * s.L, kCafThreads, 0, st>>>(
       d_caf, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
-      p.cif_floor_compl, p.caf_min_distance / stride, p.caf_min_distance != 0.0f,
-      p.caf_max_distance / stride, p.caf_max_distance > 0.0f, d_status);
+      p.cif_floor_compl, min_distance / stride, min_distance != 0.0f, max_distance / stride,
+      max_distance > 0.0f, append, d_status);
   PP_LAUNCH_CHECK("caf_scored_kernel");
   return PP_OK;
+}
+
+int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
+                      float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
+                      const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {
+  return caf_scored_launch_ex(d_caf, d_hr, sk, score_th, d_fwd, d_nfwd, d_bwd, d_nbwd, s, s, c, p,
+                              p.caf_min_distance, p.caf_max_distance, 0, d_status, st);
 }
 
 }  // namespace pp

@@ -109,14 +109,17 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
 // ---------------------------------------------------------------------------
 // K1: ordered compaction of CIF sources per (image, field).
 __global__ void __launch_bounds__(kCompactThreads)
-cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src_cap, int hh, int hw,
+cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2, CifHrWs w, pp_shape s,
+                   int src_cap, int hh, int hw,
                    float v_th, float min_scale_over_stride, int use_min_scale, int det,
                    int *__restrict__ status) {
   extern __shared__ int sm_diff[];   // nstrips + 1 difference array
   __shared__ int warp_tot[kCompactThreads / 32];
   const int bf = blockIdx.x;
   const int n = s.H * s.W;
-  const float *p = cif + (size_t)bf * (det ? 7 : 5) * n;    // CifDet fields: [v, x, y, _, w, h, _]
+  // cif2 != NULL: a multi-scale hflip pair accumulated into one map, first all sources of cif, then
+  // of cif2, each with v / neighbors / 2 (cif_hr.py:55-57,66-70)
+  const float len_cifs = cif2 ? 2.0f : 1.0f;
   const float stride = (float)s.stride;
   for (int i = threadIdx.x; i <= w.nstrips; i += blockDim.x) sm_diff[i] = 0;
   __syncthreads();
@@ -124,6 +127,8 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
   float4 *oa = w.src_a + (size_t)bf * src_cap;
   int4 *ob = w.src_b + (size_t)bf * src_cap;
   int count = 0;
+  for (int pass = 0; pass < (cif2 ? 2 : 1); pass++) {
+  const float *p = (pass ? cif2 : cif) + (size_t)bf * (det ? 7 : 5) * n;   // CifDet: [v, x, y, _, w, h, _]
   for (int base = 0; base < n; base += blockDim.x) {
     int c = base + threadIdx.x;
     bool flag = false;
@@ -150,7 +155,7 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
           sg = __fmul_rn(__fmul_rn(0.5f, __ldg(p + 4 * n + c)), stride);
         }
         float sigma = (sg != sg) ? sg : fmaxf(1.0f, sg);          // np.maximum(1.0, .) :34
-        float cv = __fdiv_rn(conf, 16.0f);                        // v / neighbors / len_cifs :40
+        float cv = __fdiv_rn(__fdiv_rn(conf, 16.0f), len_cifs);   // v / neighbors / len_cifs :40
         // functional.pyx:122-125 with truncate = 1.0
         int minx = (int)clipf(__fsub_rn(cx, sigma), 0.0f, (float)(hw - 1));
         int maxx = (int)clipf(__fadd_rn(__fadd_rn(cx, sigma), 1.0f), (float)(minx + 1), (float)hw);
@@ -163,6 +168,7 @@ cif_compact_kernel(const float *__restrict__ cif, CifHrWs w, pp_shape s, int src
       }
     }
     count += total;
+  }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -312,7 +318,7 @@ __device__ __forceinline__ int consumer_flag_scan(bool flag, int *warp_tot, int 
 
 __global__ void __launch_bounds__(kSplatBlock)
 cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
-                   int hh, int hw, int buf_floats) {
+                   int hh, int hw, int buf_floats, int merge) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float *zero = reinterpret_cast<float *>(smem_raw);
   float *tiles = zero + kZeroFloats;                      // two tile buffers
@@ -333,6 +339,9 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
 
   if (warp == kSplatWarps) {
     // ---- producer warp: every empty strip, as TMA zero stores ---------------------
+    // merge (multi-scale, cif_hr.py:62 accumulated = np.maximum(ta, accumulated)): an empty strip
+    // of this scale leaves the map as it is
+    if (merge) return;
     const int total = n_planes * n_groups;
     for (;;) {
       int item = 0;
@@ -426,6 +435,12 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
         consumer_sync();                                   // patches done before masks are cleared again
       }
     }
+    if (merge) {          // np.maximum with the map of the scales before (NaN from either side wins)
+      for (size_t i = g.gs + tid; i < g.ge; i += kSplatThreads) {
+        const float a = tile[i - g.ga], o = hr[i];
+        tile[i - g.ga] = (a != a) ? a : ((o != o) ? o : fmaxf(a, o));
+      }
+    }
     fence_async_smem();
     consumer_sync();
     emit_strip(hr, tile, g);
@@ -434,10 +449,14 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   if (tid == 0) bulk_wait_read<0>();
 }
 
-int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
-                 const pp_params &p, int *d_status, cudaStream_t st, int det) {
-  CifHrWs w = carve(d_ws, s, c);
-  const int hh = hr_h(s), hw = hr_w(s);
+// s: shape of the field set (B, F, H, W, stride); s_hr: the shape that defines the hr map (set 0 of a
+// multi-scale configuration, else s itself).  d_cif2: second field of an hflip pair or NULL.
+// merge: np.maximum into the existing map instead of overwriting it.
+int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
+                    const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
+                    int *d_status, cudaStream_t st, int det, int merge) {
+  CifHrWs w = carve(d_ws, s_hr, c);
+  const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
   if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
@@ -445,8 +464,8 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
-      d_cif, w, s, c.src_cap, hh, hw, p.cif_threshold, p.cif_min_scale / (float)s.stride,
-      p.cif_min_scale != 0.0f, det, d_status);
+      d_cif, d_cif2, w, s, c.src_cap, hh, hw, p.cif_threshold, min_scale / (float)s.stride,
+      min_scale != 0.0f, det, d_status);
   PP_LAUNCH_CHECK("cif_compact_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
@@ -463,9 +482,14 @@ int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s,
   if (grid > bf * n_groups) grid = bf * n_groups;
   prof_mark(p.profile, kStSplat, st);
   cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
-                                                    buf_floats);
+                                                    buf_floats, merge);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
   return PP_OK;
+}
+
+int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
+                 const pp_params &p, int *d_status, cudaStream_t st, int det) {
+  return cifhr_launch_ex(d_cif, nullptr, d_hr, d_ws, s, s, c, p, p.cif_min_scale, d_status, st, det, 0);
 }
 
 }  // namespace pp

@@ -166,41 +166,60 @@ size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det) {
   return n;
 }
 
-int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
-                 const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
-                 cudaStream_t st, int det) {
-  if (c.seed_cap >= (1 << 24) || s.F > 256) return PP_ERR_ARG;    // key layout: f:8 | index:24
+static SeedsWs seeds_carve(void *d_ws, int B, const pp_caps &c, int det) {
   SeedsWs w;
   char *q = (char *)d_ws;
-  w.raw = (float *)q; q += align_up((size_t)s.B * c.seed_cap * (det ? 6 : 5) * sizeof(float), 256);
-  w.n_raw = (int *)q; q += align_up((size_t)s.B * sizeof(int), 256);
+  w.raw = (float *)q; q += align_up((size_t)B * c.seed_cap * (det ? 6 : 5) * sizeof(float), 256);
+  w.n_raw = (int *)q; q += align_up((size_t)B * sizeof(int), 256);
   w.scratch = (uint64_t *)q;
   w.scratch_stride = pow2_ceil(c.seed_cap);
-  const int hh = hr_h(s), hw = hr_w(s), n = s.H * s.W;
+  return w;
+}
+
+int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, const pp_shape &s,
+                         const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
+                         int reset, cudaStream_t st, int det) {
+  if (c.seed_cap >= (1 << 24) || s.F > 256) return PP_ERR_ARG;    // key layout: f:8 | index:24
+  SeedsWs w = seeds_carve(d_ws, s.B, c, det);
+  const int hh = hr_h(s_hr), hw = hr_w(s_hr), n = s.H * s.W;
   prof_mark(p.profile, kStCollect, st);
-  PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
+  if (reset) PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
   int blocks = s.B * s.F * ((n + kCollectThreads - 1) / kCollectThreads);
   if (det)
     seeds_collect_kernel<6><<<blocks, kCollectThreads, 0, st>>>(
         d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-        p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, 0u);
+        min_scale / (float)s.stride, min_scale != 0.0f, 0u);
   else
     seeds_collect_kernel<5><<<blocks, kCollectThreads, 0, st>>>(
         d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-        p.cif_min_scale / (float)s.stride, p.cif_min_scale != 0.0f, p.seed_mask);
+        min_scale / (float)s.stride, min_scale != 0.0f, p.seed_mask);
   PP_LAUNCH_CHECK("seeds_collect_kernel");
+  return PP_OK;
+}
+
+int seeds_sort_launch(float *d_seeds, int *d_n_seeds, void *d_ws, int B, const pp_caps &c,
+                      const pp_params &p, int *d_status, cudaStream_t st, int det) {
+  SeedsWs w = seeds_carve(d_ws, B, c, det);
   // small capacities only need a small shared array
   size_t need = (size_t)(w.scratch_stride <= kSortSmemKeys ? w.scratch_stride : kSortSmemKeys) *
                 sizeof(uint64_t);
   prof_mark(p.profile, kStSort, st);
   if (det)
-    seeds_sort_kernel<6><<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
-                                                          c.seed_cap, w.scratch_stride, d_status);
+    seeds_sort_kernel<6><<<B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
+                                                        c.seed_cap, w.scratch_stride, d_status);
   else
-    seeds_sort_kernel<5><<<s.B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
-                                                          c.seed_cap, w.scratch_stride, d_status);
+    seeds_sort_kernel<5><<<B, kSortThreads, need, st>>>(w.raw, w.n_raw, d_seeds, d_n_seeds, w.scratch,
+                                                        c.seed_cap, w.scratch_stride, d_status);
   PP_LAUNCH_CHECK("seeds_sort_kernel");
   return PP_OK;
+}
+
+int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
+                 const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
+                 cudaStream_t st, int det) {
+  int rc = seeds_collect_launch(d_cif, d_hr, d_ws, s, s, c, p, p.cif_min_scale, 1, st, det);
+  if (rc) return rc;
+  return seeds_sort_launch(d_seeds, d_n_seeds, d_ws, s.B, c, p, d_status, st, det);
 }
 
 }  // namespace pp

@@ -9,7 +9,16 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c);
 // CifDetHr / CifDetSeeds (cif_hr.py:84-100, cif_seeds.py:67-90); seeds are 6 floats (v, f, x, y, w, h)
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
                  const pp_params &p, int *d_status, cudaStream_t st, int det = 0);
+int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
+                    const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
+                    int *d_status, cudaStream_t st, int det, int merge);
 size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det = 0);
+// the two halves of seeds_launch, for multi-scale: collect per field set (reset = first set), sort once
+int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, const pp_shape &s,
+                         const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
+                         int reset, cudaStream_t st, int det);
+int seeds_sort_launch(float *d_seeds, int *d_n_seeds, void *d_ws, int B, const pp_caps &c,
+                      const pp_params &p, int *d_status, cudaStream_t st, int det);
 int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
                  const pp_shape &s, const pp_caps &c, const pp_params &p, int *d_status,
                  cudaStream_t st, int det = 0);
@@ -36,6 +45,11 @@ int det_assemble_launch(const DetArgs &a, int B, const pp_det_params &p, float *
 int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                       float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st);
+// s_hr: the shape that defines the hr map; append: continue the lists of an earlier field set
+int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
+                         float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
+                         const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_distance,
+                         float max_distance, int append, int *d_status, cudaStream_t st);
 // Candidate lists re-ordered by spatial bin of their source end, for the assembly
 // scans (caf_scored.cu: caf_bin_kernel).  Per (image, link, direction): seven rows
 // (score, source x/y, target x/y/scale, original list index) of `cap` columns, and

@@ -244,6 +244,39 @@ class DeviceDecoder:
         _lib.check(rc)
         return buf
 
+    def run_device_multiscale(self, sets, params: DecoderParams, *, hflip_pairs=False, keep=('ann',)):
+        """Multi-scale FieldConfig: ``sets`` = list of ``(cif, caf, stride, cif_min_scale,
+        caf_min_distance, caf_max_distance)`` with CUDA float32 tensors ``(B,F,5,H_k,W_k)`` /
+        ``(B,L,9,H_k,W_k)``; set 0 defines the hr shape.  Enqueues only."""
+        arr = (_lib.FieldSet * len(sets))()
+        alive = []
+        seed_cap = caf_cap = src_cap = 0
+        B = F = None
+        for k, (cif, caf, stride, min_scale, min_d, max_d) in enumerate(sets):
+            assert cif.is_cuda and caf.is_cuda and cif.dtype == torch.float32 and caf.dtype == torch.float32
+            cif, caf = cif.contiguous(), caf.contiguous()
+            alive += [cif, caf]
+            B, F, five, H, W = cif.shape
+            assert five == 5 and caf.shape == (B, len(self.skeleton), 9, H, W), (cif.shape, caf.shape)
+            arr[k] = _lib.FieldSet(cif.data_ptr(), caf.data_ptr(), H, W, int(stride), float(min_scale or 0.0),
+                                   float(min_d or 0.0), float(max_d or 0.0))
+            seed_cap += F * H * W
+            caf_cap += H * W
+            src_cap = max(src_cap, (2 if hflip_pairs else 1) * H * W)
+        key = ('ms', B, F, tuple((a.H, a.W, a.stride) for a in arr), bool(hflip_pairs), tuple(sorted(keep)))
+        buf = self._buffers.get(key)
+        if buf is None:
+            shape = _lib.Shape(B, F, len(self.skeleton), arr[0].H, arr[0].W, arr[0].stride)
+            caps = _lib.Caps(min(seed_cap, (1 << 24) - 1), caf_cap, self.ann_cap, src_cap)
+            buf = BatchBuffers(shape, caps, self._device(), keep=keep)
+            self._buffers[key] = buf
+        p = params.to_c()
+        _lib.check(_lib.lib().pp_decode_batch_multiscale(
+            arr, len(sets), int(bool(hflip_pairs)), C.byref(self.c_skeleton), C.byref(buf.d_out),
+            _ptr(buf.ws), buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), _stream_ptr()))
+        buf.alive = alive           # the field tensors must outlive the enqueued kernels
+        return buf
+
     def run_host(self, cif, caf, params: DecoderParams, *, keep=('ann',)):
         """cif, caf: host float32 arrays/tensors (ideally pinned). Synchronous."""
         cif_t = torch.as_tensor(cif)

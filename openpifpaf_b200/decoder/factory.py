@@ -132,9 +132,20 @@ def factory_decode(head_nets, *,
 
     if len(head_nets) >= 2 and _is_intensity(head_nets[0].meta) \
        and _is_association(head_nets[1].meta):
-        if multi_scale:
-            raise NotImplementedError('multi-scale decoding is not built yet (SURVEY.md 8f rank 4)')
         field_config = FieldConfig()
+        if multi_scale:
+            # factory.py:153-180, kept as the reference has it: head sets of 3 (cif, caf, caf25), or
+            # of 2 with dense connections, five scales, doubled with the hflip heads.  Like the
+            # reference this indexes head_nets by the multi-scale head index, so it needs a
+            # head_nets list that long (IndexError otherwise); a FieldConfig built by hand with the
+            # true per-scale strides is the working route (CifCaf.decode_batch_multiscale).
+            per_set = 2 if dense_connections else 3
+            n_scales = 10 if multi_scale_hflip else 5
+            field_config.cif_indices = [v * per_set for v in range(n_scales)]
+            field_config.caf_indices = [v * per_set + 1 for v in range(n_scales)]
+            field_config.cif_min_scales = [0.0, 12.0, 16.0, 24.0, 40.0] * (n_scales // 5)
+            field_config.caf_min_distances = [v * 3.0 for v in field_config.cif_min_scales]
+            field_config.caf_max_distances = [160.0, 240.0, 320.0, 480.0, None] * (n_scales // 5)
         field_config.cif_strides = [head_nets[i].stride(basenet_stride)
                                     for i in field_config.cif_indices]
         field_config.caf_strides = [head_nets[i].stride(basenet_stride)

@@ -89,9 +89,7 @@ class CifCaf(Generator):
         return self._engine
 
     def _single_stride(self):
-        cfg = self.field_config
-        if not cfg.single_scale:
-            raise NotImplementedError('multi-scale field configurations are not built yet')
+        cfg = self.field_config      # multi-scale: the stride of set 0 (which defines the hr map)
         if cfg.cif_strides[0] != cfg.caf_strides[0]:
             raise NotImplementedError('cif and caf heads must share one stride')
         return int(cfg.cif_strides[0])
@@ -234,11 +232,49 @@ class CifCaf(Generator):
                     orig.frontier_order = list(orig.frontier_order) + list(ann.frontier_order)
                     anns[r] = orig
 
+    def decode_batch_multiscale(self, fields):
+        """Multi-scale FieldConfig (decoder/factory.py:153-180): ``fields[i]`` are the batched head
+        tensors addressed by ``field_config.cif_indices`` / ``caf_indices`` (each with its own
+        resolution and stride).  The reference pairs heads (k, k + 5) in CifHr when there are exactly
+        ten (cif_hr.py:66-72).  Everything runs on the device; returns List[List[Annotation]]."""
+        start = time.perf_counter()
+        cfg = self.field_config
+        cfg.verify()
+        if cfg.cif_strides != cfg.caf_strides or len(cfg.cif_indices) != len(cfg.caf_indices):
+            raise NotImplementedError('cif and caf heads of one scale share a stride')
+        eng = self.engine()
+        device = eng._device()
+
+        def dev(t):
+            if not isinstance(t, torch.Tensor):
+                t = torch.from_numpy(np.ascontiguousarray(t, dtype=np.float32))
+            return t.to(device)
+
+        sets = [(dev(fields[ci]), dev(fields[ai]), stride, min_scale, min_d, max_d)
+                for ci, ai, stride, min_scale, min_d, max_d in zip(
+                    cfg.cif_indices, cfg.caf_indices, cfg.cif_strides, cfg.cif_min_scales,
+                    cfg.caf_min_distances, cfg.caf_max_distances)]
+        buf = eng.run_device_multiscale(sets, self.params(), hflip_pairs=len(sets) == 10)
+        n_ann = buf.dev['n_ann'].cpu().numpy()
+        status = buf.dev['status'].cpu().numpy()
+        if status.any():
+            raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
+        nmax = int(n_ann.max(initial=0))
+        npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
+        result = self._annotations_from(
+            n_ann, buf.dev['ann_data'][:, :nmax].cpu().numpy(), buf.dev['ann_scales'][:, :nmax].cpu().numpy(),
+            buf.dev['ann_source'][:, :nmax].cpu().numpy(), buf.dev['pre_data'][:, :npre].cpu().numpy(),
+            buf.dev['pre_order'][:, :npre].cpu().numpy())
+        self.last_decoder_time = time.perf_counter() - start
+        return result
+
     def decode_heads(self, heads):
         """Head tensors of a batch -> annotations.  With ``head_collector`` set (a
         ``network.CifCafCollector``) the heads are the raw convolution outputs of the fused head
         networks and the epilogue (heads.py:65-88,406-448) runs on the device first."""
         cfg = self.field_config
+        if len(cfg.cif_indices) > 1:
+            return self.decode_batch_multiscale(heads)
         cif, caf = heads[cfg.cif_indices[0]], heads[cfg.caf_indices[0]]
         if self.head_collector is not None:
             cif, caf = self.head_collector(cif, caf)
@@ -253,6 +289,12 @@ class CifCaf(Generator):
         if cfg.caf_visualizers:
             for vis, caf_i in zip(cfg.caf_visualizers, cfg.caf_indices):
                 vis.predicted(fields[caf_i])
+        if len(cfg.cif_indices) > 1:
+            if initial_annotations:
+                raise NotImplementedError('initial_annotations with a multi-scale FieldConfig')
+            batched = [f.unsqueeze(0) if isinstance(f, torch.Tensor)
+                       else np.ascontiguousarray(f, dtype=np.float32)[None] for f in fields]
+            return self.decode_batch_multiscale(batched)[0]
         cif, caf = fields[cfg.cif_indices[0]], fields[cfg.caf_indices[0]]
         if isinstance(cif, torch.Tensor):
             cif, caf = cif.unsqueeze(0), caf.unsqueeze(0)

@@ -352,3 +352,17 @@ def synthetic_det_fields(image_hw=(641, 641), n_boxes=8, *, box_seed=0, jitter_s
         field[cat, 5][upd] = (h / stride * jr.uniform(0.95, 1.05, d2.shape))[upd]
         field[cat, 6][upd] = jr.uniform(-1, 1, d2.shape)[upd]
     return field, np.array(boxes, np.float64)
+
+
+def synthetic_multiscale_fields(image_hw=(641, 641), n_poses=5, *, strides=(8, 16, 24), pose_seed=0,
+                                jitter_seed=1):
+    """The same scene at several head strides, for multi-scale FieldConfig tests: one (cif, caf)
+    pair per stride, made by running the generator on the image shrunk by ``stride / 8`` (the
+    generator places poses relative to the image, so equal seeds give the same scene).
+    Returns ``[(cif, caf, stride), ...]``; set 0 defines the hr shape."""
+    out = []
+    for k, stride in enumerate(strides):
+        hw = tuple((side - 1) * 8 // stride + 1 for side in image_hw)
+        cif, caf, _ = synthetic_fields(hw, n_poses, pose_seed=pose_seed, jitter_seed=jitter_seed + 17 * k)
+        out.append((cif, caf, stride))
+    return out

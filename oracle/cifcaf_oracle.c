@@ -123,33 +123,38 @@ static float scalar_value_at(const float *field, long fh, long fw, float x, floa
 /* CifHr.fill_multiple / accumulate for one cif head -- cif_hr.py:26-65       */
 /* cif: (F,5,H,W); hr: (F,Hh,Wh) written (zero-initialised here).             */
 
-int orc_cifhr(const float *cif, int F, int H, int W, const orc_config *cfg, float *hr) {
-  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+/* CifHr.accumulate of one head into ta (not zeroed here): cif_hr.py:26-41 */
+static int cifhr_accumulate(const float *cif, int F, int H, int W, int istride, float min_scale,
+                            float cif_th, float len_cifs, long hh, long hw, float *ta) {
   long n = (long)H * W;
   float *buf = (float *)malloc(sizeof(float) * 4 * (size_t)n);
   if (!buf) return ORC_ERR_ARG;
   float *sx = buf, *sy = buf + n, *ss = buf + 2 * n, *sv = buf + 3 * n;
-  float stride = (float)cfg->stride;
-  memset(hr, 0, sizeof(float) * (size_t)F * hh * hw);
+  float stride = (float)istride;
   for (int f = 0; f < F; f++) {
     const float *p = cif + (size_t)f * 5 * n;
     long k = 0;
     for (long c = 0; c < n; c++) {
-      if (!(p[c] > cfg->cif_th)) continue;                       /* cif_hr.py:27 */
-      if (cfg->cif_min_scale != 0.0f &&
-          !(p[4 * n + c] > cfg->cif_min_scale / stride)) continue; /* :28-29 */
+      if (!(p[c] > cif_th)) continue;                            /* cif_hr.py:27 */
+      if (min_scale != 0.0f && !(p[4 * n + c] > min_scale / stride)) continue; /* :28-29 */
       sx[k] = p[n + c] * stride;                                 /* :32 */
       sy[k] = p[2 * n + c] * stride;                             /* :33 */
       float sg = 0.5f * p[4 * n + c];
       sg = sg * stride;
       ss[k] = (sg != sg) ? sg : (1.0f > sg ? 1.0f : sg);         /* np.maximum :34 */
-      sv[k] = p[c] / 16.0f / 1.0f;                               /* :40, len_cifs = 1 */
+      sv[k] = p[c] / 16.0f / len_cifs;                           /* :40 */
       k++;
     }
-    splat_gauss_with_max(hr + (size_t)f * hh * hw, hh, hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
+    splat_gauss_with_max(ta + (size_t)f * hh * hw, hh, hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
   }
   free(buf);
   return ORC_OK;
+}
+
+int orc_cifhr(const float *cif, int F, int H, int W, const orc_config *cfg, float *hr) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  memset(hr, 0, sizeof(float) * (size_t)F * hh * hw);
+  return cifhr_accumulate(cif, F, H, W, cfg->stride, cfg->cif_min_scale, cfg->cif_th, 1.0f, hh, hw, hr);
 }
 
 /* ------------------------------------------------------------------------- */
@@ -165,17 +170,18 @@ static int seed_cmp_desc(const void *a, const void *b) {
   return 0;
 }
 
-long orc_seeds(const float *cif, int F, int H, int W, const float *hr, const orc_config *cfg,
-               float *out, long cap) {
-  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
-  long n = (long)H * W, k = 0;
-  float stride = (float)cfg->stride;
+/* CifSeeds.fill_cif of one head, appended at out[5 * k ...]; returns the new count (cif_seeds.py:23-50) */
+static long seeds_append(const float *cif, int F, int H, int W, int istride, float min_scale,
+                         const float *hr, long hh, long hw, const orc_config *cfg, float *out,
+                         long cap, long k) {
+  long n = (long)H * W;
+  float stride = (float)istride;
   for (int f = 0; f < F; f++) {
     const float *p = cif + (size_t)f * 5 * n;
     for (long c = 0; c < n; c++) {
       float conf = p[c];
       if (!(conf > cfg->seed_th)) continue;                            /* :31 */
-      if (cfg->cif_min_scale != 0.0f && !(p[4 * n + c] > cfg->cif_min_scale / stride)) continue;
+      if (min_scale != 0.0f && !(p[4 * n + c] > min_scale / stride)) continue;
       float x = p[n + c] * stride, y = p[2 * n + c] * stride;
       float hv = scalar_value_at(hr + (size_t)f * hh * hw, hh, hw, x, y, 0.0f); /* :37 */
       float a = 0.9f * hv, b = 0.1f * conf;
@@ -187,6 +193,14 @@ long orc_seeds(const float *cif, int F, int H, int W, const float *hr, const orc
       o[0] = v; o[1] = (float)f; o[2] = x; o[3] = y; o[4] = p[4 * n + c] * stride;
     }
   }
+  return k;
+}
+
+long orc_seeds(const float *cif, int F, int H, int W, const float *hr, const orc_config *cfg,
+               float *out, long cap) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  long k = seeds_append(cif, F, H, W, cfg->stride, cfg->cif_min_scale, hr, hh, hw, cfg, out, cap, 0);
+  if (k < 0) return k;
   qsort(out, (size_t)k, 5 * sizeof(float), seed_cmp_desc);             /* :54 */
   return k;
 }
@@ -195,27 +209,28 @@ long orc_seeds(const float *cif, int F, int H, int W, const float *hr, const orc
 /* CafScored.fill_caf -- caf_scored.py:32-87                                  */
 /* caf: (L,9,H,W).  fwd/bwd: (L,9,cap) row-major per link, counts per link.   */
 
-int orc_caf_scored(const float *caf, int L, int H, int W, const float *hr, int F,
-                   const int *skeleton /* 2L, 1-based */, const orc_config *cfg, float score_th,
-                   float *fwd, int *nfwd, float *bwd, int *nbwd, long cap) {
-  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+static int caf_scored_append(const float *caf, int L, int H, int W, int istride, float min_distance,
+                             float max_distance, const float *hr, long hh, long hw, int F,
+                             const int *skeleton /* 2L, 1-based */, const orc_config *cfg,
+                             float score_th, float *fwd, int *nfwd, float *bwd, int *nbwd, long cap,
+                             int append) {
   long n = (long)H * W;
-  float stride = (float)cfg->stride;
+  float stride = (float)istride;
   static const int brow[9] = {0, 5, 6, 7, 8, 1, 2, 3, 4};               /* :68 */
   for (int l = 0; l < L; l++) {
     const float *p = caf + (size_t)l * 9 * n;
     float *fo = fwd + (size_t)l * 9 * cap, *bo = bwd + (size_t)l * 9 * cap;
-    int kf = 0, kb = 0;
+    int kf = append ? nfwd[l] : 0, kb = append ? nbwd[l] : 0;     /* np.concatenate :70,81 */
     int j1 = skeleton[2 * l] - 1, j2 = skeleton[2 * l + 1] - 1;
     for (long c = 0; c < n; c++) {
       float nine[9];
       if (!(p[c] > score_th)) continue;                                 /* :42 */
       for (int r = 0; r < 9; r++) nine[r] = p[(size_t)r * n + c];
-      if (cfg->caf_min_distance != 0.0f || cfg->caf_max_distance > 0.0f) {
+      if (min_distance != 0.0f || max_distance > 0.0f) {
         float dx = nine[1] - nine[5], dy = nine[2] - nine[6];
         float d = sqrtf(dx * dx + dy * dy);                             /* :48,53 */
-        if (cfg->caf_min_distance != 0.0f && !(d > cfg->caf_min_distance / stride)) continue;
-        if (cfg->caf_max_distance > 0.0f && !(d < cfg->caf_max_distance / stride)) continue;
+        if (min_distance != 0.0f && !(d > min_distance / stride)) continue;
+        if (max_distance > 0.0f && !(d < max_distance / stride)) continue;
       }
       for (int r = 1; r < 9; r++) nine[r] = nine[r] * stride;           /* :58 */
       float score = nine[0];
@@ -249,6 +264,14 @@ int orc_caf_scored(const float *caf, int L, int H, int W, const float *hr, int F
     nbwd[l] = kb;
   }
   return ORC_OK;
+}
+
+int orc_caf_scored(const float *caf, int L, int H, int W, const float *hr, int F,
+                   const int *skeleton /* 2L, 1-based */, const orc_config *cfg, float score_th,
+                   float *fwd, int *nfwd, float *bwd, int *nbwd, long cap) {
+  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
+  return caf_scored_append(caf, L, H, W, cfg->stride, cfg->caf_min_distance, cfg->caf_max_distance, hr,
+                           hh, hw, F, skeleton, cfg, score_th, fwd, nfwd, bwd, nbwd, cap, 0);
 }
 
 /* ========================================================================= */
@@ -715,7 +738,16 @@ static void export_anns(const orc_ann *anns, int n, int F, int L, float *data, f
   }
 }
 
-int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
+/* One field set of a multi-scale FieldConfig (field_config.py, decoder/factory.py:153-180). */
+typedef struct {
+  const float *cif, *caf;
+  int H, W, stride;
+  float cif_min_scale, caf_min_distance, caf_max_distance;   /* 0 = off / None */
+} orc_set;
+
+/* CifCaf.__call__ over n_sets field sets; set 0 defines the hr shape (cif_hr.py:44-51).
+ * hflip_pairs: CifHr accumulates sets (k, k + n/2) together with len_cifs = 2 (cif_hr.py:66-72). */
+int orc_decode_ms(const orc_set *sets, int n_sets, int hflip_pairs, int F, int L,
                const int *skeleton, const float *conf_scales, const orc_config *cfg,
                float *hr, float *seeds, long seed_cap, long *n_seeds,
                float *fwd, int *nfwd, float *bwd, int *nbwd, long caf_cap,
@@ -726,14 +758,43 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
   orc_graph g;
   int rc = graph_init(&g, F, L, skeleton);
   if (rc) return rc;
-  long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
-  if ((rc = orc_cifhr(cif, F, H, W, cfg, hr))) return rc;                       /* :80 */
-  long ns = orc_seeds(cif, F, H, W, hr, cfg, seeds, seed_cap);                  /* :81 */
-  if (ns < 0) return (int)ns;
+  long hh = (long)(sets[0].H - 1) * sets[0].stride + 1, hw = (long)(sets[0].W - 1) * sets[0].stride + 1;
+  size_t hr_n = (size_t)F * hh * hw;
+  int n_groups = hflip_pairs ? n_sets / 2 : n_sets;                             /* :80, cif_hr.py:66-78 */
+  float *ta = n_groups > 1 ? (float *)malloc(sizeof(float) * hr_n) : NULL;
+  for (int gi = 0; gi < n_groups; gi++) {
+    float *dst = gi == 0 ? hr : ta;
+    memset(dst, 0, sizeof(float) * hr_n);
+    const orc_set *a = &sets[gi];
+    float len_cifs = hflip_pairs ? 2.0f : 1.0f;
+    if ((rc = cifhr_accumulate(a->cif, F, a->H, a->W, a->stride, a->cif_min_scale, cfg->cif_th, len_cifs,
+                               hh, hw, dst))) return rc;
+    if (hflip_pairs) {
+      const orc_set *b = &sets[gi + n_groups];
+      if ((rc = cifhr_accumulate(b->cif, F, b->H, b->W, a->stride, a->cif_min_scale, cfg->cif_th,
+                                 len_cifs, hh, hw, dst))) return rc;
+    }
+    if (gi > 0)                                                                 /* np.maximum :62 */
+      for (size_t i = 0; i < hr_n; i++) {
+        float x = ta[i], y = hr[i];
+        hr[i] = (x != x) ? x : ((y != y) ? y : (x > y ? x : y));
+      }
+  }
+  free(ta);
+  long ns = 0;
+  for (int k = 0; k < n_sets; k++) {                                            /* :81, cif_seeds.py:56-65 */
+    ns = seeds_append(sets[k].cif, F, sets[k].H, sets[k].W, sets[k].stride, sets[k].cif_min_scale, hr,
+                      hh, hw, cfg, seeds, seed_cap, ns);
+    if (ns < 0) return (int)ns;
+  }
+  qsort(seeds, (size_t)ns, 5 * sizeof(float), seed_cmp_desc);
   *n_seeds = ns;
-  rc = orc_caf_scored(caf, L, H, W, hr, F, skeleton, cfg, cfg->caf_th, fwd, nfwd, bwd, nbwd,
-                      caf_cap);                                                 /* :82 */
-  if (rc) return rc;
+  for (int k = 0; k < n_sets; k++) {                                            /* :82, caf_scored.py:89-98 */
+    rc = caf_scored_append(sets[k].caf, L, sets[k].H, sets[k].W, sets[k].stride, sets[k].caf_min_distance,
+                           sets[k].caf_max_distance, hr, hh, hw, F, skeleton, cfg, cfg->caf_th, fwd,
+                           nfwd, bwd, nbwd, caf_cap, k > 0);
+    if (rc) return rc;
+  }
   orc_cafs cf = {fwd, bwd, nfwd, nbwd, caf_cap};
 
   orc_occ occ;
@@ -786,7 +847,10 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
     float *f2 = (float *)malloc(sizeof(float) * (size_t)L * 9 * caf_cap);
     float *b2 = (float *)malloc(sizeof(float) * (size_t)L * 9 * caf_cap);
     int *nf2 = (int *)malloc(sizeof(int) * (size_t)L), *nb2 = (int *)malloc(sizeof(int) * (size_t)L);
-    rc = orc_caf_scored(caf, L, H, W, hr, F, skeleton, cfg, 0.0001f, f2, nf2, b2, nb2, caf_cap);
+    for (int k = 0; k < n_sets && rc == ORC_OK; k++)
+      rc = caf_scored_append(sets[k].caf, L, sets[k].H, sets[k].W, sets[k].stride,
+                             sets[k].caf_min_distance, sets[k].caf_max_distance, hr, hh, hw, F, skeleton,
+                             cfg, 0.0001f, f2, nf2, b2, nb2, caf_cap, k > 0);
     if (rc == ORC_OK) {
       orc_cafs c2 = {f2, b2, nf2, nb2, caf_cap};
       for (int a = 0; a < n; a++) {
@@ -811,6 +875,21 @@ int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
   if (tie_flag) *tie_flag = tie;
   free(anns); free(fr); free(idx); free(scores);
   return rc == ORC_OK ? n : rc;
+}
+
+int orc_decode(const float *cif, const float *caf, int F, int L, int H, int W,
+               const int *skeleton, const float *conf_scales, const orc_config *cfg,
+               float *hr, float *seeds, long seed_cap, long *n_seeds,
+               float *fwd, int *nfwd, float *bwd, int *nbwd, long caf_cap,
+               int ann_cap, float *ann_data, float *ann_js, int *ann_ndec, int *ann_dec,
+               int *ann_nfront, int *ann_front,
+               int *pre_n, float *pre_data, float *pre_js, int *tie_flag,
+               int init_n, const float *init_data, const float *init_js) {
+  orc_set one = {cif, caf, H, W, cfg->stride, cfg->cif_min_scale, cfg->caf_min_distance,
+                 cfg->caf_max_distance};
+  return orc_decode_ms(&one, 1, 0, F, L, skeleton, conf_scales, cfg, hr, seeds, seed_cap, n_seeds, fwd,
+                       nfwd, bwd, nbwd, caf_cap, ann_cap, ann_data, ann_js, ann_ndec, ann_dec, ann_nfront,
+                       ann_front, pre_n, pre_data, pre_js, tie_flag, init_n, init_data, init_js);
 }
 
 /* ------------------------------------------------------------------------- */

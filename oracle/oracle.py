@@ -156,16 +156,43 @@ class Decoded:
                  'frontier_order', 'pre_data', 'pre_joint_scales', 'tie')
 
 
+class FieldSet(C.Structure):
+    """Mirror of ``orc_set``: one entry of a multi-scale FieldConfig."""
+    _fields_ = [('cif', C.c_void_p), ('caf', C.c_void_p), ('H', C.c_int), ('W', C.c_int),
+                ('stride', C.c_int), ('cif_min_scale', C.c_float), ('caf_min_distance', C.c_float),
+                ('caf_max_distance', C.c_float)]
+
+
 def decode(cif, caf, skeleton, cfg=None, *, confidence_scales=None, ann_cap=None, initial=None):
     """Full CifCaf decode of one image. Returns a ``Decoded``."""
     cfg = cfg or Config()
-    cif, caf = _f32(cif), _f32(caf)
-    F, _, H, W = cif.shape
-    L = caf.shape[0]
+    return decode_ms([(cif, caf, cfg.stride, cfg.cif_min_scale, cfg.caf_min_distance,
+                       cfg.caf_max_distance)], skeleton, cfg, confidence_scales=confidence_scales,
+                     ann_cap=ann_cap, initial=initial)
+
+
+def decode_ms(sets, skeleton, cfg=None, *, hflip_pairs=False, confidence_scales=None, ann_cap=None,
+              initial=None):
+    """CifCaf decode over several field sets (multi-scale FieldConfig).  ``sets``: list of
+    ``(cif, caf, stride, cif_min_scale, caf_min_distance, caf_max_distance or 0)``; set 0 defines
+    the hr shape.  Returns a ``Decoded``."""
+    cfg = cfg or Config()
+    keep = []
+    arr = (FieldSet * len(sets))()
+    F = L = None
+    seed_cap = caf_cap = 0
+    for k, (cif, caf, stride, min_scale, min_d, max_d) in enumerate(sets):
+        cif, caf = _f32(cif), _f32(caf)
+        keep += [cif, caf]
+        F, _, H, W = cif.shape
+        L = caf.shape[0]
+        arr[k] = FieldSet(cif.ctypes.data, caf.ctypes.data, H, W, int(stride), float(min_scale or 0.0),
+                          float(min_d or 0.0), float(max_d or 0.0))
+        seed_cap += F * H * W
+        caf_cap += H * W
     skel = np.ascontiguousarray(np.asarray(skeleton, dtype=np.int32).reshape(-1))
     assert skel.size == 2 * L
-    hr = np.empty(hr_shape(cif, cfg.stride), np.float32)
-    seed_cap, caf_cap = F * H * W, H * W
+    hr = np.empty((F, (arr[0].H - 1) * arr[0].stride + 1, (arr[0].W - 1) * arr[0].stride + 1), np.float32)
     ann_cap = ann_cap or 4096
     seeds_ = np.empty((seed_cap, 5), np.float32)
     n_seeds = C.c_long(0)
@@ -191,13 +218,13 @@ def decode(cif, caf, skeleton, cfg=None, *, confidence_scales=None, ann_cap=None
         init_data, init_js = _f32(initial[0]), _f32(initial[1])
         init_n = len(init_data)
     vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
-    n = lib().orc_decode(vp(cif), vp(caf), F, L, H, W, vp(skel),
-                         vp(cs) if cs is not None else None, C.byref(cfg),
-                         vp(hr), vp(seeds_), C.c_long(seed_cap), C.byref(n_seeds),
-                         vp(fwd), vp(nf), vp(bwd), vp(nb), C.c_long(caf_cap),
-                         ann_cap, vp(data), vp(js), vp(ndec), vp(dec), vp(nfront), vp(front),
-                         C.byref(pre_n), vp(pre_data), vp(pre_js), C.byref(tie),
-                         init_n, vp(init_data) if init_n else None, vp(init_js) if init_n else None)
+    n = lib().orc_decode_ms(arr, len(sets), int(bool(hflip_pairs)), F, L, vp(skel),
+                            vp(cs) if cs is not None else None, C.byref(cfg),
+                            vp(hr), vp(seeds_), C.c_long(seed_cap), C.byref(n_seeds),
+                            vp(fwd), vp(nf), vp(bwd), vp(nb), C.c_long(caf_cap),
+                            ann_cap, vp(data), vp(js), vp(ndec), vp(dec), vp(nfront), vp(front),
+                            C.byref(pre_n), vp(pre_data), vp(pre_js), C.byref(tie),
+                            init_n, vp(init_data) if init_n else None, vp(init_js) if init_n else None)
     if n < 0:
         raise RuntimeError('oracle decode failed with code %d' % n)
     out = Decoded()

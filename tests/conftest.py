@@ -87,8 +87,9 @@ def configured_decoder():
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
 _ALL_GOLDEN = sorted(n[:-4] for n in os.listdir(GOLDEN_DIR) if n.endswith('.npz')) \
     if os.path.isdir(GOLDEN_DIR) else []
-GOLDEN_NAMES = [n for n in _ALL_GOLDEN if not n.startswith(('head_', 'inverse_', 'det_'))]   # pose decoder cases
+GOLDEN_NAMES = [n for n in _ALL_GOLDEN if not n.startswith(('head_', 'inverse_', 'det_', 'ms_'))]   # pose decoder cases
 DET_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('det_')]            # CifDet cases
+MS_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('ms_')]              # multi-scale FieldConfig cases
 HEAD_GOLDEN_NAMES = [n for n in _ALL_GOLDEN if n.startswith('head_')]       # head epilogue cases
 TOL_HEAD_REL = 2e-6  # sigmoid / exp of the head epilogue against torch's CPU kernels
 
@@ -222,3 +223,14 @@ def det_golden(name):
                                     n_categories=int(g['n_categories']))
     assert hashlib.sha256(field.tobytes()).hexdigest() == str(g['field_sha256'])
     return field, g
+
+
+def ms_golden(name):
+    """(sets, golden npz) of a multi-scale fixture; inputs regenerated and hash-checked."""
+    import hashlib
+    from oracle.gen_golden_ms import CASES, make_sets
+    g = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    sets = make_sets(*CASES[name])
+    blob = np.concatenate([np.concatenate([s[0].ravel(), s[1].ravel()]) for s in sets])
+    assert hashlib.sha256(np.ascontiguousarray(blob).tobytes()).hexdigest() == str(g['inputs_sha256'])
+    return sets, g

@@ -101,3 +101,25 @@ def test_det_oracle_matches_reference_golden(oracle, name):
 
 def test_det_golden_covers_the_cases():
     assert len(DET_GOLDEN_NAMES) >= 5
+
+
+from conftest import MS_GOLDEN_NAMES, ms_golden  # noqa: E402
+
+
+@pytest.mark.parametrize('name', MS_GOLDEN_NAMES)
+def test_multiscale_oracle_matches_reference_golden(oracle, coco_skeleton, name):
+    """orc_decode_ms under a multi-scale FieldConfig: hr (np.maximum merge, hflip pairs), the seed
+    list and the concatenated CafScored lists bit-identical; annotations inside the tolerances."""
+    from conftest import TOL_SCORE, TOL_XY
+    sets, g = ms_golden(name)
+    o = oracle.decode_ms([(c, a, st, ms, mind, maxd or 0.0) for c, a, st, ms, mind, maxd in sets],
+                         coco_skeleton, oracle.Config(), hflip_pairs=len(sets) == 10)
+    assert sha256(o.hr) == str(g['hr_sha256'])
+    assert np.array_equal(o.seeds, g['seeds'])
+    assert [f.shape[1] for f in o.forward] == g['caf_nf'].tolist()
+    assert [sha256(f) for f in o.forward] == g['caf_f_sha256'].tolist()
+    assert [sha256(b) for b in o.backward] == g['caf_b_sha256'].tolist()
+    assert len(o.data) == len(g['ann_data']) >= 3
+    assert np.array_equal(o.data[:, :, 2] > 0, g['ann_data'][:, :, 2] > 0)
+    assert np.abs(o.data[:, :, :2] - g['ann_data'][:, :, :2]).max() <= TOL_XY
+    assert np.abs(o.data[:, :, 2] - g['ann_data'][:, :, 2]).max() <= TOL_SCORE

@@ -618,3 +618,57 @@ def test_cifdet_many_categories_and_capacity(oracle, configured_det):
     assert np.array_equal(t['det_score'][0, :n].cpu().numpy(), o.score)
     with pytest.raises(_lib.PifPafError):
         run_cifdet(field[None], 8, ann_cap=3)
+
+
+def _ms_case_names():
+    from conftest import MS_GOLDEN_NAMES
+    return MS_GOLDEN_NAMES
+
+
+@pytest.mark.parametrize('name', _ms_case_names())
+def test_multiscale_matches_oracle_and_golden(oracle, coco_skeleton, configured_decoder, name):
+    """pp_decode_batch_multiscale through CifCaf.__call__ with a multi-scale FieldConfig: hr, seeds,
+    CafScored lists and annotations bit-identical to the oracle; hr / seeds / lists also to the
+    reference's golden outputs."""
+    from conftest import TOL_SCORE, TOL_XY, ms_golden, sha256
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    sets, g = ms_golden(name)
+    pairs = len(sets) == 10
+    o = oracle.decode_ms([(c, a, st, ms, mind, maxd or 0.0) for c, a, st, ms, mind, maxd in sets],
+                         coco_skeleton, oracle.Config(exp_mode=1), hflip_pairs=pairs)
+    cfg = decoder.FieldConfig()
+    n = len(sets)
+    cfg.cif_indices, cfg.caf_indices = [2 * k for k in range(n)], [2 * k + 1 for k in range(n)]
+    cfg.cif_strides = [s[2] for s in sets]
+    cfg.caf_strides = [s[2] for s in sets]
+    cfg.cif_min_scales = [s[3] for s in sets]
+    cfg.caf_min_distances = [s[4] for s in sets]
+    cfg.caf_max_distances = [s[5] for s in sets]
+    fields = []
+    for s in sets:
+        fields += [s[0], s[1]]
+    dec = decoder.CifCaf(cfg, keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    anns = dec(fields)
+    assert len(anns) == len(o.data) >= 3
+    for ann, d, js in zip(anns, o.data, o.joint_scales):
+        assert np.array_equal(ann.data, d) and np.array_equal(ann.joint_scales, js)
+    assert np.abs(np.stack([a.data for a in anns])[:, :, :2] - g['ann_data'][:, :, :2]).max() <= TOL_XY
+    assert np.abs(np.stack([a.data for a in anns])[:, :, 2] - g['ann_data'][:, :, 2]).max() <= TOL_SCORE
+    # stage outputs
+    eng = dec.engine()
+    dsets = [(torch.from_numpy(c[None]).cuda(), torch.from_numpy(a[None]).cuda(), st, ms, mind, maxd)
+             for c, a, st, ms, mind, maxd in sets]
+    buf = eng.run_device_multiscale(dsets, dec.params(), hflip_pairs=pairs, keep=('ann', 'hr', 'seeds', 'caf'))
+    hr = buf.dev['hr'][0].cpu().numpy()
+    assert np.array_equal(hr, o.hr) and sha256(hr) == str(g['hr_sha256'])
+    ns = int(buf.dev['n_seeds'][0])
+    seeds = buf.dev['seeds'][0, :ns].cpu().numpy()
+    assert np.array_equal(seeds, o.seeds) and np.array_equal(seeds, g['seeds'])
+    nf, nb = buf.dev['n_caf_fwd'][0].cpu().numpy(), buf.dev['n_caf_bwd'][0].cpu().numpy()
+    assert nf.tolist() == g['caf_nf'].tolist() and nb.tolist() == g['caf_nb'].tolist()
+    fwd, bwd = buf.dev['caf_fwd'][0].cpu().numpy(), buf.dev['caf_bwd'][0].cpu().numpy()
+    for l in range(len(nf)):
+        assert np.array_equal(fwd[l, :, :nf[l]], o.forward[l])
+        assert np.array_equal(bwd[l, :, :nb[l]], o.backward[l])
+        assert sha256(np.ascontiguousarray(fwd[l, :, :nf[l]])) == str(g['caf_f_sha256'][l])
