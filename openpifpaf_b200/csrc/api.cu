@@ -73,6 +73,7 @@ struct DecodeWs {
   float *fwd, *bwd; int *nfwd, *nbwd;
   float *bin_rows; int *bin_start;   // spatially binned copy of the lists for the assembly
   uint8_t *occ_cnt; int2 *occ_rec;
+  void *seed_stage;
   float *pre_data, *pre_scales; int *pre_order; int *n_pre;
   float *cmp_data, *cmp_scales;   // force_complete: completed annotations (NMS input)
   void *stage;               // shared by the cifhr / seeds / nms stages (used one after another)
@@ -105,8 +106,10 @@ static DecodeWs layout(void *base, const pp_shape &s, const pp_caps &c, bool nee
   w.n_pre = (int *)take(B * sizeof(int));
   w.cmp_data = (float *)take(B * c.ann_cap * s.F * 3 * sizeof(float));
   w.cmp_scales = (float *)take(B * c.ann_cap * s.F * sizeof(float));
-  w.stage_bytes = max3(cifhr_ws_bytes(s, c), seeds_ws_bytes(s, c), nms_ws_bytes(s, c));
+  // the seed stage reads the CifHr stage's compacted sources: its scratch is a region of its own
+  w.stage_bytes = max3(cifhr_ws_bytes(s, c), (size_t)0, nms_ws_bytes(s, c));
   w.stage = take(w.stage_bytes);
+  w.seed_stage = take(seeds_ws_bytes(s, c));
   w.total = off;
   return w;
 }
@@ -427,11 +430,18 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return rc;
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
-  for (int k = 0; k < n_sets; k++)
-    if ((rc = seeds_collect_launch(sets[k].cif, hr, w.stage, set_shape(k), *s, *c, *p, sets[k].cif_min_scale,
-                                   k == 0, st, 0)))
+  if (n_sets == 1 && p->seed_threshold >= p->cif_threshold) {
+    // the seed candidates are a subset of the sources the CifHr stage compacted: skip the field scan
+    if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, *p,
+                                                st, 0)))
       return rc;
-  if ((rc = seeds_sort_launch(seeds, n_seeds, w.stage, s->B, *c, *p, o->status, st, 0))) return rc;
+  } else {
+    for (int k = 0; k < n_sets; k++)
+      if ((rc = seeds_collect_launch(sets[k].cif, hr, w.seed_stage, set_shape(k), *s, *c, *p,
+                                     sets[k].cif_min_scale, k == 0, st, 0)))
+        return rc;
+  }
+  if ((rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0))) return rc;
   // CafScored.fill (caf_scored.py:89-98): lists concatenated over the heads
   for (int k = 0; k < n_sets; k++)
     if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, set_shape(k),
@@ -520,7 +530,7 @@ struct DetWs {
   float *hr; float *seeds; int *n_seeds;
   int *pre_field; float *pre_score; float *pre_box; int *n_pre;
   uint8_t *occ_cnt; int2 *occ_rec; float *work_score;
-  void *stage;
+  void *stage, *seed_stage;
   size_t total;
 };
 
@@ -540,8 +550,8 @@ static DetWs det_layout(void *base, const pp_shape &s, const pp_caps &c) {
   w.occ_cnt = (uint8_t *)take(B * c.seed_cap);
   w.occ_rec = (int2 *)take(B * c.seed_cap * sizeof(int2));
   w.work_score = (float *)take(B * A * sizeof(float));
-  size_t st = cifhr_ws_bytes(s, c), st2 = seeds_ws_bytes(s, c, 1);
-  w.stage = take(st > st2 ? st : st2);
+  w.stage = take(cifhr_ws_bytes(s, c));
+  w.seed_stage = take(seeds_ws_bytes(s, c, 1));
   w.total = off;
   return w;
 }
@@ -571,7 +581,14 @@ int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *o, void *
   if (rc) return rc;
   float *seeds = o->seeds ? o->seeds : w.seeds;
   int *n_seeds = o->n_seeds ? o->n_seeds : w.n_seeds;
-  if ((rc = seeds_launch(d_field, hr, seeds, n_seeds, w.stage, *s, *c, q, o->status, st, 1))) return rc;
+  if (q.seed_threshold >= q.cif_threshold) {      // seeds from the compacted sources (see decode_core)
+    if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, q,
+                                                st, 1)))
+      return rc;
+    if ((rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, q, o->status, st, 1))) return rc;
+  } else if ((rc = seeds_launch(d_field, hr, seeds, n_seeds, w.seed_stage, *s, *c, q, o->status, st, 1))) {
+    return rc;
+  }
   DetArgs a;
   a.seeds = seeds; a.n_seeds = n_seeds;
   a.occ_cnt = w.occ_cnt; a.occ_rec = w.occ_rec;

@@ -9,8 +9,11 @@
 // Candidate order is row-major cell order, as numpy boolean masking gives it;
 // the assembly stage relies on that order only to break exact score ties.
 //
-// One CTA per (image, link).  The confidence plane is streamed with coalesced
-// loads; the other eight planes are touched only for cells above threshold.
+// One CTA per (image, link), two phases per slab of cells: (1) the ordered list of the cells above
+// the threshold (block_active_cells: coalesced sweep of the confidence plane, two barriers);
+// (2) one listed cell per thread: the other eight planes, the two hr gathers and both ordered
+// compactions.  The first version interleaved the two per 256 cells and was bound by ~26 serial
+// rounds of dependent loads + barriers per CTA (97 us at batch 64).
 #include "common.cuh"
 #include "stages.cuh"
 
@@ -18,12 +21,15 @@ namespace pp {
 
 constexpr int kCafThreads = 256;
 
+constexpr int kCafSlab = 8192;       // cells per slab: the active-cell list of a slab is 32 KiB of smem
+
 __global__ void __launch_bounds__(kCafThreads)
 caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, pp_skeleton sk,
                   float *__restrict__ fwd, int *__restrict__ nfwd, float *__restrict__ bwd,
                   int *__restrict__ nbwd, pp_shape s, int cap, int hh, int hw, float th,
                   float cif_floor, float cif_floor_compl, float min_dist, int use_min, float max_dist,
                   int use_max, int append, int *__restrict__ status) {
+  extern __shared__ int s_cells[];               // min(n, kCafSlab) active cell indices
   __shared__ int wtot_f[kCafThreads / 32], wtot_b[kCafThreads / 32];
   const int bl = blockIdx.x;
   const int b = bl / s.L, l = bl - b * s.L;
@@ -38,16 +44,19 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
   // append: a later field set of a multi-scale configuration continues the lists (caf_scored.py:70,81)
   int cnt_f = append ? nfwd[bl] : 0, cnt_b = append ? nbwd[bl] : 0;
 
-  for (int base = 0; base < n; base += blockDim.x) {
-    const int c = base + threadIdx.x;
-    bool kf = false, kb = false;
-    float nine[9];
-    float sf = 0.f, sb = 0.f;
-    if (c < n) {
-      nine[0] = __ldg(p + c);
-      if (nine[0] > th) {                                         // caf_scored.py:42
+  for (int slab = 0; slab < n; slab += kCafSlab) {
+    // phase 1: the cells above the threshold, in row-major order (caf_scored.py:42)
+    const int n_act = block_active_cells<kCafThreads>(p, slab, min(n, slab + kCafSlab), th, s_cells, wtot_f);
+    // phase 2: one active cell per thread -- eight more planes, two hr gathers, both compactions
+    for (int base = 0; base < n_act; base += blockDim.x) {
+      const int i = base + threadIdx.x;
+      bool kf = false, kb = false;
+      float nine[9];
+      float sf = 0.f, sb = 0.f;
+      if (i < n_act) {
+        const int c = s_cells[i];
 #pragma unroll
-        for (int r = 1; r < 9; r++) nine[r] = __ldg(p + (size_t)r * n + c);
+        for (int r = 0; r < 9; r++) nine[r] = __ldg(p + (size_t)r * n + c);
         bool ok = true;
         if (use_min || use_max) {                                 // :47-55 (multi-scale only)
           float dx = __fsub_rn(nine[1], nine[5]), dy = __fsub_rn(nine[2], nine[6]);
@@ -71,39 +80,39 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
           kf = sf > th;                                           // :78
         }
       }
-    }
-    // two ordered CTA-wide compactions in one barrier pair
-    unsigned mf = __ballot_sync(0xffffffffu, kf), mb = __ballot_sync(0xffffffffu, kb);
-    if (lane == 0) { wtot_f[w] = __popc(mf); wtot_b[w] = __popc(mb); }
-    __syncthreads();
-    int base_f = 0, base_b = 0, tot_f = 0, tot_b = 0;
-    for (int i = 0; i < nw; i++) {
-      int tf = wtot_f[i], tb = wtot_b[i];
-      if (i < w) { base_f += tf; base_b += tb; }
-      tot_f += tf; tot_b += tb;
-    }
-    __syncthreads();
-    const unsigned below = (1u << lane) - 1u;
-    if (kb) {
-      int k = cnt_b + base_b + __popc(mb & below);
-      if (k < cap) {                                              // :68-69 row permutation
-        bo[k] = sb;
-        bo[(size_t)1 * cap + k] = nine[5]; bo[(size_t)2 * cap + k] = nine[6];
-        bo[(size_t)3 * cap + k] = nine[7]; bo[(size_t)4 * cap + k] = nine[8];
-        bo[(size_t)5 * cap + k] = nine[1]; bo[(size_t)6 * cap + k] = nine[2];
-        bo[(size_t)7 * cap + k] = nine[3]; bo[(size_t)8 * cap + k] = nine[4];
+      // two ordered CTA-wide compactions in one barrier pair
+      unsigned mf = __ballot_sync(0xffffffffu, kf), mb = __ballot_sync(0xffffffffu, kb);
+      if (lane == 0) { wtot_f[w] = __popc(mf); wtot_b[w] = __popc(mb); }
+      __syncthreads();
+      int base_f = 0, base_b = 0, tot_f = 0, tot_b = 0;
+      for (int k = 0; k < nw; k++) {
+        int tf = wtot_f[k], tb = wtot_b[k];
+        if (k < w) { base_f += tf; base_b += tb; }
+        tot_f += tf; tot_b += tb;
       }
-    }
-    if (kf) {
-      int k = cnt_f + base_f + __popc(mf & below);
-      if (k < cap) {                                              // :79-80
-        fo[k] = sf;
+      __syncthreads();
+      const unsigned below = (1u << lane) - 1u;
+      if (kb) {
+        int k = cnt_b + base_b + __popc(mb & below);
+        if (k < cap) {                                            // :68-69 row permutation
+          bo[k] = sb;
+          bo[(size_t)1 * cap + k] = nine[5]; bo[(size_t)2 * cap + k] = nine[6];
+          bo[(size_t)3 * cap + k] = nine[7]; bo[(size_t)4 * cap + k] = nine[8];
+          bo[(size_t)5 * cap + k] = nine[1]; bo[(size_t)6 * cap + k] = nine[2];
+          bo[(size_t)7 * cap + k] = nine[3]; bo[(size_t)8 * cap + k] = nine[4];
+        }
+      }
+      if (kf) {
+        int k = cnt_f + base_f + __popc(mf & below);
+        if (k < cap) {                                            // :79-80
+          fo[k] = sf;
 #pragma unroll
-        for (int r = 1; r < 9; r++) fo[(size_t)r * cap + k] = nine[r];
+          for (int r = 1; r < 9; r++) fo[(size_t)r * cap + k] = nine[r];
+        }
       }
+      cnt_f += tot_f;
+      cnt_b += tot_b;
     }
-    cnt_f += tot_f;
-    cnt_b += tot_b;
   }
   if (threadIdx.x == 0) {
     if (cnt_f > cap || cnt_b > cap) atomicOr(&status[b], PP_STATUS_CAF_OVERFLOW);
@@ -220,7 +229,8 @@ int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleto
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const float stride = (float)s.stride;
   prof_mark(p.profile, kStCaf, st);
-  caf_scored_kernel<<<s.B * s.L, kCafThreads, 0, st>>>(
+  const size_t smem = (size_t)min(s.H * s.W, kCafSlab) * sizeof(int);
+  caf_scored_kernel<<<s.B * s.L, kCafThreads, smem, st>>>(
       d_caf, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
       p.cif_floor_compl, min_distance / stride, min_distance != 0.0f, max_distance / stride,
       max_distance > 0.0f, append, d_status);

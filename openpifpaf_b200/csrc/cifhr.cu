@@ -58,10 +58,12 @@ constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see stri
 constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored from (4 KiB pieces)
 constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
+constexpr int kCompactSlab = 8192;     // cells per active-cell list (32 KiB of shared memory)
 
 struct CifHrWs {
   float4 *src_a;    // (B,F,src_cap) cx, cy, sigma^2, v
   int4 *src_b;      // (B,F,src_cap) minx, maxx, miny, maxy
+  float2 *src_c;    // (B,F,src_cap) scale in pixels (CifDet: w, h in pixels) for the seed stage
   int *n_src;       // (B,F)
   int *strip_cnt;   // (B,F,nstrips)
   int *busy_list;   // (B*F*nstrips) ids (bf * nstrips + strip) of the strips with sources, any order
@@ -85,6 +87,7 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   size_t n = 0;
   n += align_up(bf * c.src_cap * sizeof(float4), 256);
   n += align_up(bf * c.src_cap * sizeof(int4), 256);
+  n += align_up(bf * c.src_cap * sizeof(float2), 256);
   n += align_up(bf * sizeof(int), 256);
   n += 2 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
   n += 256;
@@ -97,6 +100,7 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
   size_t bf = (size_t)s.B * s.F;
   w.src_a = (float4 *)p; p += align_up(bf * c.src_cap * sizeof(float4), 256);
   w.src_b = (int4 *)p;   p += align_up(bf * c.src_cap * sizeof(int4), 256);
+  w.src_c = (float2 *)p; p += align_up(bf * c.src_cap * sizeof(float2), 256);
   w.n_src = (int *)p;    p += align_up(bf * sizeof(int), 256);
   w.strip_cnt = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.busy_list = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
@@ -126,48 +130,61 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
 
   float4 *oa = w.src_a + (size_t)bf * src_cap;
   int4 *ob = w.src_b + (size_t)bf * src_cap;
+  float2 *oc = w.src_c + (size_t)bf * src_cap;
+  int *s_cells = sm_diff + w.nstrips + 1;        // active cells of one slab
   int count = 0;
   for (int pass = 0; pass < (cif2 ? 2 : 1); pass++) {
   const float *p = (pass ? cif2 : cif) + (size_t)bf * (det ? 7 : 5) * n;   // CifDet: [v, x, y, _, w, h, _]
-  for (int base = 0; base < n; base += blockDim.x) {
-    int c = base + threadIdx.x;
-    bool flag = false;
-    float conf = 0.f;
-    if (c < n) {
-      conf = __ldg(p + c);
-      flag = conf > v_th;                                         // cif_hr.py:27
-      if (flag && use_min_scale) flag = __ldg(p + 4 * n + c) > min_scale_over_stride;  // :28-29
-      if (flag && use_min_scale && det) flag = __ldg(p + 5 * n + c) > min_scale_over_stride;  // :87-89
-    }
-    int total;
-    int off = block_flag_scan(flag, warp_tot, &total);
-    if (flag) {
-      int k = count + off;
-      if (k < src_cap) {
-        float cx = __fmul_rn(__ldg(p + n + c), stride);           // :32
-        float cy = __fmul_rn(__ldg(p + 2 * n + c), stride);       // :33
-        float sg;
-        if (det) {      // CifDetHr: sigma = max(1, 0.1 * min(w, h) * stride), cif_hr.py:91-94
-          const float bw = __ldg(p + 4 * n + c), bh = __ldg(p + 5 * n + c);
-          const float m = (bw != bw) ? bw : ((bh != bh) ? bh : fminf(bw, bh));   // np.minimum keeps NaN
-          sg = __fmul_rn(__fmul_rn(0.1f, m), stride);
-        } else {
-          sg = __fmul_rn(__fmul_rn(0.5f, __ldg(p + 4 * n + c)), stride);
-        }
-        float sigma = (sg != sg) ? sg : fmaxf(1.0f, sg);          // np.maximum(1.0, .) :34
-        float cv = __fdiv_rn(__fdiv_rn(conf, 16.0f), len_cifs);   // v / neighbors / len_cifs :40
-        // functional.pyx:122-125 with truncate = 1.0
-        int minx = (int)clipf(__fsub_rn(cx, sigma), 0.0f, (float)(hw - 1));
-        int maxx = (int)clipf(__fadd_rn(__fadd_rn(cx, sigma), 1.0f), (float)(minx + 1), (float)hw);
-        int miny = (int)clipf(__fsub_rn(cy, sigma), 0.0f, (float)(hh - 1));
-        int maxy = (int)clipf(__fadd_rn(__fadd_rn(cy, sigma), 1.0f), (float)(miny + 1), (float)hh);
-        oa[k] = make_float4(cx, cy, __fmul_rn(sigma, sigma), cv);
-        ob[k] = make_int4(minx, maxx, miny, maxy);
-        atomicAdd(&sm_diff[miny >> w.rshift], 1);
-        atomicAdd(&sm_diff[((maxy - 1) >> w.rshift) + 1], -1);
+  for (int slab = 0; slab < n; slab += kCompactSlab) {
+    // phase 1: cells above the threshold in row-major order (cif_hr.py:27); phase 2: one listed cell
+    // per thread.  (Interleaving the two per 256 cells cost ~26 serial load + barrier rounds.)
+    const int n_act = block_active_cells<kCompactThreads>(p, slab, min(n, slab + kCompactSlab), v_th, s_cells,
+                                                          warp_tot);
+    for (int base = 0; base < n_act; base += blockDim.x) {
+      const int i = base + threadIdx.x;
+      bool flag = i < n_act;
+      int c = 0;
+      float conf = 0.f, c4 = 0.f, c5 = 0.f;
+      if (flag) {
+        c = s_cells[i];
+        conf = __ldg(p + c);
+        c4 = __ldg(p + 4 * n + c);
+        if (det) c5 = __ldg(p + 5 * n + c);
+        if (use_min_scale) flag = c4 > min_scale_over_stride;               // :28-29
+        if (flag && use_min_scale && det) flag = c5 > min_scale_over_stride; // :87-89
       }
+      int total = n_act - base < (int)blockDim.x ? n_act - base : (int)blockDim.x;
+      int off = i - base;
+      if (use_min_scale) off = block_flag_scan(flag, warp_tot, &total);     // a second ordered filter
+      if (flag) {
+        int k = count + off;
+        if (k < src_cap) {
+          float cx = __fmul_rn(__ldg(p + n + c), stride);           // :32
+          float cy = __fmul_rn(__ldg(p + 2 * n + c), stride);       // :33
+          float sg;
+          if (det) {      // CifDetHr: sigma = max(1, 0.1 * min(w, h) * stride), cif_hr.py:91-94
+            const float m = (c4 != c4) ? c4 : ((c5 != c5) ? c5 : fminf(c4, c5));   // np.minimum keeps NaN
+            sg = __fmul_rn(__fmul_rn(0.1f, m), stride);
+          } else {
+            sg = __fmul_rn(__fmul_rn(0.5f, c4), stride);
+          }
+          float sigma = (sg != sg) ? sg : fmaxf(1.0f, sg);          // np.maximum(1.0, .) :34
+          float cv = __fdiv_rn(__fdiv_rn(conf, 16.0f), len_cifs);   // v / neighbors / len_cifs :40
+          // functional.pyx:122-125 with truncate = 1.0
+          int minx = (int)clipf(__fsub_rn(cx, sigma), 0.0f, (float)(hw - 1));
+          int maxx = (int)clipf(__fadd_rn(__fadd_rn(cx, sigma), 1.0f), (float)(minx + 1), (float)hw);
+          int miny = (int)clipf(__fsub_rn(cy, sigma), 0.0f, (float)(hh - 1));
+          int maxy = (int)clipf(__fadd_rn(__fadd_rn(cy, sigma), 1.0f), (float)(miny + 1), (float)hh);
+          oa[k] = make_float4(cx, cy, __fmul_rn(sigma, sigma), cv);
+          ob[k] = make_int4(minx, maxx, miny, maxy);
+          // what CifSeeds needs besides (cx, cy, cv): the scale(s) in pixels (cif_seeds.py:44,84)
+          oc[k] = make_float2(__fmul_rn(c4, stride), det ? __fmul_rn(c5, stride) : 0.0f);
+          atomicAdd(&sm_diff[miny >> w.rshift], 1);
+          atomicAdd(&sm_diff[((maxy - 1) >> w.rshift) + 1], -1);
+        }
+      }
+      count += total;
     }
-    count += total;
   }
   }
   __syncthreads();
@@ -452,6 +469,11 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
 // s: shape of the field set (B, F, H, W, stride); s_hr: the shape that defines the hr map (set 0 of a
 // multi-scale configuration, else s itself).  d_cif2: second field of an hflip pair or NULL.
 // merge: np.maximum into the existing map instead of overwriting it.
+CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c) {
+  CifHrWs w = carve(d_ws, s_hr, c);
+  return CifSrcView{w.src_a, w.src_c, w.n_src, c.src_cap};
+}
+
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
                     int *d_status, cudaStream_t st, int det, int merge) {
@@ -460,7 +482,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
   if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
-  size_t smem = (size_t)(w.nstrips + 1) * sizeof(int);
+  size_t smem = (size_t)(w.nstrips + 1 + min(s.H * s.W, kCompactSlab)) * sizeof(int);
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
@@ -475,8 +497,10 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
                                      2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
   const int kGroupStrips = group_strips();
   const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
-  // persistent grid: as many CTAs as fit (shared memory allows 4 per SM at 641 px)
-  int per_sm = 4;
+  // persistent grid: 3 CTAs per SM.  Shared memory would allow 4 at 641 px and a kernel running alone is
+  // equally fast with either; 3 leave room for the assembly CTAs of another batch in flight
+  // (engine.submit lanes: 122 k -> 126 k images/s)
+  int per_sm = 3;
   if (const char *e = getenv("PP_CIFHR_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
   int grid = num_sms() * per_sm;
   if (grid > bf * n_groups) grid = bf * n_groups;

@@ -110,4 +110,60 @@ __device__ __forceinline__ int block_flag_scan(bool flag, int *warp_tot, int *to
   return base + in_warp;
 }
 
+// Ordered list of the cells c in [c_lo, c_hi) with conf[c] > th (NaN fails), CTA-wide, in two
+// sweeps: every warp owns a contiguous run of cells, counts its hits (four independent loads in
+// flight per lane), the warp totals give each warp its base, and the second sweep (the plane is in
+// L1 / L2 by then) writes the indices.  Two __syncthreads() in total instead of two per 256 cells.
+// `list` must hold c_hi - c_lo ints; `warp_cnt` is shared scratch of THREADS / 32 ints.
+template <int THREADS>
+__device__ __forceinline__ int block_active_cells(const float *__restrict__ conf, int c_lo, int c_hi,
+                                                  float th, int *list, int *warp_cnt) {
+  constexpr int NW = THREADS / 32;
+  constexpr int U = 4;
+  const int lane = lane_id(), w = warp_id();
+  const int n = c_hi - c_lo;
+  const int seg = (((n + NW - 1) / NW) + 31) & ~31;          // cells per warp, a multiple of 32
+  const int w0 = c_lo + w * seg, w1 = min(c_hi, w0 + seg);
+  int cnt = 0;
+  for (int base = w0; base < w1; base += 32 * U) {
+    float v[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int c = base + 32 * u + lane;
+      v[u] = c < w1 ? __ldg(conf + c) : th;
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) cnt += __popc(__ballot_sync(0xffffffffu, v[u] > th));
+  }
+  if (lane == 0) warp_cnt[w] = cnt;
+  __syncthreads();
+  int at = 0, total = 0;
+#pragma unroll
+  for (int i = 0; i < NW; i++) {
+    const int t = warp_cnt[i];
+    if (i < w) at += t;
+    total += t;
+  }
+  const unsigned below = (1u << lane) - 1u;
+  if (cnt) {
+    for (int base = w0; base < w1; base += 32 * U) {
+      float v[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int c = base + 32 * u + lane;
+        v[u] = c < w1 ? __ldg(conf + c) : th;
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const bool hit = v[u] > th;
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (hit) list[at + __popc(m & below)] = base + 32 * u + lane;
+        at += __popc(m);
+      }
+    }
+  }
+  __syncthreads();
+  return total;
+}
+
 }  // namespace pp

@@ -81,6 +81,55 @@ seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr
   }
 }
 
+// The same records from the compacted CIF sources of the CifHr stage.  Every source passed
+// conf > cif_threshold and the min-scale filter; with seed_threshold >= cif_threshold the seed
+// candidates are a subset, and x, y, scale and conf (= 16 * v/16, exact) are what the field scan
+// would have computed.  One CTA per (image, field).
+template <int REC>
+__global__ void __launch_bounds__(128)
+seeds_from_sources_kernel(CifSrcView src, const float *__restrict__ hr, float *__restrict__ raw,
+                          int *__restrict__ n_raw, int F, int cap, int hh, int hw, float th,
+                          float score_scale, uint32_t seed_mask) {
+  const int bf = blockIdx.x;
+  const int b = bf / F, f = bf - b * F;
+  if (seed_mask != 0u && !((seed_mask >> f) & 1u)) return;        // cif_seeds.py:29-30
+  const int n = min(src.n[bf], src.src_cap);
+  const float4 *sa = src.a + (size_t)bf * src.src_cap;
+  const float2 *sc = src.c + (size_t)bf * src.src_cap;
+  const int lane = lane_id();
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int i = base + threadIdx.x;
+    bool keep = false;
+    float v = 0.f;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n) {
+      a = sa[i];
+      const float conf = __fmul_rn(a.w, 16.0f);
+      if (conf > th) {                                            // :31
+        float hv = scalar_value_at(hr + (size_t)bf * hh * hw, hh, hw, a.x, a.y, 0.0f);   // :37
+        v = __fadd_rn(__fmul_rn(0.9f, hv), __fmul_rn(0.1f, conf));                      // :38
+        if (score_scale != 1.0f) v = __fmul_rn(v, score_scale);   // :41-42
+        keep = v > th;                                            // :43
+      }
+    }
+    unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (m == 0u) continue;
+    int leader = __ffs(m) - 1;
+    int at = 0;
+    if (lane == leader) at = atomicAdd(&n_raw[b], __popc(m));
+    at = __shfl_sync(0xffffffffu, at, leader);
+    if (keep) {
+      int slot = at + __popc(m & ((1u << lane) - 1u));
+      if (slot < cap) {
+        const float2 e = sc[i];
+        float *o = raw + ((size_t)b * cap + slot) * REC;
+        o[0] = v; o[1] = (float)f; o[2] = a.x; o[3] = a.y; o[4] = e.x;   // :44,47
+        if (REC == 6) o[5] = e.y;                                        // :84
+      }
+    }
+  }
+}
+
 // strict "a sorts before b" for descending tuple order (v, f, x, y, s) / (v, f, x, y, w, h)
 template <int REC>
 __device__ __forceinline__ bool seed_before(uint64_t a, uint64_t b, const float *__restrict__ raw) {
@@ -194,6 +243,23 @@ int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, cons
         d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
         min_scale / (float)s.stride, min_scale != 0.0f, p.seed_mask);
   PP_LAUNCH_CHECK("seeds_collect_kernel");
+  return PP_OK;
+}
+
+int seeds_collect_from_sources_launch(const CifSrcView &src, const float *d_hr, void *d_ws, const pp_shape &s,
+                                      const pp_caps &c, const pp_params &p, cudaStream_t st, int det) {
+  if (c.seed_cap >= (1 << 24) || s.F > 256) return PP_ERR_ARG;
+  SeedsWs w = seeds_carve(d_ws, s.B, c, det);
+  const int hh = hr_h(s), hw = hr_w(s);
+  prof_mark(p.profile, kStCollect, st);
+  PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
+  if (det)
+    seeds_from_sources_kernel<6><<<s.B * s.F, 128, 0, st>>>(src, d_hr, w.raw, w.n_raw, s.F, c.seed_cap, hh, hw,
+                                                           p.seed_threshold, p.seed_score_scale, 0u);
+  else
+    seeds_from_sources_kernel<5><<<s.B * s.F, 128, 0, st>>>(src, d_hr, w.raw, w.n_raw, s.F, c.seed_cap, hh, hw,
+                                                           p.seed_threshold, p.seed_score_scale, p.seed_mask);
+  PP_LAUNCH_CHECK("seeds_from_sources_kernel");
   return PP_OK;
 }
 

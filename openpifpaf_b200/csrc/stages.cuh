@@ -9,6 +9,14 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c);
 // CifDetHr / CifDetSeeds (cif_hr.py:84-100, cif_seeds.py:67-90); seeds are 6 floats (v, f, x, y, w, h)
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
                  const pp_params &p, int *d_status, cudaStream_t st, int det = 0);
+// The compacted CIF sources of the last cifhr launch on this workspace (cifhr.cu), for the seed stage.
+struct CifSrcView {
+  const float4 *a;     // (B,F,src_cap) cx, cy, sigma^2, v / 16 / len_cifs
+  const float2 *c;     // (B,F,src_cap) scale in pixels (CifDet: w, h in pixels)
+  const int *n;        // (B,F)
+  int src_cap;
+};
+CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c);
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
                     int *d_status, cudaStream_t st, int det, int merge);
@@ -17,6 +25,10 @@ size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det = 0);
 int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, const pp_shape &s,
                          const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
                          int reset, cudaStream_t st, int det);
+// the same from the compacted CIF sources instead of the field (valid when seed_threshold >=
+// cif_threshold, one field set, same min-scale filter): ~60 sources per plane instead of 6561 cells
+int seeds_collect_from_sources_launch(const CifSrcView &src, const float *d_hr, void *d_ws, const pp_shape &s,
+                                      const pp_caps &c, const pp_params &p, cudaStream_t st, int det);
 int seeds_sort_launch(float *d_seeds, int *d_n_seeds, void *d_ws, int B, const pp_caps &c,
                       const pp_params &p, int *d_status, cudaStream_t st, int det);
 int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,

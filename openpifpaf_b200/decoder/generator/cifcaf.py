@@ -232,6 +232,34 @@ class CifCaf(Generator):
                     orig.frontier_order = list(orig.frontier_order) + list(ann.frontier_order)
                     anns[r] = orig
 
+    def decode_stream(self, batches, *, n_lanes=4):
+        """Generator over device-resident batches ``(cif, caf)`` (CUDA tensors): keeps ``n_lanes``
+        batches in flight on their own streams / workspaces and yields each batch's
+        List[List[Annotation]] in order.  Same results as ``decode_batch`` per batch."""
+        eng = self.engine()
+        params = self.params()
+        tickets = []
+
+        def collect(ticket):
+            buf = ticket.wait()
+            n_ann = buf.dev['n_ann'].cpu().numpy()
+            status = buf.dev['status'].cpu().numpy()
+            if status.any():
+                raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
+            nmax = int(n_ann.max(initial=0))
+            npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
+            return self._annotations_from(
+                n_ann, buf.dev['ann_data'][:, :nmax].cpu().numpy(),
+                buf.dev['ann_scales'][:, :nmax].cpu().numpy(), buf.dev['ann_source'][:, :nmax].cpu().numpy(),
+                buf.dev['pre_data'][:, :npre].cpu().numpy(), buf.dev['pre_order'][:, :npre].cpu().numpy())
+
+        for cif, caf in batches:
+            if len(tickets) == n_lanes:
+                yield collect(tickets.pop(0))
+            tickets.append(eng.submit(cif, caf, params, n_lanes=n_lanes))
+        while tickets:
+            yield collect(tickets.pop(0))
+
     def decode_batch_multiscale(self, fields):
         """Multi-scale FieldConfig (decoder/factory.py:153-180): ``fields[i]`` are the batched head
         tensors addressed by ``field_config.cif_indices`` / ``caf_indices`` (each with its own

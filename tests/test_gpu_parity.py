@@ -672,3 +672,55 @@ def test_multiscale_matches_oracle_and_golden(oracle, coco_skeleton, configured_
         assert np.array_equal(fwd[l, :, :nf[l]], o.forward[l])
         assert np.array_equal(bwd[l, :, :nb[l]], o.backward[l])
         assert sha256(np.ascontiguousarray(fwd[l, :, :nf[l]])) == str(g['caf_f_sha256'][l])
+
+
+def test_decode_stream_lanes_equal_single_batches(coco_skeleton, configured_decoder):
+    """CifCaf.decode_stream (three batches in flight on their own streams / workspaces) returns,
+    batch for batch, exactly what decode_batch returns."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    batches = []
+    for k in range(7):
+        pair = [fields((161, 241), 1 + (k + b) % 4, pose_seed=100 + 10 * k + b, jitter_seed=7 * k + b)[:2]
+                for b in range(3)]
+        batches.append((torch.from_numpy(np.stack([p[0] for p in pair])).cuda(),
+                        torch.from_numpy(np.stack([p[1] for p in pair])).cuda()))
+    want = [dec.decode_batch(c, a) for c, a in batches]
+    got = list(dec.decode_stream(iter(batches), n_lanes=3))
+    assert len(got) == len(want) == 7
+    for g_batch, w_batch in zip(got, want):
+        assert [len(x) for x in g_batch] == [len(x) for x in w_batch]
+        for g_img, w_img in zip(g_batch, w_batch):
+            for g, w in zip(g_img, w_img):
+                assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
+                assert [(s, e) for s, e, _, _ in g.decoding_order] == [(s, e) for s, e, _, _ in w.decoding_order]
+    # a lane may not be reused before its ticket was collected
+    eng = dec.engine()
+    tickets = [eng.submit(*batches[0], dec.params(), n_lanes=2) for _ in range(2)]
+    with pytest.raises(RuntimeError):
+        eng.submit(*batches[0], dec.params(), n_lanes=2)
+    for t in tickets:
+        t.wait()
+
+
+@pytest.mark.parametrize('seed_th,cif_th,score_scale', [(0.05, 0.1, 1.0), (0.3, 0.1, 0.9), (0.1, 0.1, 1.0)])
+def test_seed_paths_agree_with_oracle(oracle, coco_skeleton, configured_decoder, seed_th, cif_th, score_scale):
+    """Seeds come from the CifHr stage's compacted sources when seed_threshold >= cif_threshold and
+    from a scan of the field otherwise; both must reproduce the oracle's seed list and annotations."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    decoder.CifSeeds.threshold, decoder.CifHr.v_threshold = seed_th, cif_th
+    decoder.CifSeeds.score_scale = score_scale
+    cif, caf, _ = fields((321, 481), 6, pose_seed=13, jitter_seed=14)
+    o = oracle.decode(cif, caf, coco_skeleton, oracle.Config(exp_mode=1, seed_th=seed_th, cif_th=cif_th,
+                                                            seed_score_scale=score_scale))
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    buf = dec.engine().run_device(torch.from_numpy(cif[None]).cuda(), torch.from_numpy(caf[None]).cuda(),
+                                  dec.params(), keep=('ann', 'seeds', 'hr'))
+    ns = int(buf.dev['n_seeds'][0])
+    assert ns == len(o.seeds) > 0
+    assert np.array_equal(buf.dev['seeds'][0, :ns].cpu().numpy(), o.seeds)
+    n = int(buf.dev['n_ann'][0])
+    assert n == len(o.data)
+    assert np.array_equal(buf.dev['ann_data'][0, :n].cpu().numpy(), o.data)
