@@ -122,6 +122,11 @@ typedef struct pp_params {
   struct pp_profile *profile;    /* optional per-stage CUDA-event timer (NULL = off)    */
   const pp_initial *initial;     /* optional initial annotations (NULL = none)          */
   const pp_inverse *inverse;     /* optional annotations_inverse after the NMS (NULL = none) */
+  int32_t host_mapped;           /* host entries only: copy just the confidence planes (1/5 of cif, 1/9
+                                    of caf) and let the kernels read the other planes of the active
+                                    cells straight from the pinned, device-mapped host buffers.  Used
+                                    when seed_threshold >= cif_threshold and no force_complete;
+                                    otherwise the full copy is made.  Same results.            */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
@@ -236,6 +241,8 @@ typedef struct pp_field_set {
   float cif_min_scale;     /* FieldConfig.cif_min_scales[k]                 */
   float caf_min_distance;  /* FieldConfig.caf_min_distances[k]              */
   float caf_max_distance;  /* FieldConfig.caf_max_distances[k]; 0 = None    */
+  const float *cif_rest;   /* optional: where the non-confidence planes of cif / caf are read from  */
+  const float *caf_rest;   /* (same layout; used by the host-mapped entries, NULL = cif / caf)      */
 } pp_field_set;
 
 /* pp_decode_batch over several field sets: CifHr maps merged with np.maximum (cif_hr.py:59-78;

@@ -43,7 +43,7 @@ class Inverse(C.Structure):
 class FieldSet(C.Structure):
     _fields_ = [('cif', C.c_void_p), ('caf', C.c_void_p), ('H', C.c_int32), ('W', C.c_int32),
                 ('stride', C.c_int32), ('cif_min_scale', C.c_float), ('caf_min_distance', C.c_float),
-                ('caf_max_distance', C.c_float)]
+                ('caf_max_distance', C.c_float), ('cif_rest', C.c_void_p), ('caf_rest', C.c_void_p)]
 
 
 class DetParams(C.Structure):
@@ -72,7 +72,7 @@ class Params(C.Structure):
         ('connection_method', C.c_int32), ('greedy', C.c_int32),
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
         ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
-        ('inverse', C.POINTER(Inverse)),
+        ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32),
     ]
 
 

@@ -426,7 +426,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
     const float *second = hflip_pairs ? sets[g + n_groups].cif : nullptr;
     if (second && (sets[g + n_groups].H != q.H || sets[g + n_groups].W != q.W)) return PP_ERR_ARG;
     if ((rc = cifhr_launch_ex(sets[g].cif, second, hr, w.stage, q, *s, *c, *p, sets[g].cif_min_scale,
-                              o->status, st, 0, g > 0)))
+                              o->status, st, 0, g > 0, second ? nullptr : sets[g].cif_rest)))
       return rc;
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
@@ -446,7 +446,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   for (int k = 0; k < n_sets; k++)
     if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, set_shape(k),
                                    *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
-                                   o->status, st)))
+                                   o->status, st, sets[k].caf_rest)))
       return rc;
   AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
@@ -473,7 +473,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
     for (int k = 0; k < n_sets; k++)
       if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, 0.0001f, w.fwd, w.nfwd, w.bwd, w.nbwd, set_shape(k),
                                      *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
-                                     o->status, st)))
+                                     o->status, st, sets[k].caf_rest)))
         return rc;
     if ((rc = caf_bin_launch(w.fwd, w.nfwd, w.bwd, w.nbwd, w.bin_rows, w.bin_start, *s, *c, st)))
       return rc;
@@ -496,7 +496,41 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
                     const pp_caps *c, const pp_params *p, void *stream) {
   if (!s || !p) return PP_ERR_ARG;
   pp_field_set one = {d_cif, d_caf, s->H, s->W, s->stride, p->cif_min_scale, p->caf_min_distance,
-                      p->caf_max_distance};
+                      p->caf_max_distance, nullptr, nullptr};
+  return decode_core(&one, 1, 0, sk, o, d_ws, ws_bytes, s, c, p, stream);
+}
+
+// ---- host-mapped input ---------------------------------------------------------
+// The decoder looks at every confidence value but at the other planes only where a cell is above
+// the threshold (~1 % of the cells).  With the fields in pinned, device-mapped host memory the
+// confidence planes are copied (strided DMA, 14 % of the bytes) and the kernels fetch the rest of
+// the active cells over PCIe on demand.
+static bool mapped_applies(const pp_params *p) {
+  return p->host_mapped && !p->force_complete && p->seed_threshold >= p->cif_threshold;
+}
+
+// device-visible alias of a pinned host buffer, or NULL
+static const float *mapped_alias(const float *h) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  if (attr.type != cudaMemoryTypeHost || !attr.devicePointer) return nullptr;
+  return (const float *)attr.devicePointer;
+}
+
+// copy the confidence plane of every (image, field) block of `planes` planes
+static int copy_conf_planes(float *d, const float *h, size_t blocks, int planes, size_t cells,
+                            cudaStream_t st) {
+  const size_t pitch = (size_t)planes * cells * sizeof(float);
+  PP_CUDA_CHECK(cudaMemcpy2DAsync(d, pitch, h, pitch, cells * sizeof(float), blocks,
+                                  cudaMemcpyHostToDevice, st));
+  return PP_OK;
+}
+
+static int decode_mapped(const float *d_cif, const float *d_caf, const float *cif_rest, const float *caf_rest,
+                         const pp_skeleton *sk, const pp_outputs *o, void *d_ws, size_t ws_bytes,
+                         const pp_shape *s, const pp_caps *c, const pp_params *p, void *stream) {
+  pp_field_set one = {d_cif, d_caf, s->H, s->W, s->stride, p->cif_min_scale, p->caf_min_distance,
+                      p->caf_max_distance, cif_rest, caf_rest};
   return decode_core(&one, 1, 0, sk, o, d_ws, ws_bytes, s, c, p, stream);
 }
 
@@ -676,11 +710,20 @@ int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, f
     return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   size_t B = s->B, cells = (size_t)s->H * s->W;
-  PP_CUDA_CHECK(cudaMemcpyAsync(d_cif, h_cif, B * s->F * 5 * cells * sizeof(float),
-                                cudaMemcpyHostToDevice, st));
-  PP_CUDA_CHECK(cudaMemcpyAsync(d_caf, h_caf, B * s->L * 9 * cells * sizeof(float),
-                                cudaMemcpyHostToDevice, st));
-  int rc = pp_decode_batch(d_cif, d_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
+  const float *m_cif = (p && mapped_applies(p)) ? mapped_alias(h_cif) : nullptr;
+  const float *m_caf = m_cif ? mapped_alias(h_caf) : nullptr;
+  int rc;
+  if (m_cif && m_caf) {
+    if ((rc = copy_conf_planes(d_cif, h_cif, B * s->F, 5, cells, st))) return rc;
+    if ((rc = copy_conf_planes(d_caf, h_caf, B * s->L, 9, cells, st))) return rc;
+    rc = decode_mapped(d_cif, d_caf, m_cif, m_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
+  } else {
+    PP_CUDA_CHECK(cudaMemcpyAsync(d_cif, h_cif, B * s->F * 5 * cells * sizeof(float),
+                                  cudaMemcpyHostToDevice, st));
+    PP_CUDA_CHECK(cudaMemcpyAsync(d_caf, h_caf, B * s->L * 9 * cells * sizeof(float),
+                                  cudaMemcpyHostToDevice, st));
+    rc = pp_decode_batch(d_cif, d_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
+  }
   if (rc) return rc;
   size_t strides[17];
   output_strides(*s, *c, strides);
@@ -758,16 +801,27 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
   size_t strides[17];
   output_strides(*s, *c, strides);
 
+  const float *m_cif = mapped_applies(p) ? mapped_alias(h_cif) : nullptr;
+  const float *m_caf = m_cif ? mapped_alias(h_caf) : nullptr;
+  const bool mapped = m_cif && m_caf;
   // the copy-in stream starts after whatever is already queued on `stream`
   PP_CUDA_CHECK(cudaEventRecord(q->ev_start, st));
   PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_in, q->ev_start, 0));
   for (int k = 0; k < n_chunks; k++) {
     const size_t b0 = (size_t)k * chunk_images;
     const size_t nb = (size_t)s->B - b0 < (size_t)chunk_images ? (size_t)s->B - b0 : (size_t)chunk_images;
-    PP_CUDA_CHECK(cudaMemcpyAsync(d_cif + b0 * cif_img, h_cif + b0 * cif_img, nb * cif_img * sizeof(float),
-                                  cudaMemcpyHostToDevice, q->s_in));
-    PP_CUDA_CHECK(cudaMemcpyAsync(d_caf + b0 * caf_img, h_caf + b0 * caf_img, nb * caf_img * sizeof(float),
-                                  cudaMemcpyHostToDevice, q->s_in));
+    if (mapped) {
+      int rcc;
+      if ((rcc = copy_conf_planes(d_cif + b0 * cif_img, h_cif + b0 * cif_img, nb * s->F, 5, cells, q->s_in)))
+        return rcc;
+      if ((rcc = copy_conf_planes(d_caf + b0 * caf_img, h_caf + b0 * caf_img, nb * s->L, 9, cells, q->s_in)))
+        return rcc;
+    } else {
+      PP_CUDA_CHECK(cudaMemcpyAsync(d_cif + b0 * cif_img, h_cif + b0 * cif_img, nb * cif_img * sizeof(float),
+                                    cudaMemcpyHostToDevice, q->s_in));
+      PP_CUDA_CHECK(cudaMemcpyAsync(d_caf + b0 * caf_img, h_caf + b0 * caf_img, nb * caf_img * sizeof(float),
+                                    cudaMemcpyHostToDevice, q->s_in));
+    }
     PP_CUDA_CHECK(cudaEventRecord(q->ev_in[k], q->s_in));
   }
   for (int k = 0; k < n_chunks; k++) {
@@ -793,8 +847,11 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
       inv_sub.meta += b0;
       p_sub.inverse = &inv_sub;
     }
-    int rc = pp_decode_batch(d_cif + b0 * cif_img, d_caf + b0 * caf_img, sk, &d_sub, d_ws, ws_bytes,
-                             &sub, c, &p_sub, stream);
+    int rc = mapped
+        ? decode_mapped(d_cif + b0 * cif_img, d_caf + b0 * caf_img, m_cif + b0 * cif_img, m_caf + b0 * caf_img,
+                        sk, &d_sub, d_ws, ws_bytes, &sub, c, &p_sub, stream)
+        : pp_decode_batch(d_cif + b0 * cif_img, d_caf + b0 * caf_img, sk, &d_sub, d_ws, ws_bytes, &sub, c,
+                          &p_sub, stream);
     if (rc) return rc;
     PP_CUDA_CHECK(cudaEventRecord(q->ev_done[k], st));
     PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_out, q->ev_done[k], 0));

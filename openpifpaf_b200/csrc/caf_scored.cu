@@ -24,7 +24,8 @@ constexpr int kCafThreads = 256;
 constexpr int kCafSlab = 8192;       // cells per slab: the active-cell list of a slab is 32 KiB of smem
 
 __global__ void __launch_bounds__(kCafThreads)
-caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, pp_skeleton sk,
+caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ caf_rest,
+                  const float *__restrict__ hr, pp_skeleton sk,
                   float *__restrict__ fwd, int *__restrict__ nfwd, float *__restrict__ bwd,
                   int *__restrict__ nbwd, pp_shape s, int cap, int hh, int hw, float th,
                   float cif_floor, float cif_floor_compl, float min_dist, int use_min, float max_dist,
@@ -35,6 +36,9 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
   const int b = bl / s.L, l = bl - b * s.L;
   const int n = s.H * s.W;
   const float *p = caf + (size_t)bl * 9 * n;
+  // caf_rest != NULL (host-mapped input): the eight geometry planes are read from the pinned host
+  // buffer, only where a cell is active; the confidence plane was copied to the device
+  const float *pr = caf_rest ? caf_rest + (size_t)bl * 9 * n : p;
   const float stride = (float)s.stride;
   const int j1 = sk.joints[l][0] - 1, j2 = sk.joints[l][1] - 1;
   const float *hr_b = hr + (size_t)b * s.F * hh * hw;
@@ -55,8 +59,9 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ hr, p
       float sf = 0.f, sb = 0.f;
       if (i < n_act) {
         const int c = s_cells[i];
+        nine[0] = __ldg(p + c);
 #pragma unroll
-        for (int r = 0; r < 9; r++) nine[r] = __ldg(p + (size_t)r * n + c);
+        for (int r = 1; r < 9; r++) nine[r] = __ldg(pr + (size_t)r * n + c);
         bool ok = true;
         if (use_min || use_max) {                                 // :47-55 (multi-scale only)
           float dx = __fsub_rn(nine[1], nine[5]), dy = __fsub_rn(nine[2], nine[6]);
@@ -225,13 +230,14 @@ int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, co
 int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                          float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                          const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_distance,
-                         float max_distance, int append, int *d_status, cudaStream_t st) {
+                         float max_distance, int append, int *d_status, cudaStream_t st,
+                         const float *caf_rest) {
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const float stride = (float)s.stride;
   prof_mark(p.profile, kStCaf, st);
   const size_t smem = (size_t)min(s.H * s.W, kCafSlab) * sizeof(int);
   caf_scored_kernel<<<s.B * s.L, kCafThreads, smem, st>>>(
-      d_caf, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
+      d_caf, caf_rest, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
       p.cif_floor_compl, min_distance / stride, min_distance != 0.0f, max_distance / stride,
       max_distance > 0.0f, append, d_status);
   PP_LAUNCH_CHECK("caf_scored_kernel");
@@ -242,7 +248,7 @@ int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &
                       float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                       const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {
   return caf_scored_launch_ex(d_caf, d_hr, sk, score_th, d_fwd, d_nfwd, d_bwd, d_nbwd, s, s, c, p,
-                              p.caf_min_distance, p.caf_max_distance, 0, d_status, st);
+                              p.caf_min_distance, p.caf_max_distance, 0, d_status, st, nullptr);
 }
 
 }  // namespace pp

@@ -113,8 +113,8 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
 // ---------------------------------------------------------------------------
 // K1: ordered compaction of CIF sources per (image, field).
 __global__ void __launch_bounds__(kCompactThreads)
-cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2, CifHrWs w, pp_shape s,
-                   int src_cap, int hh, int hw,
+cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2,
+                   const float *__restrict__ rest, CifHrWs w, pp_shape s, int src_cap, int hh, int hw,
                    float v_th, float min_scale_over_stride, int use_min_scale, int det,
                    int *__restrict__ status) {
   extern __shared__ int sm_diff[];   // nstrips + 1 difference array
@@ -135,6 +135,9 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   int count = 0;
   for (int pass = 0; pass < (cif2 ? 2 : 1); pass++) {
   const float *p = (pass ? cif2 : cif) + (size_t)bf * (det ? 7 : 5) * n;   // CifDet: [v, x, y, _, w, h, _]
+  // rest != NULL (host-mapped input, api.cu): only the confidence planes were copied to the device;
+  // the other planes are read where a cell is active, straight from the pinned host buffer
+  const float *pr = (rest && !pass) ? rest + (size_t)bf * (det ? 7 : 5) * n : p;
   for (int slab = 0; slab < n; slab += kCompactSlab) {
     // phase 1: cells above the threshold in row-major order (cif_hr.py:27); phase 2: one listed cell
     // per thread.  (Interleaving the two per 256 cells cost ~26 serial load + barrier rounds.)
@@ -148,8 +151,8 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
       if (flag) {
         c = s_cells[i];
         conf = __ldg(p + c);
-        c4 = __ldg(p + 4 * n + c);
-        if (det) c5 = __ldg(p + 5 * n + c);
+        c4 = __ldg(pr + 4 * n + c);
+        if (det) c5 = __ldg(pr + 5 * n + c);
         if (use_min_scale) flag = c4 > min_scale_over_stride;               // :28-29
         if (flag && use_min_scale && det) flag = c5 > min_scale_over_stride; // :87-89
       }
@@ -159,8 +162,8 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
       if (flag) {
         int k = count + off;
         if (k < src_cap) {
-          float cx = __fmul_rn(__ldg(p + n + c), stride);           // :32
-          float cy = __fmul_rn(__ldg(p + 2 * n + c), stride);       // :33
+          float cx = __fmul_rn(__ldg(pr + n + c), stride);          // :32
+          float cy = __fmul_rn(__ldg(pr + 2 * n + c), stride);      // :33
           float sg;
           if (det) {      // CifDetHr: sigma = max(1, 0.1 * min(w, h) * stride), cif_hr.py:91-94
             const float m = (c4 != c4) ? c4 : ((c5 != c5) ? c5 : fminf(c4, c5));   // np.minimum keeps NaN
@@ -476,7 +479,7 @@ CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c) {
 
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
-                    int *d_status, cudaStream_t st, int det, int merge) {
+                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest) {
   CifHrWs w = carve(d_ws, s_hr, c);
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const int bf = s.B * s.F;
@@ -486,7 +489,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
-      d_cif, d_cif2, w, s, c.src_cap, hh, hw, p.cif_threshold, min_scale / (float)s.stride,
+      d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold, min_scale / (float)s.stride,
       min_scale != 0.0f, det, d_status);
   PP_LAUNCH_CHECK("cif_compact_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
@@ -513,7 +516,8 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
 
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
                  const pp_params &p, int *d_status, cudaStream_t st, int det) {
-  return cifhr_launch_ex(d_cif, nullptr, d_hr, d_ws, s, s, c, p, p.cif_min_scale, d_status, st, det, 0);
+  return cifhr_launch_ex(d_cif, nullptr, d_hr, d_ws, s, s, c, p, p.cif_min_scale, d_status, st, det, 0,
+                         nullptr);
 }
 
 }  // namespace pp

@@ -19,7 +19,7 @@ struct CifSrcView {
 CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c);
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
-                    int *d_status, cudaStream_t st, int det, int merge);
+                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest = nullptr);
 size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det = 0);
 // the two halves of seeds_launch, for multi-scale: collect per field set (reset = first set), sort once
 int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, const pp_shape &s,
@@ -61,7 +61,8 @@ int caf_scored_launch(const float *d_caf, const float *d_hr, const pp_skeleton &
 int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleton &sk, float score_th,
                          float *d_fwd, int *d_nfwd, float *d_bwd, int *d_nbwd, const pp_shape &s,
                          const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_distance,
-                         float max_distance, int append, int *d_status, cudaStream_t st);
+                         float max_distance, int append, int *d_status, cudaStream_t st,
+                         const float *caf_rest = nullptr);
 // Candidate lists re-ordered by spatial bin of their source end, for the assembly
 // scans (caf_scored.cu: caf_bin_kernel).  Per (image, link, direction): seven rows
 // (score, source x/y, target x/y/scale, original list index) of `cap` columns, and

@@ -39,6 +39,9 @@ class DecoderParams:
     # annotations_inverse: (meta (B, sizeof pp_image_meta) uint8 CUDA tensor, hflip_target (F,) int32
     # CUDA tensor or None), see transforms.preprocess.pack_metas
     inverse: Optional[tuple] = None
+    # host entries: copy only the confidence planes, read the rest of the active cells from the pinned
+    # (device-mapped) host buffers over PCIe (pp_params.host_mapped)
+    host_mapped: bool = False
 
     def to_c(self):
         p = _lib.Params()
@@ -73,6 +76,7 @@ class DecoderParams:
                 mask = 1 << 31     # "no field seeds": bit outside any valid field
         p.seed_mask = mask
         p.profile = self.profile
+        p.host_mapped = int(bool(self.host_mapped))
         if self.initial is not None:
             data, scales, n = self.initial
             assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()
@@ -330,13 +334,11 @@ class DeviceDecoder:
         _lib.check(rc)
         return buf
 
-    def run_host_chunked(self, cif, caf, params, chunk, *, keep=('ann',)):
-        """Generator: enqueue the pipelined host decode, then yield ``(buf, b0, b1)`` as each
-        chunk's results land in the pinned host mirrors (later chunks still in flight)."""
-        cif_t = torch.as_tensor(cif)
-        caf_t = torch.as_tensor(caf)
+    def enqueue_host(self, cif_t, caf_t, params, chunk, *, keep=('ann',)):
+        """Enqueue the pipelined host decode of contiguous float32 host tensors (chunked H2D on the
+        pipeline's copy stream, kernels on the current stream, D2H on its copy-out stream).  Returns
+        ``(buf, chunk, n_chunks)``; collect with ``wait_host_chunk``."""
         assert cif_t.dtype == torch.float32 and caf_t.dtype == torch.float32
-        cif_t, caf_t = cif_t.contiguous(), caf_t.contiguous()
         B, F, five, H, W = cif_t.shape
         assert five == 5 and caf_t.shape == (B, len(self.skeleton), 9, H, W), (cif_t.shape, caf_t.shape)
         buf = self.buffers(B, F, H, W, keep=keep, host=True)
@@ -352,13 +354,60 @@ class DeviceDecoder:
                 self._pipeline.handle, _ptr(cif_t), _ptr(caf_t), _ptr(buf.d_cif), _ptr(buf.d_caf),
                 C.byref(self.c_skeleton), C.byref(buf.d_out), C.byref(buf.h_out), _ptr(buf.ws),
                 buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), chunk, _stream_ptr()))
-            for k in range(lib.pp_pipeline_chunks(self._pipeline.handle)):
-                rc = lib.pp_pipeline_wait(self._pipeline.handle, k)
-                if rc == _lib.PP_ERR_CAPACITY:
-                    lib.pp_pipeline_wait(self._pipeline.handle, -1)
-                    raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
-                _lib.check(rc)
-                yield buf, k * chunk, min((k + 1) * chunk, B)
+        buf.alive = (cif_t, caf_t, p)
+        return buf, chunk, lib.pp_pipeline_chunks(self._pipeline.handle)
+
+    def wait_host_chunk(self, buf, k):
+        lib = _lib.lib()
+        rc = lib.pp_pipeline_wait(self._pipeline.handle, k)
+        if rc == _lib.PP_ERR_CAPACITY:
+            lib.pp_pipeline_wait(self._pipeline.handle, -1)
+            raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
+        _lib.check(rc)
+
+    def run_host_chunked(self, cif, caf, params, chunk, *, keep=('ann',)):
+        """Generator: enqueue the pipelined host decode, then yield ``(buf, b0, b1)`` as each
+        chunk's results land in the pinned host mirrors (later chunks still in flight)."""
+        cif_t = torch.as_tensor(cif).contiguous()
+        caf_t = torch.as_tensor(caf).contiguous()
+        B = cif_t.shape[0]
+        buf, chunk, n_chunks = self.enqueue_host(cif_t, caf_t, params, chunk, keep=keep)
+        for k in range(n_chunks):
+            self.wait_host_chunk(buf, k)
+            yield buf, k * chunk, min((k + 1) * chunk, B)
+
+    def run_host_lanes(self, cif, caf, params, sub, n_lanes, *, keep=('ann',)):
+        """Like ``run_host_chunked`` but every sub-batch of ``sub`` images runs on its own lane
+        (stream + workspace + copy streams), ``n_lanes`` in flight: the kernels of one sub-batch
+        overlap those of the next.  Worth it when the copies are short (host_transfer='mapped').
+        Yields ``(buf, 0, n_images)`` per sub-batch, in order."""
+        cif_t = torch.as_tensor(cif).contiguous()
+        caf_t = torch.as_tensor(caf).contiguous()
+        B = cif_t.shape[0]
+        sub = max(1, min(int(sub), B))
+        ranges = [(b0, min(b0 + sub, B)) for b0 in range(0, B, sub)]
+        lanes = self.lanes(n_lanes)
+        cur = torch.cuda.current_stream(self._device())
+        pending = []
+
+        def submit(i):
+            b0, b1 = ranges[i]
+            lane = lanes[i % n_lanes]
+            lane.stream.wait_stream(cur)
+            with torch.cuda.stream(lane.stream):
+                buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], params, b1 - b0, keep=keep)
+            pending.append((lane, buf, b1 - b0))
+
+        nxt = min(n_lanes, len(ranges))
+        for i in range(nxt):
+            submit(i)
+        while pending:
+            lane, buf, nb = pending.pop(0)
+            lane.engine.wait_host_chunk(buf, 0)
+            yield buf, 0, nb               # the caller copies what it needs out of the pinned mirrors
+            if nxt < len(ranges):          # ... so the lane (and its buffers) can take the next sub-batch
+                submit(nxt)
+                nxt += 1
 
 
 class Lane:

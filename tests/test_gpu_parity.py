@@ -724,3 +724,36 @@ def test_seed_paths_agree_with_oracle(oracle, coco_skeleton, configured_decoder,
     n = int(buf.dev['n_ann'][0])
     assert n == len(o.data)
     assert np.array_equal(buf.dev['ann_data'][0, :n].cpu().numpy(), o.data)
+
+
+@pytest.mark.parametrize('chunk', [16, 3])
+def test_host_mapped_transfer_equals_copy(coco_skeleton, configured_decoder, chunk):
+    """host_transfer='mapped' (confidence planes copied, the other planes of the active cells read
+    from the pinned host buffers by the kernels) returns exactly what the full copy returns; with
+    unpinned inputs or force_complete it silently makes the full copy."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    items = [fields((241, 321), 1 + b % 4, pose_seed=200 + b, jitter_seed=300 + b)[:2] for b in range(10)]
+    cif = torch.from_numpy(np.stack([i[0] for i in items])).pin_memory()
+    caf = torch.from_numpy(np.stack([i[1] for i in items])).pin_memory()
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.host_chunk = dec.mapped_chunk = chunk
+    dec.host_lanes = 3
+    want = dec.decode_batch(cif, caf)
+    dec.host_transfer = 'mapped'
+    for c_in, a_in in ((cif, caf), (cif.numpy().copy(), caf.numpy().copy())):   # pinned, then pageable
+        got = dec.decode_batch(c_in, a_in)
+        assert [len(g) for g in got] == [len(w) for w in want] and sum(len(g) for g in got) >= 10
+        for g_img, w_img in zip(got, want):
+            for g, w in zip(g_img, w_img):
+                assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
+    decoder.CifCaf.force_complete = True
+    try:
+        a = dec.decode_batch(cif, caf)
+        dec.host_transfer = 'copy'
+        b = dec.decode_batch(cif, caf)
+    finally:
+        decoder.CifCaf.force_complete = False
+    for g_img, w_img in zip(a, b):
+        for g, w in zip(g_img, w_img):
+            assert np.array_equal(g.data, w.data)
