@@ -300,6 +300,12 @@ int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *d_out, vo
                            size_t ws_bytes, const pp_shape *s, const pp_caps *c,
                            const pp_det_params *p, void *stream);
 
+/* Preprocess.anndet_inverse (transforms/preprocess.py:84-94) on detection boxes, in place:
+ * d_box (B,ann_cap,4) x, y, w, h.  Rotation of the corners + bounding box (utils.rotate_box),
+ * offset, scale; like the reference, no hflip. */
+int pp_detections_inverse(float *d_box, const int32_t *d_n, const pp_inverse *inv, int32_t B,
+                          int32_t ann_cap, void *stream);
+
 /* nms.Detection.annotations (nms.py:79-102) on its own: B lists of `cap` detections in any
  * order (d_box 16-byte aligned); results in score order.  Scratch: pp_detection_nms_workspace_bytes. */
 size_t pp_detection_nms_workspace_bytes(int32_t B, int32_t cap);

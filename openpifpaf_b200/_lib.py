@@ -155,6 +155,7 @@ def lib():
     l.pp_cifdet_workspace_bytes.argtypes = [P(Shape), P(Caps)]
     l.pp_cifdet_workspace_bytes.restype = sz
     l.pp_cifdet_decode_batch.argtypes = [vp, P(DetOutputs), vp, sz, P(Shape), P(Caps), P(DetParams), vp]
+    l.pp_detections_inverse.argtypes = [vp, vp, P(Inverse), i32, i32, vp]
     l.pp_detection_nms_workspace_bytes.argtypes = [i32, i32]
     l.pp_detection_nms_workspace_bytes.restype = sz
     l.pp_detection_nms.argtypes = [vp] * 10 + [sz, i32, i32, P(DetParams), vp]
@@ -202,7 +203,7 @@ EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
     'pp_stage_name', 'pp_decode_launch_count',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
-    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detections_inverse', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',

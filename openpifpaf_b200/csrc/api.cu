@@ -637,6 +637,12 @@ int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *o, void *
   return det_assemble_launch(a, s->B, *p, w.work_score, st);
 }
 
+int pp_detections_inverse(float *d_box, const int32_t *d_n, const pp_inverse *inv, int32_t B,
+                          int32_t ann_cap, void *stream) {
+  if (!inv) return PP_ERR_ARG;
+  return detections_inverse_launch(d_box, d_n, *inv, B, ann_cap, (cudaStream_t)stream);
+}
+
 size_t pp_detection_nms_workspace_bytes(int32_t B, int32_t cap) {
   return (B > 0 && cap > 0) ? det_nms_ws_bytes(B, cap) : 0;
 }

@@ -48,6 +48,47 @@ __global__ void annotations_inverse_kernel(float *ann_data, float *ann_scales, c
   }
 }
 
+// Preprocess.anndet_inverse (transforms/preprocess.py:84-94, utils.rotate_box transforms/utils.py:5-28)
+// on detection boxes (x, y, w, h): rotation of the four corners in float32 and their bounding box,
+// then offset / scale in float64 rounded to float32 per statement.  The reference applies no hflip to
+// detections; neither does this.
+__global__ void detections_inverse_kernel(float *box, const int *n_det, const pp_image_meta *meta, int ann_cap) {
+  const int b = blockIdx.y, a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= ann_cap || a >= n_det[b]) return;
+  const pp_image_meta m = meta[b];
+  float *q = box + ((size_t)b * ann_cap + a) * 4;
+  float x = q[0], y = q[1], w = q[2], h = q[3];
+  if (m.rotate) {
+    // rotate_box is called with width = rw - 1, height = rh - 1: centre = (rw - 1) / 2 = rot_cx
+    const float cx[4] = {x, __fadd_rn(x, w), x, __fadd_rn(x, w)};
+    const float cy[4] = {y, y, __fadd_rn(y, h), __fadd_rn(y, h)};
+    float lo_x = 0.f, lo_y = 0.f, hi_x = 0.f, hi_y = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const float xo = __fsub_rn(cx[k], m.rot_cx), yo = __fsub_rn(cy[k], m.rot_cy);
+      const float rx = __fadd_rn(__fadd_rn(m.rot_cx, __fmul_rn(m.rot_cos, xo)), __fmul_rn(m.rot_sin, yo));
+      const float ry = __fadd_rn(__fsub_rn(m.rot_cy, __fmul_rn(m.rot_sin, xo)), __fmul_rn(m.rot_cos, yo));
+      lo_x = (k == 0 || rx < lo_x) ? rx : lo_x; hi_x = (k == 0 || rx > hi_x) ? rx : hi_x;
+      lo_y = (k == 0 || ry < lo_y) ? ry : lo_y; hi_y = (k == 0 || ry > hi_y) ? ry : hi_y;
+    }
+    x = lo_x; y = lo_y; w = __fsub_rn(hi_x, lo_x); h = __fsub_rn(hi_y, lo_y);
+  }
+  x = (float)((double)x + m.offset_x);
+  y = (float)((double)y + m.offset_y);
+  q[0] = (float)((double)x / m.scale_x);
+  q[1] = (float)((double)y / m.scale_y);
+  q[2] = (float)((double)w / m.scale_x);
+  q[3] = (float)((double)h / m.scale_y);
+}
+
+int detections_inverse_launch(float *box, const int *n_det, const pp_inverse &inv, int B, int ann_cap,
+                              cudaStream_t st) {
+  if (!inv.meta || !box || !n_det || B <= 0 || ann_cap <= 0) return PP_ERR_ARG;
+  detections_inverse_kernel<<<dim3((ann_cap + 127) / 128, B), 128, 0, st>>>(box, n_det, inv.meta, ann_cap);
+  PP_LAUNCH_CHECK("detections_inverse_kernel");
+  return PP_OK;
+}
+
 int annotations_inverse_launch(float *ann_data, float *ann_scales, const int *n_ann, float *pre_data,
                                const int *n_pre, const pp_inverse &inv, int B, int F, int ann_cap,
                                cudaStream_t st) {

@@ -115,6 +115,8 @@ int nms_launch(const float *in_data, const float *in_scales, const int *n_in, fl
 int annotations_inverse_launch(float *ann_data, float *ann_scales, const int *n_ann, float *pre_data,
                                const int *n_pre, const pp_inverse &inv, int B, int F, int ann_cap,
                                cudaStream_t st);
+int detections_inverse_launch(float *box, const int *n_det, const pp_inverse &inv, int B, int ann_cap,
+                              cudaStream_t st);
 int head_epilogue_launch(const float *d_x, float *d_out, int B, int nf, int nv, int h, int w, int quad,
                          cudaStream_t st);
 

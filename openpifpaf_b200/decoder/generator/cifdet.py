@@ -127,13 +127,24 @@ class CifDet(Generator):
         self.field_config = field_config
         self.categories = categories
 
-    def decode_batch(self, field):
-        """``field (B, C, 7, H, W)`` -> List[List[AnnotationDet]]."""
+    def decode_batch(self, field, metas=None):
+        """``field (B, C, 7, H, W)`` -> List[List[AnnotationDet]].  ``metas``: optional per-image
+        preprocessing meta dicts; the boxes are then mapped back to the original image on the device
+        (``Preprocess.anndet_inverse``, transforms/preprocess.py:84-94)."""
         cfg = self.field_config
         if len(cfg.cif_indices) != 1:
             raise NotImplementedError('CifDet decodes one head (cifdet.py:31-35)')
         t = run_cifdet(field, cfg.cif_strides[0], min_scale=cfg.cif_min_scales[0],
                        ann_cap=self.max_detections)
+        if metas is not None:
+            from ...transforms.preprocess import pack_metas
+            if len(metas) != t['det_box'].shape[0]:
+                raise ValueError('one meta dict per image')
+            d_meta = pack_metas(metas, t['det_box'].device)
+            inv = _lib.Inverse(d_meta.data_ptr(), None)
+            _lib.check(_lib.lib().pp_detections_inverse(
+                _stage.ptr(t['det_box']), _stage.ptr(t['n_det']), C.byref(inv), t['det_box'].shape[0],
+                t['det_box'].shape[1], _stage.stream_ptr()))
         n_det = t['n_det'].cpu().numpy()
         nmax = int(n_det.max(initial=0))
         fields = t['det_field'][:, :nmax].cpu().numpy()

@@ -67,6 +67,22 @@ class Preprocess:
     """Only the inverse mapping of the reference's abstract base class."""
 
     @staticmethod
+    def _detections_inverse(annotations, meta, device):
+        """anndet_inverse (transforms/preprocess.py:84-94) through pp_detections_inverse."""
+        from ..annotation import AnnotationDet
+        n = len(annotations)
+        box = torch.from_numpy(np.stack([np.asarray(a.bbox, np.float32) for a in annotations])[None]).to(device)
+        count = torch.tensor([n], dtype=torch.int32, device=device)
+        d_meta = pack_metas([meta], device)
+        inv = _lib.Inverse(d_meta.data_ptr(), None)
+        _lib.check(_lib.lib().pp_detections_inverse(
+            C.c_void_p(box.data_ptr()), C.c_void_p(count.data_ptr()), C.byref(inv), 1, n,
+            C.c_void_p(torch.cuda.current_stream(device).cuda_stream)))
+        out = box[0].cpu().numpy()
+        return [AnnotationDet(a.categories).set(a.field_i, a.score, out[i].copy())
+                for i, a in enumerate(annotations)]
+
+    @staticmethod
     def annotations_inverse(annotations, meta):
         """Reference signature: a list of Annotation and one meta dict; returns new
         annotations in original-image coordinates (the inputs are left untouched).
@@ -75,11 +91,13 @@ class Preprocess:
         from ..annotation import Annotation, AnnotationDet
         if not annotations:
             return []
-        if any(isinstance(a, AnnotationDet) for a in annotations):
-            raise NotImplementedError('AnnotationDet (CifDet) is outside the CifCaf path')
         if not torch.cuda.is_available():
             raise _lib.PifPafError('annotations_inverse runs on the GPU (no CPU path)')
         device = torch.device('cuda', torch.cuda.current_device())
+        if any(isinstance(a, AnnotationDet) for a in annotations):
+            if not all(isinstance(a, AnnotationDet) for a in annotations):
+                raise NotImplementedError('mixed pose / detection lists')
+            return Preprocess._detections_inverse(annotations, meta, device)
         n, F = len(annotations), len(annotations[0].data)
         data = np.stack([a.data for a in annotations]).astype(np.float32)[None]
         scales = np.stack([a.joint_scales for a in annotations]).astype(np.float32)[None]

@@ -37,6 +37,12 @@ def make_meta(kind, swap=None):
     return meta
 
 
+def detection_boxes():
+    """Seeded detection boxes (x, y, w, h) for the anndet_inverse fixture."""
+    rng = np.random.RandomState(5)
+    return np.concatenate([rng.uniform(0, 400, (12, 2)), rng.uniform(5, 200, (12, 2))], axis=1).astype(np.float32)
+
+
 def main():
     from oracle import build_ref
     ref = build_ref.import_reference()
@@ -57,6 +63,10 @@ def main():
         out[kind + '_scales'] = np.stack([a.joint_scales for a in res]).astype(np.float32)
         out[kind + '_dxy'] = np.array(
             [c[:2] for a in res for _, __, c1, c2 in a.decoding_order for c in (c1, c2)], np.float32)
+        dets = [ref.annotation.AnnotationDet(['a', 'b']).set(i % 2, np.float32(0.5), b.copy())
+                for i, b in enumerate(detection_boxes())]
+        dets = ref.transforms.Preprocess.annotations_inverse(dets, make_meta(kind, swap))
+        out[kind + '_detbox'] = np.stack([np.asarray(a.bbox, np.float32) for a in dets])
     np.savez_compressed(os.path.join(GOLDEN, 'inverse_mid.npz'), **out)
     print('inverse_mid', {k: v.shape for k, v in out.items() if k.startswith('rotated')})
 

@@ -44,3 +44,30 @@ def annotations_inverse(data, joint_scales, decoding_xy, meta, hflip_target=None
         dxy[:, i] = (dxy[:, i].astype(f64) + off[i]).astype(f32)
         dxy[:, i] = (dxy[:, i].astype(f64) / scale[i]).astype(f32)
     return data, js, dxy
+
+
+def detections_inverse(boxes, meta):
+    """Preprocess.anndet_inverse (transforms/preprocess.py:84-94 with utils.rotate_box,
+    transforms/utils.py:5-28) on boxes (N, 4) x, y, w, h float32.  Returns a transformed copy."""
+    f32, f64 = np.float32, np.float64
+    boxes = np.array(boxes, f32).reshape(-1, 4)
+    rot = meta.get('rotation') or {'angle': 0.0}
+    angle = -rot['angle']
+    if angle != 0.0:
+        c, s = f32(math.cos(angle / 180.0 * math.pi)), f32(math.sin(angle / 180.0 * math.pi))
+        hw, hh = f32((rot['width'] - 1) / 2), f32((rot['height'] - 1) / 2)      # width/2 of rotate_box
+        x0, y0 = boxes[:, 0], boxes[:, 1]
+        x1, y1 = x0 + boxes[:, 2], y0 + boxes[:, 3]
+        cx = np.stack([x0, x1, x0, x1], axis=1)
+        cy = np.stack([y0, y0, y1, y1], axis=1)
+        xo, yo = cx - hw, cy - hh
+        rx = (hw + c * xo) + s * yo
+        ry = (hh - s * xo) + c * yo
+        x, y = rx.min(axis=1), ry.min(axis=1)
+        boxes = np.stack([x, y, rx.max(axis=1) - x, ry.max(axis=1) - y], axis=1).astype(f32)
+    off = np.asarray(meta['offset'], f64)
+    scale = np.asarray(meta['scale'], f64)
+    boxes[:, :2] = (boxes[:, :2].astype(f64) + off).astype(f32)
+    boxes[:, :2] = (boxes[:, :2].astype(f64) / scale).astype(f32)
+    boxes[:, 2:] = (boxes[:, 2:].astype(f64) / scale).astype(f32)
+    return boxes

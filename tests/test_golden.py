@@ -82,6 +82,9 @@ def test_inverse_oracle_matches_reference_golden(kind):
     assert np.array_equal(got[0], g[kind + '_data'])
     assert np.array_equal(got[1], g[kind + '_scales'])
     assert np.array_equal(got[2], g[kind + '_dxy'])
+    from oracle.gen_golden_inverse import detection_boxes
+    from oracle.inverse_oracle import detections_inverse
+    assert np.array_equal(detections_inverse(detection_boxes(), meta), g[kind + '_detbox'])
 
 
 from conftest import DET_GOLDEN_NAMES, det_golden  # noqa: E402

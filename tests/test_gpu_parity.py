@@ -462,6 +462,17 @@ def test_annotations_inverse_matches_oracle_and_golden(kind):
         assert np.array_equal(got, g['%s_%s' % (kind, key)]), key
     assert np.array_equal(anns[0].data, data[0]), 'inputs are left untouched'
     assert [(s, e) for s, e, _, __ in res[0].decoding_order] == orders[0]
+    # detections (anndet_inverse): same call with AnnotationDet objects
+    from oracle.gen_golden_inverse import detection_boxes
+    from oracle.inverse_oracle import detections_inverse
+    from openpifpaf_b200.annotation import AnnotationDet
+    boxes = detection_boxes()
+    dets = [AnnotationDet(['a', 'b']).set(i % 2, np.float32(0.5), b.copy()) for i, b in enumerate(boxes)]
+    out = Preprocess.annotations_inverse(dets, meta)
+    got_boxes = np.stack([a.bbox for a in out])
+    assert np.array_equal(got_boxes, detections_inverse(boxes, meta))
+    assert np.array_equal(got_boxes, g[kind + '_detbox'])
+    assert np.array_equal(dets[0].bbox, boxes[0])
 
 
 def test_decode_batch_with_metas(oracle, coco_skeleton, configured_decoder):

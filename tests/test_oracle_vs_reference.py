@@ -302,3 +302,19 @@ def test_cifdet_decode(ref, oracle, hw, nb, seed, ncat, min_scale):
     assert np.array_equal(o.field, np.array([a.field_i for a in anns], np.int32))
     assert np.array_equal(o.score, np.array([a.score for a in anns], np.float32))
     assert np.array_equal(o.box, np.array([a.bbox for a in anns], np.float32).reshape(-1, 4))
+
+
+@pytest.mark.parametrize('kind', ['plain', 'scaled', 'flipped', 'rotated'])
+def test_detections_inverse(ref, kind):
+    """oracle detections_inverse == Preprocess.annotations_inverse on AnnotationDet objects
+    (anndet_inverse, transforms/preprocess.py:84-94), bit for bit."""
+    from oracle.inverse_oracle import detections_inverse
+    import openpifpaf.transforms  # noqa: F401
+    meta = _metas(ref)[kind]
+    rng = np.random.RandomState(5)
+    boxes = np.concatenate([rng.uniform(0, 400, (12, 2)), rng.uniform(5, 200, (12, 2))], axis=1).astype(np.float32)
+    anns = [ref.annotation.AnnotationDet(['a', 'b']).set(i % 2, np.float32(0.5), b.copy()) for i, b in enumerate(boxes)]
+    want = ref.transforms.Preprocess.annotations_inverse(anns, meta)
+    got = detections_inverse(boxes, meta)
+    assert np.array_equal(got, np.stack([np.asarray(a.bbox, np.float32) for a in want]))
+    assert all(np.asarray(a.bbox).dtype == np.float32 for a in want)
