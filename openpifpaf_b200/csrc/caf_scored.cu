@@ -21,7 +21,7 @@ namespace pp {
 
 constexpr int kCafThreads = 256;
 
-constexpr int kCafSlab = 8192;       // cells per slab: the active-cell list of a slab is 32 KiB of smem
+constexpr int kCafSlab = 8192;       // cells per slab: the active-cell list of a slab is 16 KiB of smem
 
 __global__ void __launch_bounds__(kCafThreads)
 caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ caf_rest,
@@ -30,7 +30,7 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ caf_r
                   int *__restrict__ nbwd, pp_shape s, int cap, int hh, int hw, float th,
                   float cif_floor, float cif_floor_compl, float min_dist, int use_min, float max_dist,
                   int use_max, int append, int *__restrict__ status) {
-  extern __shared__ int s_cells[];               // min(n, kCafSlab) active cell indices
+  extern __shared__ unsigned short s_cells[];    // min(n, kCafSlab) active cells, relative to the slab
   __shared__ int wtot_f[kCafThreads / 32], wtot_b[kCafThreads / 32];
   const int bl = blockIdx.x;
   const int b = bl / s.L, l = bl - b * s.L;
@@ -58,7 +58,7 @@ caf_scored_kernel(const float *__restrict__ caf, const float *__restrict__ caf_r
       float nine[9];
       float sf = 0.f, sb = 0.f;
       if (i < n_act) {
-        const int c = s_cells[i];
+        const int c = slab + s_cells[i];
         nine[0] = __ldg(p + c);
 #pragma unroll
         for (int r = 1; r < 9; r++) nine[r] = __ldg(pr + (size_t)r * n + c);
@@ -235,7 +235,7 @@ int caf_scored_launch_ex(const float *d_caf, const float *d_hr, const pp_skeleto
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const float stride = (float)s.stride;
   prof_mark(p.profile, kStCaf, st);
-  const size_t smem = (size_t)min(s.H * s.W, kCafSlab) * sizeof(int);
+  const size_t smem = (size_t)min(s.H * s.W, kCafSlab) * sizeof(unsigned short);
   caf_scored_kernel<<<s.B * s.L, kCafThreads, smem, st>>>(
       d_caf, caf_rest, d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, s, c.caf_cap, hh, hw, score_th, p.cif_floor,
       p.cif_floor_compl, min_distance / stride, min_distance != 0.0f, max_distance / stride,

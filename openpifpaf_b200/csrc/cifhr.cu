@@ -58,7 +58,7 @@ constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see stri
 constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored from (4 KiB pieces)
 constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
-constexpr int kCompactSlab = 8192;     // cells per active-cell list (32 KiB of shared memory)
+constexpr int kCompactSlab = 8192;     // cells per active-cell list (16 KiB of shared memory)
 
 struct CifHrWs {
   float4 *src_a;    // (B,F,src_cap) cx, cy, sigma^2, v
@@ -131,7 +131,7 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   float4 *oa = w.src_a + (size_t)bf * src_cap;
   int4 *ob = w.src_b + (size_t)bf * src_cap;
   float2 *oc = w.src_c + (size_t)bf * src_cap;
-  int *s_cells = sm_diff + w.nstrips + 1;        // active cells of one slab
+  unsigned short *s_cells = (unsigned short *)(sm_diff + w.nstrips + 1);   // active cells of one slab (relative)
   int count = 0;
   for (int pass = 0; pass < (cif2 ? 2 : 1); pass++) {
   const float *p = (pass ? cif2 : cif) + (size_t)bf * (det ? 7 : 5) * n;   // CifDet: [v, x, y, _, w, h, _]
@@ -149,7 +149,7 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
       int c = 0;
       float conf = 0.f, c4 = 0.f, c5 = 0.f;
       if (flag) {
-        c = s_cells[i];
+        c = slab + s_cells[i];
         conf = __ldg(p + c);
         c4 = __ldg(pr + 4 * n + c);
         if (det) c5 = __ldg(pr + 5 * n + c);
@@ -191,25 +191,43 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    if (count > src_cap) {
-      atomicOr(&status[bf / s.F], PP_STATUS_SRC_OVERFLOW);
-      count = src_cap;
+  // per-strip counts = prefix sum of the difference array; warp 0 scans it 32 strips at a time and
+  // appends the strips that have sources to the consumers' work list (order is irrelevant)
+  if (warp_id() == 0) {
+    const int lane = lane_id();
+    if (lane == 0) {
+      if (count > src_cap) {
+        atomicOr(&status[bf / s.F], PP_STATUS_SRC_OVERFLOW);
+        count = src_cap;
+      }
+      w.n_src[bf] = count;
     }
-    w.n_src[bf] = count;
-    int run = 0;
     int *sc = w.strip_cnt + (size_t)bf * w.nstrips;
-    int n_busy = 0;
-    for (int i = 0; i < w.nstrips; i++) {
-      run += sm_diff[i];
-      sc[i] = run;
-      n_busy += run != 0;
+    int run = 0, n_busy = 0;
+    for (int base = 0; base < w.nstrips; base += 32) {
+      const int i = base + lane;
+      int v = i < w.nstrips ? sm_diff[i] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      v += run;
+      if (i < w.nstrips) { sc[i] = v; sm_diff[i] = v; }
+      run = __shfl_sync(0xffffffffu, v, 31);
+      n_busy += __popc(__ballot_sync(0xffffffffu, i < w.nstrips && v != 0));
     }
-    // strips with sources go to the consumers' work list (order is irrelevant)
     if (n_busy) {
-      int at = atomicAdd(&w.cursors[0], n_busy);
-      for (int i = 0; i < w.nstrips; i++)
-        if (sc[i] != 0) w.busy_list[at++] = bf * w.nstrips + i;
+      int at = 0;
+      if (lane == 0) at = atomicAdd(&w.cursors[0], n_busy);
+      at = __shfl_sync(0xffffffffu, at, 0);
+      for (int base = 0; base < w.nstrips; base += 32) {
+        const int i = base + lane;
+        const bool busy = i < w.nstrips && sm_diff[i] != 0;
+        const unsigned m = __ballot_sync(0xffffffffu, busy);
+        if (busy) w.busy_list[at + __popc(m & ((1u << lane) - 1u))] = bf * w.nstrips + i;
+        at += __popc(m);
+      }
     }
   }
 }
@@ -485,7 +503,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
   if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
-  size_t smem = (size_t)(w.nstrips + 1 + min(s.H * s.W, kCompactSlab)) * sizeof(int);
+  size_t smem = (size_t)(w.nstrips + 1) * sizeof(int) + (size_t)min(s.H * s.W, kCompactSlab) * sizeof(unsigned short);
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(

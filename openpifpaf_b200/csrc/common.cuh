@@ -114,10 +114,11 @@ __device__ __forceinline__ int block_flag_scan(bool flag, int *warp_tot, int *to
 // sweeps: every warp owns a contiguous run of cells, counts its hits (four independent loads in
 // flight per lane), the warp totals give each warp its base, and the second sweep (the plane is in
 // L1 / L2 by then) writes the indices.  Two __syncthreads() in total instead of two per 256 cells.
-// `list` must hold c_hi - c_lo ints; `warp_cnt` is shared scratch of THREADS / 32 ints.
+// `list` receives c - c_lo (16 bits: a slab has at most 65536 cells) and must hold c_hi - c_lo
+// entries; `warp_cnt` is shared scratch of THREADS / 32 ints.
 template <int THREADS>
 __device__ __forceinline__ int block_active_cells(const float *__restrict__ conf, int c_lo, int c_hi,
-                                                  float th, int *list, int *warp_cnt) {
+                                                  float th, unsigned short *list, int *warp_cnt) {
   constexpr int NW = THREADS / 32;
   constexpr int U = 4;
   const int lane = lane_id(), w = warp_id();
@@ -157,7 +158,7 @@ __device__ __forceinline__ int block_active_cells(const float *__restrict__ conf
       for (int u = 0; u < U; u++) {
         const bool hit = v[u] > th;
         const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (hit) list[at + __popc(m & below)] = base + 32 * u + lane;
+        if (hit) list[at + __popc(m & below)] = (unsigned short)(base + 32 * u + lane - c_lo);
         at += __popc(m);
       }
     }

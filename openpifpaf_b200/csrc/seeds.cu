@@ -23,6 +23,7 @@ namespace pp {
 constexpr int kCollectThreads = 256;
 constexpr int kSortThreads = 1024;
 constexpr int kSortSmemKeys = 4096;    // 32 KiB of dynamic shared memory; larger lists sort in L2
+constexpr int kRankSortMax = 256;      // rank sort up to this many seeds (n^2 work: 1300 seeds took 250 us), bitonic above
 
 __device__ __forceinline__ uint32_t orderable(float v) {
   uint32_t b = __float_as_uint(v);
@@ -174,8 +175,38 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
     keys[i] = k;
   }
   __syncthreads();
+  if (n <= kRankSortMax) {
+    // short lists: every record counts the records that
+    // sort before it -- one barrier instead of the ~50 of the bitonic network
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const uint64_t me = keys[i];
+      int rank = 0;
+      for (int j = 0; j < n; j++) {
+        const uint64_t other = keys[j];
+        if ((other >> 24) != (me >> 24)) {
+          rank += (other >> 24) > (me >> 24);
+        } else if (j != i) {
+          const bool before = seed_before<REC>(other, me, raw);
+          // records equal in every field keep their raw order
+          rank += before || (j < i && !seed_before<REC>(me, other, raw));
+        }
+      }
+      const float *r = raw + (size_t)i * REC;
+      float *o = out + (size_t)rank * REC;
+#pragma unroll
+      for (int c = 0; c < REC; c++) o[c] = r[c];
+    }
+    if (threadIdx.x == 0) n_out[b] = n;
+    return;
+  }
+  // bitonic network.  A stage with partner distance j < 32 stays inside aligned groups of 32 keys,
+  // and a group is always handled by the same warp (position p belongs to thread p % 1024): between
+  // two such stages a warp barrier is enough; a stage with j >= 32 crosses groups on both sides.
+  bool prev_wide = false;      // the keys were loaded behind a CTA barrier
   for (int k = 2; k <= npad; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= 32 || prev_wide) __syncthreads(); else __syncwarp();
+      prev_wide = j >= 32;
       for (int i = threadIdx.x; i < npad; i += blockDim.x) {
         int l = i ^ j;
         if (l > i) {
@@ -185,9 +216,9 @@ seeds_sort_kernel(const float *__restrict__ raw_all, const int *__restrict__ n_r
           if (swap) { keys[i] = c; keys[l] = a; }
         }
       }
-      __syncthreads();
     }
   }
+  __syncthreads();
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const float *r = raw + (size_t)(keys[i] & 0xffffffu) * REC;
     float *o = out + (size_t)i * REC;
