@@ -491,7 +491,10 @@ def run_b200(args):
                        'note': "CifCaf.host_transfer='mapped': only the confidence planes are copied; the "
                                'kernels read the other planes of the cells above threshold from the pinned '
                                'host buffers over PCIe (same results)'},
-        'gpu_launches': _lib.lib().pp_decode_launch_count(None) * args.steps,
+        # kernels of this library launched in the timed `value` region (8 per decode: compact, splat, seeds
+        # from sources, seed sort, CafScored, candidate binning, assembly, NMS); 3 memsets per decode beside
+        'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 3) * args.steps,
+        'gpu_memsets': 3 * args.steps,
         'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
                      'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,
                      'peak_source': peak_src, 'algorithmic_bytes_per_launch': hr_bytes,

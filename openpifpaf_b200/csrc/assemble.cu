@@ -23,6 +23,8 @@
 //     Ties follow Python's tuple order (-score, (x, y, s, v), start, end).
 #include <cuda_pipeline.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "stages.cuh"
 #include "occupancy.cuh"
@@ -794,7 +796,11 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
   AsmArgs a2 = args;
   // one image per SM is the common case: give the lists (almost) the whole shared memory
-  const int stage_bytes = B <= num_sms() ? kStageBytesSolo : kStageBytes;
+  int stage_bytes = B <= num_sms() ? kStageBytesSolo : kStageBytes;
+  if (const char *e = getenv("PP_ASM_STAGE_KB")) {     // tuning experiments only
+    int kb = atoi(e);
+    if (kb >= 0 && kb * 1024 <= kStageBytesSolo) stage_bytes = kb * 1024;
+  }
   a2.stage_floats = stage_bytes / (int)sizeof(float);
   PP_CUDA_CHECK(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      kStageBytesSolo));
