@@ -305,6 +305,36 @@ def cpu_baseline_subprocess(args, batch):
         return {'value': None, 'unit': UNIT, 'cores': 0, 'kind': 'reference', 'sample': 'failed: %r' % e}
 
 
+def bind_to_gpu_numa(device_index):
+    """Multi-GPU runs: keep this rank (and the pinned buffers it first touches) on the CPUs NVML
+    reports as local to its GPU.  Best effort; returns the CPU list or None."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        handle = None
+        for i in range(pynvml.nvmlDeviceGetCount()):
+            h = pynvml.nvmlDeviceGetHandleByIndex(i)
+            u = pynvml.nvmlDeviceGetUUID(h)
+            u = u.decode() if isinstance(u, bytes) else u
+            if uuid in u:
+                handle = h
+                break
+        if handle is None:
+            return None
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
+        local = {c for c in range(ncpu) if (words[c // 64] >> (c % 64)) & 1}
+        allowed = local & set(os.sched_getaffinity(0))
+        if len(allowed) >= 2:
+            os.sched_setaffinity(0, allowed)
+            return sorted(allowed)
+    except Exception:  # pylint: disable=broad-except
+        pass
+    return None
+
+
 def run_b200(args):
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -326,6 +356,7 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=device)
+        bind_to_gpu_numa(local_rank)
 
     def barrier():
         torch.cuda.synchronize()

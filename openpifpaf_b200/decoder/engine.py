@@ -394,8 +394,18 @@ class DeviceDecoder:
             b0, b1 = ranges[i]
             lane = lanes[i % n_lanes]
             lane.stream.wait_stream(cur)
+            sub_params = params
+            if params.inverse is not None:      # per-image records: this sub-batch's slice
+                meta, target = params.inverse
+                sub_params = dataclasses.replace(params, inverse=(meta[b0:b1].contiguous(), target))
+            if params.initial is not None:
+                data, scales, n = params.initial
+                sub_params = dataclasses.replace(
+                    sub_params, initial=(data[b0:b1].contiguous(), scales[b0:b1].contiguous(),
+                                         n[b0:b1].contiguous()))
             with torch.cuda.stream(lane.stream):
-                buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], params, b1 - b0, keep=keep)
+                buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], sub_params, b1 - b0,
+                                                     keep=keep)
             pending.append((lane, buf, b1 - b0))
 
         nxt = min(n_lanes, len(ranges))

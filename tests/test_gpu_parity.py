@@ -768,3 +768,26 @@ def test_host_mapped_transfer_equals_copy(coco_skeleton, configured_decoder, chu
     for g_img, w_img in zip(a, b):
         for g, w in zip(g_img, w_img):
             assert np.array_equal(g.data, w.data)
+
+
+def test_host_mapped_with_metas(coco_skeleton, configured_decoder):
+    """Per-image meta records follow their images through the lane-parallel mapped host path."""
+    from conftest import HorizontalSwap, inverse_inputs
+    from oracle.gen_golden_inverse import META_KINDS, make_meta
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    swap = HorizontalSwap(inverse_inputs()[4])
+    items = [fields((161, 241), 1 + b % 3, pose_seed=400 + b, jitter_seed=500 + b)[:2] for b in range(9)]
+    cif = torch.from_numpy(np.stack([i[0] for i in items])).pin_memory()
+    caf = torch.from_numpy(np.stack([i[1] for i in items])).pin_memory()
+    metas = [make_meta(META_KINDS[b % 4], swap) for b in range(9)]
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.host_chunk = dec.mapped_chunk = 2
+    dec.host_lanes = 3
+    want = dec.decode_batch(cif, caf, metas=metas)
+    dec.host_transfer = 'mapped'
+    got = dec.decode_batch(cif, caf, metas=metas)
+    assert [len(g) for g in got] == [len(w) for w in want] and sum(len(g) for g in got) >= 9
+    for g_img, w_img in zip(got, want):
+        for g, w in zip(g_img, w_img):
+            assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
