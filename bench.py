@@ -8,14 +8,22 @@ A "step" is one pass of the hot path (CifHr -> seeds -> CafScored -> assembly
 -> keypoint NMS) over one batch of synthetic CIF/CAF fields.  One JSON line is
 printed by rank 0 (contract in DESIGN.md section "Measurement"):
 
-  value         images/s, fields already resident in HBM, pp_decode_batch
-                (8 kernels) timed with CUDA events on the launching stream;
+  value         images/s, fields already resident in HBM: K steps (one
+                pp_decode_batch = 8 kernels each) issued round-robin over
+                --lanes streams / workspaces, CUDA events around the K steps;
+  value_one_lane, stages_ms
+                the same K steps strictly one at a time on one stream, with the
+                library's per-stage CUDA-event profile;
   e2e           images/s through the public API CifCaf.decode_batch() with
-                PINNED HOST fields: H2D of the fields, kernels, D2H of the
-                results and the construction of the Annotation objects are all
-                inside the timed region;
+                PINNED HOST fields: H2D of every field plane, kernels, D2H of
+                the results and the construction of the Annotation objects are
+                all inside the timed region;
+  e2e_mapped    the same call with host_transfer='mapped' (only the confidence
+                planes are copied, the kernels read the other planes of the
+                active cells from the pinned buffers over PCIe);
   roofline      the CifHr splat kernel (the kernel that writes the hr maps)
-                against the measured HBM copy peak of MEASURED_PEAKS.json;
+                against the measured HBM copy peak of MEASURED_PEAKS.json,
+                timed in the one-lane pass; in_flight = while lanes overlap;
   cpu_baseline  the UNMODIFIED reference decoder (oracle/_ref, its Cython
                 functional module) on this box's host cores, bounded sample;
   --impl reference   the same reference decoder as its own arm.
