@@ -407,7 +407,7 @@ def run_b200(args):
         uuid = 'GPU-%s' % torch.cuda.get_device_properties(local_rank).uuid
     except Exception:  # pylint: disable=broad-except
         uuid = str(local_rank)
-    clocks = ClockSampler(uuid)
+    clocks = ClockSampler(uuid) if rank == 0 else None     # one poller per job, on the printing rank's GPU
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # (1) one batch at a time on one stream, with the per-stage profile: explains the step
     barrier()
@@ -468,7 +468,7 @@ def run_b200(args):
     e2e_mapped_s = max_over_ranks(time.perf_counter() - t0)
     dec.host_transfer = 'copy'
     assert [len(a) for a in anns_m] == [len(a) for a in anns], 'mapped and copied host paths disagree'
-    clock_info = clocks.stop()
+    clock_info = clocks.stop() if clocks is not None else None
     assert sum(len(a) for a in anns) == n_ann, 'host and device paths disagree on the annotation count'
     hbuf = eng.buffers(batch, cif.shape[1], cif.shape[3], cif.shape[4], host=True)
     d2h = sum(t.numel() * t.element_size() for t in hbuf.host.values())
