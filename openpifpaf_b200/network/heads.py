@@ -52,7 +52,7 @@ class FusedHeadEpilogue:
 
     def __call__(self, x, out=None):
         if not x.is_cuda:
-            raise _lib.PifPafError('FusedHeadEpilogue runs on CUDA tensors only (no CPU path)')
+            raise _lib.PifPafError(_lib.PP_ERR_ARG, 'FusedHeadEpilogue runs on CUDA tensors only (no CPU path)')
         x = x.detach()
         if x.dtype != torch.float32 or not x.is_contiguous():
             x = x.float().contiguous()

@@ -92,7 +92,7 @@ class Preprocess:
         if not annotations:
             return []
         if not torch.cuda.is_available():
-            raise _lib.PifPafError('annotations_inverse runs on the GPU (no CPU path)')
+            raise _lib.PifPafError(_lib.PP_ERR_CUDA, 'annotations_inverse runs on the GPU (no CPU path)')
         device = torch.device('cuda', torch.cuda.current_device())
         if any(isinstance(a, AnnotationDet) for a in annotations):
             if not all(isinstance(a, AnnotationDet) for a in annotations):

@@ -146,3 +146,88 @@ def test_json_data_batch_equals_per_annotation():
         anns.append(a)
     assert json_data_batch(anns) == [a.json_data() for a in anns]
     assert json_data_batch([]) == []
+
+
+def test_pack_metas_and_hflip_target_layout():
+    """Host packing of the reference's meta dicts into pp_image_meta records (no GPU needed)."""
+    import ctypes as C
+    import math
+    from conftest import HorizontalSwap
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, HFLIP
+    from openpifpaf_b200.transforms.preprocess import hflip_target, pack_metas
+    target = np.array([COCO_KEYPOINTS.index(HFLIP.get(k, k)) for k in COCO_KEYPOINTS], np.int32)
+    metas = [
+        {'offset': np.array((0.0, 0.0)), 'scale': np.array((1.0, 1.0)), 'hflip': False,
+         'width_height': np.array((640, 480)), 'rotation': {'angle': 0.0, 'width': None, 'height': None}},
+        {'offset': np.array((-12.0, 31.5)), 'scale': np.array((0.8, 0.7)), 'hflip': True,
+         'width_height': np.array((640, 480)), 'horizontal_swap': HorizontalSwap(target),
+         'rotation': {'angle': 30.0, 'width': 513, 'height': 385}},
+    ]
+    raw = pack_metas(metas, 'cpu').numpy()
+    assert raw.shape == (2, C.sizeof(_lib.ImageMeta))
+    recs = [_lib.ImageMeta.from_buffer_copy(raw[i].tobytes()) for i in range(2)]
+    assert (recs[0].rotate, recs[0].hflip, recs[0].scale_x, recs[0].offset_y) == (0, 0, 1.0, 0.0)
+    r = recs[1]
+    assert (r.rotate, r.hflip, r.flip_w1) == (1, 1, 639.0)
+    assert (r.offset_x, r.offset_y, r.scale_x, r.scale_y) == (-12.0, 31.5, 0.8, 0.7)
+    assert r.rot_cos == np.float32(math.cos(-30.0 / 180.0 * math.pi))       # cos / sin of MINUS the angle
+    assert r.rot_sin == np.float32(math.sin(-30.0 / 180.0 * math.pi))
+    assert (r.rot_cx, r.rot_cy) == (256.0, 192.0)
+    assert hflip_target(metas[:1], 17, 'cpu') is None
+    assert np.array_equal(hflip_target(metas, 17, 'cpu').numpy(), target)
+
+
+def test_fused_head_epilogue_shapes_and_errors():
+    """FusedHeadEpilogue validates shapes on the host and refuses CPU tensors (no CPU path)."""
+    import torch
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.network import FusedHeadEpilogue, index_field_torch
+    ep = FusedHeadEpilogue(17, 1)
+    x = torch.zeros(2, 17 * 5 * 4, 6, 9)
+    assert ep.out_shape(x) == (2, 17, 5, 11, 17)
+    assert FusedHeadEpilogue(19, 2, quad=0).out_shape(torch.zeros(1, 19 * 9, 6, 9)) == (1, 19, 9, 6, 9)
+    with pytest.raises(ValueError):
+        ep.out_shape(torch.zeros(2, 17 * 5, 6, 9))
+    with pytest.raises(_lib.PifPafError):
+        ep(x)
+    with pytest.raises(NotImplementedError):
+        FusedHeadEpilogue(17, 1, quad=2)
+    idx = index_field_torch((3, 4))
+    assert idx.shape == (2, 3, 4) and idx[0, 1, 3] == 3 and idx[1, 2, 0] == 2     # channel 0 = x, 1 = y
+
+
+def test_factory_builds_cifdet_and_multiscale_config():
+    """factory_decode: a DetectionMeta head gives a CifDet; multi_scale keeps the reference's
+    index arithmetic (and therefore its IndexError for a plain three-head network)."""
+    from openpifpaf_b200 import decoder
+
+    class Head:
+        def __init__(self, meta):
+            self.meta = meta
+
+        @staticmethod
+        def stride(basenet_stride):
+            return basenet_stride // 2
+
+    class DetMeta:
+        name, categories = 'cifdet', ['person', 'car']
+
+    class CifMeta:
+        name, keypoints = 'cif', ['a', 'b', 'c']
+
+    class CafMeta:
+        name, keypoints, skeleton = 'caf', ['a', 'b', 'c'], [(1, 2), (2, 3)]
+
+    det = decoder.factory_decode([Head(DetMeta)], basenet_stride=16)
+    assert isinstance(det, decoder.CifDet) and det.categories == ['person', 'car']
+    heads = [Head(CifMeta), Head(CafMeta), Head(CafMeta)]
+    with pytest.raises(IndexError):
+        decoder.factory_decode(heads, basenet_stride=16, multi_scale=True)
+    many = [Head(CifMeta), Head(CafMeta), Head(CafMeta)] * 10
+    dec = decoder.factory_decode(many, basenet_stride=16, multi_scale=True)
+    cfg = dec.field_config
+    assert cfg.cif_indices == [3 * v for v in range(10)] and cfg.caf_indices == [3 * v + 1 for v in range(10)]
+    assert cfg.cif_min_scales == [0.0, 12.0, 16.0, 24.0, 40.0] * 2
+    assert cfg.caf_max_distances == [160.0, 240.0, 320.0, 480.0, None] * 2
+    cfg.verify()
