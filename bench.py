@@ -54,7 +54,10 @@ WORKLOADS = {
     'coco17_641_5p': ((641, 641), 5, 64, False),
     'crowd_1281_50p': ((1281, 1281), 50, 16, False),
     'dense_641_5p': ((641, 641), 5, 64, True),
+    # CifDet: 80 categories, 20 synthetic boxes per image; a secondary line (value + reference)
+    'cifdet_641_20b': ((641, 641), 20, 64, False),
 }
+DET_CATEGORIES = 80
 DEFAULT_WORKLOAD = 'coco17_641_5p'
 
 
@@ -105,6 +108,25 @@ def make_batch(workload, batch, first_seed=0):
     return cif, caf, skeleton
 
 
+def make_det_batch(workload, batch, first_seed=0):
+    """`batch` distinct synthetic CifDet fields (B, C, 7, H, W)."""
+    from openpifpaf_b200.encoder import synthetic_det_fields
+    hw, n_boxes, _, _ = WORKLOADS[workload]
+    return np.stack([synthetic_det_fields(hw, n_boxes, box_seed=first_seed + i, jitter_seed=first_seed + i + 100,
+                                          n_categories=DET_CATEGORIES)[0] for i in range(batch)])
+
+
+def _ref_det_decode(field):
+    """One image through the reference's CifDet (worker process of the reference arm)."""
+    from oracle import build_ref
+    ref = build_ref.import_reference()
+    dec = ref.decoder
+    if dec.CifSeeds.threshold is None:
+        dec.CifHr.v_threshold, dec.CifSeeds.threshold, dec.CifSeeds.score_scale = 0.1, 0.2, 1.0
+    cats = ['c%d' % i for i in range(field.shape[0])]
+    return len(dec.generator.cifdet.CifDet(dec.FieldConfig(), cats)([field]))
+
+
 def configure_profile(decoder):
     """SURVEY.md 8d decoder settings (what decoder.cli + configure yield)."""
     decoder.CifHr.v_threshold = 0.1
@@ -136,9 +158,18 @@ class ReferenceRunner:
     def __init__(self, workload, batch, workers):
         from oracle import build_ref
         self.cores = workers or os.cpu_count() or 1
-        self.cif, self.caf, self.skeleton = make_batch(workload, batch)
         self.batch = batch
         self.kind = 'reference' if build_ref.staged() else 'port'
+        if workload.startswith('cifdet'):
+            import multiprocessing
+            if self.kind != 'reference':
+                raise SystemExit('the CifDet reference arm needs the staged reference (oracle/_ref)')
+            self.kind = 'reference-det'
+            self.det_fields = list(make_det_batch(workload, batch))
+            self.pool = multiprocessing.Pool(self.cores)
+            self.version = 'openpifpaf CifDet (oracle/_ref)'
+            return
+        self.cif, self.caf, self.skeleton = make_batch(workload, batch)
         if self.kind == 'reference':
             ref = build_ref.import_reference()
             configure_profile(ref.decoder)
@@ -157,6 +188,8 @@ class ReferenceRunner:
             self.version = 'oracle/cifcaf_oracle.c (C restatement)'
 
     def step(self):
+        if self.kind == 'reference-det':
+            return sum(self.pool.map(_ref_det_decode, self.det_fields))
         if self.kind == 'reference':
             out = self.dec.worker_pool.starmap(self.dec._mappable_annotations,
                                                zip(self.fields, [None] * self.batch))
@@ -189,13 +222,17 @@ def run_reference(args):
     value = batch * args.steps / dt
     sample = '%d steps x %d images of %s, pool of %d processes, %s' % (
         args.steps, batch, args.workload, r.cores, r.version)
+    det = args.workload.startswith('cifdet')
     line = {
-        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT,
+        'impl': 'reference',
+        'metric': 'decoded images/s (641px CifDet fields, %d categories)' % DET_CATEGORIES if det else METRIC,
+        'value': value, 'unit': UNIT,
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': 1e3 * dt / args.steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': workload_config(args.workload, batch, args.gpus),
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': r.cores, 'kind': r.kind,
+        'config': {'workload': '%s: batch %d x 641x641, %d categories' % (args.workload, batch, DET_CATEGORIES)}
+        if det else workload_config(args.workload, batch, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': r.cores, 'kind': r.kind.split('-')[0],
                          'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0, 'annotations_per_step': n_ann,
@@ -293,10 +330,10 @@ def measured_peak():
 # ----------------------------------------------------------------------------
 # B200 arm
 
-def cpu_baseline_subprocess(args, batch):
+def cpu_baseline_subprocess(args, batch, steps=20):
     """Runs the reference arm in a child process (before CUDA is initialised in
     this one, so the pool's fork is clean and the cores are idle)."""
-    cmd = [sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '20',
+    cmd = [sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', str(steps),
            '--warmup', '1', '--workload', args.workload, '--batch', str(batch)]
     env = dict(os.environ)
     for k in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE'):
@@ -343,7 +380,47 @@ def bind_to_gpu_numa(device_index):
     return None
 
 
+def run_b200_det(args):
+    """Secondary line: the CifDet path (pp_cifdet_decode_batch), device-resident fields, one GPU."""
+    import torch
+    _, n_boxes, default_batch, _ = WORKLOADS[args.workload]
+    batch = args.batch or default_batch
+    cpu_base = None if args.no_cpu_baseline else cpu_baseline_subprocess(args, batch, steps=2)
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; the B200 arm has no CPU path')
+    import openpifpaf_b200.decoder as decoder
+    from openpifpaf_b200.decoder.generator.cifdet import run_cifdet
+    decoder.CifHr.v_threshold, decoder.CifSeeds.threshold, decoder.CifSeeds.score_scale = 0.1, 0.2, 1.0
+    dev = torch.from_numpy(make_det_batch(args.workload, batch)).cuda()
+    for _ in range(max(args.warmup, 3)):
+        t = run_cifdet(dev, 8)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        t = run_cifdet(dev, 8)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / args.steps
+    hr_bytes = batch * DET_CATEGORIES * 641 * 641 * 4
+    line = {'metric': 'decoded images/s (641px CifDet fields, %d categories)' % DET_CATEGORIES,
+            'value': batch / ms * 1e3, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': ms, 'higher_is_better': True, 'dtype': 'f32',
+            'data': 'synthetic',
+            'config': {'workload': '%s: batch %d x 641x641, %d categories, %d boxes/image' % (
+                args.workload, batch, DET_CATEGORIES, n_boxes)},
+            'detections_per_step': int(t['n_det'].sum()),
+            'hr_bytes_per_step': hr_bytes, 'hr_gbs_whole_path': hr_bytes / ms / 1e6,
+            'note': 'includes per-call workspace / result allocation (run_cifdet)'}
+    if cpu_base is not None:
+        line['cpu_baseline'] = cpu_base
+    print(json.dumps(line), flush=True)
+    return 0
+
+
 def run_b200(args):
+    if args.workload.startswith('cifdet'):
+        return run_b200_det(args)
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
