@@ -791,3 +791,82 @@ def test_host_mapped_with_metas(coco_skeleton, configured_decoder):
     for g_img, w_img in zip(got, want):
         for g, w in zip(g_img, w_img):
             assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
+
+
+def test_parity_shim_primitives(oracle):
+    """The five functional.pyx-named entries of the C ABI (pp_scalar_square_add_gauss_with_max,
+    pp_scalar_values, pp_caf_center_s and, through decoder.Occupancy, pp_scalar_square_add_single /
+    pp_scalar_nonzero_clipped_with_reduction) against the oracle's primitives, which
+    test_oracle_vs_reference.py pins to the compiled reference; appendix-B edge cases included."""
+    import ctypes as C
+    from openpifpaf_b200 import _lib, decoder
+    from openpifpaf_b200.decoder import _stage
+    lib, orc = _lib.lib(), oracle.lib()
+    vp = lambda t: t.ctypes.data_as(C.c_void_p)  # noqa: E731
+    dev = lambda a: torch.from_numpy(a).cuda()    # noqa: E731
+    st = _stage.stream_ptr()
+
+    # scalar_square_add_gauss_with_max (functional.pyx:105-141)
+    rng = np.random.RandomState(3)
+    n = 400
+    x = rng.uniform(-10, 110, n).astype(np.float32)
+    y = rng.uniform(-10, 90, n).astype(np.float32)
+    s = rng.uniform(0.3, 9, n).astype(np.float32)
+    v = rng.uniform(0.01, 0.2, n).astype(np.float32)
+    x[5], s[9], x[11] = np.nan, np.inf, 1e9            # NaN coordinate, infinite sigma, far out of bounds
+    want = np.zeros((80, 100), np.float32)
+    orc.orc_scalar_square_add_gauss_with_max(vp(want), 80, 100, vp(x), vp(y), vp(s), vp(v), C.c_long(n),
+                                             C.c_float(1.0), C.c_float(1.0))
+    field = torch.zeros((80, 100), dtype=torch.float32, device='cuda')
+    dx, dy, ds, dv = dev(x), dev(y), dev(s), dev(v)      # named: a temporary would be freed and reused
+    _lib.check(lib.pp_scalar_square_add_gauss_with_max(
+        _stage.ptr(field), 80, 100, _stage.ptr(dx), _stage.ptr(dy), _stage.ptr(ds), _stage.ptr(dv),
+        n, 1.0, 1.0, st))
+    assert np.array_equal(field.cpu().numpy(), want)
+
+    # scalar_values (functional.pyx:231-244)
+    rng = np.random.RandomState(4)
+    fld = rng.uniform(0, 1, (50, 70)).astype(np.float32)
+    qx = rng.uniform(-5, 75, 300).astype(np.float32)
+    qy = rng.uniform(-5, 55, 300).astype(np.float32)
+    want = np.empty(300, np.float32)
+    orc.orc_scalar_values(vp(fld), 50, 70, vp(qx), vp(qy), C.c_long(300), C.c_float(-1.0), vp(want))
+    out = torch.empty((300,), dtype=torch.float32, device='cuda')
+    dfld, dqx, dqy = dev(fld), dev(qx), dev(qy)
+    _lib.check(lib.pp_scalar_values(_stage.ptr(dfld), 50, 70, _stage.ptr(dqx), _stage.ptr(dqy),
+                                    300, -1.0, _stage.ptr(out), st))
+    assert np.array_equal(out.cpu().numpy(), want)
+
+    # caf_center_s (functional.pyx:338-359): order-preserving compaction
+    caf = rng.uniform(0, 60, (9, 500)).astype(np.float32)
+    want = np.zeros((9, 500), np.float32)
+    orc.orc_caf_center_s.restype = C.c_long
+    k = orc.orc_caf_center_s(vp(caf), C.c_long(500), C.c_float(30.0), C.c_float(25.0), C.c_float(8.0), vp(want))
+    got = torch.zeros((9, 500), dtype=torch.float32, device='cuda')
+    cnt = torch.zeros((1,), dtype=torch.int32, device='cuda')
+    dcaf = dev(caf)
+    _lib.check(lib.pp_caf_center_s(_stage.ptr(dcaf), 500, 30.0, 25.0, 8.0, _stage.ptr(got),
+                                   _stage.ptr(cnt), st))
+    assert int(cnt.item()) == k > 0
+    assert np.array_equal(got.cpu().numpy()[:, :k], want[:, :k])   # (9, K) rows, kept columns in order
+
+    # Occupancy.set / get: scalar_square_add_single + scalar_nonzero_clipped_with_reduction
+    rng = np.random.RandomState(5)
+    occ = decoder.Occupancy((1, 120, 160), 2, min_scale=4)
+    mine = np.zeros((60, 80), np.uint8)
+    for _ in range(200):
+        px, py, ps = (np.float32(rng.uniform(-20, 180)), np.float32(rng.uniform(-20, 140)),
+                      np.float32(rng.uniform(0, 30)))
+        occ.set(0, px, py, ps)
+        orc.orc_occupancy_set(vp(mine), C.c_long(60), C.c_long(80), C.c_float(px), C.c_float(py), C.c_float(ps))
+    assert np.array_equal(occ.occupancy[0], mine)
+    for _ in range(100):
+        px, py = np.float32(rng.uniform(-20, 180)), np.float32(rng.uniform(-20, 140))
+        want_occ = orc.orc_occupancy_get(vp(mine), C.c_long(60), C.c_long(80), C.c_float(px), C.c_float(py),
+                                         C.c_float(2.0))
+        assert bool(occ.get(0, px, py)) == bool(want_occ)
+    assert occ.get(1, 5.0, 5.0) == 1.0                 # f >= F reads as occupied (occupancy.py:43-44)
+    wrap = decoder.Occupancy((1, 120, 160), 2, min_scale=4)
+    for _ in range(256):                                # uint8 wrap: 256 sets -> free again
+        wrap.set(0, 40.0, 40.0, 4.0)
+    assert wrap.get(0, 40.0, 40.0) == 0
