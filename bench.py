@@ -69,7 +69,7 @@ def parse_args():
     ap.add_argument('--impl', default='b200', choices=('b200', 'reference'))
     ap.add_argument('--workload', default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument('--batch', type=int, default=0, help='images per GPU per step (0 = workload default)')
-    ap.add_argument('--lanes', type=int, default=4,
+    ap.add_argument('--lanes', type=int, default=8,
                     help='value: batches in flight (streams + workspaces), 1 = strictly one at a time')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--host-chunk', type=int, default=0, help='e2e: images per pipeline chunk (0 = decoder default)')

@@ -127,6 +127,10 @@ typedef struct pp_params {
                                     cells straight from the pinned, device-mapped host buffers.  Used
                                     when seed_threshold >= cif_threshold and no force_complete;
                                     otherwise the full copy is made.  Same results.            */
+  int32_t in_flight;             /* hint: batches the caller keeps in flight on other streams (0/1 =
+                                    this one only).  > 1 makes the assembly kernel stage its lists in
+                                    80 KB instead of a whole SM's shared memory, so that CTAs of the
+                                    other batches' kernels can share its SMs.  Same results.     */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's

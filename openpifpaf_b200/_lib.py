@@ -72,7 +72,7 @@ class Params(C.Structure):
         ('connection_method', C.c_int32), ('greedy', C.c_int32),
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
         ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
-        ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32),
+        ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32), ('in_flight', C.c_int32),
     ]
 
 

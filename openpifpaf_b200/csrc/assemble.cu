@@ -795,8 +795,9 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   cs.has = sk.has_confidence_scales;
   for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
   AsmArgs a2 = args;
-  // one image per SM is the common case: give the lists (almost) the whole shared memory
-  int stage_bytes = B <= num_sms() ? kStageBytesSolo : kStageBytes;
+  // one image per SM and nothing else on the GPU: give the lists (almost) the whole shared memory;
+  // with other batches in flight (pp_params.in_flight) leave room for their CTAs on the same SM
+  int stage_bytes = (B <= num_sms() && p.in_flight <= 1) ? kStageBytesSolo : kStageBytes;
   if (const char *e = getenv("PP_ASM_STAGE_KB")) {     // tuning experiments only
     int kb = atoi(e);
     if (kb >= 0 && kb * 1024 <= kStageBytesSolo) stage_bytes = kb * 1024;

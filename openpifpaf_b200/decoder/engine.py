@@ -42,6 +42,8 @@ class DecoderParams:
     # host entries: copy only the confidence planes, read the rest of the active cells from the pinned
     # (device-mapped) host buffers over PCIe (pp_params.host_mapped)
     host_mapped: bool = False
+    # batches kept in flight on other streams (pp_params.in_flight); set by submit / run_host_lanes
+    in_flight: int = 1
 
     def to_c(self):
         p = _lib.Params()
@@ -77,6 +79,7 @@ class DecoderParams:
         p.seed_mask = mask
         p.profile = self.profile
         p.host_mapped = int(bool(self.host_mapped))
+        p.in_flight = int(self.in_flight)
         if self.initial is not None:
             data, scales, n = self.initial
             assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()
@@ -264,7 +267,7 @@ class DeviceDecoder:
         self._lanes = cur
         return cur[:n]
 
-    def submit(self, cif, caf, params: DecoderParams, *, n_lanes=4, keep=('ann',)):
+    def submit(self, cif, caf, params: DecoderParams, *, n_lanes=8, keep=('ann',)):
         """Enqueue one batch on the next lane and return a ``Ticket``; at most ``n_lanes`` batches
         are in flight, so the ticket that used this lane last must have been waited for."""
         lanes = self.lanes(n_lanes)
@@ -274,6 +277,8 @@ class DeviceDecoder:
             raise RuntimeError('lane still holds an uncollected batch: wait() for the ticket issued '
                                '%d submits ago before submitting more' % n_lanes)
         lane.stream.wait_stream(torch.cuda.current_stream(self._device()))
+        if n_lanes > 1 and params.in_flight != n_lanes:
+            params = dataclasses.replace(params, in_flight=n_lanes)
         with torch.cuda.stream(lane.stream):
             buf = lane.engine.run_device(cif, caf, params, keep=keep)
             done = torch.cuda.Event()
@@ -389,6 +394,8 @@ class DeviceDecoder:
         lanes = self.lanes(n_lanes)
         cur = torch.cuda.current_stream(self._device())
         pending = []
+        if n_lanes > 1 and len(ranges) > 1:
+            params = dataclasses.replace(params, in_flight=min(n_lanes, len(ranges)))
 
         def submit(i):
             b0, b1 = ranges[i]

@@ -244,7 +244,7 @@ class CifCaf(Generator):
                     orig.frontier_order = list(orig.frontier_order) + list(ann.frontier_order)
                     anns[r] = orig
 
-    def decode_stream(self, batches, *, n_lanes=4):
+    def decode_stream(self, batches, *, n_lanes=8):
         """Generator over device-resident batches ``(cif, caf)`` (CUDA tensors): keeps ``n_lanes``
         batches in flight on their own streams / workspaces and yields each batch's
         List[List[Annotation]] in order.  Same results as ``decode_batch`` per batch."""
