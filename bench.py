@@ -56,7 +56,14 @@ WORKLOADS = {
     'dense_641_5p': ((641, 641), 5, 64, True),
     # CifDet: 80 categories, 20 synthetic boxes per image; a secondary line (value + reference)
     'cifdet_641_20b': ((641, 641), 20, 64, False),
+    # BASELINE configs[1] literally: fields of a randomly initialised resnet50 + CifCaf heads on torch.randn
+    # images (degenerate, exp() scales up to 1e18, CifHr compute-bound, ~100 s/image for
+    # the reference), and the documented tamed variant (scale channels clamped to 20 cells)
+    'randinit_641': ((641, 641), 0, 64, False),
+    'randinit_641_tamed': ((641, 641), 0, 64, False),
 }
+RANDINIT_MAX_SCALE = {'randinit_641': None, 'randinit_641_tamed': 20.0}
+RANDINIT_ANN_CAP = 4096          # these fields give ~950 annotations per image (CifCaf.max_annotations)
 DET_CATEGORIES = 80
 DEFAULT_WORKLOAD = 'coco17_641_5p'
 
@@ -88,6 +95,13 @@ def make_batch(workload, batch, first_seed=0):
     hw, n_poses, _, dense = WORKLOADS[workload]
     cache = '/tmp/pifpaf_bench_%s_%d_%d.npz' % (workload, batch, first_seed)
     skeleton = list(COCO_PERSON_SKELETON)
+    if workload in RANDINIT_MAX_SCALE:
+        import torch
+        from openpifpaf_b200 import workloads
+        device = 'cuda' if torch.cuda.is_available() else 'cpu'   # the network is workload tooling only
+        cif, caf = workloads.random_init_head_fields(batch, hw, seed=0, image_seed=first_seed + 1, device=device,
+                                                     max_scale=RANDINIT_MAX_SCALE[workload])
+        return cif.cpu().numpy(), caf.cpu().numpy(), skeleton
     if dense:
         skeleton = skeleton + list(DENSER_COCO_PERSON_CONNECTIONS)
     if os.path.exists(cache):
@@ -212,11 +226,12 @@ def run_reference(args):
     batch = args.batch or default_batch
     r = ReferenceRunner(args.workload, batch, args.cpu_workers)
     n_ann = 0
-    for _ in range(max(args.warmup, 1)):
+    slow = args.workload in RANDINIT_MAX_SCALE     # ~100 s (raw) / ~10 s (tamed) per image and core
+    for _ in range(args.warmup if slow else max(args.warmup, 1)):
         n_ann = r.step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        r.step()
+        n_ann = r.step()
     dt = time.perf_counter() - t0
     r.close()
     value = batch * args.steps / dt
@@ -243,12 +258,19 @@ def run_reference(args):
 
 def workload_config(workload, batch, n_gpus, lanes=1):
     hw, n_poses, _, dense = WORKLOADS[workload]
+    if workload in RANDINIT_MAX_SCALE:
+        text = ('%s: batch %d x %dx%d per GPU, COCO 17-kp/19-link skeleton, fields of a randomly initialised '
+                'resnet50 + cif/caf heads on torch.randn images (BASELINE configs[1], SURVEY 8d config 2)%s' % (
+                    workload, batch, hw[0], hw[1],
+                    '' if RANDINIT_MAX_SCALE[workload] is None else
+                    ', scale channels clamped to %g cells (tamed variant)' % RANDINIT_MAX_SCALE[workload]))
+    else:
+        text = ('%s: batch %d x %dx%d per GPU, %s skeleton, %d synthetic persons/image, fields '
+                "from the repo's encoder + jitter (SURVEY 8d config 1 generator)" % (
+                    workload, batch, hw[0], hw[1], 'dense 44-link' if dense else 'COCO 17-kp/19-link', n_poses))
     return {
         'batches_in_flight': lanes,
-        'workload': '%s: batch %d x %dx%d per GPU, %s skeleton, %d synthetic persons/image, fields '
-                    "from the repo's encoder + jitter (SURVEY 8d config 1 generator)" % (
-                        workload, batch, hw[0], hw[1], 'dense 44-link' if dense else 'COCO 17-kp/19-link',
-                        n_poses),
+        'workload': text,
         'batch_per_gpu': batch, 'global_batch': batch * n_gpus, 'image_hw': list(hw),
         'persons_per_image': n_poses,
         'decoder': 'cif_th 0.1, seed_th 0.2, caf_th 0.1, blend, keypoint_th 0.001, nms on, '
@@ -330,11 +352,12 @@ def measured_peak():
 # ----------------------------------------------------------------------------
 # B200 arm
 
-def cpu_baseline_subprocess(args, batch, steps=20):
+def cpu_baseline_subprocess(args, batch, steps=20, warmup=1, workers=0):
     """Runs the reference arm in a child process (before CUDA is initialised in
     this one, so the pool's fork is clean and the cores are idle)."""
     cmd = [sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', str(steps),
-           '--warmup', '1', '--workload', args.workload, '--batch', str(batch)]
+           '--warmup', str(warmup), '--workload', args.workload, '--batch', str(batch),
+           '--cpu-workers', str(workers)]
     env = dict(os.environ)
     for k in ('RANK', 'LOCAL_RANK', 'WORLD_SIZE'):
         env.pop(k, None)
@@ -428,8 +451,18 @@ def run_b200(args):
     batch = args.batch or default_batch
 
     cpu_base = None
+    randinit = args.workload in RANDINIT_MAX_SCALE
     if world == 1 and not args.no_cpu_baseline:
-        cpu_base = cpu_baseline_subprocess(args, batch)
+        if not randinit:
+            cpu_base = cpu_baseline_subprocess(args, batch)
+        elif RANDINIT_MAX_SCALE[args.workload] is None:
+            # ~100 s per image and core => the reference is timed on 2 images (2 processes)
+            cpu_base = cpu_baseline_subprocess(args, 2, steps=1, warmup=0, workers=2)
+            if cpu_base.get('value'):
+                cpu_base['extrapolated_all_cores'] = cpu_base['value'] / 2 * (os.cpu_count() or 1)
+                cpu_base['sample'] += '; extrapolated_all_cores = value / 2 x os.cpu_count()'
+        else:
+            cpu_base = cpu_baseline_subprocess(args, os.cpu_count() or 1, steps=1, warmup=0)
 
     import torch
     import torch.distributed as dist
@@ -460,6 +493,8 @@ def run_b200(args):
     from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
     from openpifpaf_b200.decoder.engine import StageProfile
     configure_profile(decoder)
+    if randinit:
+        decoder.CifCaf.max_annotations = RANDINIT_ANN_CAP
     cif, caf, skeleton = make_batch(args.workload, batch, first_seed=rank * batch)
     dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=skeleton)
     if args.host_chunk:
@@ -630,6 +665,14 @@ def run_b200(args):
         'annotations_per_step': n_ann * world,
         'clocks': clock_info,
     }
+    if randinit:
+        from openpifpaf_b200 import workloads
+        stats = workloads.field_statistics(d_cif)
+        line['field_statistics'] = stats
+        line['cifhr_splat_pixel_updates_per_s'] = (
+            stats['splat_pixel_updates_per_image'] * batch / (mean_ms[i_splat] * 1e-3))
+        line['roofline']['note'] = ('degenerate fields: the splat is compute-bound here (px-updates/s above), '
+                                    'the HBM fraction is not the figure of merit for this workload')
     if cpu_base is not None:
         line['cpu_baseline'] = cpu_base
     print(json.dumps(line), flush=True)

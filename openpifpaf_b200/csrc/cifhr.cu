@@ -55,6 +55,7 @@ static int group_strips() {           // strips per CTA
   return 3;
 }
 constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see strip_rshift)
+constexpr int kWidePatches = 8;       // a source box spanning more patches than this makes its block "wide"
 constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored from (4 KiB pieces)
 constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
@@ -335,22 +336,27 @@ __device__ __forceinline__ void consumer_sync() {
   asm volatile("bar.sync 1, %0;" :: "n"(kSplatThreads) : "memory");
 }
 
-// block_flag_scan for the consumer warps
-__device__ __forceinline__ int consumer_flag_scan(bool flag, int *warp_tot, int *total) {
+// block_flag_scan for the consumer warps; *any_wide = some thread of the block passed wide = true
+// (bit 30 of a warp's total carries its vote)
+__device__ __forceinline__ int consumer_flag_scan(bool flag, bool wide, int *warp_tot, int *total,
+                                                  bool *any_wide) {
   unsigned m = __ballot_sync(0xffffffffu, flag);
+  const bool wv = __any_sync(0xffffffffu, wide);
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   int in_warp = __popc(m & ((1u << lane) - 1u));
-  if (lane == 0) warp_tot[w] = __popc(m);
+  if (lane == 0) warp_tot[w] = __popc(m) | (wv ? (1 << 30) : 0);
   consumer_sync();
-  int base = 0, tot = 0;
+  int base = 0, tot = 0, votes = 0;
 #pragma unroll
   for (int i = 0; i < kSplatWarps; i++) {
-    int t = warp_tot[i];
-    if (i < w) base += t;
-    tot += t;
+    const int t = warp_tot[i];
+    if (i < w) base += t & 0xffff;
+    tot += t & 0xffff;
+    votes |= t >> 30;
   }
   consumer_sync();
   *total = tot;
+  *any_wide = votes != 0;
   return base + in_warp;
 }
 
@@ -363,6 +369,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   __shared__ float4 s_a[kGroupCap];
   __shared__ int4 s_b[kGroupCap];
   __shared__ uint32_t s_mask[2][kMaxPatches];             // bit s of word s/32: source s touches the patch
+  __shared__ uint32_t s_sat[kMaxPatches / 32];            // bit p: every pixel of patch p has reached 1
   __shared__ int warp_tot[kSplatWarps];
   __shared__ int s_item;
 
@@ -420,36 +427,108 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
     float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
     for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
       reinterpret_cast<float4 *>(tile)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    // saturation map of the strip: the patches that do not exist count as saturated, so the strip is
+    // finished when every word reads all ones (increments are >= 0 and the result is clamped at 1)
+    if (tid < kMaxPatches / 32) {
+      const int first = tid << 5;
+      s_sat[tid] = n_patches >= first + 32 ? 0u : (n_patches <= first ? 0xffffffffu : ~((1u << (n_patches - first)) - 1u));
+    }
+    bool strip_done = false;
     const int nsrc = min(__ldg(w.n_src + bf), src_cap);
     const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
     const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
     const int py = g.r0 + row;
     const int tile_row = (int)(g.gs - g.ga) + row * hw;
 
-    for (int base = 0; base < nsrc; base += kSplatThreads) {
+    for (int base = 0; base < nsrc && !strip_done; base += kSplatThreads) {
       // ordered filter of this block of sources by the strip's rows
       const int i = base + tid;
-      bool keep = false;
+      bool keep = false, wide = false, flat = false;
       int4 bb = make_int4(0, 0, 0, 0);
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
       if (i < nsrc) {
         bb = gb_src[i];
         keep = bb.z < g.r1 && bb.w > g.r0;
       }
+      if (keep) {
+        a = ga_src[i];
+        // "flat" source: its box covers the whole strip and sigma^2 is so large that for every pixel of
+        // the strip |-0.5 d2 / sigma^2| stays below 2^-22, where approx_exp() returns exactly 1
+        // (1 + x/8 rounds to 1) and the d2 > sigma^2 cut cannot trigger: the increment is v for every
+        // pixel.  Marked by a negative sigma^2 (sigma >= 1 always); NaN coordinates never qualify.
+        if (bb.x <= 0 && bb.y >= hw && bb.z <= g.r0 && bb.w >= g.r1) {
+          const float dxm = fmaxf(fabsf(a.x), fabsf((float)(hw - 1) - a.x));
+          const float dym = fmaxf(fabsf((float)g.r0 - a.y), fabsf((float)(g.r1 - 1) - a.y));
+          const float d2m = dxm * dxm + dym * dym;       // >= every pixel's d2 (up to rounding)
+          // 2^25 leaves a factor 8 of margin; d2m < 1e38 keeps every pixel's d2 finite when sigma^2 is
+          // +inf (inf / inf is NaN in the reference too)
+          flat = d2m < 1e38f && d2m * 33554432.0f <= a.z;
+        }
+        wide = flat || ((bb.y - 1) >> cshift) - (bb.x >> cshift) >= kWidePatches;
+      }
       int n_staged;
-      const int off = consumer_flag_scan(keep, warp_tot, &n_staged);   // two barriers
-      if (keep) { s_a[off] = ga_src[i]; s_b[off] = bb; }
+      bool any_wide;
+      const int off = consumer_flag_scan(keep, wide, warp_tot, &n_staged, &any_wide);   // two barriers
+      if (keep) {
+        if (flat) a.z = -a.z;                              // only ever read by the wide path below
+        s_a[off] = a;
+        s_b[off] = bb;
+      }
       if (n_staged == 0) continue;
 
+      if (!any_wide) {
+        // narrow boxes (the usual case): one thread per source marks the few patches it touches
+        for (int c0 = 0; c0 < n_staged; c0 += kChunk) {
+          const int nchunk = min(kChunk, n_staged - c0);
+          for (int p = tid; p < 2 * kMaxPatches; p += kSplatThreads) (&s_mask[0][0])[p] = 0u;
+          consumer_sync();                                 // staged list + cleared masks visible
+          if (tid < nchunk) {
+            const int4 b = s_b[c0 + tid];
+            const int p0 = b.x >> cshift, p1 = (b.y - 1) >> cshift;
+            uint32_t *word = s_mask[tid >> 5];
+            const uint32_t bit = 1u << (tid & 31);
+            for (int p = p0; p <= p1; p++) atomicOr(&word[p], bit);
+          }
+          consumer_sync();
+          for (int p = warp; p < n_patches; p += kSplatWarps) {
+            unsigned long long m = (unsigned long long)s_mask[0][p] | ((unsigned long long)s_mask[1][p] << 32);
+            if (m == 0ull) continue;
+            const int px = (p << cshift) + cg;
+            const bool ok = py < g.r1 && px < hw;
+            float acc = ok ? tile[tile_row + px] : 0.f;
+            int seen = 0;
+            while (m) {
+              const int s = __ffsll((long long)m) - 1;
+              m &= m - 1ull;
+              splat_px(acc, px, py, s_a[c0 + s], s_b[c0 + s]);
+              if ((++seen & 7) == 0) {
+                // once every pixel of the patch reached 1 nothing can change any more
+                if (__all_sync(0xffffffffu, !(acc < 1.f))) break;
+              }
+            }
+            if (ok) tile[tile_row + px] = clamp1(acc);
+          }
+          consumer_sync();                                 // patches done before masks are cleared again
+        }
+        continue;
+      }
+
+      // blocks with boxes spanning many patches (whole-map sources of degenerate fields): one thread per
+      // patch builds its mask from the chunk (no atomics), patches whose 32 pixels all reached 1 are
+      // remembered in s_sat and skipped, and the strip ends as soon as every patch is saturated
       for (int c0 = 0; c0 < n_staged; c0 += kChunk) {
         const int nchunk = min(kChunk, n_staged - c0);
-        for (int p = tid; p < 2 * kMaxPatches; p += kSplatThreads) (&s_mask[0][0])[p] = 0u;
-        consumer_sync();                                   // staged list + cleared masks visible
-        if (tid < nchunk) {
-          const int4 b = s_b[c0 + tid];
-          const int p0 = b.x >> cshift, p1 = (b.y - 1) >> cshift;
-          uint32_t *word = s_mask[tid >> 5];
-          const uint32_t bit = 1u << (tid & 31);
-          for (int p = p0; p <= p1; p++) atomicOr(&word[p], bit);
+        consumer_sync();                                   // staged list visible
+        for (int p = tid; p < n_patches; p += kSplatThreads) {
+          unsigned long long m = 0ull;
+          if (!((s_sat[p >> 5] >> (p & 31)) & 1u)) {
+            for (int q = 0; q < nchunk; q++) {
+              const int4 b = s_b[c0 + q];
+              if (p >= (b.x >> cshift) && p <= ((b.y - 1) >> cshift)) m |= 1ull << q;
+            }
+          }
+          s_mask[0][p] = (uint32_t)m;
+          s_mask[1][p] = (uint32_t)(m >> 32);
         }
         consumer_sync();
         for (int p = warp; p < n_patches; p += kSplatWarps) {
@@ -457,20 +536,28 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
           if (m == 0ull) continue;
           const int px = (p << cshift) + cg;
           const bool ok = py < g.r1 && px < hw;
-          float acc = ok ? tile[tile_row + px] : 0.f;
+          float acc = ok ? tile[tile_row + px] : 1.f;      // lanes outside the map never hold a patch open
           int seen = 0;
+          bool sat = false;
           while (m) {
             const int s = __ffsll((long long)m) - 1;
             m &= m - 1ull;
-            splat_px(acc, px, py, s_a[c0 + s], s_b[c0 + s]);
+            const float4 sa = s_a[c0 + s];
+            if (sa.z < 0.f) acc = __fadd_rn(acc, sa.w);    // flat source
+            else splat_px(acc, px, py, sa, s_b[c0 + s]);
             if ((++seen & 7) == 0) {
-              // once every pixel of the patch reached 1 nothing can change any more
-              if (__all_sync(0xffffffffu, !(acc < 1.f))) break;
+              sat = __all_sync(0xffffffffu, !(acc < 1.f));
+              if (sat) break;
             }
           }
           if (ok) tile[tile_row + px] = clamp1(acc);
+          if (sat && lane == 0) atomicOr(&s_sat[p >> 5], 1u << (p & 31));
         }
-        consumer_sync();                                   // patches done before masks are cleared again
+        consumer_sync();                                   // patches done before the masks are rebuilt
+        bool all = true;
+#pragma unroll
+        for (int q = 0; q < kMaxPatches / 32; q++) all = all && (s_sat[q] == 0xffffffffu);
+        if (all) { strip_done = true; break; }             // uniform: every consumer reads the same words
       }
     }
     if (merge) {          // np.maximum with the map of the scales before (NaN from either side wins)

@@ -315,6 +315,25 @@ def test_random_init_like_fields_bit_exact(oracle, coco_skeleton, configured_dec
     assert len(o.data) >= 20
 
 
+@pytest.mark.parametrize('scale_sigma,conf_shift', [(8.0, 0.0), (2.0, 3.0), (1.5, 3.0)])
+def test_saturating_strips_hr_bit_exact(oracle, coco_skeleton, configured_decoder, scale_sigma, conf_shift):
+    """Strips whose every pixel reaches 1 long before the source list ends (the splat kernel's
+    saturation map, its patch-centric masks for wide boxes and the early strip exit), on a map wide
+    enough for 65 patches per strip; hr, seeds and CafScored lists against the oracle."""
+    from openpifpaf_b200.encoder import random_init_like_fields
+    cif, caf = random_init_like_fields((29, 33), 5, scale_sigma=scale_sigma)
+    if conf_shift:
+        logit = np.log(cif[:, 0] / (1.0 - cif[:, 0])) + conf_shift
+        cif[:, 0] = (1.0 / (1.0 + np.exp(-logit))).astype(np.float32)
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, nms=False)
+    o_hr = oracle.cifhr(cif)
+    assert (o_hr == 1.0).mean() > 0.25
+    assert np.array_equal(out['hr'][0], o_hr)
+    o_seeds = oracle.seeds(cif, o_hr)
+    n = out['n_seeds'][0]
+    assert n == len(o_seeds) and np.array_equal(out['seeds'][0, :n], o_seeds)
+
+
 def test_nonfinite_sources_stage_outputs_gpu(oracle, coco_skeleton, configured_decoder):
     from openpifpaf_b200.encoder import random_init_like_fields
     for seed in range(4):
