@@ -15,12 +15,14 @@ printed by rank 0 (contract in DESIGN.md section "Measurement"):
                 the same K steps strictly one at a time on one stream, with the
                 library's per-stage CUDA-event profile;
   e2e           images/s through the public API CifCaf.decode_batch() with
-                PINNED HOST fields: H2D of every field plane, kernels, D2H of
-                the results and the construction of the Annotation objects are
-                all inside the timed region;
-  e2e_mapped    the same call with host_transfer='mapped' (only the confidence
-                planes are copied, the kernels read the other planes of the
-                active cells from the pinned buffers over PCIe);
+                PINNED HOST fields and default settings: host -> device
+                transfer, kernels, D2H of the results and the construction of
+                the Annotation objects are all inside the timed region.  The
+                default host_transfer='auto' moves what the decode reads: the
+                confidence planes by DMA, the other planes of the cells above
+                threshold by zero-copy reads from the pinned buffers;
+  e2e_full_copy the same call with host_transfer='copy': every plane of every
+                field is copied (PCIe-bound: 430 MB per 64 images);
   roofline      the CifHr splat kernel (the kernel that writes the hr maps)
                 against the measured HBM copy peak of MEASURED_PEAKS.json,
                 timed in the one-lane pass; in_flight = while lanes overlap;
@@ -559,6 +561,10 @@ def run_b200(args):
     params.profile = None
 
     # ---- end to end through the public API, host fields ------------------------
+    # (1) the call a user makes: CifCaf.decode_batch on pinned host tensors with the default
+    # host_transfer='auto', which takes the 'mapped' route here (confidence planes by DMA, the other
+    # planes of the cells above threshold read by the kernels from the pinned buffers over PCIe)
+    assert dec.host_transfer == 'auto'
     for _ in range(2):
         anns = dec.decode_batch(h_cif, h_caf)
     barrier()
@@ -567,24 +573,31 @@ def run_b200(args):
         anns = dec.decode_batch(h_cif, h_caf)
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
-    # the same call with host_transfer='mapped': confidence planes by DMA, the other planes of the
-    # active cells fetched by the kernels from the pinned buffers (reported beside e2e, not as e2e)
-    dec.host_transfer = 'mapped'
+    e2e_mapped = dec._use_mapped(h_cif, h_caf, dec.params())
+    # (2) the same call with host_transfer='copy': every plane of every field is copied
+    dec.host_transfer = 'copy'
     for _ in range(2):
-        anns_m = dec.decode_batch(h_cif, h_caf)
+        anns_c = dec.decode_batch(h_cif, h_caf)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        anns_m = dec.decode_batch(h_cif, h_caf)
+        anns_c = dec.decode_batch(h_cif, h_caf)
     torch.cuda.synchronize()
-    e2e_mapped_s = max_over_ranks(time.perf_counter() - t0)
-    dec.host_transfer = 'copy'
-    assert [len(a) for a in anns_m] == [len(a) for a in anns], 'mapped and copied host paths disagree'
+    e2e_copy_s = max_over_ranks(time.perf_counter() - t0)
+    dec.host_transfer = 'auto'
+    assert [len(a) for a in anns_c] == [len(a) for a in anns], 'mapped and copied host paths disagree'
+    for la, lc in zip(anns, anns_c):
+        for x, y in zip(la, lc):
+            assert np.array_equal(x.data, y.data), 'mapped and copied host paths disagree'
     clock_info = clocks.stop() if clocks is not None else None
     assert sum(len(a) for a in anns) == n_ann, 'host and device paths disagree on the annotation count'
     hbuf = eng.buffers(batch, cif.shape[1], cif.shape[3], cif.shape[4], host=True)
     d2h = sum(t.numel() * t.element_size() for t in hbuf.host.values())
     h2d = cif.nbytes + caf.nbytes
+    h2d_dma = cif.nbytes // 5 + caf.nbytes // 9
+    h2d_zero = int((cif[:, :, 0] > params.cif_threshold).sum()) * 4 * 4 + \
+        int((caf[:, :, 0] > params.caf_threshold).sum()) * 8 * 4
+    h2d_mapped = h2d_dma + h2d_zero
 
     # pure host->device copy of one step's fields: the PCIe floor under e2e
     for _ in range(2):
@@ -631,17 +644,24 @@ def run_b200(args):
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': workload_config(args.workload, batch, world, lanes),
         'e2e': {'value': world * batch * args.steps / e2e_s, 'unit': UNIT,
-                'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]]',
-                'host_chunk': decoder.CifCaf.host_chunk, 'ms_per_step': 1e3 * e2e_s / args.steps,
-                'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
-                'pcie_floor_frac': h2d_ms / (1e3 * e2e_s / args.steps)},
-        'e2e_mapped': {'value': world * batch * args.steps / e2e_mapped_s, 'unit': UNIT,
-                       'ms_per_step': 1e3 * e2e_mapped_s / args.steps,
-                       'h2d_dma_bytes_per_step': (cif.nbytes // 5) + (caf.nbytes // 9),
-                       'note': "CifCaf.host_transfer='mapped': only the confidence planes are copied; the "
-                               'kernels read the other planes of the cells above threshold from the pinned '
-                               'host buffers over PCIe (same results)'},
+                'h2d_bytes_per_step': h2d_mapped if e2e_mapped else h2d, 'd2h_bytes_per_step': d2h,
+                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]], defaults',
+                'ms_per_step': 1e3 * e2e_s / args.steps,
+                'host_transfer': "auto -> %s" % ('mapped' if e2e_mapped else 'copy'),
+                'h2d_dma_bytes_per_step': h2d_dma if e2e_mapped else h2d,
+                'h2d_zero_copy_bytes_per_step': h2d_zero if e2e_mapped else 0,
+                'field_bytes_per_step': h2d,
+                'note': 'the fields stay in pinned host memory; per step the confidence planes are copied '
+                        '(strided DMA) and the kernels read the other planes of the cells above threshold '
+                        'from the pinned buffers over PCIe (zero-copy bytes = active cells x planes x 4 B, '
+                        'sector granularity not counted); results identical to the full copy, which is '
+                        'e2e_full_copy'},
+        'e2e_full_copy': {'value': world * batch * args.steps / e2e_copy_s, 'unit': UNIT,
+                          'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                          'api': "CifCaf.decode_batch with host_transfer='copy' (every plane copied)",
+                          'host_chunk': decoder.CifCaf.host_chunk, 'ms_per_step': 1e3 * e2e_copy_s / args.steps,
+                          'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
+                          'pcie_floor_frac': h2d_ms / (1e3 * e2e_copy_s / args.steps)},
         # kernels of this library launched in the timed `value` region (8 per decode: compact, splat, seeds
         # from sources, seed sort, CafScored, candidate binning, assembly, NMS); 3 memsets per decode beside
         'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 3) * args.steps,

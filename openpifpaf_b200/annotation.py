@@ -79,15 +79,46 @@ class Annotation:
         ann.score_weights = _score_weights(len(keypoints))
         return ann
 
+    @classmethod
+    def wrap_batch(cls, keypoints, skeleton, data, joint_scales, pre, order, graph):
+        """``wrap`` for the rows of ``data (n, F, 3)``, ``joint_scales (n, F)``: n annotations that own
+        row views of these (private) arrays.  ``pre (n, F, 3)`` / ``order (n, F, 2)`` stay whole; row k is
+        looked up when ``decoding_order`` / ``frontier_order`` are first read, and ``score_weights`` is
+        created on first access."""
+        new = cls.__new__
+        out = []
+        k = 0
+        for d, js in zip(data, joint_scales):
+            ann = new(cls)
+            ann.__dict__ = {
+                'keypoints': keypoints, 'skeleton': skeleton, 'category_id': 1,
+                'suppress_score_index': None, 'data': d, 'joint_scales': js, 'fixed_score': NOTSET,
+                '_decoding_order': None, '_frontier_order': None, '_lazy': (pre, order, graph, k)}
+            out.append(ann)
+            k += 1
+        return out
+
+    def __getattr__(self, name):
+        # only reached when the attribute is missing: score_weights of wrap_batch instances
+        if name == 'score_weights':
+            w = _score_weights(len(self.keypoints), bool(self.suppress_score_index))
+            self.__dict__['score_weights'] = w
+            return w
+        raise AttributeError(name)
+
     def _materialise(self):
         if self._lazy is None:
             return
-        pre, order, graph = self._lazy
+        pre, order, graph = self._lazy[:3]
+        if len(self._lazy) == 4:                 # wrap_batch: row k of the batch arrays
+            k = self._lazy[3]
+            pre, order = pre[k], order[k]
         self._lazy = None
         steps = [(int(s), int(e)) for s, e in order if s >= 0]
         # force_complete marker (-2, n1): the first n1 steps belong to the first _grow
         first = [int(e) for s, e in order if s == -2]
         self._decoding_order = [(s, e, np.copy(pre[s]), np.copy(pre[e])) for s, e in steps]
+        self._frontier_order = []
         if graph is not None:
             self._frontier_order = _replay_frontier(pre, steps, graph,
                                                     first[0] if first else None)

@@ -339,10 +339,12 @@ class DeviceDecoder:
         _lib.check(rc)
         return buf
 
-    def enqueue_host(self, cif_t, caf_t, params, chunk, *, keep=('ann',)):
+    def enqueue_host(self, cif_t, caf_t, params, chunk, *, keep=('ann',), p_c=None, stream_ptr=None):
         """Enqueue the pipelined host decode of contiguous float32 host tensors (chunked H2D on the
         pipeline's copy stream, kernels on the current stream, D2H on its copy-out stream).  Returns
-        ``(buf, chunk, n_chunks)``; collect with ``wait_host_chunk``."""
+        ``(buf, chunk, n_chunks)``; collect with ``wait_host_chunk``.  ``p_c`` / ``stream_ptr``: an
+        already converted parameter struct and the stream to issue on (callers that enqueue many
+        sub-batches convert once and skip the stream context)."""
         assert cif_t.dtype == torch.float32 and caf_t.dtype == torch.float32
         B, F, five, H, W = cif_t.shape
         assert five == 5 and caf_t.shape == (B, len(self.skeleton), 9, H, W), (cif_t.shape, caf_t.shape)
@@ -352,15 +354,20 @@ class DeviceDecoder:
         chunk = max(1, min(int(chunk), B))
         if (B + chunk - 1) // chunk > HostPipeline.MAX_CHUNKS:
             chunk = (B + HostPipeline.MAX_CHUNKS - 1) // HostPipeline.MAX_CHUNKS
-        p = params.to_c()
+        p = params.to_c() if p_c is None else p_c
         lib = _lib.lib()
-        with torch.cuda.device(buf.device):
-            _lib.check(lib.pp_decode_batch_host_async(
-                self._pipeline.handle, _ptr(cif_t), _ptr(caf_t), _ptr(buf.d_cif), _ptr(buf.d_caf),
-                C.byref(self.c_skeleton), C.byref(buf.d_out), C.byref(buf.h_out), _ptr(buf.ws),
-                buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), chunk, _stream_ptr()))
+        args = (self._pipeline.handle, C.c_void_p(cif_t.data_ptr()), C.c_void_p(caf_t.data_ptr()),
+                _ptr(buf.d_cif), _ptr(buf.d_caf), C.byref(self.c_skeleton), C.byref(buf.d_out),
+                C.byref(buf.h_out), _ptr(buf.ws), buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps),
+                C.byref(p), chunk)
+        if stream_ptr is not None and torch.cuda.current_device() == buf.device.index:
+            _lib.check(lib.pp_decode_batch_host_async(*args, stream_ptr))
+        else:
+            with torch.cuda.device(buf.device):
+                _lib.check(lib.pp_decode_batch_host_async(
+                    *args, _stream_ptr() if stream_ptr is None else stream_ptr))
         buf.alive = (cif_t, caf_t, p)
-        return buf, chunk, lib.pp_pipeline_chunks(self._pipeline.handle)
+        return buf, chunk, (B + chunk - 1) // chunk
 
     def wait_host_chunk(self, buf, k):
         lib = _lib.lib()
@@ -397,10 +404,14 @@ class DeviceDecoder:
         if n_lanes > 1 and len(ranges) > 1:
             params = dataclasses.replace(params, in_flight=min(n_lanes, len(ranges)))
 
+        sliced = params.inverse is not None or params.initial is not None
+        p_all = None if sliced else params.to_c()      # one conversion for all sub-batches
+
         def submit(i):
             b0, b1 = ranges[i]
             lane = lanes[i % n_lanes]
-            lane.stream.wait_stream(cur)
+            if i < n_lanes:                     # order the lane after the caller's stream once per call
+                lane.stream.wait_stream(cur)
             sub_params = params
             if params.inverse is not None:      # per-image records: this sub-batch's slice
                 meta, target = params.inverse
@@ -410,9 +421,13 @@ class DeviceDecoder:
                 sub_params = dataclasses.replace(
                     sub_params, initial=(data[b0:b1].contiguous(), scales[b0:b1].contiguous(),
                                          n[b0:b1].contiguous()))
-            with torch.cuda.stream(lane.stream):
+            if sliced:                          # the slices are made on the lane's stream
+                with torch.cuda.stream(lane.stream):
+                    buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], sub_params, b1 - b0,
+                                                         keep=keep)
+            else:
                 buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], sub_params, b1 - b0,
-                                                     keep=keep)
+                                                     keep=keep, p_c=p_all, stream_ptr=lane.stream_ptr)
             pending.append((lane, buf, b1 - b0))
 
         nxt = min(n_lanes, len(ranges))
@@ -430,6 +445,7 @@ class DeviceDecoder:
 class Lane:
     def __init__(self, engine, stream):
         self.engine, self.stream, self.pending = engine, stream, None
+        self.stream_ptr = C.c_void_p(stream.cuda_stream)
 
 
 class Ticket:

@@ -44,8 +44,11 @@ class CifCaf(Generator):
     head_collector = None         # network.CifCafCollector when the model emits raw head outputs
     # host fields: 'copy' moves every plane to the device; 'mapped' copies the confidence planes only
     # and lets the kernels fetch the other planes of the active cells from the pinned host buffers
-    # (needs pinned inputs, seed_threshold >= CifHr.v_threshold, no force_complete; else it copies)
-    host_transfer = 'copy'
+    # (needs pinned inputs, seed_threshold >= CifHr.v_threshold, no force_complete; else it copies);
+    # 'auto' (default) = 'mapped' when those conditions hold, else 'copy'.  Like the reference, which
+    # reads every confidence value but the other planes only under the threshold mask
+    # (cif_hr.py:27-31, caf_scored.py:42-45), the mapped route moves just the bytes the decode reads.
+    host_transfer = 'auto'
     host_lanes = 8                # sub-batches in flight in 'mapped' mode ...
     mapped_chunk = 8              # ... of this many images (641 px, batch 64: 8 x 8 -> 2.4 ms, 64 x 1 -> 3.3 ms)
 
@@ -125,26 +128,39 @@ class CifCaf(Generator):
             nms=kp is not None,
             deterministic_exp=self.deterministic_exp,
             seed_mask=cfg.seed_mask,
-            host_mapped=self.host_transfer == 'mapped',
+            host_mapped=self.host_transfer in ('mapped', 'auto'),
         )
+
+    def _use_mapped(self, cif, caf, params):
+        """True when the host fields go the 'mapped' route (see ``host_transfer``)."""
+        if self.host_transfer not in ('mapped', 'auto'):
+            return False
+        if self.host_transfer == 'mapped':
+            return True       # as asked; the library itself falls back to copying when it must
+        return (isinstance(cif, torch.Tensor) and isinstance(caf, torch.Tensor)
+                and cif.is_pinned() and caf.is_pinned()
+                and not params.force_complete and params.seed_threshold >= params.cif_threshold)
 
     def _annotations_from(self, n_ann, data, scales, source, pre_data, pre_order, b0=0, b1=None):
         """Host arrays of one batch (images b0..b1) -> List[List[Annotation]].
 
         The rows are copied out of the (reused, pinned) result buffers once per image;
         each Annotation owns views of those private copies."""
-        out = []
         b1 = len(n_ann) if b1 is None else b1
-        kps, skel, graph = self.keypoints, self.out_skeleton, self._neighbours
-        for b, n in zip(range(b0, b1), n_ann[b0:b1].tolist()):
-            if n == 0:
-                out.append([])
-                continue
-            src = source[b, :n]
-            d, sc = data[b, :n].copy(), scales[b, :n].copy()
-            pre, order = pre_data[b][src], pre_order[b][src]     # fancy index = copies
-            out.append([Annotation.wrap(kps, skel, d[r], sc[r], (pre[r], order[r], graph))
-                        for r in range(n)])
+        counts = n_ann[b0:b1]
+        nmax = int(counts.max(initial=0))
+        if nmax == 0:
+            return [[] for _ in range(b0, b1)]
+        # one gather per array for all images of the range (fancy indexing = private copies)
+        img, row = np.nonzero(np.arange(nmax)[None, :] < counts[:, None])
+        img += b0
+        src = source[img, row]
+        anns = Annotation.wrap_batch(self.keypoints, self.out_skeleton, data[img, row], scales[img, row],
+                                     pre_data[img, src], pre_order[img, src], self._neighbours)
+        out, k = [], 0
+        for n in counts.tolist():
+            out.append(anns[k:k + n])
+            k += n
         return out
 
     # -------------------------------------------------------------- decode
@@ -212,7 +228,7 @@ class CifCaf(Generator):
             # pipelined: annotations of chunk k are built while chunk k+1.. are still
             # being copied / decoded (engine.run_host_chunked)
             result = []
-            if self.host_transfer == 'mapped':
+            if self._use_mapped(cif, caf, params):
                 # short copies: the GPU is the bottleneck, so sub-batches go to lanes of their own
                 chunks = eng.run_host_lanes(cif, caf, params, self.mapped_chunk, self.host_lanes)
             else:

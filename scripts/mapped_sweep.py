@@ -23,8 +23,8 @@ cif = torch.from_numpy(np.stack([f[0] for f in fields])).pin_memory()
 caf = torch.from_numpy(np.stack([f[1] for f in fields])).pin_memory()
 dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=[list(l) for l in COCO_PERSON_SKELETON])
 dec.host_transfer = 'mapped'
-for sub, lanes in ((8, 4), (8, 8), (16, 2), (16, 4), (32, 2), (64, 1)):
-    dec.host_chunk, dec.host_lanes = sub, lanes
+for sub, lanes in ((4, 8), (8, 4), (8, 8), (16, 2), (16, 4), (32, 2), (64, 1)):
+    dec.mapped_chunk, dec.host_lanes = sub, lanes
     for _ in range(3):
         dec.decode_batch(cif, caf)
     t0 = time.perf_counter()

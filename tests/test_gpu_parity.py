@@ -287,6 +287,7 @@ def test_pipelined_host_decode_matches_device(configured_decoder, coco_skeleton)
     caf = np.stack([i[1] for i in items])
     dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
     want = dec.decode_batch(torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda())
+    dec.host_transfer = 'copy'        # the chunked full-copy pipeline (pinned inputs would go 'mapped')
     saved = decoder.CifCaf.host_chunk
     try:
         for chunk in (1, 3, 7, 100):
@@ -769,9 +770,16 @@ def test_host_mapped_transfer_equals_copy(coco_skeleton, configured_decoder, chu
     dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
     dec.host_chunk = dec.mapped_chunk = chunk
     dec.host_lanes = 3
+    dec.host_transfer = 'copy'
     want = dec.decode_batch(cif, caf)
-    dec.host_transfer = 'mapped'
-    for c_in, a_in in ((cif, caf), (cif.numpy().copy(), caf.numpy().copy())):   # pinned, then pageable
+    # the default 'auto' takes the mapped route for pinned tensors only
+    dec.host_transfer = 'auto'
+    assert decoder.CifCaf.host_transfer == 'auto'
+    assert dec._use_mapped(cif, caf, dec.params())
+    assert not dec._use_mapped(cif.numpy().copy(), caf.numpy().copy(), dec.params())
+    for mode, c_in, a_in in (('auto', cif, caf), ('mapped', cif, caf),
+                             ('mapped', cif.numpy().copy(), caf.numpy().copy())):   # pinned, then pageable
+        dec.host_transfer = mode
         got = dec.decode_batch(c_in, a_in)
         assert [len(g) for g in got] == [len(w) for w in want] and sum(len(g) for g in got) >= 10
         for g_img, w_img in zip(got, want):
@@ -803,6 +811,7 @@ def test_host_mapped_with_metas(coco_skeleton, configured_decoder):
     dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
     dec.host_chunk = dec.mapped_chunk = 2
     dec.host_lanes = 3
+    dec.host_transfer = 'copy'
     want = dec.decode_batch(cif, caf, metas=metas)
     dec.host_transfer = 'mapped'
     got = dec.decode_batch(cif, caf, metas=metas)
