@@ -34,6 +34,13 @@ namespace pp {
 constexpr int kAsmThreads = 256;
 constexpr int kAsmWarps = kAsmThreads / 32;
 constexpr int kMaxEdges = 2 * PP_MAX_L;
+// Occupancy bookkeeping.  Up to kHeavySeeds seeds every seed's counter is tested against the boxes of
+// each finished pose (a few thousand tests).  Above that (crowded scenes, degenerate fields with 60 k
+// seeds and ~1000 poses per image) the seeds are counting-sorted once by (field, band of kOccBands
+// occupancy-row bands), a box then only visits the bins it overlaps, and a box that covers the whole
+// map just bumps a per-field counter.
+constexpr int kHeavySeeds = 4096;
+constexpr int kOccBands = 32;
 constexpr int kStageBytes = 80 * 1024;        // staged candidate lists, 2 CTAs / SM (batches > #SMs)
 constexpr int kStageBytesSolo = 192 * 1024;   // ... 1 CTA / SM
 
@@ -343,6 +350,9 @@ struct AsmShared {
   int found;
   int warp_min[kAsmWarps];
   struct Flood { float key, sx, sy, sv, s; int end; } ff[4 * PP_MAX_L];
+  // heavy mode (more than kHeavySeeds seeds): seeds are indexed by (field, band of occupancy rows)
+  int occ_bin[PP_MAX_F * kOccBands];   // end offset of bin (field, band) in the field-major seed order
+  int occ_all[PP_MAX_F];               // Occupancy.set boxes that cover the whole map, per field
   int list_n[2 * PP_MAX_L];      // candidate-list lengths, [2l] forward / [2l+1] backward
   int list_off[2 * PP_MAX_L];    // float offsets into the staged copy
   int stage_total;               // entries over all lists
@@ -560,12 +570,59 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
 
   // every seed's Occupancy.get cell is fixed: compute it once (occupancy.py:41-47)
   int2 *rec = a.occ_rec + (size_t)b * a.seed_cap;
-  for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) {
-    const float *sd = seeds + (size_t)i * 5;
-    long long cx, cy;
-    occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
-    rec[i] = make_int2((int)cx, (int)cy | ((int)__ldg(sd + 1) << 24));
-    occ[i] = 0;
+  const bool heavy = n_seeds > a.heavy_seeds && n_seeds < (1 << 24) && ow < 65536 && oh < 32768;
+  int bshift = 0;
+  while (((oh - 1) >> bshift) >= kOccBands) bshift++;
+  if (!heavy) {
+    for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) {
+      const float *sd = seeds + (size_t)i * 5;
+      long long cx, cy;
+      occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
+      rec[i] = make_int2((int)cx, (int)cy | ((int)__ldg(sd + 1) << 24));
+      occ[i] = 0;
+    }
+  } else {
+    // counting sort by (field, band): rec[i].x = position | field << 24 of seed i (score order),
+    // rec[k].y = cell x | cell y << 16 and occ[k] = counter of the seed at position k
+    for (int i = threadIdx.x; i < PP_MAX_F * kOccBands; i += blockDim.x) sh.occ_bin[i] = 0;
+    if (threadIdx.x < PP_MAX_F) sh.occ_all[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) {
+      const float *sd = seeds + (size_t)i * 5;
+      long long cx, cy;
+      occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
+      atomicAdd(&sh.occ_bin[(int)__ldg(sd + 1) * kOccBands + (int)(cy >> bshift)], 1);
+    }
+    __syncthreads();
+    if (warp_id() == 0) {                       // exclusive scan of the PP_MAX_F * kOccBands counts
+      constexpr int kPer = PP_MAX_F * kOccBands / 32;
+      const int first = lane_id() * kPer;
+      int sum = 0;
+      for (int q = 0; q < kPer; q++) sum += sh.occ_bin[first + q];
+      int incl = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane_id() >= d) incl += v;
+      }
+      int run = incl - sum;
+      for (int q = 0; q < kPer; q++) {
+        const int cnt = sh.occ_bin[first + q];
+        sh.occ_bin[first + q] = run;
+        run += cnt;
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_seeds; i += blockDim.x) {
+      const float *sd = seeds + (size_t)i * 5;
+      long long cx, cy;
+      occupancy_cell(__ldg(sd + 2), __ldg(sd + 3), ow, oh, &cx, &cy);
+      const int f = (int)__ldg(sd + 1);
+      const int pos = atomicAdd(&sh.occ_bin[f * kOccBands + (int)(cy >> bshift)], 1);   // start -> end
+      rec[i].x = pos | (f << 24);
+      rec[pos].y = (int)cx | ((int)cy << 16);
+      occ[pos] = 0;
+    }
   }
   __syncthreads();
 
@@ -579,7 +636,15 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
     int found = -1;
     for (int base = cursor; !from_init && base < n_seeds; base += blockDim.x) {
       int i = base + threadIdx.x;
-      bool hit = i < n_seeds && occ[i] == 0;
+      bool hit = false;
+      if (i < n_seeds) {
+        if (!heavy) {
+          hit = occ[i] == 0;
+        } else {
+          const int r = rec[i].x;
+          hit = ((occ[r & 0xffffff] + sh.occ_all[r >> 24]) & 255) == 0;
+        }
+      }
       unsigned m = __ballot_sync(0xffffffffu, hit);
       if (lane_id() == 0) sh.warp_min[warp_id()] = m ? (base + warp_id() * 32 + __ffs(m) - 1) : -1;
       __syncthreads();
@@ -635,6 +700,35 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
     n_ann++;
     __syncthreads();
     PP_TICK(5);
+    if (heavy) {
+      // one warp per joint: a box that covers the whole map bumps the field's counter, any other box
+      // visits the seeds of its field in the row bands it overlaps
+      for (int j = warp_id(); j < F; j += kAsmWarps) {
+        if (!sh.box_valid[j]) continue;
+        const long long minx = sh.box[j][0], maxx = sh.box[j][1], miny = sh.box[j][2], maxy = sh.box[j][3];
+        if (minx >= maxx || miny >= maxy) continue;        // box outside the map: empty numpy slice
+        if (minx <= 0 && maxx >= ow && miny <= 0 && maxy >= oh) {
+          if (lane_id() == 0) sh.occ_all[j]++;
+          continue;
+        }
+        const int b0 = j * kOccBands + (int)(miny >> bshift), b1 = j * kOccBands + (int)((maxy - 1) >> bshift);
+        const int k0 = b0 == 0 ? 0 : sh.occ_bin[b0 - 1], k1 = sh.occ_bin[b1];
+        for (int kk = k0 + lane_id(); kk < k1; kk += 4 * 32) {
+          int c[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) c[q] = kk + q * 32 < k1 ? rec[kk + q * 32].y : -1;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (kk + q * 32 >= k1) continue;
+            const long long cx = c[q] & 0xffff, cy = (unsigned)c[q] >> 16;
+            if (cx >= minx && cx < maxx && cy >= miny && cy < maxy) occ[kk + q * 32]++;   // uint8 wraps
+          }
+        }
+      }
+      __syncthreads();
+      PP_TICK(6);
+      continue;
+    }
     // Occupancy.set of the pose's joints, seen from the seeds: four seeds per thread and
     // trip so that four loads are in flight
     for (int i0 = cursor + threadIdx.x; i0 < n_seeds; i0 += 4 * blockDim.x) {
@@ -798,6 +892,8 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   // one image per SM and nothing else on the GPU: give the lists (almost) the whole shared memory;
   // with other batches in flight (pp_params.in_flight) leave room for their CTAs on the same SM
   int stage_bytes = (B <= num_sms() && p.in_flight <= 1) ? kStageBytesSolo : kStageBytes;
+  a2.heavy_seeds = kHeavySeeds;
+  if (const char *e = getenv("PP_ASM_HEAVY_SEEDS")) a2.heavy_seeds = atoi(e);   // tests: force either mode
   if (const char *e = getenv("PP_ASM_STAGE_KB")) {     // tuning experiments only
     int kb = atoi(e);
     if (kb >= 0 && kb * 1024 <= kStageBytesSolo) stage_bytes = kb * 1024;

@@ -97,6 +97,7 @@ struct AsmArgs {
   int seed_cap, caf_cap, ann_cap, L;
   int hh, hw;
   int stage_floats;   // set by assemble_launch
+  int heavy_seeds;    // set by assemble_launch: above this many seeds the (field, band) seed index is used
   const float *init_data, *init_scales;   // initial annotations (optional)
   const int *init_n;
   int init_cap;
