@@ -616,6 +616,18 @@ def run_b200(args):
     for la, lc in zip(anns, anns_c):
         for x, y in zip(la, lc):
             assert np.array_equal(x.data, y.data), 'mapped and copied host paths disagree'
+    # latency of one image through the reference-shaped call CifCaf.__call__([cif, caf]) (video.py's use)
+    lat = {}
+    if rank == 0 and not randinit:
+        for name, fields in (('cuda_tensors', [d_cif[0], d_caf[0]]), ('numpy_arrays', [cif[0], caf[0]])):
+            for _ in range(3):
+                dec(fields)
+            ts = []
+            for _ in range(30):
+                t0 = time.perf_counter()
+                dec(fields)
+                ts.append(time.perf_counter() - t0)
+            lat[name + '_ms'] = 1e3 * float(np.median(ts))
     clock_info = clocks.stop() if clocks is not None else None
     assert sum(len(a) for a in anns) == n_ann, 'host and device paths disagree on the annotation count'
     hbuf = eng.buffers(batch, cif.shape[1], cif.shape[3], cif.shape[4], host=True)
@@ -710,6 +722,8 @@ def run_b200(args):
         'stages_ms': {n: float(v) for n, v in zip(names, mean_ms)},
         'stages_ms_in_flight': {n: float(v) for n, v in zip(names, lane_mean_ms)},
         'annotations_per_step': n_ann * world,
+        'latency_one_image': dict(lat, api='CifCaf.__call__([cif, caf]) -> List[Annotation], median of 30 calls, '
+                                           'synchronous (includes the result copy and the Annotation objects)'),
         'clocks': clock_info,
     }
     if randinit:

@@ -360,6 +360,7 @@ class CifCaf(Generator):
         annotations = self.decode_batch(
             cif, caf, [list(initial_annotations)] if initial_annotations else None)[0]
         LOG.debug('annotations %d, %.3fs', len(annotations), time.perf_counter() - start)
-        LOG.info('%d annotations: %s', len(annotations),
-                 [np.sum(ann.data[:, 2] > 0.1) for ann in annotations])
+        if LOG.isEnabledFor(logging.INFO):
+            LOG.info('%d annotations: %s', len(annotations),
+                     [np.sum(ann.data[:, 2] > 0.1) for ann in annotations])
         return annotations
