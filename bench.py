@@ -651,6 +651,20 @@ def run_b200(args):
     torch.cuda.synchronize()
     h2d_ms = ev0.elapsed_time(ev1) / 5
 
+    # pure write stream of the size of one step's hr maps (cudaMemset through torch): the ceiling a kernel
+    # that only writes can reach on this part, next to the driver's copy peak (half reads, half writes)
+    fill = torch.empty((batch * cif.shape[1] * hw[0] * hw[1],), dtype=torch.float32, device=device)
+    for _ in range(2):
+        fill.zero_()
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(5):
+        fill.zero_()
+    ev1.record()
+    torch.cuda.synchronize()
+    write_peak_gbs = fill.numel() * 4 / (ev0.elapsed_time(ev1) / 5 * 1e-3) / 1e9
+    del fill
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -708,6 +722,9 @@ def run_b200(args):
         'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
                      'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,
                      'peak_source': peak_src, 'algorithmic_bytes_per_launch': hr_bytes,
+                     'write_only_peak': {'gbs': write_peak_gbs, 'frac': splat_gbs / write_peak_gbs,
+                                         'how': 'memset of a buffer of the same size, timed here (5 runs): the '
+                                                'kernel only writes, the copy peak moves half its bytes as reads'},
                      'ms_per_launch': float(mean_ms[i_splat]),
                      'timed': 'one batch at a time on one stream (%d steps, value_one_lane); with %d '
                               'batches in flight the event-bracketed duration also contains the time the '
