@@ -231,3 +231,47 @@ def test_factory_builds_cifdet_and_multiscale_config():
     assert cfg.cif_min_scales == [0.0, 12.0, 16.0, 24.0, 40.0] * 2
     assert cfg.caf_max_distances == [160.0, 240.0, 320.0, 480.0, None] * 2
     cfg.verify()
+
+
+def test_wrap_batch_equals_from_buffers():
+    """Annotation.wrap_batch (one gather per result array, lazy score_weights / decoding order) builds
+    the same objects as the per-annotation constructor."""
+    import copy
+    import pickle
+    from openpifpaf_b200.annotation import Annotation
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS, COCO_PERSON_SKELETON
+    rng = np.random.RandomState(0)
+    n, F = 6, len(COCO_KEYPOINTS)
+    data = rng.rand(n, F, 3).astype(np.float32)
+    data[:, ::3, 2] = 0.0
+    scales = rng.rand(n, F).astype(np.float32)
+    pre = rng.rand(n, F, 3).astype(np.float32)
+    order = np.full((n, F, 2), -1, np.int32)
+    order[:, 0] = (5, 7)
+    order[:, 1] = (7, 9)
+    graph = {j: [] for j in range(F)}
+    graph[5], graph[7] = [7], [9]
+    anns = Annotation.wrap_batch(COCO_KEYPOINTS, COCO_PERSON_SKELETON, data.copy(), scales.copy(), pre, order,
+                                 graph)
+    assert len(anns) == n
+    for k, ann in enumerate(anns):
+        want = Annotation.from_buffers(COCO_KEYPOINTS, COCO_PERSON_SKELETON, data[k], scales[k],
+                                       pre_data=pre[k], order=order[k], graph=graph)
+        assert np.array_equal(ann.data, want.data) and np.array_equal(ann.joint_scales, want.joint_scales)
+        assert ann.score() == want.score()
+        assert np.array_equal(ann.score_weights, want.score_weights)
+        assert [(s, e) for s, e, _, _ in ann.decoding_order] == [(5, 7), (7, 9)]
+        for (_, _, a1, a2), (_, _, b1, b2) in zip(ann.decoding_order, want.decoding_order):
+            assert np.array_equal(a1, b1) and np.array_equal(a2, b2)
+        assert ann.frontier_order == want.frontier_order
+        assert ann.json_data() == want.json_data()
+    # rows are private to their annotation; copies and pickles keep working before the lazy parts exist
+    fresh = Annotation.wrap_batch(COCO_KEYPOINTS, COCO_PERSON_SKELETON, data.copy(), scales.copy(), pre, order,
+                                  graph)
+    fresh[0].data[0, 0] = -1.0
+    assert fresh[1].data[0, 0] != -1.0
+    clone = pickle.loads(pickle.dumps(fresh[2]))
+    assert clone.score() == fresh[2].score() and len(clone.decoding_order) == 2
+    assert copy.deepcopy(fresh[3]).score() == fresh[3].score()
+    with pytest.raises(AttributeError):
+        fresh[4].no_such_attribute  # pylint: disable=pointless-statement
