@@ -288,7 +288,7 @@ class CifCaf(Generator):
         while tickets:
             yield collect(tickets.pop(0))
 
-    def decode_batch_multiscale(self, fields):
+    def decode_batch_multiscale(self, fields, initial_annotations=None):
         """Multi-scale FieldConfig (decoder/factory.py:153-180): ``fields[i]`` are the batched head
         tensors addressed by ``field_config.cif_indices`` / ``caf_indices`` (each with its own
         resolution and stride).  The reference pairs heads (k, k + 5) in CifHr when there are exactly
@@ -310,17 +310,23 @@ class CifCaf(Generator):
                 for ci, ai, stride, min_scale, min_d, max_d in zip(
                     cfg.cif_indices, cfg.caf_indices, cfg.cif_strides, cfg.cif_min_scales,
                     cfg.caf_min_distances, cfg.caf_max_distances)]
-        buf = eng.run_device_multiscale(sets, self.params(), hflip_pairs=len(sets) == 10)
+        params = self.params()
+        has_initial = bool(initial_annotations) and any(len(a) for a in initial_annotations)
+        if has_initial:
+            params.initial = self._initial_tensors(initial_annotations, device)
+        buf = eng.run_device_multiscale(sets, params, hflip_pairs=len(sets) == 10)
         n_ann = buf.dev['n_ann'].cpu().numpy()
         status = buf.dev['status'].cpu().numpy()
         if status.any():
             raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
         nmax = int(n_ann.max(initial=0))
         npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
+        source = buf.dev['ann_source'][:, :nmax].cpu().numpy()
         result = self._annotations_from(
             n_ann, buf.dev['ann_data'][:, :nmax].cpu().numpy(), buf.dev['ann_scales'][:, :nmax].cpu().numpy(),
-            buf.dev['ann_source'][:, :nmax].cpu().numpy(), buf.dev['pre_data'][:, :npre].cpu().numpy(),
-            buf.dev['pre_order'][:, :npre].cpu().numpy())
+            source, buf.dev['pre_data'][:, :npre].cpu().numpy(), buf.dev['pre_order'][:, :npre].cpu().numpy())
+        if has_initial:
+            self._adopt_initial(result, source, initial_annotations)
         self.last_decoder_time = time.perf_counter() - start
         return result
 
@@ -346,11 +352,10 @@ class CifCaf(Generator):
             for vis, caf_i in zip(cfg.caf_visualizers, cfg.caf_indices):
                 vis.predicted(fields[caf_i])
         if len(cfg.cif_indices) > 1:
-            if initial_annotations:
-                raise NotImplementedError('initial_annotations with a multi-scale FieldConfig')
             batched = [f.unsqueeze(0) if isinstance(f, torch.Tensor)
                        else np.ascontiguousarray(f, dtype=np.float32)[None] for f in fields]
-            return self.decode_batch_multiscale(batched)[0]
+            return self.decode_batch_multiscale(
+                batched, [list(initial_annotations)] if initial_annotations else None)[0]
         cif, caf = fields[cfg.cif_indices[0]], fields[cfg.caf_indices[0]]
         if isinstance(cif, torch.Tensor):
             cif, caf = cif.unsqueeze(0), caf.unsqueeze(0)

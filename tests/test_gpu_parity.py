@@ -722,6 +722,46 @@ def test_multiscale_matches_oracle_and_golden(oracle, coco_skeleton, configured_
         assert sha256(np.ascontiguousarray(fwd[l, :, :nf[l]])) == str(g['caf_f_sha256'][l])
 
 
+def test_multiscale_initial_annotations(oracle, coco_skeleton, configured_decoder):
+    """initial_annotations with a multi-scale FieldConfig (cifcaf.py:67-71,95-98 on the merged fields):
+    grown first, marked occupied, the caller's objects returned."""
+    from conftest import ms_golden
+    from openpifpaf_b200.annotation import Annotation
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    sets, _ = ms_golden('ms_3scales_321x481')
+    plain = oracle.decode_ms([(c, a, st, ms, mind, maxd or 0.0) for c, a, st, ms, mind, maxd in sets],
+                             coco_skeleton, oracle.Config(exp_mode=1))
+    # seed the decode with two joints of the strongest pose and one of another
+    init_data = np.zeros((2, 17, 3), np.float32)
+    init_js = np.zeros((2, 17), np.float32)
+    for i, (src, joints) in enumerate(((0, (5, 6)), (1, (11,)))):
+        for j in joints:
+            init_data[i, j] = plain.data[src][j]
+            init_data[i, j, 2] = 0.8
+            init_js[i, j] = max(plain.joint_scales[src][j], 4.0)
+    o = oracle.decode_ms([(c, a, st, ms, mind, maxd or 0.0) for c, a, st, ms, mind, maxd in sets],
+                         coco_skeleton, oracle.Config(exp_mode=1), initial=(init_data, init_js))
+    cfg = decoder.FieldConfig()
+    n = len(sets)
+    cfg.cif_indices, cfg.caf_indices = [2 * k for k in range(n)], [2 * k + 1 for k in range(n)]
+    cfg.cif_strides = cfg.caf_strides = [s[2] for s in sets]
+    cfg.cif_min_scales = [s[3] for s in sets]
+    cfg.caf_min_distances = [s[4] for s in sets]
+    cfg.caf_max_distances = [s[5] for s in sets]
+    fields_ms = []
+    for s in sets:
+        fields_ms += [s[0], s[1]]
+    dec = decoder.CifCaf(cfg, keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    initial = [Annotation(COCO_KEYPOINTS, coco_skeleton).set(init_data[i].copy(), init_js[i].copy())
+               for i in range(2)]
+    anns = dec(fields_ms, initial_annotations=initial)
+    assert len(anns) == len(o.data) >= 2
+    for ann, d, js in zip(anns, o.data, o.joint_scales):
+        assert np.array_equal(ann.data, d) and np.array_equal(ann.joint_scales, js)
+    assert sum(any(a is i for a in anns) for i in initial) >= 1, 'initial objects are returned'
+
+
 def test_decode_stream_lanes_equal_single_batches(coco_skeleton, configured_decoder):
     """CifCaf.decode_stream (three batches in flight on their own streams / workspaces) returns,
     batch for batch, exactly what decode_batch returns."""
