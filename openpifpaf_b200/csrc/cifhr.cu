@@ -60,12 +60,16 @@ constexpr int kZeroFloats = 1024;     // zeroed smem the empty strips are stored
 constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
 constexpr int kCompactSlab = 8192;     // cells per active-cell list (16 KiB of shared memory)
+constexpr int kBoundBlock = 64;        // sources per row-bound record (see CifHrWs::blk)
 
 struct CifHrWs {
   float4 *src_a;    // (B,F,src_cap) cx, cy, sigma^2, v
   int4 *src_b;      // (B,F,src_cap) minx, maxx, miny, maxy
   float2 *src_c;    // (B,F,src_cap) scale in pixels (CifDet: w, h in pixels) for the seed stage
   int *n_src;       // (B,F)
+  int2 *blk;        // (B,F,blk_cap) [min miny, max maxy) over each run of kBoundBlock sources: sources are in
+                    // row-major cell order, so a strip only meets a short range of runs (crowded scenes)
+  int blk_cap;
   int *strip_cnt;   // (B,F,nstrips)
   int *busy_list;   // (B*F*nstrips) ids (bf * nstrips + strip) of the strips with sources, any order
   int *cursors;     // [0] number of busy strips, [1] producer group cursor, [2] consumer strip cursor
@@ -90,6 +94,7 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   n += align_up(bf * c.src_cap * sizeof(int4), 256);
   n += align_up(bf * c.src_cap * sizeof(float2), 256);
   n += align_up(bf * sizeof(int), 256);
+  n += align_up(bf * ((c.src_cap + kBoundBlock - 1) / kBoundBlock) * sizeof(int2), 256);
   n += 2 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
   n += 256;
   return n;
@@ -103,6 +108,8 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
   w.src_b = (int4 *)p;   p += align_up(bf * c.src_cap * sizeof(int4), 256);
   w.src_c = (float2 *)p; p += align_up(bf * c.src_cap * sizeof(float2), 256);
   w.n_src = (int *)p;    p += align_up(bf * sizeof(int), 256);
+  w.blk_cap = (c.src_cap + kBoundBlock - 1) / kBoundBlock;
+  w.blk = (int2 *)p;     p += align_up(bf * w.blk_cap * sizeof(int2), 256);
   w.strip_cnt = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.busy_list = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.cursors = (int *)p;
@@ -192,6 +199,23 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   }
   }
   __syncthreads();
+  // row bounds of every run of kBoundBlock sources (one warp per run)
+  {
+    const int n_kept = min(count, src_cap);
+    int2 *bb = w.blk + (size_t)bf * w.blk_cap;
+    for (int blk = warp_id(); blk * kBoundBlock < n_kept; blk += kCompactThreads / 32) {
+      int lo = 0x7fffffff, hi = -0x7fffffff;
+      const int k1 = min(n_kept, (blk + 1) * kBoundBlock);
+      for (int k = blk * kBoundBlock + lane_id(); k < k1; k += 32) {
+        const int4 b = ob[k];
+        lo = min(lo, b.z);
+        hi = max(hi, b.w);
+      }
+      lo = __reduce_min_sync(0xffffffffu, lo);
+      hi = __reduce_max_sync(0xffffffffu, hi);
+      if (lane_id() == 0) bb[blk] = make_int2(lo, hi);
+    }
+  }
   // per-strip counts = prefix sum of the difference array; warp 0 scans it 32 strips at a time and
   // appends the strips that have sources to the consumers' work list (order is irrelevant)
   if (warp_id() == 0) {
@@ -371,6 +395,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   __shared__ uint32_t s_mask[2][kMaxPatches];             // bit s of word s/32: source s touches the patch
   __shared__ uint32_t s_sat[kMaxPatches / 32];            // bit p: every pixel of patch p has reached 1
   __shared__ int warp_tot[kSplatWarps];
+  __shared__ int s_first[kSplatWarps], s_last[kSplatWarps];
   __shared__ int s_item;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -440,13 +465,32 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
     const int py = g.r0 + row;
     const int tile_row = (int)(g.gs - g.ga) + row * hw;
 
-    for (int base = 0; base < nsrc && !strip_done; base += kSplatThreads) {
+    // long source lists (crowded scenes): the range of kBoundBlock-runs whose rows meet the strip
+    int i_lo = 0, i_hi = nsrc;
+    if (nsrc > kSplatThreads) {
+      const int2 *bounds = w.blk + (size_t)bf * w.blk_cap;
+      int first = 0x7fffffff, last = -1;
+      for (int blk = tid; blk * kBoundBlock < nsrc; blk += kSplatThreads) {
+        const int2 b = bounds[blk];
+        if (b.x < g.r1 && b.y > g.r0) { first = min(first, blk); last = max(last, blk); }
+      }
+      first = __reduce_min_sync(0xffffffffu, first);
+      last = __reduce_max_sync(0xffffffffu, last);
+      if (lane == 0) { s_first[warp] = first; s_last[warp] = last; }
+      consumer_sync();
+      first = 0x7fffffff; last = -1;
+#pragma unroll
+      for (int q = 0; q < kSplatWarps; q++) { first = min(first, s_first[q]); last = max(last, s_last[q]); }
+      i_lo = last < 0 ? nsrc : first * kBoundBlock;
+      i_hi = last < 0 ? nsrc : min(nsrc, (last + 1) * kBoundBlock);
+    }
+    for (int base = i_lo; base < i_hi && !strip_done; base += kSplatThreads) {
       // ordered filter of this block of sources by the strip's rows
       const int i = base + tid;
       bool keep = false, wide = false, flat = false;
       int4 bb = make_int4(0, 0, 0, 0);
       float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (i < nsrc) {
+      if (i < i_hi) {
         bb = gb_src[i];
         keep = bb.z < g.r1 && bb.w > g.r0;
       }
