@@ -362,8 +362,10 @@ __device__ __forceinline__ void consumer_sync() {
 
 // block_flag_scan for the consumer warps; *any_wide = some thread of the block passed wide = true
 // (bit 30 of a warp's total carries its vote)
+// `clear` (2 * kMaxPatches words) is zeroed between the two barriers when anything was flagged: every
+// consumer has then left the code before the scan, and nobody reads `clear` before the second barrier
 __device__ __forceinline__ int consumer_flag_scan(bool flag, bool wide, int *warp_tot, int *total,
-                                                  bool *any_wide) {
+                                                  bool *any_wide, uint32_t *clear) {
   unsigned m = __ballot_sync(0xffffffffu, flag);
   const bool wv = __any_sync(0xffffffffu, wide);
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -378,6 +380,8 @@ __device__ __forceinline__ int consumer_flag_scan(bool flag, bool wide, int *war
     tot += t & 0xffff;
     votes |= t >> 30;
   }
+  if (tot != 0)
+    for (int q = threadIdx.x; q < 2 * kMaxPatches; q += kSplatThreads) clear[q] = 0u;
   consumer_sync();
   *total = tot;
   *any_wide = votes != 0;
@@ -512,7 +516,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
       }
       int n_staged;
       bool any_wide;
-      const int off = consumer_flag_scan(keep, wide, warp_tot, &n_staged, &any_wide);   // two barriers
+      const int off = consumer_flag_scan(keep, wide, warp_tot, &n_staged, &any_wide, &s_mask[0][0]);   // two barriers, masks cleared
       if (keep) {
         if (flat) a.z = -a.z;                              // only ever read by the wide path below
         s_a[off] = a;
@@ -520,8 +524,39 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
       }
       if (n_staged == 0) continue;
 
+      if (!any_wide && n_staged <= kChunk) {
+        // the usual case, one chunk of narrow boxes: the thread that staged a source also marks the patches
+        // it touches (the masks were cleared inside the scan), so one barrier separates staging from the
+        // patch loop; the next scan's first barrier ends the patch loop
+        if (keep) {
+          const int p0 = bb.x >> cshift, p1 = (bb.y - 1) >> cshift;
+          uint32_t *word = s_mask[off >> 5];
+          const uint32_t bit = 1u << (off & 31);
+          for (int p = p0; p <= p1; p++) atomicOr(&word[p], bit);
+        }
+        consumer_sync();
+        for (int p = warp; p < n_patches; p += kSplatWarps) {
+          unsigned long long m = (unsigned long long)s_mask[0][p] | ((unsigned long long)s_mask[1][p] << 32);
+          if (m == 0ull) continue;
+          const int px = (p << cshift) + cg;
+          const bool ok = py < g.r1 && px < hw;
+          float acc = ok ? tile[tile_row + px] : 0.f;
+          int seen = 0;
+          while (m) {
+            const int s = __ffsll((long long)m) - 1;
+            m &= m - 1ull;
+            splat_px(acc, px, py, s_a[s], s_b[s]);
+            if ((++seen & 7) == 0) {
+              // once every pixel of the patch reached 1 nothing can change any more
+              if (__all_sync(0xffffffffu, !(acc < 1.f))) break;
+            }
+          }
+          if (ok) tile[tile_row + px] = clamp1(acc);
+        }
+        continue;
+      }
       if (!any_wide) {
-        // narrow boxes (the usual case): one thread per source marks the few patches it touches
+        // more than one chunk of narrow boxes: one thread per source marks the few patches it touches
         for (int c0 = 0; c0 < n_staged; c0 += kChunk) {
           const int nchunk = min(kChunk, n_staged - c0);
           for (int p = tid; p < 2 * kMaxPatches; p += kSplatThreads) (&s_mask[0][0])[p] = 0u;
@@ -605,6 +640,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
       }
     }
     if (merge) {          // np.maximum with the map of the scales before (NaN from either side wins)
+      consumer_sync();    // the last patch loop may have ended without a barrier
       for (size_t i = g.gs + tid; i < g.ge; i += kSplatThreads) {
         const float a = tile[i - g.ga], o = hr[i];
         tile[i - g.ga] = (a != a) ? a : ((o != o) ? o : fmaxf(a, o));
