@@ -14,8 +14,9 @@ printed by rank 0 (contract in DESIGN.md section "Measurement"):
   value_one_lane, stages_ms
                 the same K steps strictly one at a time on one stream, with the
                 library's per-stage CUDA-event profile;
-  e2e           images/s through the public API CifCaf.decode_batch() with
-                PINNED HOST fields and default settings: host -> device
+  e2e           images/s through the public API CifCaf.decode_stream(batches) with
+                PINNED HOST fields and default settings (e2e.one_call_per_step:
+                one synchronous CifCaf.decode_batch per step): host -> device
                 transfer, kernels, D2H of the results and the construction of
                 the Annotation objects are all inside the timed region.  The
                 default host_transfer='auto' moves what the decode reads: the
@@ -603,8 +604,26 @@ def run_b200(args):
     for _ in range(args.steps):
         anns = dec.decode_batch(h_cif, h_caf)
     torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_sync_s = max_over_ranks(time.perf_counter() - t0)
     e2e_mapped = dec._use_mapped(h_cif, h_caf, dec.params())
+    # (1b) the same K batches through CifCaf.decode_stream: every batch still crosses PCIe and comes back as
+    # Annotation lists inside the timed region, but the transfer of batch k + 1 overlaps the tail of batch k
+    # (this is how `value` is issued as well: K steps over the lanes)
+
+    def host_batches(n):
+        for _ in range(n):
+            yield h_cif, h_caf
+
+    for _ in dec.decode_stream(host_batches(2)):
+        pass
+    barrier()
+    t0 = time.perf_counter()
+    n_stream = 0
+    for anns_s in dec.decode_stream(host_batches(args.steps)):
+        n_stream += sum(len(a) for a in anns_s)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    assert n_stream == args.steps * sum(len(a) for a in anns), 'streamed and single-batch host paths disagree'
     # (2) the same call with host_transfer='copy': every plane of every field is copied
     dec.host_transfer = 'copy'
     for _ in range(2):
@@ -613,6 +632,14 @@ def run_b200(args):
     t0 = time.perf_counter()
     for _ in range(args.steps):
         anns_c = dec.decode_batch(h_cif, h_caf)
+    torch.cuda.synchronize()
+    e2e_copy_sync_s = max_over_ranks(time.perf_counter() - t0)
+    for _ in dec.decode_stream(host_batches(2)):
+        pass
+    barrier()
+    t0 = time.perf_counter()
+    for _ in dec.decode_stream(host_batches(args.steps)):
+        pass
     torch.cuda.synchronize()
     e2e_copy_s = max_over_ranks(time.perf_counter() - t0)
     dec.host_transfer = 'auto'
@@ -702,8 +729,13 @@ def run_b200(args):
         'config': workload_config(args.workload, batch, world, lanes),
         'e2e': {'value': world * batch * args.steps / e2e_s, 'unit': UNIT,
                 'h2d_bytes_per_step': h2d_mapped if e2e_mapped else h2d, 'd2h_bytes_per_step': d2h,
-                'api': 'CifCaf.decode_batch(pinned host cif, caf) -> List[List[Annotation]], defaults',
+                'api': 'CifCaf.decode_stream(K pinned host (cif, caf) batches) -> List[List[Annotation]] per '
+                       'batch, defaults',
                 'ms_per_step': 1e3 * e2e_s / args.steps,
+                'one_call_per_step': {'value': world * batch * args.steps / e2e_sync_s, 'unit': UNIT,
+                                      'ms_per_step': 1e3 * e2e_sync_s / args.steps,
+                                      'api': 'CifCaf.decode_batch(pinned host cif, caf), one synchronous call '
+                                             'per step (no overlap between steps)'},
                 'host_transfer': "auto -> %s" % ('mapped' if e2e_mapped else 'copy'),
                 'h2d_dma_bytes_per_step': h2d_dma if e2e_mapped else h2d,
                 'h2d_zero_copy_bytes_per_step': h2d_zero if e2e_mapped else 0,
@@ -715,8 +747,11 @@ def run_b200(args):
                         'e2e_full_copy'},
         'e2e_full_copy': {'value': world * batch * args.steps / e2e_copy_s, 'unit': UNIT,
                           'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                          'api': "CifCaf.decode_batch with host_transfer='copy' (every plane copied)",
-                          'host_chunk': decoder.CifCaf.host_chunk, 'ms_per_step': 1e3 * e2e_copy_s / args.steps,
+                          'api': "CifCaf.decode_stream with host_transfer='copy' (every plane copied)",
+                          'ms_per_step': 1e3 * e2e_copy_s / args.steps,
+                          'one_call_per_step': {'value': world * batch * args.steps / e2e_copy_sync_s,
+                                                'unit': UNIT, 'ms_per_step': 1e3 * e2e_copy_sync_s / args.steps,
+                                                'host_chunk': decoder.CifCaf.host_chunk},
                           'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
                           'pcie_floor_frac': h2d_ms / (1e3 * e2e_copy_s / args.steps)},
         # kernels of this library launched in the timed `value` region (8 per decode: compact, splat, seeds

@@ -442,6 +442,55 @@ class DeviceDecoder:
                 nxt += 1
 
 
+    def run_host_stream(self, batches, params, sub, n_lanes, *, keep=('ann',)):
+        """``run_host_lanes`` over a stream of host batches: the sub-batches of successive batches follow
+        each other through the lanes without a gap, so the copies of batch k + 1 run while the kernels of
+        the last sub-batches of batch k are still in flight.  ``batches``: iterable of ``(cif, caf)`` host
+        tensors / arrays.  Yields ``(batch index, buf, n images, last sub-batch of its batch)`` in order;
+        the caller copies what it needs out of ``buf.host`` before asking for the next item."""
+        if params.inverse is not None or params.initial is not None:
+            raise NotImplementedError('per-image records (metas, initial annotations) go through decode_batch')
+        lanes = self.lanes(n_lanes)
+        cur = torch.cuda.current_stream(self._device())
+        if n_lanes > 1:
+            params = dataclasses.replace(params, in_flight=n_lanes)
+        p_all = params.to_c()
+        pending = []
+        n_sub = [0]
+
+        def items():
+            for bid, (cif, caf) in enumerate(batches):
+                cif_t = torch.as_tensor(cif).contiguous()
+                caf_t = torch.as_tensor(caf).contiguous()
+                B = cif_t.shape[0]
+                step = max(1, min(int(sub), B))
+                for b0 in range(0, B, step):
+                    yield bid, cif_t, caf_t, b0, min(b0 + step, B), b0 + step >= B
+
+        def submit(item):
+            bid, cif_t, caf_t, b0, b1, last = item
+            lane = lanes[n_sub[0] % n_lanes]
+            if n_sub[0] < n_lanes:
+                lane.stream.wait_stream(cur)
+            buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], params, b1 - b0, keep=keep,
+                                                 p_c=p_all, stream_ptr=lane.stream_ptr)
+            pending.append((lane, buf, bid, b1 - b0, last))
+            n_sub[0] += 1
+
+        it = items()
+        for item in it:
+            submit(item)
+            if len(pending) == n_lanes:
+                break
+        while pending:
+            lane, buf, bid, nb, last = pending.pop(0)
+            lane.engine.wait_host_chunk(buf, 0)
+            yield bid, buf, nb, last
+            nxt = next(it, None)           # the lane just collected is the one the next sub-batch takes
+            if nxt is not None:
+                submit(nxt)
+
+
 class Lane:
     def __init__(self, engine, stream):
         self.engine, self.stream, self.pending = engine, stream, None

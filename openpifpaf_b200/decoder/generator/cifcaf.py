@@ -51,6 +51,11 @@ class CifCaf(Generator):
     host_transfer = 'auto'
     host_lanes = 8                # sub-batches in flight in 'mapped' mode ...
     mapped_chunk = 8              # ... of this many images (641 px, batch 64: 8 x 8 -> 2.4 ms, 64 x 1 -> 3.3 ms)
+    # decode_stream on host batches: successive batches overlap, so larger sub-batches (fewer submissions,
+    # fewer Annotation-building rounds) win: 641 px, batch 64: 32 x 4 lanes -> 1.59 ms per batch (the PCIe
+    # time of the bytes that move), 8 x 8 -> 1.77 ms
+    stream_chunk = 32
+    stream_lanes = 4
 
     def __init__(self, field_config: FieldConfig, *,
                  keypoints,
@@ -261,11 +266,35 @@ class CifCaf(Generator):
                     anns[r] = orig
 
     def decode_stream(self, batches, *, n_lanes=8):
-        """Generator over device-resident batches ``(cif, caf)`` (CUDA tensors): keeps ``n_lanes``
-        batches in flight on their own streams / workspaces and yields each batch's
-        List[List[Annotation]] in order.  Same results as ``decode_batch`` per batch."""
+        """Generator over batches ``(cif, caf)``: yields each batch's List[List[Annotation]] in order,
+        with the same results as ``decode_batch`` per batch.
+
+        CUDA tensors: ``n_lanes`` batches are in flight on their own streams / workspaces.  Host
+        tensors / arrays (ideally pinned, see ``host_transfer``): the sub-batches of successive batches
+        follow each other through ``host_lanes`` lanes, so the transfer of the next batch overlaps the
+        kernels, the result copies and the construction of the ``Annotation`` objects of this one
+        (``stream_chunk`` images per sub-batch on ``stream_lanes`` lanes)."""
         eng = self.engine()
         params = self.params()
+        batches = iter(batches)
+        first = next(batches, None)
+        if first is None:
+            return
+        if not (isinstance(first[0], torch.Tensor) and first[0].is_cuda):
+            import itertools
+            result = []
+            for _, buf, nb, last in eng.run_host_stream(itertools.chain([first], batches), params,
+                                                        self.stream_chunk, self.stream_lanes):
+                h = buf.host
+                result.extend(self._annotations_from(
+                    h['n_ann'].numpy(), h['ann_data'].numpy(), h['ann_scales'].numpy(),
+                    h['ann_source'].numpy(), h['pre_data'].numpy(), h['pre_order'].numpy(), 0, nb))
+                if last:
+                    yield result
+                    result = []
+            return
+        import itertools
+        batches = itertools.chain([first], batches)
         tickets = []
 
         def collect(ticket):

@@ -854,6 +854,34 @@ def test_host_mapped_transfer_equals_copy(coco_skeleton, configured_decoder, chu
             assert np.array_equal(g.data, w.data)
 
 
+@pytest.mark.parametrize('pinned', [True, False])
+def test_decode_stream_host_batches(coco_skeleton, configured_decoder, pinned):
+    """CifCaf.decode_stream over host batches (sub-batches of successive batches back to back on the
+    lanes, ragged batch sizes) returns, batch for batch, what decode_batch returns."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.stream_chunk, dec.stream_lanes = 4, 3
+    batches = []
+    for k, n in enumerate((10, 7, 1, 3, 9)):
+        items = [fields((161, 241), 1 + (b + k) % 3, pose_seed=600 + 20 * k + b, jitter_seed=700 + 20 * k + b)[:2]
+                 for b in range(n)]
+        cif = torch.from_numpy(np.stack([i[0] for i in items]))
+        caf = torch.from_numpy(np.stack([i[1] for i in items]))
+        batches.append((cif.pin_memory(), caf.pin_memory()) if pinned else (cif.numpy(), caf.numpy()))
+    want = [dec.decode_batch(torch.as_tensor(c).cuda(), torch.as_tensor(a).cuda()) for c, a in batches]
+    got = list(dec.decode_stream(iter(batches)))
+    assert len(got) == len(want)
+    for g_batch, w_batch in zip(got, want):
+        assert [len(g) for g in g_batch] == [len(w) for w in w_batch]
+        for g_img, w_img in zip(g_batch, w_batch):
+            for g, w in zip(g_img, w_img):
+                assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
+                assert [(s, e) for s, e, _, _ in g.decoding_order] == [(s, e) for s, e, _, _ in w.decoding_order]
+    assert sum(len(g) for b in got for g in b) >= 30
+    assert list(dec.decode_stream(iter([]))) == []
+
+
 def test_host_mapped_with_metas(coco_skeleton, configured_decoder):
     """Per-image meta records follow their images through the lane-parallel mapped host path."""
     from conftest import HorizontalSwap, inverse_inputs
