@@ -120,7 +120,7 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
 
 // ---------------------------------------------------------------------------
 // K1: ordered compaction of CIF sources per (image, field).
-__global__ void __launch_bounds__(kCompactThreads)
+__global__ void __launch_bounds__(kCompactThreads, 8)
 cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2,
                    const float *__restrict__ rest, CifHrWs w, pp_shape s, int src_cap, int hh, int hw,
                    float v_th, float min_scale_over_stride, int use_min_scale, int det,
