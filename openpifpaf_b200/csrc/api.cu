@@ -399,6 +399,13 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return PP_ERR_ARG;
   if (sets[0].H != s->H || sets[0].W != s->W || sets[0].stride != s->stride) return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
+#ifdef PP_DEBUG_SKIP
+  // timing experiments only (scripts/stage_skip_probe.py): leave stages out; results are those of the last
+  // full call on the same buffers.  1 seeds + sort, 2 CafScored + binning, 4 assembly, 8 NMS, 16 CifHr
+  const int dbg_skip = getenv("PP_DEBUG_SKIP") ? atoi(getenv("PP_DEBUG_SKIP")) : 0;
+#else
+  const int dbg_skip = 0;
+#endif
   const bool need_hr = o->hr == nullptr;
   DecodeWs w = layout(d_ws, *s, *c, need_hr);
   if (ws_bytes < w.total) return PP_ERR_WORKSPACE;
@@ -421,7 +428,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   // CifHr.fill (cif_hr.py:66-78): one map per group, merged with np.maximum; with 10 heads the
   // groups are the hflip pairs (i, i + 5), each accumulated with v / neighbors / 2
   const int n_groups = hflip_pairs ? n_sets / 2 : n_sets;
-  for (int g = 0; g < n_groups; g++) {
+  for (int g = 0; g < n_groups && !(dbg_skip & 16); g++) {
     const pp_shape q = set_shape(g);
     const float *second = hflip_pairs ? sets[g + n_groups].cif : nullptr;
     if (second && (sets[g + n_groups].H != q.H || sets[g + n_groups].W != q.W)) return PP_ERR_ARG;
@@ -430,7 +437,8 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return rc;
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
-  if (n_sets == 1 && p->seed_threshold >= p->cif_threshold) {
+  if (dbg_skip & 1) {
+  } else if (n_sets == 1 && p->seed_threshold >= p->cif_threshold) {
     // the seed candidates are a subset of the sources the CifHr stage compacted: skip the field scan
     if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, *p,
                                                 st, 0)))
@@ -441,16 +449,18 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
                                      sets[k].cif_min_scale, k == 0, st, 0)))
         return rc;
   }
-  if ((rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0))) return rc;
+  if (!(dbg_skip & 1) && (rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0)))
+    return rc;
   // CafScored.fill (caf_scored.py:89-98): lists concatenated over the heads
-  for (int k = 0; k < n_sets; k++)
+  for (int k = 0; k < n_sets && !(dbg_skip & 2); k++)
     if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, set_shape(k),
                                    *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
                                    o->status, st, sets[k].caf_rest)))
       return rc;
   AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
-  if ((rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st))) return rc;
+  if (!(dbg_skip & 2) && (rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st)))
+    return rc;
   a.rows = w.bin_rows; a.start = w.bin_start; a.geo = bin_geo(*s); a.nfwd = nfwd; a.nbwd = nbwd;
   a.occ_cnt = w.occ_cnt; a.occ_rec = w.occ_rec;
   a.pre_data = o->pre_data ? o->pre_data : w.pre_data;
@@ -465,7 +475,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
     a.init_data = p->initial->data; a.init_scales = p->initial->scales;
     a.init_n = p->initial->n; a.init_cap = p->initial->cap;
   }
-  if ((rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
+  if (!(dbg_skip & 4) && (rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
   const float *nms_data = a.pre_data, *nms_scales = a.pre_scales;
   if (p->force_complete) {                                           // cifcaf.py:110-115
     // second CafScored(score_th=0.0001) into the workspace lists (the first
@@ -482,8 +492,9 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return rc;
     nms_data = w.cmp_data; nms_scales = w.cmp_scales;
   }
-  rc = nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
-                  o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  rc = (dbg_skip & 8) ? PP_OK
+                      : nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+                                   o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
   if (!rc && p->inverse)      // optional Preprocess.annotations_inverse on the results (inside the nms stage time)
     rc = annotations_inverse_launch(o->ann_data, o->ann_scales, o->n_ann, a.pre_data, a.n_pre, *p->inverse,
                                     s->B, s->F, c->ann_cap, st);
