@@ -800,6 +800,11 @@ def run_b200(args):
 
 def main():
     args = parse_args()
+    # exactly one line on stdout: Python's prints keep the real stdout, whatever libraries write to file
+    # descriptor 1 (NCCL's version banner under torchrun) goes to stderr
+    sys.stdout.flush()
+    sys.stdout = os.fdopen(os.dup(1), 'w', buffering=1)
+    os.dup2(2, 1)
     if args.impl == 'reference':
         return run_reference(args)
     return run_b200(args)
