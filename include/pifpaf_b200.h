@@ -131,6 +131,13 @@ typedef struct pp_params {
                                     this one only).  > 1 makes the assembly kernel stage its lists in
                                     80 KB instead of a whole SM's shared memory, so that CTAs of the
                                     other batches' kernels can share its SMs.  Same results.     */
+  /* tuning knobs (0 = the library's choice).  They change the schedule, never a result. */
+  int32_t asm_heavy_seeds;       /* seeds per image above which the assembly indexes the seeds by
+                                    (field, row band) for its occupancy updates (default 4096; < 0 = always) */
+  int32_t asm_stage_kb;          /* KB of shared memory for the staged candidate lists (< 0 = none)      */
+  int32_t cifhr_group;           /* strips per splat work item (default 3)                               */
+  int32_t cifhr_ctas_per_sm;     /* persistent splat CTAs per SM (default 3)                             */
+  int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's

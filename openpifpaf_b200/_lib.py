@@ -73,6 +73,8 @@ class Params(C.Structure):
         ('force_complete', C.c_int32), ('nms', C.c_int32), ('exp_mode', C.c_int32),
         ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
         ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32), ('in_flight', C.c_int32),
+        ('asm_heavy_seeds', C.c_int32), ('asm_stage_kb', C.c_int32), ('cifhr_group', C.c_int32),
+        ('cifhr_ctas_per_sm', C.c_int32), ('cifhr_rshift', C.c_int32),
     ]
 
 

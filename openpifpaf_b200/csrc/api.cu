@@ -16,15 +16,16 @@ void set_cuda_error(cudaError_t e, const char *where) {
            cudaGetErrorString(e));
 }
 
+// SM count of the current device (cached per device ordinal)
 int num_sms() {
-  static int cached = 0;
-  if (cached == 0) {
-    int dev = 0, n = 148;
-    if (cudaGetDevice(&dev) == cudaSuccess)
-      cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    cached = n > 0 ? n : 148;
-  }
-  return cached;
+  constexpr int kMaxDev = 64;
+  static int cached[kMaxDev] = {0};
+  int dev = 0, n = 148;
+  if (cudaGetDevice(&dev) != cudaSuccess) return n;
+  if (dev >= 0 && dev < kMaxDev && cached[dev] > 0) return cached[dev];
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  if (dev >= 0 && dev < kMaxDev) cached[dev] = n;
+  return n;
 }
 
 }  // namespace pp
@@ -183,8 +184,8 @@ const char *pp_stage_name(int stage) {
 int pp_decode_launch_count(const pp_params *p) {
   // 8 kernels (compact, splat, seeds collect, seeds sort, CafScored, candidate binning, assembly, NMS)
   // + 3 memsets (status, work cursors, raw seed counts)
-  int n = PP_N_STAGES + 4;
-  if (p && p->force_complete) n += 3;   // second CafScored, its binning, complete_kernel
+  int n = PP_N_STAGES + 3;              // the NMS is the tail of the assembly kernel ...
+  if (p && p->force_complete) n += 4;   // ... unless: second CafScored, its binning, complete_kernel, nms_kernel
   if (p && p->inverse) n += 1;          // annotations_inverse_kernel
   return n;
 }
@@ -347,6 +348,11 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
     a.init_data = p->initial->data; a.init_scales = p->initial->scales;
     a.init_n = p->initial->n; a.init_cap = p->initial->cap;
   }
+  if (!p->force_complete) {
+    a.fuse_nms = 1;
+    a.nms = nms_make_args(a.pre_data, a.pre_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
+                          d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p);
+  }
   int rc = assemble_launch(a, *sk, s->B, s->F, *p, st);
   if (rc) return rc;
   if (p->force_complete) {
@@ -358,8 +364,7 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
     return nms_launch(cmp_data, cmp_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
                       d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p, st);
   }
-  return nms_launch(a.pre_data, a.pre_scales, a.n_pre, d_out->ann_data, d_out->ann_scales,
-                    d_out->ann_score, d_out->ann_source, d_out->n_ann, q, *s, *c, *p, st);
+  return PP_OK;      // the NMS ran inside the assembly kernel
 }
 
 int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
@@ -475,6 +480,13 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
     a.init_data = p->initial->data; a.init_scales = p->initial->scales;
     a.init_n = p->initial->n; a.init_cap = p->initial->cap;
   }
+  // without force_complete the keypoint NMS of an image runs as the tail of its assembly CTA
+  const bool fuse_nms = !p->force_complete && !(dbg_skip & (4 | 8));
+  if (fuse_nms) {
+    a.fuse_nms = 1;
+    a.nms = nms_make_args(a.pre_data, a.pre_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+                          o->ann_source, o->n_ann, w.stage, *s, *c, *p);
+  }
   if (!(dbg_skip & 4) && (rc = assemble_launch(a, *sk, s->B, s->F, *p, st))) return rc;
   const float *nms_data = a.pre_data, *nms_scales = a.pre_scales;
   if (p->force_complete) {                                           // cifcaf.py:110-115
@@ -492,9 +504,14 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return rc;
     nms_data = w.cmp_data; nms_scales = w.cmp_scales;
   }
-  rc = (dbg_skip & 8) ? PP_OK
-                      : nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
-                                   o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  if (fuse_nms) {
+    prof_mark(p->profile, kStNms, st);      // (its time is inside the assembly stage)
+    rc = PP_OK;
+  } else {
+    rc = (dbg_skip & 8) ? PP_OK
+                        : nms_launch(nms_data, nms_scales, a.n_pre, o->ann_data, o->ann_scales, o->ann_score,
+                                     o->ann_source, o->n_ann, w.stage, *s, *c, *p, st);
+  }
   if (!rc && p->inverse)      // optional Preprocess.annotations_inverse on the results (inside the nms stage time)
     rc = annotations_inverse_launch(o->ann_data, o->ann_scales, o->n_ann, a.pre_data, a.n_pre, *p->inverse,
                                     s->B, s->F, c->ann_cap, st);

@@ -6,34 +6,39 @@
 // caf_center_s (functional.pyx:338-359) and Occupancy (decoder/occupancy.py,
 // decoder/utils.py:61-66, functional.pyx:281-286).
 //
-// One CTA per image.  What is parallel inside an image:
-//   * "next seed that is not occupied" is a CTA-wide search over the sorted
-//     seed list -- occupancy only changes after a pose has been grown;
-//   * the occupancy map is never rasterised: Occupancy.get(f, x, y) is the
-//     number (mod 256, the reference's uint8 wrap) of Occupancy.set boxes of
-//     field f covering the cell, so each seed carries a uint8 counter that is
-//     bumped, CTA-wide, against the <= F boxes of the pose just finished;
-//   * the frontier is evaluated eagerly: when a joint is set, one WARP per
-//     outgoing edge scans the link's candidate list (lanes over candidates,
-//     per-lane top-2, butterfly merge), applies blend/max and the reverse
-//     match.  The reference evaluates lazily through a PriorityQueue whose
-//     unevaluated keys are upper bounds of the evaluated ones, so "always take
-//     the best evaluated edge whose target is still empty" visits the same
-//     edges in the same order (validated by the tests).
-//     Ties follow Python's tuple order (-score, (x, y, s, v), start, end).
+// One CTA per image, one WARP per pose:
+//   * _grow(seed) is a pure function of the seed and the CafScored lists -- it never looks at the
+//     occupancy map (cifcaf.py:247-307).  Only the DECISION which seeds start a pose is serial: a
+//     seed is used iff no pose committed before it covers its cell.  So the kernel grows poses
+//     speculatively, one warp each, side by side: when the seed loop reaches a free seed for which
+//     no grown pose is at hand, warp 0 picks that seed plus the next free seeds that do not lie in
+//     the Occupancy.set box an earlier pick is certain to set (its own joint), every warp grows one
+//     of them, and the seed loop then continues exactly as the reference's: next free seed -> take
+//     its grown pose if there is one (else start a new wave) -> store, mark occupied.  Speculation
+//     changes the time, never the result: a grown pose whose seed gets covered first is dropped.
+//   * inside a warp the frontier is evaluated eagerly: when a joint is set the warp scans the
+//     candidate list of every outgoing edge (lanes over candidates), applies blend / max and the
+//     reverse match, and keeps the scored entries; "take the best evaluated edge whose target is
+//     still empty" then visits the same edges in the same order as the reference's lazy
+//     PriorityQueue, whose unevaluated keys are upper bounds of the evaluated ones (SURVEY.md
+//     appendix A4; validated by the tests).  Ties follow Python's tuple order
+//     (-score, (x, y, s, v), start, end).  No CTA barrier inside a pose.
+//   * the occupancy map is never rasterised: Occupancy.get(f, x, y) is the number (mod 256, the
+//     reference's uint8 wrap) of Occupancy.set boxes of field f covering the cell, so each seed
+//     carries a uint8 counter that is bumped, CTA-wide, against the <= F boxes of a committed pose;
+//     "next free seed" is a CTA-wide ballot search;
+//   * nms.Keypoints (nms.cuh) runs as the tail of the same CTA unless force_complete is on.
 #include <cuda_pipeline.h>
-
-#include <stdlib.h>
 
 #include "common.cuh"
 #include "stages.cuh"
 #include "occupancy.cuh"
+#include "nms.cuh"
 
 namespace pp {
 
-constexpr int kAsmThreads = 256;
-constexpr int kAsmWarps = kAsmThreads / 32;
-constexpr int kMaxEdges = 2 * PP_MAX_L;
+constexpr int kAsmWarps = 8;                  // poses grown side by side per image
+constexpr int kAsmThreads = 32 * kAsmWarps;
 // Occupancy bookkeeping.  Up to kHeavySeeds seeds every seed's counter is tested against the boxes of
 // each finished pose (a few thousand tests).  Above that (crowded scenes, degenerate fields with 60 k
 // seeds and ~1000 poses per image) the seeds are counting-sorted once by (field, band of kOccBands
@@ -41,8 +46,8 @@ constexpr int kMaxEdges = 2 * PP_MAX_L;
 // map just bumps a per-field counter.
 constexpr int kHeavySeeds = 4096;
 constexpr int kOccBands = 32;
-constexpr int kStageBytes = 80 * 1024;        // staged candidate lists, 2 CTAs / SM (batches > #SMs)
-constexpr int kStageBytesSolo = 192 * 1024;   // ... 1 CTA / SM
+constexpr int kStageBytes = 72 * 1024;        // staged candidate lists when other batches are in flight
+constexpr int kPickScan = 4096;               // seeds examined beyond the first one when a wave is picked
 
 struct Graph {
   int F;
@@ -82,6 +87,12 @@ int build_graph(const pp_skeleton &sk, int F, Graph *g) {
   return PP_OK;
 }
 
+static int directed_edges(const Graph &g) {
+  int n = 0;
+  for (int j = 0; j < g.F; j++) n += g.deg[j];
+  return n;
+}
+
 struct Cand {      // (score, index) with the tie rule of the connection method
   float s;
   int i;
@@ -115,7 +126,7 @@ struct Cand2 {     // a candidate with its column in the binned store
 // `stride` floats apart; K columns sorted by spatial bin, bin b occupying
 // columns [start[b], start[b+1])) -- either the shared-memory copy or global.
 //
-// Three steps keep the serial chain of the one active warp short: (0) only the
+// Three steps keep the serial chain of the warp short: (0) only the
 // bin rows that intersect the caf_center_s box are visited; (1) a tight loop
 // tests the box exactly (functional.pyx:346-353) and compacts the columns of
 // the candidates inside it into `scratch`; (2) each lane scores ONE of them
@@ -288,22 +299,59 @@ __device__ __forceinline__ Xysv scan_list(const CafLists &cf, int l, bool fw, fl
                               cf.geo, scratch, method, exp_mode);
 }
 
+// ---- one pose per warp ---------------------------------------------------------------------------
+// A warp's private state, carved from dynamic shared memory (grow_words(F, E) 4-byte words per warp,
+// E = directed edges of the skeleton; every directed edge is queued at most once, cifcaf.py:255-262).
+struct GrowView {
+  float *data;       // (F, 3) x, y, v
+  float *js;         // (F)    joint_scales
+  uint32_t *queued;  // (F)    in_frontier bits, [start] bit end
+  // evaluated frontier entries (-score, (x, y, s, v), start, end), one array per member
+  float *p_key, *p_x, *p_y, *p_s, *p_v;
+  int *p_start, *p_end;
+  int *dec;          // (F, 2) decoding_order (start, end)
+  int *scratch;      // (kScratch)
+  int *meta;         // [0] decoding steps
+};
+
+__host__ __device__ inline int grow_words(int F, int E) {
+  return (3 * F + F + F + 7 * E + 2 * F + kScratch + 4 + 3) & ~3;
+}
+
+__device__ __forceinline__ GrowView grow_view(float *base, int F, int E) {
+  GrowView w;
+  w.data = base;                  base += 3 * F;
+  w.js = base;                    base += F;
+  w.queued = (uint32_t *)base;    base += F;
+  w.p_key = base;                 base += E;
+  w.p_x = base;                   base += E;
+  w.p_y = base;                   base += E;
+  w.p_s = base;                   base += E;
+  w.p_v = base;                   base += E;
+  w.p_start = (int *)base;        base += E;
+  w.p_end = (int *)base;          base += E;
+  w.dec = (int *)base;            base += 2 * F;
+  w.scratch = (int *)base;        base += kScratch;
+  w.meta = (int *)base;
+  return w;
+}
+
 // connection_value (cifcaf.py:194-217), warp-collective.
-__device__ Xysv warp_connection_value(const float (*data)[3], const float *js, const Graph &g,
-                                      const CafLists &cf, int start, int k, bool reverse_match,
-                                      float keypoint_th, int method, int exp_mode, int *scratch) {
+__device__ Xysv warp_connection_value(const GrowView &w, const Graph &g, const CafLists &cf, int start,
+                                      int k, bool reverse_match, float keypoint_th, int method,
+                                      int exp_mode) {
   Xysv zero = {0.f, 0.f, 0.f, 0.f};
   const int l = g.nb_link[start][k];
   const bool fw = g.nb_fwd[start][k] != 0;
-  const float sx = data[start][0], sy = data[start][1], sv = data[start][2];
-  const float ss = js[start] > 0.0f ? js[start] : 0.0f;           // max(0.0, .)
-  Xysv nw = scan_list(cf, l, fw, sx, sy, ss, scratch, method, exp_mode);
+  const float sx = w.data[3 * start], sy = w.data[3 * start + 1], sv = w.data[3 * start + 2];
+  const float ss = w.js[start] > 0.0f ? w.js[start] : 0.0f;       // max(0.0, .)
+  Xysv nw = scan_list(cf, l, fw, sx, sy, ss, w.scratch, method, exp_mode);
   float kp = __fsqrt_rn(__fmul_rn(nw.v, sv));                     // :201
   if (kp < keypoint_th) return zero;
   if (nw.v == 0.0f) return zero;
   float st = nw.s > 0.0f ? nw.s : 0.0f;
   if (reverse_match) {                                            // :208-215
-    Xysv rv = scan_list(cf, l, !fw, nw.x, nw.y, st, scratch, method, exp_mode);
+    Xysv rv = scan_list(cf, l, !fw, nw.x, nw.y, st, w.scratch, method, exp_mode);
     if (rv.s == 0.0f) return zero;
     float dist = __fadd_rn(fabsf(__fsub_rn(sx, rv.x)), fabsf(__fsub_rn(sy, rv.y)));
     if (dist > ss) return zero;
@@ -312,9 +360,134 @@ __device__ Xysv warp_connection_value(const float (*data)[3], const float *js, c
   return nw;
 }
 
+// Heap order of the reference's frontier.  Non-greedy: evaluated entries
+// (-score, (x, y, s, v), start, end).  Greedy (cifcaf.py:280-281): an entry is
+// applied the moment it is evaluated, so only the unevaluated keys
+// (-sqrt(v_start) [* confidence_scale], None, start, end) are ever compared;
+// `key` then holds that bound.
+__device__ __forceinline__ bool pending_less(const GrowView &w, int a, int b, int greedy) {
+  if (w.p_key[a] != w.p_key[b]) return w.p_key[a] < w.p_key[b];
+  if (!greedy) {
+    if (w.p_x[a] != w.p_x[b]) return w.p_x[a] < w.p_x[b];
+    if (w.p_y[a] != w.p_y[b]) return w.p_y[a] < w.p_y[b];
+    if (w.p_s[a] != w.p_s[b]) return w.p_s[a] < w.p_s[b];
+    if (w.p_v[a] != w.p_v[b]) return w.p_v[a] < w.p_v[b];
+  }
+  if (w.p_start[a] != w.p_start[b]) return w.p_start[a] < w.p_start[b];
+  return w.p_end[a] < w.p_end[b];
+}
+
+// ascending float order as ascending unsigned order (NaN excluded by the caller)
+__device__ __forceinline__ uint32_t float_orderable(float v) {
+  uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// add_to_frontier (cifcaf.py:251-263) for one start joint + the eager evaluation of the edges it
+// queues, warp-collective (lane = neighbour slot for the queueing).  Returns the new number of
+// frontier entries.
+__device__ __forceinline__ int queue_and_evaluate(const GrowView &w, const Graph &g, const CScale &cscale,
+                                                  const CafLists &cf, int start, int n_pend,
+                                                  bool reverse_match, const pp_params &p) {
+  const int lane = lane_id();
+  const unsigned full = 0xffffffffu;
+  bool ok = false;
+  int end = 0;
+  if (lane < g.deg[start]) {
+    end = g.nb_end[start][lane];
+    ok = !(w.data[3 * end + 2] > 0.0f) && !(w.queued[start] & (1u << end));           // :253-256
+  }
+  unsigned m = __ballot_sync(full, ok);
+  const unsigned bits = __reduce_or_sync(full, ok ? (1u << end) : 0u);
+  if (lane == 0) w.queued[start] |= bits;
+  while (m) {
+    const int k = __ffs(m) - 1;
+    m &= m - 1u;
+    const Xysv r = warp_connection_value(w, g, cf, start, k, reverse_match, p.keypoint_threshold,
+                                         p.connection_method, p.exp_mode);
+    if (lane == 0) {
+      const int q = n_pend;
+      float score = r.v;
+      if (p.greedy) score = __fsqrt_rn(w.data[3 * start + 2]);                        // :258 (the bound)
+      if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);        // :259-260, :282-284
+      w.p_key[q] = -score; w.p_x[q] = r.x; w.p_y[q] = r.y; w.p_s[q] = r.s; w.p_v[q] = r.v;
+      w.p_start[q] = start;
+      w.p_end[q] = (r.v == 0.0f) ? -1 : g.nb_end[start][k];                           // :277-278
+    }
+    n_pend++;
+  }
+  __syncwarp();
+  return n_pend;
+}
+
+// _grow (cifcaf.py:247-307) in its eager form, by one warp on its own state.  w.data / w.js hold the
+// annotation, w.meta[0] the decoding steps recorded so far (appended to).
+__device__ void warp_grow(const GrowView &w, const Graph &g, const CScale &cscale, const CafLists &cf,
+                          bool reverse_match, const pp_params &p) {
+  const int lane = lane_id();
+  const unsigned full = 0xffffffffu;
+  const int F = g.F;
+  if (lane < F) w.queued[lane] = 0u;
+  __syncwarp();
+  int n_pend = 0;
+  for (int j = 0; j < F; j++) {                                   // :288-291
+    if (w.data[3 * j + 2] == 0.0f) continue;
+    n_pend = queue_and_evaluate(w, g, cscale, cf, j, n_pend, reverse_match, p);
+  }
+  int n_dec = w.meta[0];
+  for (;;) {
+    // best evaluated entry whose target is still empty (frontier_get + :297-298)
+    int best = -1;
+    uint32_t bu = 0xffffffffu;
+    bool odd = false;                      // NaN key: leave the integer fast path
+    for (int i = lane; i < n_pend; i += 32) {
+      const int end = w.p_end[i];
+      if (end < 0 || w.data[3 * end + 2] > 0.0f) continue;
+      const float key = w.p_key[i];
+      if (key != key) odd = true;
+      const uint32_t u = float_orderable(key);
+      if (best < 0 || u < bu || (u == bu && pending_less(w, i, best, p.greedy))) { best = i; bu = u; }
+    }
+    const unsigned have = __ballot_sync(full, best >= 0);
+    if (have == 0u) break;
+    if (!__any_sync(full, odd)) {
+      // primary key by one integer reduction; full tuple order only among exact ties
+      const uint32_t m = __reduce_min_sync(full, best >= 0 ? bu : 0xffffffffu);
+      unsigned tie = __ballot_sync(full, best >= 0 && bu == m);
+      int win = __shfl_sync(full, best, __ffs(tie) - 1);
+      for (tie &= tie - 1u; tie; tie &= tie - 1u) {
+        const int o = __shfl_sync(full, best, __ffs(tie) - 1);
+        if (pending_less(w, o, win, p.greedy)) win = o;
+      }
+      best = win;
+    } else {
+#pragma unroll 1
+      for (int off = 16; off > 0; off >>= 1) {
+        int o = __shfl_xor_sync(full, best, off);
+        if (o >= 0 && (best < 0 || pending_less(w, o, best, p.greedy))) best = o;
+      }
+    }
+    const int end = w.p_end[best];
+    __syncwarp();
+    if (lane == 0) {
+      w.data[3 * end] = w.p_x[best]; w.data[3 * end + 1] = w.p_y[best];               // :300-302
+      w.data[3 * end + 2] = w.p_v[best];
+      w.js[end] = w.p_s[best];
+      w.dec[2 * n_dec] = w.p_start[best]; w.dec[2 * n_dec + 1] = end;                 // :303-304
+      w.p_end[best] = -1;
+    }
+    n_dec++;
+    __syncwarp();
+    n_pend = queue_and_evaluate(w, g, cscale, cf, end, n_pend, reverse_match, p);     // :305
+  }
+  if (lane == 0) w.meta[0] = n_dec;
+  __syncwarp();
+}
+
 // Phase timing for tuning (build with PP_EXTRA_NVCC=-DPP_ASM_TIMING): thread 0
 // accumulates clock64 deltas per phase into g_asm_cycles; read them with
 // pp_debug_asm_cycles.  Compiled out otherwise.
+// slots: 0 setup, 1 seed search, 2 wave pick, 3 wave grow, 5 store, 6 occupancy update, 7 nms tail
 #ifdef PP_ASM_TIMING
 __device__ unsigned long long g_asm_cycles[8];
 #define PP_TICK(slot)                                                              \
@@ -329,64 +502,35 @@ __device__ unsigned long long g_asm_cycles[8];
 #define PP_TICK(slot) do { } while (0)
 #endif
 
+struct ListShared {
+  int list_n[2 * PP_MAX_L];      // candidate-list lengths, [2l] forward / [2l+1] backward
+  int list_off[2 * PP_MAX_L];    // float offsets into the staged copy
+  int stage_total;               // entries over all lists
+};
+
 struct AsmShared {
 #ifdef PP_ASM_TIMING
   long long tick;
 #endif
-  float data[PP_MAX_F][3];
-  float js[PP_MAX_F];
-  // evaluated frontier entries (-score, (x, y, s, v), start, end), one array per member
-  float p_key[kMaxEdges], p_x[kMaxEdges], p_y[kMaxEdges], p_s[kMaxEdges], p_v[kMaxEdges];
-  int p_start[kMaxEdges], p_end[kMaxEdges];
-  int n_pend;
-  uint32_t queued[PP_MAX_F];
-  int new_start[kMaxEdges], new_k[kMaxEdges];
-  int n_new;
-  int dec[PP_MAX_F][2];
-  int n_dec;
-  int best;
+  ListShared ls;
   long long box[PP_MAX_F][4];
   int box_valid[PP_MAX_F];
-  int found;
   int warp_min[kAsmWarps];
-  struct Flood { float key, sx, sy, sv, s; int end; } ff[4 * PP_MAX_L];
+  // the wave: seeds whose poses the warps have grown (pick k lives in warp k's state)
+  int n_pick;
+  int pick_seed[kAsmWarps];
+  int pick_f[kAsmWarps];
+  int pick_box[kAsmWarps][4];
   // heavy mode (more than kHeavySeeds seeds): seeds are indexed by (field, band of occupancy rows)
   int occ_bin[PP_MAX_F * kOccBands];   // end offset of bin (field, band) in the field-major seed order
   int occ_all[PP_MAX_F];               // Occupancy.set boxes that cover the whole map, per field
-  int list_n[2 * PP_MAX_L];      // candidate-list lengths, [2l] forward / [2l+1] backward
-  int list_off[2 * PP_MAX_L];    // float offsets into the staged copy
-  int stage_total;               // entries over all lists
-  int scratch[kAsmWarps][kScratch];
 };
-
-// Heap order of the reference's frontier.  Non-greedy: evaluated entries
-// (-score, (x, y, s, v), start, end).  Greedy (cifcaf.py:280-281): an entry is
-// applied the moment it is evaluated, so only the unevaluated keys
-// (-sqrt(v_start) [* confidence_scale], None, start, end) are ever compared;
-// `key` then holds that bound.
-__device__ __forceinline__ bool pending_less(const AsmShared &sh, int a, int b, int greedy) {
-  if (sh.p_key[a] != sh.p_key[b]) return sh.p_key[a] < sh.p_key[b];
-  if (!greedy) {
-    if (sh.p_x[a] != sh.p_x[b]) return sh.p_x[a] < sh.p_x[b];
-    if (sh.p_y[a] != sh.p_y[b]) return sh.p_y[a] < sh.p_y[b];
-    if (sh.p_s[a] != sh.p_s[b]) return sh.p_s[a] < sh.p_s[b];
-    if (sh.p_v[a] != sh.p_v[b]) return sh.p_v[a] < sh.p_v[b];
-  }
-  if (sh.p_start[a] != sh.p_start[b]) return sh.p_start[a] < sh.p_start[b];
-  return sh.p_end[a] < sh.p_end[b];
-}
-
-// ascending float order as ascending unsigned order (NaN excluded by the caller)
-__device__ __forceinline__ uint32_t float_orderable(float v) {
-  uint32_t b = __float_as_uint(v);
-  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
 
 // Load the list lengths of one image into shared memory and, when everything
 // fits into `stage_floats` of dynamic shared memory, copy the rows of all 2L
 // binned lists there with cp.async (all copies in flight at once).
 // CTA-collective.  Returns the CafLists the growth code reads through.
-__device__ CafLists load_lists(AsmShared &sh, const float *rows, const int *start, BinGeo geo,
+__device__ CafLists load_lists(ListShared &sh, const float *rows, const int *start, BinGeo geo,
                                const int *nfwd, const int *nbwd, int L, int cap, float *stage,
                                int stage_floats) {
   const int tid = threadIdx.x;
@@ -416,149 +560,99 @@ __device__ CafLists load_lists(AsmShared &sh, const float *rows, const int *star
   return cf;
 }
 
-// add_to_frontier (cifcaf.py:251-263), run by one thread.
-__device__ void queue_edges(AsmShared &sh, const Graph &g, int start) {
-  for (int k = 0; k < g.deg[start]; k++) {
-    int end = g.nb_end[start][k];
-    if (sh.data[end][2] > 0.0f) continue;
-    if (sh.queued[start] & (1u << end)) continue;
-    sh.queued[start] |= 1u << end;
-    sh.new_start[sh.n_new] = start;
-    sh.new_k[sh.n_new] = k;
-    sh.n_new++;
+// Everything the seed loop of one image works on.
+struct SeedCtx {
+  const float *seeds;
+  int n_seeds;
+  uint8_t *occ;
+  int2 *rec;
+  bool heavy;
+  int bshift;
+  long long ow, oh;
+};
+
+// Occupancy.get of seed i (score order) right now
+__device__ __forceinline__ bool seed_free(const AsmShared &sh, const SeedCtx &c, int i) {
+  if (!c.heavy) return c.occ[i] == 0;
+  const int r = c.rec[i].x;
+  return ((c.occ[r & 0xffffff] + sh.occ_all[r >> 24]) & 255) == 0;
+}
+
+// field and occupancy cell of seed i
+__device__ __forceinline__ void seed_cell(const SeedCtx &c, int i, int *f, int *cx, int *cy) {
+  if (!c.heavy) {
+    const int2 r = c.rec[i];
+    *f = r.y >> 24; *cx = r.x; *cy = r.y & 0xffffff;
+  } else {
+    const int r = c.rec[i].x;
+    const int cell = c.rec[r & 0xffffff].y;
+    *f = r >> 24; *cx = cell & 0xffff; *cy = (unsigned)cell >> 16;
   }
 }
 
-// the same for one start joint, by a whole warp (lane = neighbour slot); sets n_new
-__device__ __forceinline__ void queue_edges_warp(AsmShared &sh, const Graph &g, int start) {
+// Warp 0: the seeds of the next wave.  Pick 0 is `found` (free, next in the reference's order); the
+// others are the next free seeds, in order, that lie outside the Occupancy.set boxes the earlier
+// picks' own joints are certain to set if those picks are committed (occupancy.py:31-39 on the
+// seed's (x, y, scale)).  Whatever is picked only decides which poses are grown ahead of time.
+__device__ void pick_wave(AsmShared &sh, const SeedCtx &c, int found) {
   const int lane = lane_id();
-  bool ok = false;
-  int end = 0;
-  if (lane < g.deg[start]) {
-    end = g.nb_end[start][lane];
-    ok = !(sh.data[end][2] > 0.0f) && !(sh.queued[start] & (1u << end));
-  }
-  const unsigned m = __ballot_sync(0xffffffffu, ok);
-  const unsigned bits = __reduce_or_sync(0xffffffffu, ok ? (1u << end) : 0u);
-  if (ok) {
-    const int pos = __popc(m & ((1u << lane) - 1u));
-    sh.new_start[pos] = start;
-    sh.new_k[pos] = lane;
-  }
-  if (lane == 0) {
-    sh.queued[start] |= bits;
-    sh.n_new = __popc(m);
-  }
-}
-
-// _grow (cifcaf.py:247-307) in its eager form; CTA-collective.
-__device__ void grow(AsmShared &sh, const Graph &g, const CScale &cscale, const CafLists &cf,
-                     bool reverse_match, const pp_params &p) {
-  const int warp = warp_id(), lane = lane_id();
   const unsigned full = 0xffffffffu;
-  if (threadIdx.x == 0) {
-    sh.n_pend = 0;
-    sh.n_new = 0;
-    for (int j = 0; j < g.F; j++) sh.queued[j] = 0u;
-    for (int j = 0; j < g.F; j++) {                               // :288-291
-      if (sh.data[j][2] == 0.0f) continue;
-      queue_edges(sh, g, j);
+  int n_pick = 0;
+  auto add = [&](int i) {          // one lane
+    const float *sd = c.seeds + (size_t)i * 5;
+    long long bx[4];
+    occupancy_box(__ldg(sd + 2), __ldg(sd + 3), __ldg(sd + 4), c.ow, c.oh, bx);
+    sh.pick_seed[n_pick] = i;
+    sh.pick_f[n_pick] = (int)__ldg(sd + 1);
+    for (int q = 0; q < 4; q++) sh.pick_box[n_pick][q] = (int)bx[q];
+  };
+  if (lane == 0) add(found);
+  n_pick = 1;
+  __syncwarp();
+  const int last = min(c.n_seeds, found + 1 + kPickScan);
+  for (int base = found + 1; base < last && n_pick < kAsmWarps; base += 32) {
+    const int i = base + lane;
+    bool cand = i < last && seed_free(sh, c, i);
+    int f = 0, cx = 0, cy = 0;
+    if (cand) {
+      seed_cell(c, i, &f, &cx, &cy);
+      for (int k = 0; k < n_pick && cand; k++)
+        if (sh.pick_f[k] == f && cx >= sh.pick_box[k][0] && cx < sh.pick_box[k][1] &&
+            cy >= sh.pick_box[k][2] && cy < sh.pick_box[k][3])
+          cand = false;
+    }
+    unsigned m = __ballot_sync(full, cand);
+    while (m && n_pick < kAsmWarps) {
+      const int l = __ffs(m) - 1;
+      if (lane == l) add(i);
+      __syncwarp();
+      const int k = n_pick++;
+      if (cand && lane > l && sh.pick_f[k] == f && cx >= sh.pick_box[k][0] && cx < sh.pick_box[k][1] &&
+          cy >= sh.pick_box[k][2] && cy < sh.pick_box[k][3])
+        cand = false;
+      m = __ballot_sync(full, cand) & ~((2u << l) - 1u);
     }
   }
-  __syncthreads();
-  PP_TICK(7);
-  for (;;) {
-    // evaluate the newly queued edges, one warp each
-    const int n_new = sh.n_new, base = sh.n_pend;
-    for (int e = warp; e < n_new; e += kAsmWarps) {
-      int start = sh.new_start[e], k = sh.new_k[e];
-      Xysv r = warp_connection_value(sh.data, sh.js, g, cf, start, k, reverse_match,
-                                     p.keypoint_threshold, p.connection_method, p.exp_mode,
-                                     sh.scratch[warp]);
-      if (lane == 0) {
-        const int q = base + e;
-        float score = r.v;
-        if (p.greedy) score = __fsqrt_rn(sh.data[start][2]);                       // :258 (the bound)
-        if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);   // :259-260, :282-284
-        sh.p_key[q] = -score; sh.p_x[q] = r.x; sh.p_y[q] = r.y; sh.p_s[q] = r.s; sh.p_v[q] = r.v;
-        sh.p_start[q] = start;
-        sh.p_end[q] = (r.v == 0.0f) ? -1 : g.nb_end[start][k];                     // :277-278
-      }
-    }
-    __syncthreads();
-    PP_TICK(3);
-    if (warp == 0) {
-      // best evaluated entry whose target is still empty (frontier_get + :297-298)
-      const int n_pend = base + n_new;
-      int best = -1;
-      uint32_t bu = 0xffffffffu;
-      bool odd = false;                      // NaN key: leave the integer fast path
-      for (int i = lane; i < n_pend; i += 32) {
-        const int end = sh.p_end[i];
-        if (end < 0 || sh.data[end][2] > 0.0f) continue;
-        const float key = sh.p_key[i];
-        if (key != key) odd = true;
-        const uint32_t u = float_orderable(key);
-        if (best < 0 || u < bu || (u == bu && pending_less(sh, i, best, p.greedy))) { best = i; bu = u; }
-      }
-      const unsigned have = __ballot_sync(full, best >= 0);
-      if (have == 0u) {
-        best = -1;
-      } else if (!__any_sync(full, odd)) {
-        // primary key by one integer reduction; full tuple order only among exact ties
-        const uint32_t m = __reduce_min_sync(full, best >= 0 ? bu : 0xffffffffu);
-        unsigned tie = __ballot_sync(full, best >= 0 && bu == m);
-        int w = __shfl_sync(full, best, __ffs(tie) - 1);
-        for (tie &= tie - 1u; tie; tie &= tie - 1u) {
-          const int o = __shfl_sync(full, best, __ffs(tie) - 1);
-          if (pending_less(sh, o, w, p.greedy)) w = o;
-        }
-        best = w;
-      } else {
-#pragma unroll 1
-        for (int off = 16; off > 0; off >>= 1) {
-          int o = __shfl_xor_sync(full, best, off);
-          if (o >= 0 && (best < 0 || pending_less(sh, o, best, p.greedy))) best = o;
-        }
-      }
-      if (lane == 0) {
-        sh.n_pend = n_pend;
-        sh.n_new = 0;
-        sh.best = best;
-      }
-      if (best >= 0) {
-        const int end = sh.p_end[best];
-        if (lane == 0) {
-          sh.data[end][0] = sh.p_x[best]; sh.data[end][1] = sh.p_y[best];          // :300-302
-          sh.data[end][2] = sh.p_v[best];
-          sh.js[end] = sh.p_s[best];
-          sh.dec[sh.n_dec][0] = sh.p_start[best]; sh.dec[sh.n_dec][1] = end;       // :303-304
-          sh.n_dec++;
-          sh.p_end[best] = -1;
-        }
-        __syncwarp();
-        queue_edges_warp(sh, g, end);                                              // :305
-      }
-    }
-    __syncthreads();
-    PP_TICK(4);
-    if (sh.best < 0) break;
-  }
+  if (lane == 0) sh.n_pick = n_pick;
 }
 
 __global__ void __launch_bounds__(kAsmThreads)
-assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
+assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
   __shared__ AsmShared sh;
   const int b = blockIdx.x;
   const int F = g.F;
+  const int warp = warp_id(), lane = lane_id();
   const float *seeds = a.seeds + (size_t)b * a.seed_cap * 5;
   const int n_seeds = min(a.n_seeds[b], a.seed_cap);
   uint8_t *occ = a.occ_cnt + (size_t)b * a.seed_cap;
-  extern __shared__ __align__(16) float stage_buf[];
+  extern __shared__ __align__(16) float dyn_smem[];
+  const int gw = grow_words(F, n_edges);
+  const GrowView w = grow_view(dyn_smem + (size_t)warp * gw, F, n_edges);
+  float *stage_buf = dyn_smem + (size_t)kAsmWarps * gw;
 #ifdef PP_ASM_TIMING
   if (threadIdx.x == 0) sh.tick = clock64();
 #endif
-  const CafLists cf = load_lists(sh, a.rows + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
+  const CafLists cf = load_lists(sh.ls, a.rows + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
                                  a.start + (size_t)b * a.L * 2 * (a.geo.nb + 1), a.geo,
                                  a.nfwd + (size_t)b * a.L, a.nbwd + (size_t)b * a.L, a.L, a.caf_cap,
                                  stage_buf, a.stage_floats);
@@ -594,16 +688,16 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
       atomicAdd(&sh.occ_bin[(int)__ldg(sd + 1) * kOccBands + (int)(cy >> bshift)], 1);
     }
     __syncthreads();
-    if (warp_id() == 0) {                       // exclusive scan of the PP_MAX_F * kOccBands counts
+    if (warp == 0) {                            // exclusive scan of the PP_MAX_F * kOccBands counts
       constexpr int kPer = PP_MAX_F * kOccBands / 32;
-      const int first = lane_id() * kPer;
+      const int first = lane * kPer;
       int sum = 0;
       for (int q = 0; q < kPer; q++) sum += sh.occ_bin[first + q];
       int incl = sum;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         const int v = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane_id() >= d) incl += v;
+        if (lane >= d) incl += v;
       }
       int run = incl - sum;
       for (int q = 0; q < kPer; q++) {
@@ -624,78 +718,27 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
       occ[pos] = 0;
     }
   }
+  if (threadIdx.x == 0) sh.n_pick = 0;
   __syncthreads();
+  const SeedCtx ctx = {seeds, n_seeds, occ, rec, heavy, bshift, ow, oh};
 
-  // initial_annotations (cifcaf.py:95-98) are grown first, then the seeds
-  const int n_init = a.init_n ? min(a.init_n[b], a.init_cap) : 0;
-  int n_ann = 0, cursor = 0, ia = 0;
+  int n_ann = 0, cursor = 0;
+  bool overflow = false;
   PP_TICK(0);
-  for (;;) {
-    const bool from_init = ia < n_init;
-    // ---- next seed whose cell is free (cifcaf.py:100-102) -------------------
-    int found = -1;
-    for (int base = cursor; !from_init && base < n_seeds; base += blockDim.x) {
-      int i = base + threadIdx.x;
-      bool hit = false;
-      if (i < n_seeds) {
-        if (!heavy) {
-          hit = occ[i] == 0;
-        } else {
-          const int r = rec[i].x;
-          hit = ((occ[r & 0xffffff] + sh.occ_all[r >> 24]) & 255) == 0;
-        }
-      }
-      unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (lane_id() == 0) sh.warp_min[warp_id()] = m ? (base + warp_id() * 32 + __ffs(m) - 1) : -1;
-      __syncthreads();
-      for (int w = 0; w < kAsmWarps; w++)
-        if (sh.warp_min[w] >= 0) { found = sh.warp_min[w]; break; }
-      __syncthreads();
-      if (found >= 0) break;
-    }
-    PP_TICK(1);
-    if (!from_init) {
-      if (found < 0) break;
-      cursor = found + 1;
-    }
-    if (n_ann >= a.ann_cap) {
-      if (threadIdx.x == 0) atomicOr(&a.status[b], PP_STATUS_ANN_OVERFLOW);
-      break;
-    }
-    // ---- new annotation from the seed (:104-105), or the next initial annotation ----
-    if (from_init) {
-      const float *idata = a.init_data + ((size_t)b * a.init_cap + ia) * F * 3;
-      const float *iscales = a.init_scales + ((size_t)b * a.init_cap + ia) * F;
-      for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = idata[i];
-      for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = iscales[i];
-      if (threadIdx.x == 0) sh.n_dec = 0;
-      ia++;
-    } else {
-      for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = 0.0f;
-      for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = 0.0f;
-    }
-    __syncthreads();
-    if (!from_init && threadIdx.x == 0) {
-      const float *sd = seeds + (size_t)found * 5;
-      int f = (int)sd[1];
-      sh.data[f][0] = sd[2]; sh.data[f][1] = sd[3]; sh.data[f][2] = sd[0];
-      sh.js[f] = sd[4];
-      sh.n_dec = 0;
-    }
-    __syncthreads();
-    PP_TICK(2);
-    grow(sh, g, cscale, cf, true, p);                             // :106
-    // ---- store + mark_occupied (:87-93, :107-108) -------------------------
-    for (int i = threadIdx.x; i < F * 3; i += blockDim.x)
-      pre_data[(size_t)n_ann * F * 3 + i] = (&sh.data[0][0])[i];
+
+  // store the pose grown in warp k's state + mark_occupied (:87-93, :107-108); CTA-collective
+  auto commit = [&](int k) {
+    const GrowView v = grow_view(dyn_smem + (size_t)k * gw, F, n_edges);
+    const int n_dec = v.meta[0];
+    for (int i = threadIdx.x; i < F * 3; i += blockDim.x) pre_data[(size_t)n_ann * F * 3 + i] = v.data[i];
     for (int i = threadIdx.x; i < F; i += blockDim.x) {
-      pre_scales[(size_t)n_ann * F + i] = sh.js[i];
+      pre_scales[(size_t)n_ann * F + i] = v.js[i];
       if (pre_order) {
-        pre_order[((size_t)n_ann * F + i) * 2] = i < sh.n_dec ? sh.dec[i][0] : -1;
-        pre_order[((size_t)n_ann * F + i) * 2 + 1] = i < sh.n_dec ? sh.dec[i][1] : -1;
+        pre_order[((size_t)n_ann * F + i) * 2] = i < n_dec ? v.dec[2 * i] : -1;
+        pre_order[((size_t)n_ann * F + i) * 2 + 1] = i < n_dec ? v.dec[2 * i + 1] : -1;
       }
-      sh.box_valid[i] = sh.data[i][2] != 0.0f;
-      if (sh.box_valid[i]) occupancy_box(sh.data[i][0], sh.data[i][1], sh.js[i], ow, oh, sh.box[i]);
+      sh.box_valid[i] = v.data[3 * i + 2] != 0.0f;
+      if (sh.box_valid[i]) occupancy_box(v.data[3 * i], v.data[3 * i + 1], v.js[i], ow, oh, sh.box[i]);
     }
     n_ann++;
     __syncthreads();
@@ -703,17 +746,17 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
     if (heavy) {
       // one warp per joint: a box that covers the whole map bumps the field's counter, any other box
       // visits the seeds of its field in the row bands it overlaps
-      for (int j = warp_id(); j < F; j += kAsmWarps) {
+      for (int j = warp; j < F; j += kAsmWarps) {
         if (!sh.box_valid[j]) continue;
         const long long minx = sh.box[j][0], maxx = sh.box[j][1], miny = sh.box[j][2], maxy = sh.box[j][3];
         if (minx >= maxx || miny >= maxy) continue;        // box outside the map: empty numpy slice
         if (minx <= 0 && maxx >= ow && miny <= 0 && maxy >= oh) {
-          if (lane_id() == 0) sh.occ_all[j]++;
+          if (lane == 0) sh.occ_all[j]++;
           continue;
         }
         const int b0 = j * kOccBands + (int)(miny >> bshift), b1 = j * kOccBands + (int)((maxy - 1) >> bshift);
         const int k0 = b0 == 0 ? 0 : sh.occ_bin[b0 - 1], k1 = sh.occ_bin[b1];
-        for (int kk = k0 + lane_id(); kk < k1; kk += 4 * 32) {
+        for (int kk = k0 + lane; kk < k1; kk += 4 * 32) {
           int c[4];
 #pragma unroll
           for (int q = 0; q < 4; q++) c[q] = kk + q * 32 < k1 ? rec[kk + q * 32].y : -1;
@@ -725,43 +768,124 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p) {
           }
         }
       }
-      __syncthreads();
-      PP_TICK(6);
-      continue;
-    }
-    // Occupancy.set of the pose's joints, seen from the seeds: four seeds per thread and
-    // trip so that four loads are in flight
-    for (int i0 = cursor + threadIdx.x; i0 < n_seeds; i0 += 4 * blockDim.x) {
-      int2 r[4];
-      uint8_t c[4];
+    } else {
+      // Occupancy.set of the pose's joints, seen from the seeds the loop has not passed yet: four
+      // seeds per thread and trip so that four loads are in flight
+      for (int i0 = cursor + threadIdx.x; i0 < n_seeds; i0 += 4 * blockDim.x) {
+        int2 r[4];
+        uint8_t c[4];
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const int i = i0 + j * blockDim.x;
-        r[j] = i < n_seeds ? rec[i] : make_int2(0, 0);
-        c[j] = i < n_seeds ? occ[i] : 0;
-      }
+        for (int j = 0; j < 4; j++) {
+          const int i = i0 + j * blockDim.x;
+          r[j] = i < n_seeds ? rec[i] : make_int2(0, 0);
+          c[j] = i < n_seeds ? occ[i] : 0;
+        }
 #pragma unroll
-      for (int j = 0; j < 4; j++) {
-        const int i = i0 + j * blockDim.x;
-        if (i >= n_seeds) continue;
-        const int f = r[j].y >> 24;
-        if (!sh.box_valid[f]) continue;
-        const long long cx = r[j].x, cy = r[j].y & 0xffffff;
-        if (cx >= sh.box[f][0] && cx < sh.box[f][1] && cy >= sh.box[f][2] && cy < sh.box[f][3])
-          occ[i] = (uint8_t)(c[j] + 1);                           // uint8 += 1 wraps (utils.py:66)
+        for (int j = 0; j < 4; j++) {
+          const int i = i0 + j * blockDim.x;
+          if (i >= n_seeds) continue;
+          const int f = r[j].y >> 24;
+          if (!sh.box_valid[f]) continue;
+          const long long cx = r[j].x, cy = r[j].y & 0xffffff;
+          if (cx >= sh.box[f][0] && cx < sh.box[f][1] && cy >= sh.box[f][2] && cy < sh.box[f][3])
+            occ[i] = (uint8_t)(c[j] + 1);                           // uint8 += 1 wraps (utils.py:66)
+        }
       }
     }
     __syncthreads();
     PP_TICK(6);
+  };
+
+  // ---- initial_annotations (cifcaf.py:95-98): grown and marked before the seeds, kAsmWarps at a time
+  const int n_init = a.init_n ? min(a.init_n[b], a.init_cap) : 0;
+  for (int base = 0; base < n_init && !overflow; base += kAsmWarps) {
+    const int n = min(kAsmWarps, n_init - base);
+    if (warp < n) {
+      const float *idata = a.init_data + ((size_t)b * a.init_cap + base + warp) * F * 3;
+      const float *iscales = a.init_scales + ((size_t)b * a.init_cap + base + warp) * F;
+      for (int i = lane; i < F * 3; i += 32) w.data[i] = idata[i];
+      for (int i = lane; i < F; i += 32) w.js[i] = iscales[i];
+      if (lane == 0) w.meta[0] = 0;
+      __syncwarp();
+      warp_grow(w, g, cscale, cf, true, p);
+    }
+    __syncthreads();
+    PP_TICK(3);
+    for (int k = 0; k < n; k++) {
+      if (n_ann >= a.ann_cap) { overflow = true; break; }
+      commit(k);
+    }
   }
+
+  // ---- the seed loop (cifcaf.py:100-108)
+  int n_pick = 0;
+  while (!overflow) {
+    // next seed whose cell is free (:100-102)
+    int found = -1;
+    for (int base = cursor; base < n_seeds; base += blockDim.x) {
+      const int i = base + threadIdx.x;
+      const bool hit = i < n_seeds && seed_free(sh, ctx, i);
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (lane == 0) sh.warp_min[warp] = m ? (base + warp * 32 + __ffs(m) - 1) : -1;
+      __syncthreads();
+      for (int q = 0; q < kAsmWarps; q++)
+        if (sh.warp_min[q] >= 0) { found = sh.warp_min[q]; break; }
+      __syncthreads();
+      if (found >= 0) break;
+    }
+    PP_TICK(1);
+    if (found < 0) break;
+    cursor = found + 1;
+    if (n_ann >= a.ann_cap) { overflow = true; break; }
+    // is its pose at hand?
+    int k = -1;
+    for (int q = 0; q < n_pick; q++)
+      if (sh.pick_seed[q] == found) k = q;
+    if (k < 0) {
+      // ---- a new wave: `found` and the free seeds after it, one pose per warp
+      if (warp == 0) pick_wave(sh, ctx, found);
+      __syncthreads();
+      PP_TICK(2);
+      n_pick = sh.n_pick;
+      if (warp < n_pick) {
+        // new annotation from the seed (:104-105)
+        const float *sd = seeds + (size_t)sh.pick_seed[warp] * 5;
+        for (int i = lane; i < F * 3; i += 32) w.data[i] = 0.0f;
+        for (int i = lane; i < F; i += 32) w.js[i] = 0.0f;
+        __syncwarp();
+        if (lane == 0) {
+          const int f = (int)sd[1];
+          w.data[3 * f] = sd[2]; w.data[3 * f + 1] = sd[3]; w.data[3 * f + 2] = sd[0];
+          w.js[f] = sd[4];
+          w.meta[0] = 0;
+        }
+        __syncwarp();
+        warp_grow(w, g, cscale, cf, true, p);                       // :106
+      }
+      __syncthreads();
+      PP_TICK(3);
+      k = 0;
+    }
+    commit(k);
+  }
+  if (overflow && threadIdx.x == 0) atomicOr(&a.status[b], PP_STATUS_ANN_OVERFLOW);
   if (threadIdx.x == 0) a.n_pre[b] = n_ann;
+  if (a.fuse_nms) {
+    // nms.Keypoints.annotations (nms.py:17-57) on the poses this CTA just wrote
+    __threadfence_block();
+    __syncthreads();
+    nms_image(a.nms, b);
+    PP_TICK(7);
+  }
 }
 
 // ---------------------------------------------------------------------------
 // complete_annotations (cifcaf.py:333-351) + _flood_fill (:309-331).
-// Annotations are independent here, so the grid is (annotation, image).
+// Annotations are independent here: one warp each, grid (annotations / kAsmWarps, image).
 
-__device__ __forceinline__ bool flood_less(const AsmShared::Flood &a, const AsmShared::Flood &b) {
+struct Flood { float key, sx, sy, sv, s; int end; };
+
+__device__ __forceinline__ bool flood_less(const Flood &a, const Flood &b) {
   // Python tuple order of (-v, end_i, [x, y, v], s)
   if (a.key != b.key) return a.key < b.key;
   if (a.end != b.end) return a.end < b.end;
@@ -772,94 +896,111 @@ __device__ __forceinline__ bool flood_less(const AsmShared::Flood &a, const AsmS
 }
 
 // one thread; `prio` is the closure quirk of cifcaf.py:317,325 (see oracle flood_fill)
-__device__ void flood_add(AsmShared &sh, const Graph &g, int &n, int start, float prio) {
+__device__ void flood_add(const GrowView &w, Flood *ff, int ff_cap, const Graph &g, int &n, int start,
+                          float prio) {
   for (int k = 0; k < g.deg[start]; k++) {
     int end = g.nb_end[start][k];
-    if (sh.data[end][2] > 0.0f) continue;
-    if (n >= 4 * PP_MAX_L) return;     // cannot happen: <= 2 pushes per directed edge
-    AsmShared::Flood &e = sh.ff[n++];
+    if (w.data[3 * end + 2] > 0.0f) continue;
+    if (n >= ff_cap) return;     // cannot happen: <= 2 pushes per directed edge
+    Flood &e = ff[n++];
     e.key = -prio; e.end = end;
-    e.sx = sh.data[start][0]; e.sy = sh.data[start][1]; e.sv = sh.data[start][2];
-    e.s = sh.js[start];
+    e.sx = w.data[3 * start]; e.sy = w.data[3 * start + 1]; e.sv = w.data[3 * start + 2];
+    e.s = w.js[start];
   }
 }
 
-__device__ void flood_fill(AsmShared &sh, const Graph &g) {
+__device__ void flood_fill(const GrowView &w, Flood *ff, int ff_cap, const Graph &g) {
   int n = 0;
   for (int j = 0; j < g.F; j++) {
-    if (sh.data[j][2] == 0.0f) continue;
-    flood_add(sh, g, n, j, sh.data[j][2]);
+    if (w.data[3 * j + 2] == 0.0f) continue;
+    flood_add(w, ff, ff_cap, g, n, j, w.data[3 * j + 2]);
   }
   while (n > 0) {
     int m = 0;
     for (int i = 1; i < n; i++)
-      if (flood_less(sh.ff[i], sh.ff[m])) m = i;
-    AsmShared::Flood e = sh.ff[m];
-    sh.ff[m] = sh.ff[--n];
-    if (sh.data[e.end][2] > 0.0f) continue;
-    sh.data[e.end][0] = e.sx; sh.data[e.end][1] = e.sy;
-    sh.data[e.end][2] = 0.00001f;
-    sh.js[e.end] = e.s;
-    flood_add(sh, g, n, e.end, e.sv);
+      if (flood_less(ff[i], ff[m])) m = i;
+    Flood e = ff[m];
+    ff[m] = ff[--n];
+    if (w.data[3 * e.end + 2] > 0.0f) continue;
+    w.data[3 * e.end] = e.sx; w.data[3 * e.end + 1] = e.sy;
+    w.data[3 * e.end + 2] = 0.00001f;
+    w.js[e.end] = e.s;
+    flood_add(w, ff, ff_cap, g, n, e.end, e.sv);
   }
 }
+
+__host__ __device__ inline int flood_words(int n_edges) { return 2 * n_edges * (int)(sizeof(Flood) / 4); }
 
 __global__ void __launch_bounds__(kAsmThreads)
 complete_kernel(AsmArgs a, const float *__restrict__ rows2, const int *__restrict__ start2,
                 const int *__restrict__ nfwd2, const int *__restrict__ nbwd2,
                 float *__restrict__ cmp_data, float *__restrict__ cmp_scales, Graph g, CScale cscale,
-                pp_params p) {
-  __shared__ AsmShared sh;
-  __shared__ int unfilled[PP_MAX_F];
-  const int b = blockIdx.y, an = blockIdx.x;
+                pp_params p, int n_edges) {
+  __shared__ ListShared ls;
+  extern __shared__ __align__(16) float dyn_smem[];
+  const int b = blockIdx.y, an = blockIdx.x * kAsmWarps + warp_id();
+  const int lane = lane_id();
   const int F = g.F;
-  if (an >= min(a.n_pre[b], a.ann_cap)) return;
   // the score_th = 1e-4 lists hold nearly every cell: read them in place
-  const CafLists cf = load_lists(sh, rows2 + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
+  const CafLists cf = load_lists(ls, rows2 + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
                                  start2 + (size_t)b * a.L * 2 * (a.geo.nb + 1), a.geo,
                                  nfwd2 + (size_t)b * a.L, nbwd2 + (size_t)b * a.L, a.L, a.caf_cap,
                                  nullptr, 0);
+  if (an >= min(a.n_pre[b], a.ann_cap)) return;       // no CTA barrier below
+  const int per_warp = grow_words(F, n_edges) + flood_words(n_edges);
+  float *mine = dyn_smem + (size_t)warp_id() * per_warp;
+  const GrowView w = grow_view(mine, F, n_edges);
+  Flood *ff = reinterpret_cast<Flood *>(mine + grow_words(F, n_edges));
   float *pre_data = a.pre_data + ((size_t)b * a.ann_cap + an) * F * 3;
   float *pre_scales = a.pre_scales + ((size_t)b * a.ann_cap + an) * F;
   int *pre_order = a.pre_order + ((size_t)b * a.ann_cap + an) * F * 2;
-  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) (&sh.data[0][0])[i] = pre_data[i];
-  for (int i = threadIdx.x; i < F; i += blockDim.x) sh.js[i] = pre_scales[i];
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int n1 = 0;
+  for (int i = lane; i < F * 3; i += 32) w.data[i] = pre_data[i];
+  for (int i = lane; i < F; i += 32) w.js[i] = pre_scales[i];
+  __syncwarp();
+  int n1 = 0;                                          // decoding steps of the first _grow
+  if (lane == 0) {
     while (n1 < F && pre_order[2 * n1] >= 0) {
-      sh.dec[n1][0] = pre_order[2 * n1]; sh.dec[n1][1] = pre_order[2 * n1 + 1];
+      w.dec[2 * n1] = pre_order[2 * n1]; w.dec[2 * n1 + 1] = pre_order[2 * n1 + 1];
       n1++;
     }
-    sh.n_dec = n1;
-    sh.found = n1;     // decoding steps of the first _grow
+    w.meta[0] = n1;
   }
-  for (int i = threadIdx.x; i < F; i += blockDim.x) unfilled[i] = sh.data[i][2] == 0.0f;   // :340
-  __syncthreads();
-  grow(sh, g, cscale, cf, false, p);                                // :341
+  n1 = __shfl_sync(0xffffffffu, n1, 0);
+  const unsigned unfilled = __ballot_sync(0xffffffffu, lane < F && w.data[3 * lane + 2] == 0.0f);   // :340
+  __syncwarp();
+  warp_grow(w, g, cscale, cf, false, p);                            // :341
+  const int n_dec = w.meta[0];
   // as-grown state (scores not yet clamped) for the host's decoding_order replay
-  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) pre_data[i] = (&sh.data[0][0])[i];
-  for (int i = threadIdx.x; i < F; i += blockDim.x) {
-    pre_scales[i] = sh.js[i];
-    int s0 = i < sh.n_dec ? sh.dec[i][0] : -1, s1 = i < sh.n_dec ? sh.dec[i][1] : -1;
-    if (i == F - 1 && sh.n_dec < F) { s0 = -2; s1 = sh.found; }   // marker: steps of the first grow
+  for (int i = lane; i < F * 3; i += 32) pre_data[i] = w.data[i];
+  for (int i = lane; i < F; i += 32) {
+    pre_scales[i] = w.js[i];
+    int s0 = i < n_dec ? w.dec[2 * i] : -1, s1 = i < n_dec ? w.dec[2 * i + 1] : -1;
+    if (i == F - 1 && n_dec < F) { s0 = -2; s1 = n1; }   // marker: steps of the first grow
     pre_order[2 * i] = s0; pre_order[2 * i + 1] = s1;
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
+  __syncwarp();
+  if (lane == 0) {
     bool any_empty = false;
     for (int j = 0; j < F; j++) {
-      if (unfilled[j] && sh.data[j][2] > 0.0f)                     // :342-344
-        sh.data[j][2] = 0.001f < sh.data[j][2] ? 0.001f : sh.data[j][2];
-      if (sh.data[j][2] == 0.0f) any_empty = true;
+      if (((unfilled >> j) & 1u) && w.data[3 * j + 2] > 0.0f)        // :342-344
+        w.data[3 * j + 2] = 0.001f < w.data[3 * j + 2] ? 0.001f : w.data[3 * j + 2];
+      if (w.data[3 * j + 2] == 0.0f) any_empty = true;
     }
-    if (any_empty) flood_fill(sh, g);                              // :347-348
+    if (any_empty) flood_fill(w, ff, 2 * n_edges, g);                // :347-348
   }
-  __syncthreads();
+  __syncwarp();
   float *od = cmp_data + ((size_t)b * a.ann_cap + an) * F * 3;
   float *os = cmp_scales + ((size_t)b * a.ann_cap + an) * F;
-  for (int i = threadIdx.x; i < F * 3; i += blockDim.x) od[i] = (&sh.data[0][0])[i];
-  for (int i = threadIdx.x; i < F; i += blockDim.x) os[i] = sh.js[i];
+  for (int i = lane; i < F * 3; i += 32) od[i] = w.data[i];
+  for (int i = lane; i < F; i += 32) os[i] = w.js[i];
+}
+
+static CScale make_cscale(const pp_skeleton &sk) {
+  CScale cs;
+  memset(&cs, 0, sizeof cs);
+  cs.has = sk.has_confidence_scales;
+  for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  return cs;
 }
 
 int complete_launch(const AsmArgs &args, const float *rows2, const int *start2, const int *nfwd2,
@@ -868,15 +1009,30 @@ int complete_launch(const AsmArgs &args, const float *rows2, const int *start2, 
   Graph g;
   int rc = build_graph(sk, F, &g);
   if (rc) return rc;
-  CScale cs;
-  memset(&cs, 0, sizeof cs);
-  cs.has = sk.has_confidence_scales;
-  for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
-  dim3 grid(args.ann_cap, B);
-  complete_kernel<<<grid, kAsmThreads, 0, st>>>(args, rows2, start2, nfwd2, nbwd2, cmp_data, cmp_scales,
-                                               g, cs, p);
+  const CScale cs = make_cscale(sk);
+  const int n_edges = directed_edges(g);
+  const size_t dyn = (size_t)kAsmWarps * (grow_words(F, n_edges) + flood_words(n_edges)) * sizeof(float);
+  PP_CUDA_CHECK(cudaFuncSetAttribute(complete_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)dyn));
+  dim3 grid((args.ann_cap + kAsmWarps - 1) / kAsmWarps, B);
+  complete_kernel<<<grid, kAsmThreads, dyn, st>>>(args, rows2, start2, nfwd2, nbwd2, cmp_data, cmp_scales,
+                                                 g, cs, p, n_edges);
   PP_LAUNCH_CHECK("complete_kernel");
   return PP_OK;
+}
+
+// dynamic shared memory an assembly CTA may use at most (the SM's 227 KB minus the kernel's static
+// part and the 1 KB the system reserves per CTA)
+static int max_dynamic_smem() {
+  static int cached = 0;
+  if (cached == 0) {
+    cudaFuncAttributes at;
+    int v = 227 * 1024 - 1024 - 16 * 1024;
+    if (cudaFuncGetAttributes(&at, assemble_kernel) == cudaSuccess)
+      v = 227 * 1024 - 1024 - (int)at.sharedSizeBytes;
+    cached = v;
+  }
+  return cached;
 }
 
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
@@ -884,25 +1040,24 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
   Graph g;
   int rc = build_graph(sk, F, &g);
   if (rc) return rc;
-  CScale cs;
-  memset(&cs, 0, sizeof cs);
-  cs.has = sk.has_confidence_scales;
-  for (int l = 0; l < sk.L; l++) cs.v[l] = sk.confidence_scales[l];
+  const CScale cs = make_cscale(sk);
+  const int n_edges = directed_edges(g);
   AsmArgs a2 = args;
+  const int state_bytes = kAsmWarps * grow_words(F, n_edges) * (int)sizeof(float);
+  const int max_dyn = max_dynamic_smem();
+  if (state_bytes > max_dyn) return PP_ERR_ARG;
   // one image per SM and nothing else on the GPU: give the lists (almost) the whole shared memory;
   // with other batches in flight (pp_params.in_flight) leave room for their CTAs on the same SM
-  int stage_bytes = (B <= num_sms() && p.in_flight <= 1) ? kStageBytesSolo : kStageBytes;
-  a2.heavy_seeds = kHeavySeeds;
-  if (const char *e = getenv("PP_ASM_HEAVY_SEEDS")) a2.heavy_seeds = atoi(e);   // tests: force either mode
-  if (const char *e = getenv("PP_ASM_STAGE_KB")) {     // tuning experiments only
-    int kb = atoi(e);
-    if (kb >= 0 && kb * 1024 <= kStageBytesSolo) stage_bytes = kb * 1024;
-  }
+  int stage_bytes = (B <= num_sms() && p.in_flight <= 1) ? max_dyn - state_bytes : kStageBytes;
+  if (p.asm_stage_kb > 0) stage_bytes = p.asm_stage_kb * 1024;        // tuning knob
+  if (p.asm_stage_kb < 0) stage_bytes = 0;
+  if (stage_bytes > max_dyn - state_bytes) stage_bytes = max_dyn - state_bytes;
+  stage_bytes &= ~15;
+  a2.heavy_seeds = p.asm_heavy_seeds > 0 ? p.asm_heavy_seeds : (p.asm_heavy_seeds < 0 ? 0 : kHeavySeeds);
   a2.stage_floats = stage_bytes / (int)sizeof(float);
-  PP_CUDA_CHECK(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     kStageBytesSolo));
+  PP_CUDA_CHECK(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
   prof_mark(p.profile, kStAssemble, st);
-  assemble_kernel<<<B, kAsmThreads, stage_bytes, st>>>(a2, g, cs, p);
+  assemble_kernel<<<B, kAsmThreads, (size_t)state_bytes + stage_bytes, st>>>(a2, g, cs, p, n_edges);
   PP_LAUNCH_CHECK("assemble_kernel");
   return PP_OK;
 }

@@ -50,9 +50,8 @@ constexpr int kSplatBlock = kSplatThreads + 32; // + the producer warp
 constexpr int kChunk = 64;            // sources per mask chunk (one bit each)
 constexpr int kGroupCap = kSplatThreads;   // sources staged per ordered-filter block
 constexpr int kGroupStripsMax = 32;
-static int group_strips() {           // strips per CTA
-  if (const char *e = getenv("PP_CIFHR_GROUP")) { int g = atoi(e); if (g >= 1 && g <= kGroupStripsMax) return g; }
-  return 3;
+static int group_strips(const pp_params &p) {           // strips per CTA (pp_params.cifhr_group)
+  return (p.cifhr_group >= 1 && p.cifhr_group <= kGroupStripsMax) ? p.cifhr_group : 3;
 }
 constexpr int kMaxPatches = 192;      // patches per strip (hw <= 6136, see strip_rshift)
 constexpr int kWidePatches = 8;       // a source box spanning more patches than this makes its block "wide"
@@ -78,9 +77,8 @@ struct CifHrWs {
 };
 
 // rows per strip: the largest power of two <= 8 whose strip fits the smem budget
-static int strip_rshift(int hw) {
-  int r = 3;
-  if (const char *e = getenv("PP_CIFHR_RSHIFT")) r = atoi(e) & 3;   // tuning experiments only
+static int strip_rshift(int hw, int pref = 0) {    // pref: pp_params.cifhr_rshift (log2 rows + 1), 0 = 8 rows
+  int r = (pref >= 1 && pref <= 4) ? pref - 1 : 3;
   while (r > 0 && ((size_t)hw << r) * sizeof(float) > (size_t)kStripBytesMax - 32) r--;
   return r;
 }
@@ -100,7 +98,7 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   return n;
 }
 
-static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
+static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c, int rshift_pref = 0) {
   CifHrWs w;
   char *p = (char *)ws;
   size_t bf = (size_t)s.B * s.F;
@@ -113,7 +111,7 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c) {
   w.strip_cnt = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.busy_list = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.cursors = (int *)p;
-  w.rshift = strip_rshift(hr_w(s));
+  w.rshift = strip_rshift(hr_w(s), rshift_pref);
   w.nstrips = num_strips(hr_h(s), w.rshift);
   return w;
 }
@@ -665,7 +663,7 @@ CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c) {
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
                     int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest) {
-  CifHrWs w = carve(d_ws, s_hr, c);
+  CifHrWs w = carve(d_ws, s_hr, c, p.cifhr_rshift);
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
@@ -683,13 +681,12 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   // per device and cheap: set on every launch rather than caching per process
   PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_splat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
-  const int kGroupStrips = group_strips();
+  const int kGroupStrips = group_strips(p);
   const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
   // persistent grid: 3 CTAs per SM.  Shared memory would allow 4 at 641 px and a kernel running alone is
   // equally fast with either; 3 leave room for the assembly CTAs of another batch in flight
   // (engine.submit lanes: 122 k -> 126 k images/s)
-  int per_sm = 3;
-  if (const char *e = getenv("PP_CIFHR_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
+  const int per_sm = p.cifhr_ctas_per_sm > 0 ? p.cifhr_ctas_per_sm : 3;
   int grid = num_sms() * per_sm;
   if (grid > bf * n_groups) grid = bf * n_groups;
   prof_mark(p.profile, kStSplat, st);

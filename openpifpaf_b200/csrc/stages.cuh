@@ -80,6 +80,30 @@ size_t binned_start_bytes(const pp_shape &s);
 int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, const int *d_nbwd,
                    float *d_rows, int *d_start, const pp_shape &s, const pp_caps &c, cudaStream_t st);
 
+struct NmsArgs {
+  const float *in_data;    // (B,ann_cap,F,3)
+  const float *in_scales;  // (B,ann_cap,F)
+  const int *n_in;         // (B)
+  float *work;             // (B,ann_cap,F,3) scratch copy of data
+  double *score;           // (B,ann_cap) scratch
+  int *order;              // (B,ann_cap) scratch
+  int *order2;             // (B,ann_cap) scratch
+  long long *boxes;        // (B,F,ann_cap,4) scratch
+  float *out_data;         // (B,ann_cap,F,3)
+  float *out_scales;       // (B,ann_cap,F)
+  double *out_score;       // optional (B,ann_cap)
+  int *out_source;         // optional (B,ann_cap)
+  int *n_out;              // (B)
+  int ann_cap, F;
+  int do_nms;
+  float kp_th, suppression;
+  double inst_th;
+};
+// the argument block of one NMS over a batch; d_ws as sized by nms_ws_bytes
+NmsArgs nms_make_args(const float *in_data, const float *in_scales, const int *n_in, float *out_data,
+                      float *out_scales, double *out_score, int *out_source, int *n_out, void *d_ws,
+                      const pp_shape &s, const pp_caps &c, const pp_params &p);
+
 struct AsmArgs {
   const float *seeds;
   const int *n_seeds;
@@ -101,6 +125,8 @@ struct AsmArgs {
   const float *init_data, *init_scales;   // initial annotations (optional)
   const int *init_n;
   int init_cap;
+  int fuse_nms;       // run nms.Keypoints (or the nms=None copy) for the image right after its seed loop
+  NmsArgs nms;
 };
 int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, const pp_params &p,
                     cudaStream_t st);

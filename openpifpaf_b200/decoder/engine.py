@@ -44,6 +44,9 @@ class DecoderParams:
     host_mapped: bool = False
     # batches kept in flight on other streams (pp_params.in_flight); set by submit / run_host_lanes
     in_flight: int = 1
+    # schedule knobs of pp_params (0 = the library's choice; results never change): asm_heavy_seeds,
+    # asm_stage_kb, cifhr_group, cifhr_ctas_per_sm, cifhr_rshift
+    tuning: Optional[dict] = None
 
     def to_c(self):
         p = _lib.Params()
@@ -80,6 +83,11 @@ class DecoderParams:
         p.profile = self.profile
         p.host_mapped = int(bool(self.host_mapped))
         p.in_flight = int(self.in_flight)
+        for name, value in (self.tuning or {}).items():
+            if name not in ('asm_heavy_seeds', 'asm_stage_kb', 'cifhr_group', 'cifhr_ctas_per_sm',
+                            'cifhr_rshift'):
+                raise KeyError('unknown tuning knob %r' % name)
+            setattr(p, name, int(value))
         if self.initial is not None:
             data, scales, n = self.initial
             assert data.is_cuda and data.dtype == torch.float32 and data.is_contiguous()

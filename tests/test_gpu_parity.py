@@ -91,20 +91,20 @@ def test_crowded_1281(oracle, coco_skeleton, configured_decoder):
     assert len(o.data) >= 45
 
 
-@pytest.mark.parametrize('heavy_seeds', ['0', '1000000000'])
-def test_occupancy_seed_index_modes(oracle, coco_skeleton, configured_decoder, monkeypatch, heavy_seeds):
+@pytest.mark.parametrize('heavy_seeds', [-1, 1000000000])
+def test_occupancy_seed_index_modes(oracle, coco_skeleton, configured_decoder, heavy_seeds):
     """Both occupancy bookkeepings of the assembly kernel -- per-seed counters tested against every
     box, and the (field, row band) seed index with whole-map counters used above 4096 seeds -- on
     poses, on a crowd and on random-init-like fields (whole-map and off-map boxes, ~100 annotations)."""
     from openpifpaf_b200.encoder import random_init_like_fields
-    monkeypatch.setenv('PP_ASM_HEAVY_SEEDS', heavy_seeds)
+    tuning = {'asm_heavy_seeds': heavy_seeds}       # < 0: always the seed index; huge: never
     items = [fields((321, 481), 8, pose_seed=3, jitter_seed=4)[:2], fields((641, 641), 20, pose_seed=8)[:2]]
     for cif, caf in items:
-        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton)
+        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, tuning=tuning)
         assert len(check_image(oracle, out, 0, cif, caf, coco_skeleton).data) >= 8
     for seed in (0, 1, 2, 3):
         cif, caf = random_init_like_fields((13, 17), seed, scale_sigma=3.0 + seed)
-        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton)
+        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, tuning=tuning)
         assert len(check_image(oracle, out, 0, cif, caf, coco_skeleton).data) >= 10
 
 
