@@ -37,7 +37,10 @@
 
 namespace pp {
 
-constexpr int kAsmWarps = 8;                  // poses grown side by side per image
+#ifndef PP_ASM_WARPS
+#define PP_ASM_WARPS 8
+#endif
+constexpr int kAsmWarps = PP_ASM_WARPS;       // poses grown side by side per image
 constexpr int kAsmThreads = 32 * kAsmWarps;
 // Occupancy bookkeeping.  Up to kHeavySeeds seeds every seed's counter is tested against the boxes of
 // each finished pose (a few thousand tests).  Above that (crowded scenes, degenerate fields with 60 k
@@ -489,7 +492,8 @@ __device__ void warp_grow(const GrowView &w, const Graph &g, const CScale &cscal
 // pp_debug_asm_cycles.  Compiled out otherwise.
 // slots: 0 setup, 1 seed search, 2 wave pick, 3 wave grow, 5 store, 6 occupancy update, 7 nms tail
 #ifdef PP_ASM_TIMING
-__device__ unsigned long long g_asm_cycles[8];
+__device__ unsigned long long g_asm_cycles[12];   // 8 waves, 9 picks, 10 commits
+#define PP_COUNT(slot, n) do { if (threadIdx.x == 0) atomicAdd(&g_asm_cycles[slot], (unsigned long long)(n)); } while (0)
 #define PP_TICK(slot)                                                              \
   do {                                                                             \
     if (threadIdx.x == 0) {                                                        \
@@ -500,6 +504,7 @@ __device__ unsigned long long g_asm_cycles[8];
   } while (0)
 #else
 #define PP_TICK(slot) do { } while (0)
+#define PP_COUNT(slot, n) do { } while (0)
 #endif
 
 struct ListShared {
@@ -594,43 +599,60 @@ __device__ __forceinline__ void seed_cell(const SeedCtx &c, int i, int *f, int *
 // others are the next free seeds, in order, that lie outside the Occupancy.set boxes the earlier
 // picks' own joints are certain to set if those picks are committed (occupancy.py:31-39 on the
 // seed's (x, y, scale)).  Whatever is picked only decides which poses are grown ahead of time.
+// 128 seeds per trip: their counters, cells and positions are loaded together, then examined in order.
 __device__ void pick_wave(AsmShared &sh, const SeedCtx &c, int found) {
   const int lane = lane_id();
   const unsigned full = 0xffffffffu;
+  constexpr int U = 4;
   int n_pick = 0;
-  auto add = [&](int i) {          // one lane
-    const float *sd = c.seeds + (size_t)i * 5;
+  auto add = [&](int i, int f, float x, float y, float s) {          // one lane
     long long bx[4];
-    occupancy_box(__ldg(sd + 2), __ldg(sd + 3), __ldg(sd + 4), c.ow, c.oh, bx);
+    occupancy_box(x, y, s, c.ow, c.oh, bx);
     sh.pick_seed[n_pick] = i;
-    sh.pick_f[n_pick] = (int)__ldg(sd + 1);
+    sh.pick_f[n_pick] = f;
     for (int q = 0; q < 4; q++) sh.pick_box[n_pick][q] = (int)bx[q];
   };
-  if (lane == 0) add(found);
+  if (lane == 0) {
+    const float *sd = c.seeds + (size_t)found * 5;
+    add(found, (int)__ldg(sd + 1), __ldg(sd + 2), __ldg(sd + 3), __ldg(sd + 4));
+  }
   n_pick = 1;
   __syncwarp();
   const int last = min(c.n_seeds, found + 1 + kPickScan);
-  for (int base = found + 1; base < last && n_pick < kAsmWarps; base += 32) {
-    const int i = base + lane;
-    bool cand = i < last && seed_free(sh, c, i);
-    int f = 0, cx = 0, cy = 0;
-    if (cand) {
-      seed_cell(c, i, &f, &cx, &cy);
-      for (int k = 0; k < n_pick && cand; k++)
-        if (sh.pick_f[k] == f && cx >= sh.pick_box[k][0] && cx < sh.pick_box[k][1] &&
-            cy >= sh.pick_box[k][2] && cy < sh.pick_box[k][3])
-          cand = false;
+  for (int base = found + 1; base < last && n_pick < kAsmWarps; base += 32 * U) {
+    bool cand[U];
+    int f[U], cx[U], cy[U];
+    float sx[U], sy[U], ss[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int i = base + 32 * u + lane;
+      cand[u] = i < last && seed_free(sh, c, i);
+      f[u] = cx[u] = cy[u] = 0;
+      sx[u] = sy[u] = ss[u] = 0.0f;
+      if (cand[u]) {
+        seed_cell(c, i, &f[u], &cx[u], &cy[u]);
+        const float *sd = c.seeds + (size_t)i * 5;
+        sx[u] = __ldg(sd + 2); sy[u] = __ldg(sd + 3); ss[u] = __ldg(sd + 4);
+      }
     }
-    unsigned m = __ballot_sync(full, cand);
-    while (m && n_pick < kAsmWarps) {
-      const int l = __ffs(m) - 1;
-      if (lane == l) add(i);
-      __syncwarp();
-      const int k = n_pick++;
-      if (cand && lane > l && sh.pick_f[k] == f && cx >= sh.pick_box[k][0] && cx < sh.pick_box[k][1] &&
-          cy >= sh.pick_box[k][2] && cy < sh.pick_box[k][3])
-        cand = false;
-      m = __ballot_sync(full, cand) & ~((2u << l) - 1u);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (n_pick >= kAsmWarps) break;
+      for (int k = 0; k < n_pick && cand[u]; k++)
+        if (sh.pick_f[k] == f[u] && cx[u] >= sh.pick_box[k][0] && cx[u] < sh.pick_box[k][1] &&
+            cy[u] >= sh.pick_box[k][2] && cy[u] < sh.pick_box[k][3])
+          cand[u] = false;
+      unsigned m = __ballot_sync(full, cand[u]);
+      while (m && n_pick < kAsmWarps) {
+        const int l = __ffs(m) - 1;
+        if (lane == l) add(base + 32 * u + lane, f[u], sx[u], sy[u], ss[u]);
+        __syncwarp();
+        const int k = n_pick++;
+        if (cand[u] && lane > l && sh.pick_f[k] == f[u] && cx[u] >= sh.pick_box[k][0] &&
+            cx[u] < sh.pick_box[k][1] && cy[u] >= sh.pick_box[k][2] && cy[u] < sh.pick_box[k][3])
+          cand[u] = false;
+        m = __ballot_sync(full, cand[u]) & ~((2u << l) - 1u);
+      }
     }
   }
   if (lane == 0) sh.n_pick = n_pick;
@@ -741,6 +763,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
       if (sh.box_valid[i]) occupancy_box(v.data[3 * i], v.data[3 * i + 1], v.js[i], ow, oh, sh.box[i]);
     }
     n_ann++;
+    PP_COUNT(10, 1);
     __syncthreads();
     PP_TICK(5);
     if (heavy) {
@@ -847,6 +870,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
       __syncthreads();
       PP_TICK(2);
       n_pick = sh.n_pick;
+      PP_COUNT(8, 1); PP_COUNT(9, n_pick);
       if (warp < n_pick) {
         // new annotation from the seed (:104-105)
         const float *sd = seeds + (size_t)sh.pick_seed[warp] * 5;
@@ -874,7 +898,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
     // nms.Keypoints.annotations (nms.py:17-57) on the poses this CTA just wrote
     __threadfence_block();
     __syncthreads();
-    nms_image(a.nms, b);
+    nms_image(a.nms, b, dyn_smem, (size_t)(kAsmWarps * gw + a.stage_floats) * sizeof(float));
     PP_TICK(7);
   }
 }
@@ -1065,10 +1089,10 @@ int assemble_launch(const AsmArgs &args, const pp_skeleton &sk, int B, int F, co
 }  // namespace pp
 
 #ifdef PP_ASM_TIMING
-extern "C" int pp_debug_asm_cycles(unsigned long long *out8, int reset) {
-  if (cudaMemcpyFromSymbol(out8, pp::g_asm_cycles, 8 * sizeof(unsigned long long)) != cudaSuccess) return -3;
+extern "C" int pp_debug_asm_cycles(unsigned long long *out12, int reset) {
+  if (cudaMemcpyFromSymbol(out12, pp::g_asm_cycles, 12 * sizeof(unsigned long long)) != cudaSuccess) return -3;
   if (reset) {
-    unsigned long long z[8] = {0};
+    unsigned long long z[12] = {0};
     cudaMemcpyToSymbol(pp::g_asm_cycles, z, sizeof z);
   }
   return 0;

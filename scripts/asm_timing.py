@@ -17,14 +17,16 @@ eng, params = dec.engine(), dec.params()
 d_cif, d_caf = torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda()
 for _ in range(3): eng.run_device(d_cif, d_caf, params)
 torch.cuda.synchronize()
-out = (C.c_ulonglong * 8)()
+out = (C.c_ulonglong * 12)()
 _lib.lib().pp_debug_asm_cycles(out, 1)
 N = 3 if WL in bench.RANDINIT_MAX_SCALE else 10
 for _ in range(N): eng.run_device(d_cif, d_caf, params)
 torch.cuda.synchronize()
 _lib.lib().pp_debug_asm_cycles(out, 1)
-names = ['setup', 'seed_search', 'init_ann', 'grow_eval', 'grow_select', 'store_boxes', 'occ_update', 'grow_init']
-tot = sum(out)
-for n, v in zip(names, out):
+names = ['setup', 'seed_search', 'wave_pick', 'wave_grow', '-', 'store_boxes', 'occ_update', 'nms_tail']
+tot = sum(out[:8])
+print('%s: per image %.2f waves, %.2f grown poses, %.2f committed' % (
+    WL, out[8] / N / NB, out[9] / N / NB, out[10] / N / NB))
+for n, v in zip(names, out[:8]):
     print('%-12s %8.1f us/image  %5.1f%%' % (n, v / N / NB / 1965.0, 100.0 * v / tot))
 print('total %.1f us/image' % (tot / N / NB / 1965.0))
