@@ -44,6 +44,7 @@ extern "C" {
 #define PP_ERR_CAPACITY (-2)  /* a pp_caps capacity was exceeded               */
 #define PP_ERR_CUDA (-3)      /* a CUDA runtime call failed (see pp_last_cuda_error) */
 #define PP_ERR_WORKSPACE (-4) /* workspace too small                           */
+#define PP_ERR_STATIC_LIMIT (-5) /* request exceeds the built-in scratch of a *_noalloc entry */
 
 #define PP_MAX_F 32           /* keypoint types  */
 #define PP_MAX_L 64           /* CAF links       */
@@ -229,6 +230,25 @@ int pp_cifcaf_assemble(const float *d_seeds, const int32_t *d_n_seeds, const flo
 int pp_keypoint_nms(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
                     int32_t *d_source, void *d_ws, size_t ws_bytes, const pp_shape *s,
                     const pp_caps *c, const pp_params *p, void *stream);
+
+/* pp_keypoint_nms without any device allocation by the caller or the library.  NO COUNTERPART IN
+ * THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and results as pp_keypoint_nms; the scratch that entry takes as d_ws lives
+ * in a static device array of PP_NMS_NOALLOC_BYTES inside the library (every GPU that loads the
+ * library holds it until exit).  A request needing more (pp_keypoint_nms_noalloc_bytes(s, c) >
+ * pp_keypoint_nms_noalloc_max_bytes(); with F = 17 that is B * ann_cap > 3577 annotation slots for B = 1)
+ * returns PP_ERR_STATIC_LIMIT and enqueues nothing.  The call makes no cudaMalloc / cudaFree and
+ * uses no allocating library routine; it only enqueues three device-to-device copies and one
+ * kernel on `stream`.  All calls on one GPU share the array: calls that overlap on the GPU race --
+ * keep them on one stream or order them with events.  Nothing in the array has to be cleared
+ * between calls (every word read is written earlier in the same call). */
+#define PP_NMS_NOALLOC_BYTES (4 * 1024 * 1024)
+size_t pp_keypoint_nms_noalloc_max_bytes(void);
+size_t pp_keypoint_nms_noalloc_bytes(const pp_shape *s, const pp_caps *c);   /* 0 = bad shape */
+int pp_keypoint_nms_noalloc(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
+                            int32_t *d_source, const pp_shape *s, const pp_caps *c,
+                            const pp_params *p, void *stream);
 
 /* Inference epilogue of a fused head network + field collection, one pass:
  * PixelShuffle(2) and crop (quad = 1), sigmoid on confidences, exp on scales,

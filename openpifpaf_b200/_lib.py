@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(HERE, 'libpifpaf_b200.so')
 
 PP_MAX_F, PP_MAX_L = 32, 64
 PP_N_STAGES = 7
-PP_OK, PP_ERR_ARG, PP_ERR_CAPACITY, PP_ERR_CUDA, PP_ERR_WORKSPACE = 0, -1, -2, -3, -4
+PP_OK, PP_ERR_ARG, PP_ERR_CAPACITY, PP_ERR_CUDA, PP_ERR_WORKSPACE, PP_ERR_STATIC_LIMIT = 0, -1, -2, -3, -4, -5
 STATUS_BITS = {1: 'seed_cap', 2: 'caf_cap', 4: 'ann_cap', 8: 'src_cap'}
 
 
@@ -174,6 +174,11 @@ def lib():
     l.pp_cifcaf_assemble.argtypes = [vp] * 10 + [P(Skeleton), P(Outputs), vp, sz, P(Shape), P(Caps),
                                                  P(Params), vp]
     l.pp_keypoint_nms.argtypes = [vp, vp, vp, vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp]
+    l.pp_keypoint_nms_noalloc.argtypes = [vp, vp, vp, vp, vp, P(Shape), P(Caps), P(Params), vp]
+    l.pp_keypoint_nms_noalloc_max_bytes.restype = sz
+    l.pp_keypoint_nms_noalloc_max_bytes.argtypes = []
+    l.pp_keypoint_nms_noalloc_bytes.restype = sz
+    l.pp_keypoint_nms_noalloc_bytes.argtypes = [P(Shape), P(Caps)]
     l.pp_decode_batch.argtypes = [vp, vp, P(Skeleton), P(Outputs), vp, sz, P(Shape), P(Caps),
                                   P(Params), vp]
     l.pp_decode_batch_host.argtypes = [vp, vp, vp, vp, P(Skeleton), P(Outputs), P(Outputs), vp, sz,
@@ -208,6 +213,7 @@ EXPORTS = (
     'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detections_inverse', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
+    'pp_keypoint_nms_noalloc', 'pp_keypoint_nms_noalloc_max_bytes', 'pp_keypoint_nms_noalloc_bytes',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
     'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
     'pp_caf_center_s', 'pp_scalar_nonzero_clipped_with_reduction', 'pp_scalar_square_add_single',

@@ -128,6 +128,7 @@ const char *pp_error_string(int code) {
     case PP_ERR_CAPACITY: return "a pp_caps capacity was exceeded";
     case PP_ERR_CUDA: return "CUDA runtime error (see pp_last_cuda_error)";
     case PP_ERR_WORKSPACE: return "workspace too small";
+    case PP_ERR_STATIC_LIMIT: return "request exceeds the static scratch of a *_noalloc entry point";
     default: return "unknown error code";
   }
 }

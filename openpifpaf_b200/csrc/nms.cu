@@ -74,3 +74,79 @@ size_t nms_ws_staging_offset(const pp_shape &s, const pp_caps &c) {
 }
 
 }  // namespace pp
+
+namespace pp {
+
+// ---------------------------------------------------------------------------------------------
+// pp_keypoint_nms_noalloc: pp_keypoint_nms for callers that cannot allocate device memory (CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  The scratch pp_keypoint_nms takes from
+// the caller's workspace lives in the file-scope device array below, so the call allocates
+// nothing: no cudaMalloc / cudaFree, no allocating library routine.
+//   * Every GPU that loads the library holds PP_NMS_NOALLOC_BYTES of this array until exit.
+//   * Requests whose scratch (nms_ws_bytes(shape, caps)) exceeds it are rejected with
+//     PP_ERR_STATIC_LIMIT before anything is enqueued.
+//   * All calls (of every host thread and stream, per GPU) share the array: calls that overlap on
+//     the GPU race.  Issue them on one stream, or order them with events.
+//   * The array keeps the last call's contents.  Nothing in it has to start at zero: every word
+//     the kernel reads (staged input rows and counts, working rows, scores, ranks, occupancy
+//     boxes) is written earlier in the same call, so nothing is cleared.
+static __device__ __align__(256) unsigned char g_nms_noalloc_scratch[PP_NMS_NOALLOC_BYTES];
+
+// In host code the array's name is a host-side stand-in, not a device address: the address the
+// kernel gets comes from cudaGetSymbolAddress, once per device, with that device current.
+static int nms_noalloc_scratch(void **out) {
+  constexpr int kMaxDev = 64;
+  static void *cached[kMaxDev] = {nullptr};
+  int dev = 0;
+  PP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return PP_ERR_ARG;
+  void *ptr = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+  if (ptr == nullptr) {
+    PP_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_nms_noalloc_scratch));
+    if (ptr == nullptr) return PP_ERR_CUDA;
+    __atomic_store_n(&cached[dev], ptr, __ATOMIC_RELEASE);     // every thread gets the same value
+  }
+  *out = ptr;
+  return PP_OK;
+}
+
+}  // namespace pp
+
+extern "C" {
+
+size_t pp_keypoint_nms_noalloc_max_bytes(void) { return (size_t)PP_NMS_NOALLOC_BYTES; }
+
+size_t pp_keypoint_nms_noalloc_bytes(const pp_shape *s, const pp_caps *c) {
+  if (!s || !c || s->B <= 0 || s->F <= 0 || s->F > PP_MAX_F || c->ann_cap <= 0) return 0;
+  return pp::nms_ws_bytes(*s, *c);
+}
+
+int pp_keypoint_nms_noalloc(float *d_ann_data, float *d_ann_scales, int32_t *d_n_ann, double *d_score,
+                            int32_t *d_source, const pp_shape *s, const pp_caps *c, const pp_params *p,
+                            void *stream) {
+  using namespace pp;
+  if (!s || !c || !p || !d_ann_data || !d_ann_scales || !d_n_ann) return PP_ERR_ARG;
+  if (s->B <= 0 || s->F <= 0 || s->F > PP_MAX_F || c->ann_cap <= 0) return PP_ERR_ARG;
+  if (nms_ws_bytes(*s, *c) > (size_t)PP_NMS_NOALLOC_BYTES) return PP_ERR_STATIC_LIMIT;
+  void *ws = nullptr;
+  int rc = nms_noalloc_scratch(&ws);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // in place, like pp_keypoint_nms: the input rows are staged inside the scratch first
+  const size_t bc = (size_t)s->B * c->ann_cap;
+  const size_t data_bytes = align_up(bc * s->F * 3 * sizeof(float), 256);
+  char *stage = (char *)ws + nms_ws_staging_offset(*s, *c);
+  float *in_data = (float *)stage;
+  float *in_scales = (float *)(stage + data_bytes);
+  int *n_in = (int *)(stage + 2 * data_bytes);
+  PP_CUDA_CHECK(cudaMemcpyAsync(in_data, d_ann_data, bc * s->F * 3 * sizeof(float),
+                                cudaMemcpyDeviceToDevice, st));
+  PP_CUDA_CHECK(cudaMemcpyAsync(in_scales, d_ann_scales, bc * s->F * sizeof(float),
+                                cudaMemcpyDeviceToDevice, st));
+  PP_CUDA_CHECK(cudaMemcpyAsync(n_in, d_n_ann, (size_t)s->B * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  return nms_launch(in_data, in_scales, n_in, d_ann_data, d_ann_scales, d_score, d_source, d_n_ann, ws,
+                    *s, *c, *p, st);
+}
+
+}  // extern "C"
