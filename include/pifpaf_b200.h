@@ -170,7 +170,32 @@ typedef struct pp_outputs {
   int32_t *pre_order;   /* optional (B,ann_cap,F,2) decoding_order (start,end), -1 padded */
   int32_t *n_pre;       /* optional (B)                                  */
   int32_t *status;      /* (B) PP_STATUS_* bits                          */
+  void *packed;         /* optional, pp_packed_bytes(shape, caps) bytes, 256-byte aligned: the live
+                           result rows of the batch gathered into one dense block (see "Packed
+                           results" below) so that ONE small copy brings a batch's results to the host */
 } pp_outputs;
+
+/* ---- Packed results ---------------------------------------------------------------------------
+ * The fixed-capacity result arrays above hold ann_cap rows per image of which a handful are live
+ * (the reference returns a Python list of exactly the live annotations, cifcaf.py:110-122).  When
+ * pp_outputs.packed is set, the decode entries finish with a gather kernel that writes, for the
+ * images [0, B) of the call, one block of 32-bit words:
+ *     word 0..3            B, F, total (= sum of n_ann), record_words
+ *     word 4..4+B          n_ann[B]
+ *     then                 status[B], n_pre[B], pad to an even word count
+ *     then                 `total` records of record_words = pp_packed_record_words(F) words, image
+ *                          after image, score order inside an image:
+ *         [0..1] Annotation.score() as float64   [2] ann_source   [3] 0
+ *         [4 ..)  ann_data (F,3)   ann_scales (F)   pre_data[ann_source] (F,3)   pre_order[ann_source] (F,2)
+ * Host entries given h_out->packed copy header + live records only (pp_decode_batch_host: counts
+ * first, then the rows; the pipelined entry: a guessed size in one copy, the rare remainder in
+ * pp_pipeline_wait) and skip every other result array whose h_out member is NULL.  A chunk of the
+ * pipelined entry starting at image b0 writes its block at packed + b0 * pp_packed_bytes(1 image). */
+size_t pp_packed_bytes(const pp_shape *s, const pp_caps *c);   /* capacity for the worst case */
+int32_t pp_packed_record_words(int32_t F);
+size_t pp_packed_header_words(int32_t B);                      /* words before the first record */
+/* The gather on its own (the decode entries call it when d_out->packed is set). */
+int pp_pack_results(const pp_outputs *d_out, const pp_shape *s, const pp_caps *c, void *stream);
 
 /* Per-stage device timing.  When pp_params.profile is set, pp_decode_batch
  * records one CUDA event before every stage and one after the last, on the

@@ -103,7 +103,7 @@ class Skeleton(C.Structure):
 
 _OUT_FIELDS = ('hr', 'seeds', 'n_seeds', 'caf_fwd', 'caf_bwd', 'n_caf_fwd', 'n_caf_bwd',
                'ann_data', 'ann_scales', 'ann_score', 'ann_source', 'n_ann', 'pre_data',
-               'pre_scales', 'pre_order', 'n_pre', 'status')
+               'pre_scales', 'pre_order', 'n_pre', 'status', 'packed')
 
 
 class Outputs(C.Structure):
@@ -164,6 +164,12 @@ def lib():
     l.pp_decode_batch_multiscale.argtypes = [P(FieldSet), i32, i32, P(Skeleton), P(Outputs), vp, sz,
                                              P(Shape), P(Caps), P(Params), vp]
     l.pp_sizeof.argtypes = [i32]
+    l.pp_packed_bytes.restype = sz
+    l.pp_packed_bytes.argtypes = [P(Shape), P(Caps)]
+    l.pp_packed_record_words.argtypes = [i32]
+    l.pp_packed_header_words.restype = sz
+    l.pp_packed_header_words.argtypes = [i32]
+    l.pp_pack_results.argtypes = [P(Outputs), P(Shape), P(Caps), vp]
     l.pp_sizeof.restype = i32
     l.pp_annotations_inverse.argtypes = [vp, vp, vp, vp, vp, C.POINTER(Inverse), i32, i32, i32, vp]
     l.pp_head_epilogue.argtypes = [vp, vp, i32, i32, i32, i32, i32, i32, vp]
@@ -214,6 +220,7 @@ EXPORTS = (
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_keypoint_nms_noalloc', 'pp_keypoint_nms_noalloc_max_bytes', 'pp_keypoint_nms_noalloc_bytes',
+    'pp_packed_bytes', 'pp_packed_record_words', 'pp_packed_header_words', 'pp_pack_results',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
     'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
     'pp_caf_center_s', 'pp_scalar_nonzero_clipped_with_reduction', 'pp_scalar_square_add_single',

@@ -181,12 +181,12 @@ const char *pp_stage_name(int stage) {
   return (stage >= 0 && stage < PP_N_STAGES) ? names[stage] : "?";
 }
 
-/* 7 stage kernels + the candidate binning kernel + the status, CifHr-cursor and seed-counter memsets */
+/* Launches one pp_decode_batch enqueues with d_out->packed set (the bindings always set it): 8 kernels
+ * (compact, splat, seeds from sources, seed sort, CafScored, candidate binning, assembly with the NMS as
+ * its tail, result gather) + 3 memsets (status, work cursors, raw seed counts). */
 int pp_decode_launch_count(const pp_params *p) {
-  // 8 kernels (compact, splat, seeds collect, seeds sort, CafScored, candidate binning, assembly, NMS)
-  // + 3 memsets (status, work cursors, raw seed counts)
-  int n = PP_N_STAGES + 3;              // the NMS is the tail of the assembly kernel ...
-  if (p && p->force_complete) n += 4;   // ... unless: second CafScored, its binning, complete_kernel, nms_kernel
+  int n = PP_N_STAGES + 4;
+  if (p && p->force_complete) n += 4;   // second CafScored, its binning, complete_kernel, nms_kernel
   if (p && p->inverse) n += 1;          // annotations_inverse_kernel
   return n;
 }
@@ -238,6 +238,17 @@ int pp_coco_skeleton(pp_skeleton *sk) {
 size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c) {
   if (!shape_ok(s) || !caps_ok(s, c)) return 0;
   return layout(nullptr, *s, *c, true).total;
+}
+
+size_t pp_packed_bytes(const pp_shape *s, const pp_caps *c) {
+  if (!s || !c || s->B <= 0 || s->F <= 0 || s->F > PP_MAX_F || c->ann_cap <= 0) return 0;
+  return (size_t)s->B * packed_image_bytes(s->F, c->ann_cap);
+}
+int32_t pp_packed_record_words(int32_t F) { return F > 0 ? packed_record_words(F) : 0; }
+size_t pp_packed_header_words(int32_t B) { return B > 0 ? packed_header_words(B) : 0; }
+int pp_pack_results(const pp_outputs *d_out, const pp_shape *s, const pp_caps *c, void *stream) {
+  if (!d_out || !s || !c || s->B <= 0 || s->F <= 0 || s->F > PP_MAX_F || c->ann_cap <= 0) return PP_ERR_ARG;
+  return pack_launch(*d_out, *s, *c, (cudaStream_t)stream);
 }
 
 int32_t pp_sizeof(int32_t which) {
@@ -516,6 +527,11 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   if (!rc && p->inverse)      // optional Preprocess.annotations_inverse on the results (inside the nms stage time)
     rc = annotations_inverse_launch(o->ann_data, o->ann_scales, o->n_ann, a.pre_data, a.n_pre, *p->inverse,
                                     s->B, s->F, c->ann_cap, st);
+  if (!rc && o->packed) {      // one dense block of the live rows for the result copy
+    pp_outputs po = *o;
+    po.pre_data = a.pre_data; po.pre_scales = a.pre_scales; po.pre_order = a.pre_order; po.n_pre = a.n_pre;
+    rc = pack_launch(po, *s, *c, st);
+  }
   prof_end_step(p->profile, st);
   return rc;
 }
@@ -693,7 +709,7 @@ int pp_detection_nms(const int32_t *d_field, const float *d_score, const float *
 struct OutField { size_t offset; size_t bytes_per_image; };
 
 // byte size of one image's slice of every pp_outputs member, in declaration order
-static void output_strides(const pp_shape &s, const pp_caps &c, size_t out[17]) {
+static void output_strides(const pp_shape &s, const pp_caps &c, size_t out[18]) {
   const size_t F = s.F, L = s.L, A = c.ann_cap;
   const size_t f = sizeof(float), i = sizeof(int32_t);
   out[0] = F * hr_h(s) * hr_w(s) * f;   // hr
@@ -713,28 +729,44 @@ static void output_strides(const pp_shape &s, const pp_caps &c, size_t out[17]) 
   out[14] = A * F * 2 * i;              // pre_order
   out[15] = i;                          // n_pre
   out[16] = i;                          // status
+  out[17] = packed_image_bytes(s.F, c.ann_cap);   // packed: block of a chunk starts at its first image's share
 }
 
-static_assert(sizeof(pp_outputs) == 17 * sizeof(void *), "pp_outputs member table out of date");
+static_assert(sizeof(pp_outputs) == 18 * sizeof(void *), "pp_outputs member table out of date");
+constexpr int kOutPacked = 17;
 
 // the outputs of images [b0, ...) as their own pp_outputs
-static pp_outputs slice_outputs(const pp_outputs &o, const size_t strides[17], size_t b0) {
+static pp_outputs slice_outputs(const pp_outputs &o, const size_t strides[18], size_t b0) {
   pp_outputs r = o;
   char **src = (char **)&r;
-  for (int k = 0; k < 17; k++)
+  for (int k = 0; k < 18; k++)
     if (src[k]) src[k] += b0 * strides[k];
   return r;
 }
 
-static int copy_outputs_to_host(const pp_outputs &d, const pp_outputs &h, const size_t strides[17],
+// every result array both sides have, except the packed block (its live part only: below)
+static int copy_outputs_to_host(const pp_outputs &d, const pp_outputs &h, const size_t strides[18],
                                 size_t b0, size_t nb, cudaStream_t st) {
   char *const *dp = (char *const *)&d;
   char *const *hp = (char *const *)&h;
-  for (int k = 0; k < 17; k++)
+  for (int k = 0; k < kOutPacked; k++)
     if (dp[k] && hp[k])
       PP_CUDA_CHECK(cudaMemcpyAsync(hp[k] + b0 * strides[k], dp[k] + b0 * strides[k], nb * strides[k],
                                     cudaMemcpyDeviceToHost, st));
   return PP_OK;
+}
+
+// bytes of a packed block of nb images that hold the header and the first `records` records
+static size_t packed_prefix_bytes(size_t nb, int F, size_t records) {
+  return (packed_header_words((int)nb) + records * (size_t)packed_record_words(F)) * sizeof(int32_t);
+}
+
+// status words of a finished packed block
+static bool packed_block_overflowed(const void *h_block, size_t nb) {
+  const int32_t *w = (const int32_t *)h_block;
+  for (size_t b = 0; b < nb; b++)
+    if (w[4 + nb + b] != 0) return true;
+  return false;
 }
 
 int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, float *d_caf,
@@ -760,10 +792,24 @@ int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, f
     rc = pp_decode_batch(d_cif, d_caf, sk, d_out, d_ws, ws_bytes, s, c, p, stream);
   }
   if (rc) return rc;
-  size_t strides[17];
+  size_t strides[18];
   output_strides(*s, *c, strides);
   if ((rc = copy_outputs_to_host(*d_out, *h_out, strides, 0, B, st))) return rc;
+  const bool packed = d_out->packed && h_out->packed;
+  if (packed)      // counts first ...
+    PP_CUDA_CHECK(cudaMemcpyAsync(h_out->packed, d_out->packed, packed_prefix_bytes(B, s->F, 0),
+                                  cudaMemcpyDeviceToHost, st));
   PP_CUDA_CHECK(cudaStreamSynchronize(st));
+  if (packed) {    // ... then exactly the live rows
+    const size_t total = (size_t)((const int32_t *)h_out->packed)[2];
+    const size_t head = packed_prefix_bytes(B, s->F, 0);
+    if (total > 0) {
+      PP_CUDA_CHECK(cudaMemcpyAsync((char *)h_out->packed + head, (const char *)d_out->packed + head,
+                                    packed_prefix_bytes(B, s->F, total) - head, cudaMemcpyDeviceToHost, st));
+      PP_CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+    if (packed_block_overflowed(h_out->packed, B)) return PP_ERR_CAPACITY;
+  }
   if (h_out->status)
     for (size_t b = 0; b < B; b++)
       if (h_out->status[b] != 0) return PP_ERR_CAPACITY;
@@ -778,6 +824,12 @@ struct pp_pipeline {
   cudaEvent_t ev_start;
   cudaEvent_t *ev_in, *ev_done, *ev_out;   // (max_chunks) each
   const int32_t *h_status;
+  // packed result blocks (one per chunk): the copy-out moves header + rec_guess records per image; a chunk
+  // with more live rows gets its remainder in pp_pipeline_wait, which also raises the guess
+  char *h_packed;
+  const char *d_packed;
+  size_t packed_stride;
+  int F, rec_guess;
 };
 
 extern "C" {
@@ -787,6 +839,7 @@ pp_pipeline *pp_pipeline_create(int max_chunks) {
   pp_pipeline *q = (pp_pipeline *)calloc(1, sizeof(pp_pipeline));
   if (!q) return nullptr;
   q->max_chunks = max_chunks;
+  q->rec_guess = 8;
   q->ev_in = (cudaEvent_t *)calloc(3 * (size_t)max_chunks, sizeof(cudaEvent_t));
   bool ok = q->ev_in != nullptr;
   if (ok) {
@@ -829,12 +882,20 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
   const int n_chunks = (s->B + chunk_images - 1) / chunk_images;
   if (n_chunks > q->max_chunks) return PP_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
-  q->n_chunks = n_chunks; q->chunk_images = chunk_images; q->B = s->B;
+  // n_chunks is set once every chunk has been enqueued: after a failed submit pp_pipeline_wait returns
+  // PP_ERR_ARG instead of waiting on events this call never recorded
+  q->n_chunks = 0; q->chunk_images = chunk_images; q->B = s->B;
   q->h_status = h_out->status;
   const size_t cells = (size_t)s->H * s->W;
   const size_t cif_img = (size_t)s->F * 5 * cells, caf_img = (size_t)s->L * 9 * cells;
-  size_t strides[17];
+  size_t strides[18];
   output_strides(*s, *c, strides);
+  const bool packed = d_out->packed && h_out->packed;
+  q->h_packed = packed ? (char *)h_out->packed : nullptr;
+  q->d_packed = packed ? (const char *)d_out->packed : nullptr;
+  q->packed_stride = strides[kOutPacked];
+  q->F = s->F;
+  if (q->rec_guess > c->ann_cap) q->rec_guess = c->ann_cap;
 
   const float *m_cif = mapped_applies(p) ? mapped_alias(h_cif) : nullptr;
   const float *m_caf = m_cif ? mapped_alias(h_caf) : nullptr;
@@ -891,10 +952,15 @@ int pp_decode_batch_host_async(pp_pipeline *q, const float *h_cif, const float *
     PP_CUDA_CHECK(cudaEventRecord(q->ev_done[k], st));
     PP_CUDA_CHECK(cudaStreamWaitEvent(q->s_out, q->ev_done[k], 0));
     if ((rc = copy_outputs_to_host(*d_out, *h_out, strides, b0, nb, q->s_out))) return rc;
+    if (packed)
+      PP_CUDA_CHECK(cudaMemcpyAsync(q->h_packed + b0 * q->packed_stride, q->d_packed + b0 * q->packed_stride,
+                                    packed_prefix_bytes(nb, s->F, nb * (size_t)q->rec_guess),
+                                    cudaMemcpyDeviceToHost, q->s_out));
     PP_CUDA_CHECK(cudaEventRecord(q->ev_out[k], q->s_out));
   }
   // later work on `stream` is ordered after the last copy-out
   PP_CUDA_CHECK(cudaStreamWaitEvent(st, q->ev_out[n_chunks - 1], 0));
+  q->n_chunks = n_chunks;
   return PP_OK;
 }
 
@@ -902,6 +968,22 @@ int pp_pipeline_wait(pp_pipeline *q, int chunk) {
   if (!q || chunk >= q->n_chunks) return PP_ERR_ARG;
   const int k0 = chunk < 0 ? 0 : chunk, k1 = chunk < 0 ? q->n_chunks : chunk + 1;
   for (int k = k0; k < k1; k++) PP_CUDA_CHECK(cudaEventSynchronize(q->ev_out[k]));
+  bool overflow = false;
+  for (int k = k0; k < k1 && q->h_packed; k++) {
+    const size_t b0 = (size_t)k * q->chunk_images;
+    const size_t nb = (size_t)q->B - b0 < (size_t)q->chunk_images ? (size_t)q->B - b0 : (size_t)q->chunk_images;
+    char *hb = q->h_packed + b0 * q->packed_stride;
+    const size_t total = (size_t)((const int32_t *)hb)[2], have = nb * (size_t)q->rec_guess;
+    if (total > have) {       // more live rows than guessed: fetch the rest now, guess higher from here on
+      const size_t from = packed_prefix_bytes(nb, q->F, have), to = packed_prefix_bytes(nb, q->F, total);
+      PP_CUDA_CHECK(cudaMemcpyAsync(hb + from, q->d_packed + b0 * q->packed_stride + from, to - from,
+                                    cudaMemcpyDeviceToHost, q->s_out));
+      PP_CUDA_CHECK(cudaStreamSynchronize(q->s_out));
+      q->rec_guess = (int)((total + nb - 1) / nb) + 2;
+    }
+    overflow = overflow || packed_block_overflowed(hb, nb);
+  }
+  if (overflow) return PP_ERR_CAPACITY;
   if (q->h_status) {
     const int b0 = k0 * q->chunk_images;
     const int b1 = k1 * q->chunk_images < q->B ? k1 * q->chunk_images : q->B;

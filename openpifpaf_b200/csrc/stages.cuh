@@ -144,6 +144,11 @@ int annotations_inverse_launch(float *ann_data, float *ann_scales, const int *n_
                                cudaStream_t st);
 int detections_inverse_launch(float *box, const int *n_det, const pp_inverse &inv, int B, int ann_cap,
                               cudaStream_t st);
+// packed results (pack.cu)
+int packed_record_words(int F);
+size_t packed_header_words(int B);
+size_t packed_image_bytes(int F, int ann_cap);      // capacity share of one image (block stride of a chunk)
+int pack_launch(const pp_outputs &o, const pp_shape &s, const pp_caps &c, cudaStream_t st);
 int head_epilogue_launch(const float *d_x, float *d_out, int B, int nf, int nv, int h, int w, int quad,
                          cudaStream_t st);
 

@@ -4,6 +4,7 @@ and streams only; every computation happens in the CUDA library.
 """
 import ctypes as C
 import dataclasses
+import time
 from typing import Optional
 
 import numpy as np
@@ -148,6 +149,35 @@ def _stream_ptr():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+class PackedResult:
+    """The live result rows of ``n`` images, parsed from one packed block (include/pifpaf_b200.h,
+    "Packed results").  All arrays are views of ONE private copy of the records, flat over the images:
+    ``n_ann (n,)`` rows per image; ``data (T, F, 3)``, ``scales (T, F)``, ``score (T,)`` float64,
+    ``source (T,)``, ``pre (T, F, 3)`` / ``order (T, F, 2)`` = the as-grown rows / decoding order of the
+    pre-NMS annotation each final annotation came from."""
+
+    def __init__(self, words, nb, F):
+        hdr = (4 + 3 * nb + 1) & ~1
+        total, rw = int(words[2]), int(words[3])
+        assert int(words[0]) == nb and int(words[1]) == F, 'packed block header does not match the call'
+        self.n_ann = np.array(words[4:4 + nb])
+        self.status = np.array(words[4 + nb:4 + 2 * nb])
+        self.n_pre = np.array(words[4 + 2 * nb:4 + 3 * nb])
+        rec = np.array(words[hdr:hdr + total * rw]).reshape(total, rw)     # the private copy
+        self.total = total
+        self.score = rec[:, 0:2].view(np.float64)[:, 0]
+        self.source = rec[:, 2]
+        self.data = rec[:, 4:4 + 3 * F].view(np.float32).reshape(total, F, 3)
+        self.scales = rec[:, 4 + 3 * F:4 + 4 * F].view(np.float32)
+        self.pre = rec[:, 4 + 4 * F:4 + 7 * F].view(np.float32).reshape(total, F, 3)
+        self.order = rec[:, 4 + 7 * F:4 + 9 * F].reshape(total, F, 2)
+
+    def check(self):
+        if self.status.any():
+            raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(self.status))
+        return self
+
+
 class BatchBuffers:
     """Caller-owned device (and optional pinned host) buffers for one batch shape."""
 
@@ -178,6 +208,14 @@ class BatchBuffers:
             t['caf_bwd'] = torch.empty((B, L, 9, caps.caf_cap), dtype=f32, **dev)
             t['n_caf_fwd'] = torch.zeros((B, L), dtype=i32, **dev)
             t['n_caf_bwd'] = torch.zeros((B, L), dtype=i32, **dev)
+        lib = _lib.lib()
+        self.packed_bytes = lib.pp_packed_bytes(C.byref(shape), C.byref(caps))
+        self.rec_words = lib.pp_packed_record_words(F)
+        self.image_stride = self.packed_bytes // B          # block of a chunk starts at b0 * image_stride
+        t['packed'] = torch.empty((self.packed_bytes,), dtype=torch.uint8, **dev)
+        self.h_packed = None
+        self.h_words = None
+        self.fetched_records = 0
         self.dev = t
         self.d_out = _lib.Outputs()
         for name, tensor in t.items():
@@ -193,21 +231,51 @@ class BatchBuffers:
         if host:
             self.enable_host()
 
-    HOST_COPIED = ('ann_data', 'ann_scales', 'ann_score', 'ann_source', 'n_ann', 'pre_data',
-                   'pre_order', 'n_pre', 'status')
+    def pin(self):
+        """Pinned host mirror of the packed result block (the only result bytes that cross PCIe)."""
+        if self.h_packed is None:
+            self.h_packed = torch.empty((self.packed_bytes,), dtype=torch.uint8, pin_memory=True)
+            self.h_words = self.h_packed.numpy().view(np.int32)
+        return self.h_packed
 
     def enable_host(self):
-        """Pinned host mirrors + device staging for pp_decode_batch_host."""
+        """Pinned host mirror + device staging of the fields for pp_decode_batch_host."""
         if self.host is not None:
             return
         s = self.shape
-        self.host = {n: torch.empty(self.dev[n].shape, dtype=self.dev[n].dtype, pin_memory=True)
-                     for n in self.HOST_COPIED}
+        self.host = {'packed': self.pin()}
         self.h_out = _lib.Outputs()
-        for name, tensor in self.host.items():
-            setattr(self.h_out, name, tensor.data_ptr())
+        self.h_out.packed = self.h_packed.data_ptr()
         self.d_cif = torch.empty((s.B, s.F, 5, s.H, s.W), dtype=torch.float32, device=self.device)
         self.d_caf = torch.empty((s.B, s.L, 9, s.H, s.W), dtype=torch.float32, device=self.device)
+
+    def prefix_bytes(self, nb, records):
+        return 4 * (((4 + 3 * nb + 1) & ~1) + records * self.rec_words)
+
+    def enqueue_fetch(self, records_per_image):
+        """Device path: copy header + the first ``records_per_image * B`` records to the pinned mirror on
+        the current stream (after the kernels already enqueued there)."""
+        self.pin()
+        B = self.shape.B
+        self.fetched_records = min(records_per_image, self.caps.ann_cap) * B
+        n = self.prefix_bytes(B, self.fetched_records)
+        self.h_packed[:n].copy_(self.dev['packed'][:n], non_blocking=True)
+
+    def finish_fetch(self):
+        """After the stream (or the event behind ``enqueue_fetch``) has been waited for: fetch the rare
+        remainder and parse.  Returns ``(PackedResult, records per image worth guessing next time)``."""
+        B = self.shape.B
+        total = int(self.h_words[2])
+        if total > self.fetched_records:
+            a, b = self.prefix_bytes(B, self.fetched_records), self.prefix_bytes(B, total)
+            self.h_packed[a:b].copy_(self.dev['packed'][a:b])          # synchronous
+            self.fetched_records = total
+        return PackedResult(self.h_words, B, self.shape.F), (total + B - 1) // B + 2
+
+    def host_result(self, b0=0, nb=None):
+        """Host entries: the parsed block of the chunk that starts at image ``b0`` (``nb`` images)."""
+        nb = self.shape.B if nb is None else nb
+        return PackedResult(self.h_words[b0 * self.image_stride // 4:], nb, self.shape.F)
 
 
 class DeviceDecoder:
@@ -245,8 +313,18 @@ class DeviceDecoder:
             buf.enable_host()
         return buf
 
-    def run_device(self, cif, caf, params: DecoderParams, *, keep=('ann',)):
-        """cif (B,F,5,H,W), caf (B,L,9,H,W): CUDA float32 tensors. Enqueues only."""
+    fetch_guess = 8       # records per image copied with the header; grows to what the batches need
+
+    def collect(self, buf):
+        """Results of a ``run_device(..., fetch=True)`` batch whose stream / event has been waited for."""
+        res, guess = buf.finish_fetch()
+        if guess > self.fetch_guess:
+            DeviceDecoder.fetch_guess = guess
+        return res.check()
+
+    def run_device(self, cif, caf, params: DecoderParams, *, keep=('ann',), fetch=False):
+        """cif (B,F,5,H,W), caf (B,L,9,H,W): CUDA float32 tensors. Enqueues only.  ``fetch``: also
+        enqueue the copy of the packed results to the pinned mirror (finish with ``collect``)."""
         assert cif.is_cuda and caf.is_cuda and cif.dtype == torch.float32 and caf.dtype == torch.float32
         cif, caf = cif.contiguous(), caf.contiguous()
         B, F, five, H, W = cif.shape
@@ -258,6 +336,8 @@ class DeviceDecoder:
                                         C.byref(buf.shape), C.byref(buf.caps), C.byref(p),
                                         _stream_ptr())
         _lib.check(rc)
+        if fetch:
+            buf.enqueue_fetch(self.fetch_guess)
         return buf
 
     # ---- several batches in flight -------------------------------------------------------
@@ -275,7 +355,7 @@ class DeviceDecoder:
         self._lanes = cur
         return cur[:n]
 
-    def submit(self, cif, caf, params: DecoderParams, *, n_lanes=8, keep=('ann',)):
+    def submit(self, cif, caf, params: DecoderParams, *, n_lanes=8, keep=('ann',), fetch=False):
         """Enqueue one batch on the next lane and return a ``Ticket``; at most ``n_lanes`` batches
         are in flight, so the ticket that used this lane last must have been waited for."""
         lanes = self.lanes(n_lanes)
@@ -288,13 +368,14 @@ class DeviceDecoder:
         if n_lanes > 1 and params.in_flight != n_lanes:
             params = dataclasses.replace(params, in_flight=n_lanes)
         with torch.cuda.stream(lane.stream):
-            buf = lane.engine.run_device(cif, caf, params, keep=keep)
+            buf = lane.engine.run_device(cif, caf, params, keep=keep, fetch=fetch)
             done = torch.cuda.Event()
             done.record(lane.stream)
         lane.pending = Ticket(buf, done, (cif, caf))
         return lane.pending
 
-    def run_device_multiscale(self, sets, params: DecoderParams, *, hflip_pairs=False, keep=('ann',)):
+    def run_device_multiscale(self, sets, params: DecoderParams, *, hflip_pairs=False, keep=('ann',),
+                              fetch=False):
         """Multi-scale FieldConfig: ``sets`` = list of ``(cif, caf, stride, cif_min_scale,
         caf_min_distance, caf_max_distance)`` with CUDA float32 tensors ``(B,F,5,H_k,W_k)`` /
         ``(B,L,9,H_k,W_k)``; set 0 defines the hr shape.  Enqueues only."""
@@ -325,6 +406,8 @@ class DeviceDecoder:
             arr, len(sets), int(bool(hflip_pairs)), C.byref(self.c_skeleton), C.byref(buf.d_out),
             _ptr(buf.ws), buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), _stream_ptr()))
         buf.alive = alive           # the field tensors must outlive the enqueued kernels
+        if fetch:
+            buf.enqueue_fetch(self.fetch_guess)
         return buf
 
     def run_host(self, cif, caf, params: DecoderParams, *, keep=('ann',)):
@@ -343,7 +426,7 @@ class DeviceDecoder:
                 C.byref(self.c_skeleton), C.byref(buf.d_out), C.byref(buf.h_out), _ptr(buf.ws),
                 buf.ws_bytes, C.byref(buf.shape), C.byref(buf.caps), C.byref(p), _stream_ptr())
         if rc == _lib.PP_ERR_CAPACITY:
-            raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
+            raise _lib.PifPafError(rc, describe_status(buf.host_result().status))
         _lib.check(rc)
         return buf
 
@@ -375,6 +458,7 @@ class DeviceDecoder:
                 _lib.check(lib.pp_decode_batch_host_async(
                     *args, _stream_ptr() if stream_ptr is None else stream_ptr))
         buf.alive = (cif_t, caf_t, p)
+        buf.chunk = chunk
         return buf, chunk, (B + chunk - 1) // chunk
 
     def wait_host_chunk(self, buf, k):
@@ -382,7 +466,10 @@ class DeviceDecoder:
         rc = lib.pp_pipeline_wait(self._pipeline.handle, k)
         if rc == _lib.PP_ERR_CAPACITY:
             lib.pp_pipeline_wait(self._pipeline.handle, -1)
-            raise _lib.PifPafError(rc, describe_status(buf.host['status'].numpy()))
+            B, chunk = buf.shape.B, buf.chunk
+            status = np.concatenate([buf.host_result(b0, min(chunk, B - b0)).status
+                                     for b0 in range(0, B, chunk)])
+            raise _lib.PifPafError(rc, describe_status(status))
         _lib.check(rc)
 
     def run_host_chunked(self, cif, caf, params, chunk, *, keep=('ann',)):
@@ -450,7 +537,7 @@ class DeviceDecoder:
                 nxt += 1
 
 
-    def run_host_stream(self, batches, params, sub, n_lanes, *, keep=('ann',)):
+    def run_host_stream(self, batches, params, sub, n_lanes, *, keep=('ann',), stats=None):
         """``run_host_lanes`` over a stream of host batches: the sub-batches of successive batches follow
         each other through the lanes without a gap, so the copies of batch k + 1 run while the kernels of
         the last sub-batches of batch k are still in flight.  ``batches``: iterable of ``(cif, caf)`` host
@@ -485,18 +572,26 @@ class DeviceDecoder:
             pending.append((lane, buf, bid, b1 - b0, last))
             n_sub[0] += 1
 
+        clock = time.perf_counter
+        stats = stats if stats is not None else {}
         it = items()
+        t0 = clock()
         for item in it:
             submit(item)
             if len(pending) == n_lanes:
                 break
+        stats['submit_s'] = stats.get('submit_s', 0.0) + clock() - t0
         while pending:
             lane, buf, bid, nb, last = pending.pop(0)
+            t0 = clock()
             lane.engine.wait_host_chunk(buf, 0)
+            stats['wait_s'] = stats.get('wait_s', 0.0) + clock() - t0
             yield bid, buf, nb, last
+            t0 = clock()
             nxt = next(it, None)           # the lane just collected is the one the next sub-batch takes
             if nxt is not None:
                 submit(nxt)
+            stats['submit_s'] += clock() - t0
 
 
 class Lane:

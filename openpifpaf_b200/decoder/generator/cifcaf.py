@@ -20,7 +20,7 @@ from .. import nms as nms_module
 from ..caf_scored import CafScored
 from ..cif_hr import CifHr
 from ..cif_seeds import CifSeeds
-from ..engine import DecoderParams, DeviceDecoder, describe_status
+from ..engine import DecoderParams, DeviceDecoder
 from ..field_config import FieldConfig
 from ... import _lib
 from .generator import Generator
@@ -56,6 +56,7 @@ class CifCaf(Generator):
     # time of the bytes that move), 8 x 8 -> 1.77 ms
     stream_chunk = 32
     stream_lanes = 4
+    stream_stats = None           # host-time breakdown of the last decode_stream call
 
     def __init__(self, field_config: FieldConfig, *,
                  keypoints,
@@ -146,24 +147,17 @@ class CifCaf(Generator):
                 and cif.is_pinned() and caf.is_pinned()
                 and not params.force_complete and params.seed_threshold >= params.cif_threshold)
 
-    def _annotations_from(self, n_ann, data, scales, source, pre_data, pre_order, b0=0, b1=None):
-        """Host arrays of one batch (images b0..b1) -> List[List[Annotation]].
+    def _annotations_from(self, res):
+        """``engine.PackedResult`` of some images -> List[List[Annotation]].
 
-        The rows are copied out of the (reused, pinned) result buffers once per image;
-        each Annotation owns views of those private copies."""
-        b1 = len(n_ann) if b1 is None else b1
-        counts = n_ann[b0:b1]
-        nmax = int(counts.max(initial=0))
-        if nmax == 0:
-            return [[] for _ in range(b0, b1)]
-        # one gather per array for all images of the range (fancy indexing = private copies)
-        img, row = np.nonzero(np.arange(nmax)[None, :] < counts[:, None])
-        img += b0
-        src = source[img, row]
-        anns = Annotation.wrap_batch(self.keypoints, self.out_skeleton, data[img, row], scales[img, row],
-                                     pre_data[img, src], pre_order[img, src], self._neighbours)
+        The records were copied out of the (reused, pinned) result block once; each Annotation owns
+        row views of that private copy."""
+        if res.total == 0:
+            return [[] for _ in range(len(res.n_ann))]
+        anns = Annotation.wrap_batch(self.keypoints, self.out_skeleton, res.data, res.scales, res.pre,
+                                     res.order, self._neighbours)
         out, k = [], 0
-        for n in counts.tolist():
+        for n in res.n_ann.tolist():
             out.append(anns[k:k + n])
             k += n
         return out
@@ -217,18 +211,10 @@ class CifCaf(Generator):
             params.inverse = (pack_metas(metas, device),
                               hflip_target(metas, len(self.keypoints), device))
         if isinstance(cif, torch.Tensor) and cif.is_cuda:
-            buf = eng.run_device(cif, caf, params)
-            n_ann = buf.dev['n_ann'].cpu().numpy()         # synchronises the stream
-            status = buf.dev['status'].cpu().numpy()
-            if status.any():
-                raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
-            nmax = int(n_ann.max(initial=0))
-            npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
-            data = buf.dev['ann_data'][:, :nmax].cpu().numpy()
-            scales = buf.dev['ann_scales'][:, :nmax].cpu().numpy()
-            source = buf.dev['ann_source'][:, :nmax].cpu().numpy()
-            pre_data = buf.dev['pre_data'][:, :npre].cpu().numpy()
-            pre_order = buf.dev['pre_order'][:, :npre].cpu().numpy()
+            # kernels + one small copy (header and live rows of the packed result block), one sync
+            buf = eng.run_device(cif, caf, params, fetch=True)
+            torch.cuda.current_stream(cif.device).synchronize()
+            res = eng.collect(buf)
         else:
             # pipelined: annotations of chunk k are built while chunk k+1.. are still
             # being copied / decoded (engine.run_host_chunked)
@@ -239,24 +225,24 @@ class CifCaf(Generator):
             else:
                 chunks = eng.run_host_chunked(cif, caf, params, self.host_chunk)
             for buf, b0, b1 in chunks:
-                h = buf.host
-                result.extend(self._annotations_from(
-                    h['n_ann'].numpy(), h['ann_data'].numpy(), h['ann_scales'].numpy(),
-                    h['ann_source'].numpy(), h['pre_data'].numpy(), h['pre_order'].numpy(), b0, b1))
+                result.extend(self._annotations_from(buf.host_result(b0, b1 - b0)))
             self.last_decoder_time = time.perf_counter() - start
             return result
-        result = self._annotations_from(n_ann, data, scales, source, pre_data, pre_order)
+        result = self._annotations_from(res)
         if has_initial:
-            self._adopt_initial(result, source, initial_annotations)
+            self._adopt_initial(result, res.source, initial_annotations)
         self.last_decoder_time = time.perf_counter() - start
         return result
 
     @staticmethod
     def _adopt_initial(result, source, initial):
-        """The reference mutates and returns the caller's initial Annotation objects."""
+        """The reference mutates and returns the caller's initial Annotation objects.
+        ``source``: flat over the images, like the annotations of ``result``."""
+        k = 0
         for b, anns in enumerate(result):
             for r, ann in enumerate(anns):
-                src = int(source[b, r])
+                src = int(source[k])
+                k += 1
                 if src < len(initial[b]):
                     orig = initial[b][src]
                     orig.data = ann.data
@@ -280,15 +266,18 @@ class CifCaf(Generator):
         first = next(batches, None)
         if first is None:
             return
+        # where the host thread's time went (seconds, this call): enqueueing work, blocked waiting for
+        # results, building the Annotation objects; the rest is the caller's own time between items
+        stats = self.stream_stats = {'submit_s': 0.0, 'wait_s': 0.0, 'build_s': 0.0}
+        clock = time.perf_counter
         if not (isinstance(first[0], torch.Tensor) and first[0].is_cuda):
             import itertools
             result = []
             for _, buf, nb, last in eng.run_host_stream(itertools.chain([first], batches), params,
-                                                        self.stream_chunk, self.stream_lanes):
-                h = buf.host
-                result.extend(self._annotations_from(
-                    h['n_ann'].numpy(), h['ann_data'].numpy(), h['ann_scales'].numpy(),
-                    h['ann_source'].numpy(), h['pre_data'].numpy(), h['pre_order'].numpy(), 0, nb))
+                                                        self.stream_chunk, self.stream_lanes, stats=stats):
+                t0 = clock()
+                result.extend(self._annotations_from(buf.host_result(0, nb)))
+                stats['build_s'] += clock() - t0
                 if last:
                     yield result
                     result = []
@@ -298,22 +287,20 @@ class CifCaf(Generator):
         tickets = []
 
         def collect(ticket):
+            t0 = clock()
             buf = ticket.wait()
-            n_ann = buf.dev['n_ann'].cpu().numpy()
-            status = buf.dev['status'].cpu().numpy()
-            if status.any():
-                raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
-            nmax = int(n_ann.max(initial=0))
-            npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
-            return self._annotations_from(
-                n_ann, buf.dev['ann_data'][:, :nmax].cpu().numpy(),
-                buf.dev['ann_scales'][:, :nmax].cpu().numpy(), buf.dev['ann_source'][:, :nmax].cpu().numpy(),
-                buf.dev['pre_data'][:, :npre].cpu().numpy(), buf.dev['pre_order'][:, :npre].cpu().numpy())
+            t1 = clock()
+            out = self._annotations_from(eng.collect(buf))
+            stats['wait_s'] += t1 - t0
+            stats['build_s'] += clock() - t1
+            return out
 
         for cif, caf in batches:
             if len(tickets) == n_lanes:
                 yield collect(tickets.pop(0))
-            tickets.append(eng.submit(cif, caf, params, n_lanes=n_lanes))
+            t0 = clock()
+            tickets.append(eng.submit(cif, caf, params, n_lanes=n_lanes, fetch=True))
+            stats['submit_s'] += clock() - t0
         while tickets:
             yield collect(tickets.pop(0))
 
@@ -343,19 +330,12 @@ class CifCaf(Generator):
         has_initial = bool(initial_annotations) and any(len(a) for a in initial_annotations)
         if has_initial:
             params.initial = self._initial_tensors(initial_annotations, device)
-        buf = eng.run_device_multiscale(sets, params, hflip_pairs=len(sets) == 10)
-        n_ann = buf.dev['n_ann'].cpu().numpy()
-        status = buf.dev['status'].cpu().numpy()
-        if status.any():
-            raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(status))
-        nmax = int(n_ann.max(initial=0))
-        npre = int(buf.dev['n_pre'].max().item()) if nmax else 0
-        source = buf.dev['ann_source'][:, :nmax].cpu().numpy()
-        result = self._annotations_from(
-            n_ann, buf.dev['ann_data'][:, :nmax].cpu().numpy(), buf.dev['ann_scales'][:, :nmax].cpu().numpy(),
-            source, buf.dev['pre_data'][:, :npre].cpu().numpy(), buf.dev['pre_order'][:, :npre].cpu().numpy())
+        buf = eng.run_device_multiscale(sets, params, hflip_pairs=len(sets) == 10, fetch=True)
+        torch.cuda.current_stream(device).synchronize()
+        res = eng.collect(buf)
+        result = self._annotations_from(res)
         if has_initial:
-            self._adopt_initial(result, source, initial_annotations)
+            self._adopt_initial(result, res.source, initial_annotations)
         self.last_decoder_time = time.perf_counter() - start
         return result
 

@@ -36,8 +36,12 @@ class ShardedDecoder:
     :param group: torch.distributed process group (None = default / single process).
     """
 
-    def __init__(self, decode_batch: Callable, *, chunk: int = 64, group=None):
+    def __init__(self, decode_batch: Callable, *, chunk: int = 64, group=None, decode_stream: Callable = None):
         self.decode_batch = decode_batch
+        # optional ``CifCaf.decode_stream``: the chunks of the shard are kept in flight (copies, kernels,
+        # result copies and Annotation construction of successive chunks overlap) instead of one
+        # synchronous call per chunk; same results
+        self.decode_stream = decode_stream
         self.chunk = chunk
         self.group = group
 
@@ -60,11 +64,14 @@ class ShardedDecoder:
         rank, world = self.rank_world()
         lo, hi = shard_bounds(n_images, world, rank)
         results = []
-        for a, b in chunk_ranges(lo, hi, self.chunk):
-            cif, caf = get_fields(a, b)
-            out = self.decode_batch(cif, caf)
+        ranges = list(chunk_ranges(lo, hi, self.chunk))
+        if self.decode_stream is not None:
+            outs = self.decode_stream(get_fields(a, b) for a, b in ranges)
+        else:
+            outs = (self.decode_batch(*get_fields(a, b)) for a, b in ranges)
+        for (a, b), out in zip(ranges, outs):
             if len(out) != b - a:
-                raise RuntimeError('decode_batch returned %d results for %d images' % (len(out), b - a))
+                raise RuntimeError('decode returned %d results for %d images' % (len(out), b - a))
             results.extend(out)
         return lo, results
 

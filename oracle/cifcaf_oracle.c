@@ -27,7 +27,10 @@
  * tests/test_oracle_vs_reference.py and by the fixtures in tests/golden/
  * written by oracle/gen_golden.py.
  */
+#define _POSIX_C_SOURCE 200809L
 #include <math.h>
+#include <pthread.h>
+#include <unistd.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -124,31 +127,64 @@ static float scalar_value_at(const float *field, long fh, long fw, float x, floa
 /* cif: (F,5,H,W); hr: (F,Hh,Wh) written (zero-initialised here).             */
 
 /* CifHr.accumulate of one head into ta (not zeroed here): cif_hr.py:26-41 */
-static int cifhr_accumulate(const float *cif, int F, int H, int W, int istride, float min_scale,
-                            float cif_th, float len_cifs, long hh, long hw, float *ta) {
-  long n = (long)H * W;
+/* Fields are independent (one map each, cif_hr.py:26-41): worker threads take whole fields from a
+ * shared counter, so every map is still filled by ONE thread in the reference's source order and
+ * nothing changes but the wall time (a raw random-init 641 px image: 91 s -> ~8 s on 16 cores). */
+static int g_threads = 0;     /* 0 = one per online core */
+void orc_set_threads(int n) { g_threads = n > 0 ? n : 0; }
+
+typedef struct {
+  const float *cif; int F, H, W; float stride, min_scale, cif_th, len_cifs; long hh, hw; float *ta;
+  int next, failed;
+} cifhr_job;
+
+static void *cifhr_worker(void *arg) {
+  cifhr_job *j = (cifhr_job *)arg;
+  long n = (long)j->H * j->W;
   float *buf = (float *)malloc(sizeof(float) * 4 * (size_t)n);
-  if (!buf) return ORC_ERR_ARG;
+  if (!buf) { j->failed = 1; return NULL; }
   float *sx = buf, *sy = buf + n, *ss = buf + 2 * n, *sv = buf + 3 * n;
-  float stride = (float)istride;
-  for (int f = 0; f < F; f++) {
-    const float *p = cif + (size_t)f * 5 * n;
+  const float stride = j->stride, min_scale = j->min_scale;
+  for (;;) {
+    int f = __sync_fetch_and_add(&j->next, 1);
+    if (f >= j->F) break;
+    const float *p = j->cif + (size_t)f * 5 * n;
     long k = 0;
     for (long c = 0; c < n; c++) {
-      if (!(p[c] > cif_th)) continue;                            /* cif_hr.py:27 */
+      if (!(p[c] > j->cif_th)) continue;                         /* cif_hr.py:27 */
       if (min_scale != 0.0f && !(p[4 * n + c] > min_scale / stride)) continue; /* :28-29 */
       sx[k] = p[n + c] * stride;                                 /* :32 */
       sy[k] = p[2 * n + c] * stride;                             /* :33 */
       float sg = 0.5f * p[4 * n + c];
       sg = sg * stride;
       ss[k] = (sg != sg) ? sg : (1.0f > sg ? 1.0f : sg);         /* np.maximum :34 */
-      sv[k] = p[c] / 16.0f / len_cifs;                           /* :40 */
+      sv[k] = p[c] / 16.0f / j->len_cifs;                        /* :40 */
       k++;
     }
-    splat_gauss_with_max(ta + (size_t)f * hh * hw, hh, hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
+    splat_gauss_with_max(j->ta + (size_t)f * j->hh * j->hw, j->hh, j->hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
   }
   free(buf);
-  return ORC_OK;
+  return NULL;
+}
+
+static int cifhr_accumulate(const float *cif, int F, int H, int W, int istride, float min_scale,
+                            float cif_th, float len_cifs, long hh, long hw, float *ta) {
+  cifhr_job job = {cif, F, H, W, (float)istride, min_scale, cif_th, len_cifs, hh, hw, ta, 0, 0};
+  long nt = g_threads > 0 ? g_threads : sysconf(_SC_NPROCESSORS_ONLN);
+  if (nt > F) nt = F;
+  if (nt > 64) nt = 64;
+  /* small maps: not worth a thread */
+  if (nt <= 1 || (size_t)F * hh * hw < (size_t)1 << 21) {
+    cifhr_worker(&job);
+    return job.failed ? ORC_ERR_ARG : ORC_OK;
+  }
+  pthread_t th[64];
+  int started = 0;
+  for (long t = 0; t < nt - 1; t++)
+    if (pthread_create(&th[started], NULL, cifhr_worker, &job) == 0) started++;
+  cifhr_worker(&job);
+  for (int t = 0; t < started; t++) pthread_join(th[t], NULL);
+  return job.failed ? ORC_ERR_ARG : ORC_OK;
 }
 
 int orc_cifhr(const float *cif, int F, int H, int W, const orc_config *cfg, float *hr) {
@@ -1143,3 +1179,4 @@ double orc_annotation_score(const float *data /* (F,3) */, int F) {
 
 float orc_detexp(float x) { return pp_expf(x); }
 int orc_config_size(void) { return (int)sizeof(orc_config); }
+

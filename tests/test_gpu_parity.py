@@ -21,9 +21,9 @@ CASES = [
 ]
 
 
-def run_gpu(decoder, cifs, cafs, skeleton, keep=('ann', 'hr', 'seeds', 'caf'), **param_kw):
+def run_gpu(decoder, cifs, cafs, skeleton, keep=('ann', 'hr', 'seeds', 'caf'), ann_cap=256, **param_kw):
     from openpifpaf_b200.decoder.engine import DecoderParams, DeviceDecoder
-    eng = DeviceDecoder(skeleton)
+    eng = DeviceDecoder(skeleton, ann_cap=ann_cap)
     cif = torch.from_numpy(np.stack(cifs)).cuda()
     caf = torch.from_numpy(np.stack(cafs)).cuda()
     buf = eng.run_device(cif, caf, DecoderParams(**param_kw), keep=keep)
@@ -205,6 +205,56 @@ def test_gpu_matches_reference_golden(configured_decoder, name):
 
 
 # ---------------------------------------------------------------------------
+# BASELINE configs[1] and configs[4] at their stated sizes
+
+@pytest.mark.parametrize('max_scale', [20.0, None], ids=['tamed', 'raw'])
+def test_real_random_init_image_bit_exact(oracle, coco_skeleton, configured_decoder, max_scale):
+    """BASELINE configs[1]: the fields of a randomly initialised resnet50 + cif / caf heads on a
+    torch.randn 641 x 641 image (openpifpaf_b200.workloads, the network of network/factory.py:62-133),
+    raw (scales up to 1e18, ~39 k seeds, ~940 annotations) and with the scale channels clamped to 20
+    cells.  The reference raises TypeError on such fields (frontier tie, cifcaf.py:261,285); the C oracle
+    decodes them (raw: ~10-16 s on the host cores, tamed: ~1 s) and the CUDA path must agree with it on
+    hr, seeds, both CafScored lists, grown and final annotations, decoding order and scores."""
+    from openpifpaf_b200 import workloads
+    cif, caf = workloads.random_init_head_fields(1, (641, 641), seed=0, image_seed=1, device='cuda',
+                                                 max_scale=max_scale)
+    cif, caf = cif[0].cpu().numpy(), caf[0].cpu().numpy()
+    assert (cif[:, 0] > 0.1).mean() > 0.4                    # SURVEY 8d: 56 % of the cells are active
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, ann_cap=4096)
+    o = check_image(oracle, out, 0, cif, caf, coco_skeleton)
+    assert len(o.seeds) > 30000 and len(o.data) > 800
+
+
+def test_dense_641_batch256(oracle, configured_decoder):
+    """BASELINE configs[4]: dense 44-link skeleton, 641 x 641, batch 256.  Image 0 is the
+    `dense_641_5p` golden (checked against the running reference above) and is compared with the oracle
+    here; every image of the batch of 256 must equal the same image decoded alone."""
+    from openpifpaf_b200.datasets.constants import COCO_PERSON_SKELETON, DENSER_COCO_PERSON_CONNECTIONS
+    skeleton = list(COCO_PERSON_SKELETON) + list(DENSER_COCO_PERSON_CONNECTIONS)
+    n_distinct = 8
+    items = [fields((641, 641), 5, pose_seed=s, jitter_seed=s + 1, dense=True) for s in range(n_distinct)]
+    singles = []
+    for i, (cif, caf, _) in enumerate(items):
+        out = run_gpu(configured_decoder, [cif], [caf], skeleton)
+        if i in (0, 5):
+            assert len(check_image(oracle, out, 0, cif, caf, skeleton).data) >= 5
+        singles.append(out)
+    idx = [(7 * i + i // n_distinct) % n_distinct for i in range(256)]
+    big = run_gpu(configured_decoder, [items[j][0] for j in idx], [items[j][1] for j in idx], skeleton,
+                  keep=('ann', 'seeds'))
+    assert not big['status'].any()
+    for i, j in enumerate(idx):
+        one = singles[j]
+        n, ns, npre = one['n_ann'][0], one['n_seeds'][0], one['n_pre'][0]
+        assert big['n_ann'][i] == n and big['n_seeds'][i] == ns and big['n_pre'][i] == npre
+        assert np.array_equal(big['seeds'][i, :ns], one['seeds'][0, :ns])
+        assert np.array_equal(big['ann_data'][i, :n], one['ann_data'][0, :n])
+        assert np.array_equal(big['ann_scales'][i, :n], one['ann_scales'][0, :n])
+        assert np.array_equal(big['ann_score'][i, :n], one['ann_score'][0, :n])
+        assert np.array_equal(big['pre_order'][i, :npre], one['pre_order'][0, :npre])
+
+
+# ---------------------------------------------------------------------------
 # full-size properties (BASELINE config sizes; no oracle needed)
 
 def test_batch64_properties(configured_decoder, coco_skeleton):
@@ -246,16 +296,34 @@ def test_host_entry_equals_device_entry(configured_decoder, coco_skeleton):
     eng = DeviceDecoder(coco_skeleton)
     buf = eng.run_host(torch.from_numpy(cif).pin_memory(), torch.from_numpy(caf).pin_memory(),
                        DecoderParams())
-    for k in ('n_ann', 'ann_data', 'ann_scales', 'ann_score', 'ann_source', 'pre_order'):
-        h = buf.host[k].numpy()
-        for b in range(3):
-            n = dev['n_ann'][b]
-            if k == 'n_ann':
-                assert h[b] == n
-            elif k == 'pre_order':
-                assert np.array_equal(h[b, :dev['n_pre'][b]], dev[k][b, :dev['n_pre'][b]])
-            else:
-                assert np.array_equal(h[b, :n], dev[k][b, :n]), k
+    res = buf.host_result()          # the packed block is all that comes back (pp_outputs.packed)
+    assert np.array_equal(res.n_ann, dev['n_ann']) and np.array_equal(res.n_pre, dev['n_pre'])
+    assert not res.status.any()
+    k = 0
+    for b in range(3):
+        n = dev['n_ann'][b]
+        rows = slice(k, k + n)
+        assert np.array_equal(res.data[rows], dev['ann_data'][b, :n])
+        assert np.array_equal(res.scales[rows], dev['ann_scales'][b, :n])
+        assert np.array_equal(res.score[rows], dev['ann_score'][b, :n])
+        assert np.array_equal(res.source[rows], dev['ann_source'][b, :n])
+        src = dev['ann_source'][b, :n]
+        assert np.array_equal(res.pre[rows], dev['pre_data'][b][src])
+        assert np.array_equal(res.order[rows], dev['pre_order'][b][src])
+        k += n
+    assert k == res.total
+    # and the standalone gather on the device buffers of the first run
+    from openpifpaf_b200 import _lib
+    import ctypes as C
+    eng2 = DeviceDecoder(coco_skeleton)
+    buf2 = eng2.run_device(torch.from_numpy(cif).cuda(), torch.from_numpy(caf).cuda(), DecoderParams())
+    buf2.dev['packed'].zero_()
+    _lib.check(_lib.lib().pp_pack_results(C.byref(buf2.d_out), C.byref(buf2.shape), C.byref(buf2.caps), None))
+    torch.cuda.synchronize()
+    buf2.enqueue_fetch(1)            # a guess that is too small: the remainder path
+    torch.cuda.synchronize()
+    res2, _ = buf2.finish_fetch()
+    assert res2.total == res.total and np.array_equal(res2.data, res.data) and np.array_equal(res2.order, res.order)
 
 
 def test_sharded_single_rank(configured_decoder, coco_skeleton):
