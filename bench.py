@@ -108,6 +108,8 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--host-chunk', type=int, default=0, help='e2e: images per pipeline chunk (0 = decoder default)')
     ap.add_argument('--cpu-workers', type=int, default=0, help='reference arm: pool size (0 = all cores)')
+    ap.add_argument('--tuning', default='', help='experiments: schedule knobs of pp_params, e.g. cifhr_ctas_per_sm=2')
+    ap.add_argument('--value-only', action='store_true', help='experiments: print value / one-lane stages and stop')
     return ap.parse_args()
 
 
@@ -675,6 +677,8 @@ def run_b200(args):
         decoder.CifCaf.host_chunk = args.host_chunk
     eng = dec.engine()
     params = dec.params()
+    if args.tuning:
+        params.tuning = {k: int(v) for k, v in (kv.split('=') for kv in args.tuning.split(','))}
     d_batches = [(torch.from_numpy(np.ascontiguousarray(c)).to(device),
                   torch.from_numpy(np.ascontiguousarray(a)).to(device)) for c, a in zip(cifs, cafs)]
     h_batches = [(torch.from_numpy(np.ascontiguousarray(c)).pin_memory(),
@@ -747,6 +751,17 @@ def run_b200(args):
     dev_ms = _median(pass_ms)
     lane_stage_ms = prof.read().astype(np.float64)
     params.profile = None
+    if args.value_only:
+        if rank == 0:
+            print(json.dumps({'value': world * batch * steps / (dev_ms * 1e-3), 'ms_per_step': dev_ms / steps,
+                              'one_lane_ms_per_step': single_ms / steps, 'tuning': args.tuning, 'lanes': lanes,
+                              'stages_ms': {n: round(float(v), 4) for n, v in zip(prof.names, stage_ms.mean(axis=0))},
+                              'stages_ms_in_flight': {n: round(float(v), 4) for n, v in
+                                                      zip(prof.names, lane_stage_ms.mean(axis=0))}}), flush=True)
+            clocks.stop()
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
 
     # ---- end to end through the public API ---------------------------------------------------------
     # Every leg: E2E_PASSES passes of K steps, wall clock around a pass (perf_counter between a barrier and

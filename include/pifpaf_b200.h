@@ -28,6 +28,9 @@
  *   cif  (B, F, 5, H, W)  channels [conf, x, y, logb, scale], x/y in field cells
  *   caf  (B, L, 9, H, W)  channels [conf, x1, y1, logb1, s1, x2, y2, logb2, s2]
  *   hr   (B, F, Hh, Wh)   Hh = (H-1)*stride+1, Wh = (W-1)*stride+1
+ * cif / caf device pointers may point anywhere (4-byte aligned) inside an allocation whose base is
+ * 16-byte aligned (cudaMalloc: 256): the kernels stage whole confidence planes with bulk copies
+ * that round their byte range out to 16-byte boundaries.
  */
 #ifndef PIFPAF_B200_H_
 #define PIFPAF_B200_H_

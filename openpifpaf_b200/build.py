@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libpifpaf_b200.so')
 SOURCES = ['api.cu', 'cifhr.cu', 'seeds.cu', 'caf_scored.cu', 'assemble.cu', 'nms.cu', 'shim.cu', 'head.cu', 'inverse.cu', 'det.cu', 'pack.cu']
-HEADERS = ['common.cuh', 'stages.cuh', 'nms.cuh', 'occupancy.cuh', '../../include/pifpaf_b200.h',
+HEADERS = ['common.cuh', 'stages.cuh', 'nms.cuh', 'occupancy.cuh', 'caf_prescan.cuh', '../../include/pifpaf_b200.h',
            '../../include/pifpaf_detmath.h']
 NVCC_FLAGS = [
     '-gencode', 'arch=compute_100a,code=sm_100a',

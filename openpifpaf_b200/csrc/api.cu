@@ -181,11 +181,12 @@ const char *pp_stage_name(int stage) {
   return (stage >= 0 && stage < PP_N_STAGES) ? names[stage] : "?";
 }
 
-/* Launches one pp_decode_batch enqueues with d_out->packed set (the bindings always set it): 8 kernels
- * (compact, splat, seeds from sources, seed sort, CafScored, candidate binning, assembly with the NMS as
- * its tail, result gather) + 3 memsets (status, work cursors, raw seed counts). */
+/* Launches one single-scale pp_decode_batch enqueues with d_out->packed set (the bindings always set it):
+ * 7 kernels (field scan = CIF compact + raw CAF candidates, splat, seeds from sources, seed sort, CafScored
+ * scoring + binning, assembly with the NMS as its tail, result gather) + 3 memsets (status, work cursors,
+ * raw seed counts). */
 int pp_decode_launch_count(const pp_params *p) {
-  int n = PP_N_STAGES + 4;
+  int n = PP_N_STAGES + 3;
   if (p && p->force_complete) n += 4;   // second CafScored, its binning, complete_kernel, nms_kernel
   if (p && p->inverse) n += 1;          // annotations_inverse_kernel
   return n;
@@ -445,12 +446,25 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   // CifHr.fill (cif_hr.py:66-78): one map per group, merged with np.maximum; with 10 heads the
   // groups are the hflip pairs (i, i + 5), each accumulated with v / neighbors / 2
   const int n_groups = hflip_pairs ? n_sets / 2 : n_sets;
+  // One field set with worst-case list capacity: the hr-independent half of CafScored rides in the CIF
+  // compact launch (raw candidates into the forward lists) and one kernel after the splat finishes the
+  // lists and bins them.  Otherwise (multi-scale, shrunken caf_cap) the stage kernels run one by one.
+  const bool caf_split = n_sets == 1 && c->caf_cap >= s->H * s->W && !(dbg_skip & (2 | 16));
+  CafPreArgs pre = {};
+  if (caf_split) {
+    const float stride = (float)s->stride;
+    pre.caf = sets[0].caf; pre.caf_rest = sets[0].caf_rest; pre.raw = fwd; pre.n_raw = nfwd;
+    pre.L = s->L; pre.cap = c->caf_cap; pre.th = p->caf_threshold;
+    pre.min_dist = sets[0].caf_min_distance / stride; pre.use_min = sets[0].caf_min_distance != 0.0f;
+    pre.max_dist = sets[0].caf_max_distance / stride; pre.use_max = sets[0].caf_max_distance > 0.0f;
+  }
   for (int g = 0; g < n_groups && !(dbg_skip & 16); g++) {
     const pp_shape q = set_shape(g);
     const float *second = hflip_pairs ? sets[g + n_groups].cif : nullptr;
     if (second && (sets[g + n_groups].H != q.H || sets[g + n_groups].W != q.W)) return PP_ERR_ARG;
     if ((rc = cifhr_launch_ex(sets[g].cif, second, hr, w.stage, q, *s, *c, *p, sets[g].cif_min_scale,
-                              o->status, st, 0, g > 0, second ? nullptr : sets[g].cif_rest)))
+                              o->status, st, 0, g > 0, second ? nullptr : sets[g].cif_rest,
+                              caf_split ? &pre : nullptr)))
       return rc;
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
@@ -469,15 +483,20 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   if (!(dbg_skip & 1) && (rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0)))
     return rc;
   // CafScored.fill (caf_scored.py:89-98): lists concatenated over the heads
-  for (int k = 0; k < n_sets && !(dbg_skip & 2); k++)
+  for (int k = 0; k < n_sets && !(dbg_skip & 2) && !caf_split; k++)
     if ((rc = caf_scored_launch_ex(sets[k].caf, hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, set_shape(k),
                                    *s, *c, *p, sets[k].caf_min_distance, sets[k].caf_max_distance, k > 0,
                                    o->status, st, sets[k].caf_rest)))
       return rc;
   AsmArgs a = {};
   a.seeds = seeds; a.n_seeds = n_seeds;
-  if (!(dbg_skip & 2) && (rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st)))
+  if (caf_split) {
+    if ((rc = caf_score_bin_launch(hr, *sk, p->caf_threshold, fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s,
+                                   *c, *p, o->status, st)))
+      return rc;
+  } else if (!(dbg_skip & 2) && (rc = caf_bin_launch(fwd, nfwd, bwd, nbwd, w.bin_rows, w.bin_start, *s, *c, st))) {
     return rc;
+  }
   a.rows = w.bin_rows; a.start = w.bin_start; a.geo = bin_geo(*s); a.nfwd = nfwd; a.nbwd = nbwd;
   a.occ_cnt = w.occ_cnt; a.occ_rec = w.occ_rec;
   a.pre_data = o->pre_data ? o->pre_data : w.pre_data;

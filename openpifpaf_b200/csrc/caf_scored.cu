@@ -165,17 +165,11 @@ __device__ __forceinline__ int bin_of(float x, float y, const BinGeo &g, float i
   return bin_coord(y, inv, g.nby) * g.nbx + bin_coord(x, inv, g.nbx);
 }
 
-__global__ void __launch_bounds__(kCafThreads)
-caf_bin_kernel(const float *__restrict__ fwd, const int *__restrict__ nfwd,
-               const float *__restrict__ bwd, const int *__restrict__ nbwd, float *__restrict__ rows,
-               int *__restrict__ start, int cap, BinGeo g) {
-  __shared__ int hist[kMaxBins];
-  __shared__ int warp_sum[kCafThreads / 32];
-  const int bl = blockIdx.x >> 1, dir = blockIdx.x & 1;
-  const int K = min(dir ? nbwd[bl] : nfwd[bl], cap);
-  const float *src = (dir ? bwd : fwd) + (size_t)bl * 9 * cap;
-  float *dst = rows + (size_t)blockIdx.x * kBinRows * cap;
-  int *st = start + (size_t)blockIdx.x * (g.nb + 1);
+// counting sort of one directed list by spatial bin; CTA-collective (kCafThreads threads).
+// hist: kMaxBins ints, warp_sum: kCafThreads / 32 ints of shared memory.
+__device__ __forceinline__ void bin_one_list(const float *__restrict__ src, const int K, float *__restrict__ dst,
+                                             int *__restrict__ st, const int cap, const BinGeo &g, int *hist,
+                                             int *warp_sum) {
   const float inv = 1.0f / (float)(1 << g.bshift);
   const int tid = threadIdx.x;
   for (int i = tid; i < g.nb; i += kCafThreads) hist[i] = 0;
@@ -217,6 +211,110 @@ caf_bin_kernel(const float *__restrict__ fwd, const int *__restrict__ nfwd,
     dst[5 * (size_t)cap + pos] = src[8 * (size_t)cap + k];
     dst[6 * (size_t)cap + pos] = __int_as_float(k);
   }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kCafThreads)
+caf_bin_kernel(const float *__restrict__ fwd, const int *__restrict__ nfwd,
+               const float *__restrict__ bwd, const int *__restrict__ nbwd, float *__restrict__ rows,
+               int *__restrict__ start, int cap, BinGeo g) {
+  __shared__ int hist[kMaxBins];
+  __shared__ int warp_sum[kCafThreads / 32];
+  const int bl = blockIdx.x >> 1, dir = blockIdx.x & 1;
+  const int K = min(dir ? nbwd[bl] : nfwd[bl], cap);
+  bin_one_list((dir ? bwd : fwd) + (size_t)bl * 9 * cap, K, rows + (size_t)blockIdx.x * kBinRows * cap,
+               start + (size_t)blockIdx.x * (g.nb + 1), cap, g, hist, warp_sum);
+}
+
+// CafScored.fill_caf (caf_scored.py:59-81) from the raw candidates the prescan left in fwd / nfwd
+// (threshold, distance filters and stride scaling already applied; cell order), then the spatial
+// binning of both lists for the assembly -- one CTA per (image, link).  The forward list is
+// compacted IN PLACE: entries are read 256 at a time into registers, a barrier, then written at
+// positions that can only be at or below the ones just read.
+__global__ void __launch_bounds__(kCafThreads)
+caf_score_bin_kernel(const float *__restrict__ hr, pp_skeleton sk, float *__restrict__ fwd,
+                     int *__restrict__ nfwd, float *__restrict__ bwd, int *__restrict__ nbwd,
+                     float *__restrict__ rows, int *__restrict__ start, pp_shape s, int cap, int hh, int hw,
+                     float th, float cif_floor, float cif_floor_compl, BinGeo g) {
+  __shared__ int hist[kMaxBins];
+  __shared__ int wtot_f[kCafThreads / 32], wtot_b[kCafThreads / 32];
+  const int bl = blockIdx.x;
+  const int b = bl / s.L, l = bl - b * s.L;
+  const int j1 = sk.joints[l][0] - 1, j2 = sk.joints[l][1] - 1;
+  const float *hr_b = hr + (size_t)b * s.F * hh * hw;
+  float *fo = fwd + (size_t)bl * 9 * cap;
+  float *bo = bwd + (size_t)bl * 9 * cap;
+  const int lane = lane_id(), w = warp_id(), nw = blockDim.x >> 5;
+  const int n_raw = min(nfwd[bl], cap);
+  int cnt_f = 0, cnt_b = 0;
+  for (int base = 0; base < n_raw; base += kCafThreads) {
+    const int i = base + threadIdx.x;
+    bool kf = false, kb = false;
+    float nine[9];
+    float sf = 0.f, sb = 0.f;
+    if (i < n_raw) {
+#pragma unroll
+      for (int r = 0; r < 9; r++) nine[r] = fo[(size_t)r * cap + i];
+      sb = sf = nine[0];
+      if (cif_floor < 1.0f && j1 < s.F) {                     // :61-64
+        float h = scalar_value_at(hr_b + (size_t)j1 * hh * hw, hh, hw, nine[1], nine[2], 0.0f);
+        sb = __fmul_rn(nine[0], __fadd_rn(cif_floor, __fmul_rn(cif_floor_compl, h)));
+      }
+      if (cif_floor < 1.0f && j2 < s.F) {                     // :72-75
+        float h = scalar_value_at(hr_b + (size_t)j2 * hh * hw, hh, hw, nine[5], nine[6], 0.0f);
+        sf = __fmul_rn(nine[0], __fadd_rn(cif_floor, __fmul_rn(cif_floor_compl, h)));
+      }
+      kb = sb > th;                                           // :67
+      kf = sf > th;                                           // :78
+    }
+    // two ordered CTA-wide compactions in one barrier pair (the first barrier also orders this
+    // round's reads of the forward rows before its in-place writes)
+    unsigned mf = __ballot_sync(0xffffffffu, kf), mb = __ballot_sync(0xffffffffu, kb);
+    if (lane == 0) { wtot_f[w] = __popc(mf); wtot_b[w] = __popc(mb); }
+    __syncthreads();
+    int base_f = 0, base_b = 0, tot_f = 0, tot_b = 0;
+    for (int k = 0; k < nw; k++) {
+      int tf = wtot_f[k], tb = wtot_b[k];
+      if (k < w) { base_f += tf; base_b += tb; }
+      tot_f += tf; tot_b += tb;
+    }
+    __syncthreads();
+    const unsigned below = (1u << lane) - 1u;
+    if (kb) {
+      const int k = cnt_b + base_b + __popc(mb & below);      // :68-69 row permutation
+      bo[k] = sb;
+      bo[(size_t)1 * cap + k] = nine[5]; bo[(size_t)2 * cap + k] = nine[6];
+      bo[(size_t)3 * cap + k] = nine[7]; bo[(size_t)4 * cap + k] = nine[8];
+      bo[(size_t)5 * cap + k] = nine[1]; bo[(size_t)6 * cap + k] = nine[2];
+      bo[(size_t)7 * cap + k] = nine[3]; bo[(size_t)8 * cap + k] = nine[4];
+    }
+    if (kf) {
+      const int k = cnt_f + base_f + __popc(mf & below);      // :79-80
+      fo[k] = sf;
+#pragma unroll
+      for (int r = 1; r < 9; r++) fo[(size_t)r * cap + k] = nine[r];
+    }
+    cnt_f += tot_f;
+    cnt_b += tot_b;
+  }
+  if (threadIdx.x == 0) { nfwd[bl] = cnt_f; nbwd[bl] = cnt_b; }
+  __syncthreads();          // the lists this CTA wrote are read back below
+  bin_one_list(fo, cnt_f, rows + (size_t)(2 * bl) * kBinRows * cap, start + (size_t)(2 * bl) * (g.nb + 1), cap, g,
+               hist, wtot_f);
+  bin_one_list(bo, cnt_b, rows + (size_t)(2 * bl + 1) * kBinRows * cap, start + (size_t)(2 * bl + 1) * (g.nb + 1),
+               cap, g, hist, wtot_f);
+}
+
+int caf_score_bin_launch(const float *d_hr, const pp_skeleton &sk, float score_th, float *d_fwd, int *d_nfwd,
+                         float *d_bwd, int *d_nbwd, float *d_rows, int *d_start, const pp_shape &s,
+                         const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st) {
+  (void)d_status;          // cap >= H * W on this path: nothing can overflow
+  prof_mark(p.profile, kStCaf, st);
+  caf_score_bin_kernel<<<s.B * s.L, kCafThreads, 0, st>>>(d_hr, sk, d_fwd, d_nfwd, d_bwd, d_nbwd, d_rows, d_start,
+                                                         s, c.caf_cap, hr_h(s), hr_w(s), score_th, p.cif_floor,
+                                                         p.cif_floor_compl, bin_geo(s));
+  PP_LAUNCH_CHECK("caf_score_bin_kernel");
+  return PP_OK;
 }
 
 int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, const int *d_nbwd,

@@ -118,26 +118,42 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c, int rshift_p
 
 // ---------------------------------------------------------------------------
 // K1: ordered compaction of CIF sources per (image, field).
-__global__ void __launch_bounds__(kCompactThreads, 8)
-cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2,
-                   const float *__restrict__ rest, CifHrWs w, pp_shape s, int src_cap, int hh, int hw,
-                   float v_th, float min_scale_over_stride, int use_min_scale, int det,
-                   int *__restrict__ status) {
-  extern __shared__ int sm_diff[];   // nstrips + 1 difference array
-  __shared__ int warp_tot[kCompactThreads / 32];
-  const int bf = blockIdx.x;
+struct CompactArgs {
+  const float *cif, *cif2, *rest;
+  CifHrWs w;
+  pp_shape s;
+  int src_cap, hh, hw;
+  float v_th, min_scale_over_stride;
+  int use_min_scale, det;
+  int *status;
+};
+
+// dynamic shared memory of a scan CTA (compact or CAF prescan): [nstrips + 1 ints, padded to 16 bytes]
+// [staged confidence values: 4 * slab + 32 bytes][active-cell list: 2 * slab bytes]
+__host__ __device__ inline size_t scan_smem_diff_bytes(int nstrips) { return ((size_t)(nstrips + 1) * 4 + 15) & ~(size_t)15; }
+__host__ __device__ inline size_t scan_smem_bytes(int nstrips, int cells) {
+  const size_t slab = (size_t)(cells < kCompactSlab ? cells : kCompactSlab);
+  return scan_smem_diff_bytes(nstrips) + 4 * slab + 32 + 2 * slab;
+}
+
+__device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int bf, int *sm_diff, float *stage,
+                                                 unsigned short *s_cells, uint64_t *bar, int *warp_tot) {
+  const float *__restrict__ cif = a.cif, *__restrict__ cif2 = a.cif2, *__restrict__ rest = a.rest;
+  const CifHrWs &w = a.w;
+  const pp_shape &s = a.s;
+  const int src_cap = a.src_cap, hh = a.hh, hw = a.hw, use_min_scale = a.use_min_scale, det = a.det;
+  const float v_th = a.v_th, min_scale_over_stride = a.min_scale_over_stride;
+  int *__restrict__ status = a.status;
+  uint32_t phase = 0;
   const int n = s.H * s.W;
   // cif2 != NULL: a multi-scale hflip pair accumulated into one map, first all sources of cif, then
   // of cif2, each with v / neighbors / 2 (cif_hr.py:55-57,66-70)
   const float len_cifs = cif2 ? 2.0f : 1.0f;
   const float stride = (float)s.stride;
-  for (int i = threadIdx.x; i <= w.nstrips; i += blockDim.x) sm_diff[i] = 0;
-  __syncthreads();
 
   float4 *oa = w.src_a + (size_t)bf * src_cap;
   int4 *ob = w.src_b + (size_t)bf * src_cap;
   float2 *oc = w.src_c + (size_t)bf * src_cap;
-  unsigned short *s_cells = (unsigned short *)(sm_diff + w.nstrips + 1);   // active cells of one slab (relative)
   int count = 0;
   for (int pass = 0; pass < (cif2 ? 2 : 1); pass++) {
   const float *p = (pass ? cif2 : cif) + (size_t)bf * (det ? 7 : 5) * n;   // CifDet: [v, x, y, _, w, h, _]
@@ -147,8 +163,10 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   for (int slab = 0; slab < n; slab += kCompactSlab) {
     // phase 1: cells above the threshold in row-major order (cif_hr.py:27); phase 2: one listed cell
     // per thread.  (Interleaving the two per 256 cells cost ~26 serial load + barrier rounds.)
-    const int n_act = block_active_cells<kCompactThreads>(p, slab, min(n, slab + kCompactSlab), v_th, s_cells,
-                                                          warp_tot);
+    // the slab's confidence values arrive in shared memory by one bulk copy (common.cuh)
+    const int m = min(n, slab + kCompactSlab) - slab;
+    const float *sp = stage_floats(p + slab, m, stage, bar, phase);
+    const int n_act = block_active_cells_smem<kCompactThreads>(sp, m, v_th, s_cells, warp_tot);
     for (int base = 0; base < n_act; base += blockDim.x) {
       const int i = base + threadIdx.x;
       bool flag = i < n_act;
@@ -156,7 +174,7 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
       float conf = 0.f, c4 = 0.f, c5 = 0.f;
       if (flag) {
         c = slab + s_cells[i];
-        conf = __ldg(p + c);
+        conf = sp[s_cells[i]];
         c4 = __ldg(pr + 4 * n + c);
         if (det) c5 = __ldg(pr + 5 * n + c);
         if (use_min_scale) flag = c4 > min_scale_over_stride;               // :28-29
@@ -194,6 +212,7 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
       }
       count += total;
     }
+    __syncthreads();        // everyone is done with the staged slab before the next copy lands in it
   }
   }
   __syncthreads();
@@ -255,6 +274,37 @@ cif_compact_kernel(const float *__restrict__ cif, const float *__restrict__ cif2
   }
 }
 
+
+}  // namespace pp
+
+#include "caf_prescan.cuh"
+
+namespace pp {
+
+// One launch for every confidence-plane scan of a decode: blocks [0, n_cif) compact the CIF sources
+// of one (image, field) each, the others collect the raw CAF candidates of one (image, link) each
+// (caf_prescan.cuh; nothing there depends on the hr map, which does not exist yet).
+__global__ void __launch_bounds__(kCompactThreads, 4)
+fields_scan_kernel(CompactArgs a, CafPreArgs pa, int n_cif) {
+  extern __shared__ __align__(16) unsigned char scan_smem[];
+  __shared__ int warp_tot[kCompactThreads / 32];
+  __shared__ __align__(8) uint64_t bar;
+  const int cells = a.s.H * a.s.W;
+  const size_t slab = (size_t)min(cells, kCompactSlab);
+  int *sm_diff = reinterpret_cast<int *>(scan_smem);
+  float *stage = reinterpret_cast<float *>(scan_smem + scan_smem_diff_bytes(a.w.nstrips));
+  unsigned short *s_cells = reinterpret_cast<unsigned short *>(scan_smem + scan_smem_diff_bytes(a.w.nstrips) +
+                                                               4 * slab + 32);
+  if (threadIdx.x == 0) mbar_init(&bar, 1);
+  __syncthreads();
+  if ((int)blockIdx.x < n_cif) {
+    for (int i = threadIdx.x; i <= a.w.nstrips; i += blockDim.x) sm_diff[i] = 0;
+    __syncthreads();
+    cif_compact_body(a, blockIdx.x, sm_diff, stage, s_cells, &bar, warp_tot);
+  } else {
+    caf_prescan_body<kCompactThreads, kCompactSlab>(pa, a.s, blockIdx.x - n_cif, stage, s_cells, &bar, warp_tot);
+  }
+}
 
 // ---------------------------------------------------------------------------
 // K2: strips -> HBM.
@@ -662,19 +712,30 @@ CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c) {
 
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
-                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest) {
+                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest,
+                    const CafPreArgs *caf_pre) {
   CifHrWs w = carve(d_ws, s_hr, c, p.cifhr_rshift);
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
   if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
-  size_t smem = (size_t)(w.nstrips + 1) * sizeof(int) + (size_t)min(s.H * s.W, kCompactSlab) * sizeof(unsigned short);
+  // (the bulk loads of the confidence planes round their range out to 16-byte boundaries: field tensors
+  // must live in allocations whose base is 16-byte aligned -- cudaMalloc gives 256 -- see pifpaf_b200.h)
+  const size_t smem = scan_smem_bytes(w.nstrips, s.H * s.W);
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
-  cif_compact_kernel<<<bf, kCompactThreads, smem, st>>>(
-      d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold, min_scale / (float)s.stride,
-      min_scale != 0.0f, det, d_status);
-  PP_LAUNCH_CHECK("cif_compact_kernel");
+  CompactArgs ca = {d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold,
+                    min_scale / (float)s.stride, min_scale != 0.0f, det, d_status};
+  CafPreArgs pa = {};
+  int n_caf = 0;
+  if (caf_pre) {
+    pa = *caf_pre;
+    n_caf = s.B * pa.L;
+  }
+  PP_CUDA_CHECK(cudaFuncSetAttribute(fields_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)scan_smem_bytes(4096, kCompactSlab)));
+  fields_scan_kernel<<<bf + n_caf, kCompactThreads, smem, st>>>(ca, pa, bf);
+  PP_LAUNCH_CHECK("fields_scan_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
   const size_t dyn = ((size_t)kZeroFloats + 2 * (size_t)buf_floats) * sizeof(float);
@@ -699,7 +760,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,
                  const pp_params &p, int *d_status, cudaStream_t st, int det) {
   return cifhr_launch_ex(d_cif, nullptr, d_hr, d_ws, s, s, c, p, p.cif_min_scale, d_status, st, det, 0,
-                         nullptr);
+                         nullptr, nullptr);
 }
 
 }  // namespace pp

@@ -167,4 +167,86 @@ __device__ __forceinline__ int block_active_cells(const float *__restrict__ conf
   return total;
 }
 
+// ---- TMA bulk staging of a linear run of floats into shared memory --------------------------------
+// One elected thread arms an mbarrier with the byte count and issues ONE cp.async.bulk (global ->
+// shared, no tensor map: a confidence plane is linear memory); everybody waits on the barrier.  A
+// whole plane (26 KB at 641 px) is in flight at once instead of a few loads per thread per round
+// trip, which is what bounded the compact / CafScored kernels.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+
+// Stage the floats [g, g + n) into `stage` (16-byte aligned, room for 4 n + 32 bytes).  The copy
+// starts at the 16-byte boundary at or below g and ends at the one at or above g + n: callers pass
+// planes that are followed by more planes of the same tensor and whose tensor base is 16-byte
+// aligned, so the few extra bytes are inside the allocation.  CTA-collective: every thread calls it
+// with the same arguments, `phase` is the per-thread parity of the barrier (starts at 0, flipped
+// here).  The previous contents of `stage` must no longer be read by anyone (__syncthreads before).
+__device__ __forceinline__ const float *stage_floats(const float *g, int n, float *stage, uint64_t *bar,
+                                                     uint32_t &phase) {
+  const uintptr_t a = (uintptr_t)g;
+  const uint32_t mis = (uint32_t)(a & 15u);
+  const uint32_t bytes = (mis + 4u * (uint32_t)n + 15u) & ~15u;
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                 ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(stage)), "l"(a - mis), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+  }
+  mbar_wait(bar, phase);
+  phase ^= 1u;
+  return reinterpret_cast<const float *>(reinterpret_cast<const char *>(stage) + mis);
+}
+
+// block_active_cells on a plane staged in shared memory: `sp` = the n staged values.  Same result
+// (ordered list of the cells with value > th, as 16-bit offsets) and the same two barriers.
+template <int THREADS>
+__device__ __forceinline__ int block_active_cells_smem(const float *sp, int n, float th, unsigned short *list,
+                                                       int *warp_cnt) {
+  constexpr int NW = THREADS / 32;
+  const int lane = lane_id(), w = warp_id();
+  const int seg = (((n + NW - 1) / NW) + 31) & ~31;          // cells per warp, a multiple of 32
+  const int w0 = w * seg, w1 = min(n, w0 + seg);
+  int cnt = 0;
+  for (int base = w0; base < w1; base += 32) {
+    const int c = base + lane;
+    cnt += __popc(__ballot_sync(0xffffffffu, c < w1 && sp[c] > th));
+  }
+  if (lane == 0) warp_cnt[w] = cnt;
+  __syncthreads();
+  int at = 0, total = 0;
+#pragma unroll
+  for (int i = 0; i < NW; i++) {
+    const int t = warp_cnt[i];
+    if (i < w) at += t;
+    total += t;
+  }
+  const unsigned below = (1u << lane) - 1u;
+  if (cnt) {
+    for (int base = w0; base < w1; base += 32) {
+      const int c = base + lane;
+      const bool hit = c < w1 && sp[c] > th;
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) list[at + __popc(m & below)] = (unsigned short)c;
+      at += __popc(m);
+    }
+  }
+  __syncthreads();
+  return total;
+}
+
 }  // namespace pp

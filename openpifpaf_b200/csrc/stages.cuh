@@ -17,9 +17,22 @@ struct CifSrcView {
   int src_cap;
 };
 CifSrcView cifhr_sources(void *d_ws, const pp_shape &s_hr, const pp_caps &c);
+// Raw CAF candidate collection riding in the CIF compact launch (single field set; the part of
+// CafScored.fill_caf that does not need the hr map: threshold, distance filters, stride scaling --
+// caf_scored.py:42-58).  The lists are finished by caf_score_bin_launch once the hr map exists.
+struct CafPreArgs {
+  const float *caf;        // (B,L,9,H,W)
+  const float *caf_rest;   // where planes 1..8 are read (host-mapped input), or NULL = caf
+  float *raw;              // (B,L,9,cap): candidates above the threshold, rows 1..8 scaled by the stride, cell order
+  int *n_raw;              // (B,L)
+  int L, cap;
+  float th, min_dist, max_dist;      // distances in field cells
+  int use_min, use_max;
+};
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
-                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest = nullptr);
+                    int *d_status, cudaStream_t st, int det, int merge, const float *cif_rest = nullptr,
+                    const CafPreArgs *caf_pre = nullptr);
 size_t seeds_ws_bytes(const pp_shape &s, const pp_caps &c, int det = 0);
 // the two halves of seeds_launch, for multi-scale: collect per field set (reset = first set), sort once
 int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, const pp_shape &s,
@@ -77,6 +90,11 @@ constexpr int kMaxBins = 2048;
 BinGeo bin_geo(const pp_shape &s);
 size_t binned_rows_bytes(const pp_shape &s, const pp_caps &c);    // one (fwd + bwd) store
 size_t binned_start_bytes(const pp_shape &s);
+// CafScored.fill_caf from the raw candidates of CafPreArgs (in d_fwd / d_nfwd): hr gathers, both
+// ordered compactions (the forward list in place), then the spatial binning of both lists.
+int caf_score_bin_launch(const float *d_hr, const pp_skeleton &sk, float score_th, float *d_fwd, int *d_nfwd,
+                         float *d_bwd, int *d_nbwd, float *d_rows, int *d_start, const pp_shape &s,
+                         const pp_caps &c, const pp_params &p, int *d_status, cudaStream_t st);
 int caf_bin_launch(const float *d_fwd, const int *d_nfwd, const float *d_bwd, const int *d_nbwd,
                    float *d_rows, int *d_start, const pp_shape &s, const pp_caps &c, cudaStream_t st);
 
