@@ -122,7 +122,8 @@ typedef struct pp_params {
   int32_t force_complete;        /* CifCaf.force_complete      */
   int32_t nms;                   /* 0: CifCaf(nms=None)        */
   int32_t exp_mode;              /* 1 = deterministic pp_expf (default), 0 = CUDA expf */
-  uint32_t seed_mask;            /* FieldConfig.seed_mask as bits (0 = all fields seed) */
+  uint32_t seed_mask;            /* FieldConfig.seed_mask as bits (0 = all fields seed, unless
+                                    seed_mask_enabled); fields beyond PP_MAX_F cannot be masked */
   struct pp_profile *profile;    /* optional per-stage CUDA-event timer (NULL = off)    */
   const pp_initial *initial;     /* optional initial annotations (NULL = none)          */
   const pp_inverse *inverse;     /* optional annotations_inverse after the NMS (NULL = none) */
@@ -142,6 +143,8 @@ typedef struct pp_params {
   int32_t cifhr_group;           /* strips per splat work item (default 3)                               */
   int32_t cifhr_ctas_per_sm;     /* persistent splat CTAs per SM (default 3)                             */
   int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
+  float cif_neighbors;           /* CifHr.neighbors (cif_hr.py:15,40): v / neighbors; 0 = 16            */
+  int32_t seed_mask_enabled;     /* 1: seed_mask applies even when it is all zero (no field seeds)      */
 } pp_params;
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
@@ -233,6 +236,15 @@ size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c);
 int pp_cifhr_accumulate(const float *d_cif, float *d_hr, void *d_ws, size_t ws_bytes,
                         const pp_shape *s, const pp_caps *c, const pp_params *p,
                         int32_t *d_status, void *stream);
+
+/* CifHr.fill_multiple (cif_hr.py:42-64): up to two heads accumulated into ONE map with v / neighbors / n_heads
+ * (d_cif2 = the second head of an hflip pair, or NULL), then either stored (merge = 0, the first call
+ * of a CifHr object) or merged into the existing d_hr with np.maximum (merge = 1, every later scale). */
+/* det != 0: CifDet fields (B,C,7,H,W), sigma = max(1, 0.1 min(w, h) stride) (CifDetHr, cif_hr.py:84-100).
+ * s_hr: the shape (H, W, stride of the FIRST head filled) that defines the hr map, NULL = s. */
+int pp_cifhr_accumulate_ex(const float *d_cif, const float *d_cif2, float *d_hr, int32_t merge, int32_t det,
+                           void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_shape *s_hr,
+                           const pp_caps *c, const pp_params *p, int32_t *d_status, void *stream);
 
 /* CifSeeds.fill + get(): sorted seeds (v,f,x,y,s).  cif_seeds.py:23-54. */
 int pp_cif_seeds(const float *d_cif, const float *d_hr, float *d_seeds, int32_t *d_n_seeds,

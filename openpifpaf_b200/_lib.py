@@ -74,7 +74,8 @@ class Params(C.Structure):
         ('seed_mask', C.c_uint32), ('profile', C.c_void_p), ('initial', C.POINTER(Initial)),
         ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32), ('in_flight', C.c_int32),
         ('asm_heavy_seeds', C.c_int32), ('asm_stage_kb', C.c_int32), ('cifhr_group', C.c_int32),
-        ('cifhr_ctas_per_sm', C.c_int32), ('cifhr_rshift', C.c_int32),
+        ('cifhr_ctas_per_sm', C.c_int32), ('cifhr_rshift', C.c_int32), ('cif_neighbors', C.c_float),
+        ('seed_mask_enabled', C.c_int32),
     ]
 
 
@@ -180,6 +181,8 @@ def lib():
     l.pp_cifcaf_assemble.argtypes = [vp] * 10 + [P(Skeleton), P(Outputs), vp, sz, P(Shape), P(Caps),
                                                  P(Params), vp]
     l.pp_keypoint_nms.argtypes = [vp, vp, vp, vp, vp, vp, sz, P(Shape), P(Caps), P(Params), vp]
+    l.pp_cifhr_accumulate_ex.argtypes = [vp, vp, vp, i32, i32, vp, sz, P(Shape), P(Shape), P(Caps), P(Params),
+                                         vp, vp]
     l.pp_keypoint_nms_noalloc.argtypes = [vp, vp, vp, vp, vp, P(Shape), P(Caps), P(Params), vp]
     l.pp_keypoint_nms_noalloc_max_bytes.restype = sz
     l.pp_keypoint_nms_noalloc_max_bytes.argtypes = []
@@ -220,7 +223,7 @@ EXPORTS = (
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_keypoint_nms_noalloc', 'pp_keypoint_nms_noalloc_max_bytes', 'pp_keypoint_nms_noalloc_bytes',
-    'pp_packed_bytes', 'pp_packed_record_words', 'pp_packed_header_words', 'pp_pack_results',
+    'pp_cifhr_accumulate_ex', 'pp_packed_bytes', 'pp_packed_record_words', 'pp_packed_header_words', 'pp_pack_results',
     'pp_decode_batch_host', 'pp_decode_batch_host_async', 'pp_pipeline_create',
     'pp_pipeline_destroy', 'pp_pipeline_wait', 'pp_pipeline_chunks', 'pp_scalar_square_add_gauss_with_max', 'pp_scalar_values',
     'pp_caf_center_s', 'pp_scalar_nonzero_clipped_with_reduction', 'pp_scalar_square_add_single',

@@ -288,6 +288,21 @@ int pp_cifhr_accumulate(const float *d_cif, float *d_hr, void *d_ws, size_t ws_b
   return cifhr_launch(d_cif, d_hr, d_ws, *s, *c, *p, d_status, (cudaStream_t)stream);
 }
 
+int pp_cifhr_accumulate_ex(const float *d_cif, const float *d_cif2, float *d_hr, int32_t merge, int32_t det,
+                           void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_shape *s_hr,
+                           const pp_caps *c, const pp_params *p, int32_t *d_status, void *stream) {
+  if (!s || !(det ? (s->B > 0 && s->F > 0 && s->F <= PP_MAX_CATEGORIES && s->H > 0 && s->W > 0 && s->stride > 0)
+                  : shape_ok(s)))
+    return PP_ERR_ARG;
+  if (!caps_ok(s, c) || !p || !d_cif || !d_hr || !d_ws || !d_status) return PP_ERR_ARG;
+  pp_shape q = s_hr ? *s_hr : *s;
+  q.B = s->B; q.F = s->F; q.L = s->L;
+  if (q.H <= 0 || q.W <= 0 || q.stride <= 0) return PP_ERR_ARG;
+  if (ws_bytes < cifhr_ws_bytes(q, *c)) return PP_ERR_WORKSPACE;
+  return cifhr_launch_ex(d_cif, d_cif2, d_hr, d_ws, *s, q, *c, *p, p->cif_min_scale, d_status,
+                         (cudaStream_t)stream, det != 0, merge != 0, nullptr, nullptr);
+}
+
 int pp_cif_seeds(const float *d_cif, const float *d_hr, float *d_seeds, int32_t *d_n_seeds,
                  void *d_ws, size_t ws_bytes, const pp_shape *s, const pp_caps *c,
                  const pp_params *p, int32_t *d_status, void *stream) {
@@ -469,7 +484,8 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
   if (dbg_skip & 1) {
-  } else if (n_sets == 1 && p->seed_threshold >= p->cif_threshold) {
+  } else if (n_sets == 1 && p->seed_threshold >= p->cif_threshold &&
+             (p->cif_neighbors == 0.0f || p->cif_neighbors == 16.0f)) {
     // the seed candidates are a subset of the sources the CifHr stage compacted: skip the field scan
     if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, *p,
                                                 st, 0)))
@@ -570,7 +586,8 @@ int pp_decode_batch(const float *d_cif, const float *d_caf, const pp_skeleton *s
 // confidence planes are copied (strided DMA, 14 % of the bytes) and the kernels fetch the rest of
 // the active cells over PCIe on demand.
 static bool mapped_applies(const pp_params *p) {
-  return p->host_mapped && !p->force_complete && p->seed_threshold >= p->cif_threshold;
+  return p->host_mapped && !p->force_complete && p->seed_threshold >= p->cif_threshold &&
+         (p->cif_neighbors == 0.0f || p->cif_neighbors == 16.0f);     // = the seeds come from the compacted sources
 }
 
 // device-visible alias of a pinned host buffer, or NULL

@@ -126,6 +126,7 @@ struct CompactArgs {
   float v_th, min_scale_over_stride;
   int use_min_scale, det;
   int *status;
+  float neighbors;       // CifHr.neighbors
 };
 
 // dynamic shared memory of a scan CTA (compact or CAF prescan): [nstrips + 1 ints, padded to 16 bytes]
@@ -196,7 +197,7 @@ __device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int
             sg = __fmul_rn(__fmul_rn(0.5f, c4), stride);
           }
           float sigma = (sg != sg) ? sg : fmaxf(1.0f, sg);          // np.maximum(1.0, .) :34
-          float cv = __fdiv_rn(__fdiv_rn(conf, 16.0f), len_cifs);   // v / neighbors / len_cifs :40
+          float cv = __fdiv_rn(__fdiv_rn(conf, a.neighbors), len_cifs);   // v / neighbors / len_cifs :40
           // functional.pyx:122-125 with truncate = 1.0
           int minx = (int)clipf(__fsub_rn(cx, sigma), 0.0f, (float)(hw - 1));
           int maxx = (int)clipf(__fadd_rn(__fadd_rn(cx, sigma), 1.0f), (float)(minx + 1), (float)hw);
@@ -725,7 +726,8 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
   CompactArgs ca = {d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold,
-                    min_scale / (float)s.stride, min_scale != 0.0f, det, d_status};
+                    min_scale / (float)s.stride, min_scale != 0.0f, det, d_status,
+                    p.cif_neighbors > 0.0f ? p.cif_neighbors : 16.0f};
   CafPreArgs pa = {};
   int n_caf = 0;
   if (caf_pre) {

@@ -37,13 +37,13 @@ __global__ void __launch_bounds__(kCollectThreads)
 seeds_collect_kernel(const float *__restrict__ cif, const float *__restrict__ hr,
                      float *__restrict__ raw, int *__restrict__ n_raw, pp_shape s, int cap, int hh,
                      int hw, float th, float score_scale, float min_scale_over_stride,
-                     int use_min_scale, uint32_t seed_mask) {
+                     int use_min_scale, uint32_t seed_mask, int mask_on) {
   const int n = s.H * s.W;
   const int blocks_per_field = (n + kCollectThreads - 1) / kCollectThreads;
   const int bf = blockIdx.x / blocks_per_field;
   const int c = (blockIdx.x - bf * blocks_per_field) * kCollectThreads + threadIdx.x;
   const int b = bf / s.F, f = bf - b * s.F;
-  if (seed_mask != 0u && !((seed_mask >> f) & 1u)) return;        // cif_seeds.py:29-30
+  if (mask_on && !((seed_mask >> (f & 31)) & 1u)) return;         // cif_seeds.py:29-30
   const float *p = cif + (size_t)bf * (REC == 6 ? 7 : 5) * n;
   const float stride = (float)s.stride;
   bool keep = false;
@@ -90,10 +90,10 @@ template <int REC>
 __global__ void __launch_bounds__(128)
 seeds_from_sources_kernel(CifSrcView src, const float *__restrict__ hr, float *__restrict__ raw,
                           int *__restrict__ n_raw, int F, int cap, int hh, int hw, float th,
-                          float score_scale, uint32_t seed_mask) {
+                          float score_scale, uint32_t seed_mask, int mask_on) {
   const int bf = blockIdx.x;
   const int b = bf / F, f = bf - b * F;
-  if (seed_mask != 0u && !((seed_mask >> f) & 1u)) return;        // cif_seeds.py:29-30
+  if (mask_on && !((seed_mask >> (f & 31)) & 1u)) return;         // cif_seeds.py:29-30
   const int n = min(src.n[bf], src.src_cap);
   const float4 *sa = src.a + (size_t)bf * src.src_cap;
   const float2 *sc = src.c + (size_t)bf * src.src_cap;
@@ -268,11 +268,12 @@ int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, cons
   if (det)
     seeds_collect_kernel<6><<<blocks, kCollectThreads, 0, st>>>(
         d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-        min_scale / (float)s.stride, min_scale != 0.0f, 0u);
+        min_scale / (float)s.stride, min_scale != 0.0f, 0u, 0);
   else
     seeds_collect_kernel<5><<<blocks, kCollectThreads, 0, st>>>(
         d_cif, d_hr, w.raw, w.n_raw, s, c.seed_cap, hh, hw, p.seed_threshold, p.seed_score_scale,
-        min_scale / (float)s.stride, min_scale != 0.0f, p.seed_mask);
+        min_scale / (float)s.stride, min_scale != 0.0f, p.seed_mask,
+        p.seed_mask_enabled || p.seed_mask != 0u);
   PP_LAUNCH_CHECK("seeds_collect_kernel");
   return PP_OK;
 }
@@ -286,10 +287,11 @@ int seeds_collect_from_sources_launch(const CifSrcView &src, const float *d_hr, 
   PP_CUDA_CHECK(cudaMemsetAsync(w.n_raw, 0, (size_t)s.B * sizeof(int), st));
   if (det)
     seeds_from_sources_kernel<6><<<s.B * s.F, 128, 0, st>>>(src, d_hr, w.raw, w.n_raw, s.F, c.seed_cap, hh, hw,
-                                                           p.seed_threshold, p.seed_score_scale, 0u);
+                                                           p.seed_threshold, p.seed_score_scale, 0u, 0);
   else
     seeds_from_sources_kernel<5><<<s.B * s.F, 128, 0, st>>>(src, d_hr, w.raw, w.n_raw, s.F, c.seed_cap, hh, hw,
-                                                           p.seed_threshold, p.seed_score_scale, p.seed_mask);
+                                                           p.seed_threshold, p.seed_score_scale, p.seed_mask,
+                                                           p.seed_mask_enabled || p.seed_mask != 0u);
   PP_LAUNCH_CHECK("seeds_from_sources_kernel");
   return PP_OK;
 }

@@ -26,6 +26,7 @@ class DecoderParams:
     nms_instance_threshold: float = 0.0
     nms_suppression: float = 0.0
     cif_min_scale: float = 0.0
+    cif_neighbors: float = 16.0
     caf_min_distance: float = 0.0
     caf_max_distance: Optional[float] = None
     connection_method: str = 'blend'
@@ -64,6 +65,7 @@ class DecoderParams:
         p.nms_keypoint_threshold = self.nms_keypoint_threshold
         p.nms_suppression = self.nms_suppression
         p.cif_min_scale = self.cif_min_scale or 0.0
+        p.cif_neighbors = float(self.cif_neighbors)
         p.caf_min_distance = self.caf_min_distance or 0.0
         p.caf_max_distance = self.caf_max_distance or 0.0
         if self.connection_method not in ('blend', 'max'):
@@ -75,11 +77,13 @@ class DecoderParams:
         p.exp_mode = 1 if self.deterministic_exp else 0
         mask = 0
         if self.seed_mask is not None:
+            if len(self.seed_mask) > _lib.PP_MAX_F:
+                raise ValueError('seed_mask has %d entries, the library masks at most %d fields' % (
+                    len(self.seed_mask), _lib.PP_MAX_F))
             for i, m in enumerate(self.seed_mask):
                 if m:
                     mask |= 1 << i
-            if mask == 0:
-                mask = 1 << 31     # "no field seeds": bit outside any valid field
+            p.seed_mask_enabled = 1        # an all-False mask means "no field seeds"
         p.seed_mask = mask
         p.profile = self.profile
         p.host_mapped = int(bool(self.host_mapped))
@@ -544,7 +548,8 @@ class DeviceDecoder:
         tensors / arrays.  Yields ``(batch index, buf, n images, last sub-batch of its batch)`` in order;
         the caller copies what it needs out of ``buf.host`` before asking for the next item."""
         if params.inverse is not None or params.initial is not None:
-            raise NotImplementedError('per-image records (metas, initial annotations) go through decode_batch')
+            raise NotImplementedError('per-batch records ride in the batch tuples: (cif, caf, inverse); '
+                                      'initial annotations go through decode_batch')
         lanes = self.lanes(n_lanes)
         cur = torch.cuda.current_stream(self._device())
         if n_lanes > 1:
@@ -554,21 +559,32 @@ class DeviceDecoder:
         n_sub = [0]
 
         def items():
-            for bid, (cif, caf) in enumerate(batches):
+            # a batch is (cif, caf) or (cif, caf, inverse) with inverse = (packed metas (B, .) on the
+            # device, hflip targets) for annotations_inverse on the device (DecoderParams.inverse)
+            for bid, batch in enumerate(batches):
+                cif, caf = batch[0], batch[1]
+                inverse = batch[2] if len(batch) > 2 else None
                 cif_t = torch.as_tensor(cif).contiguous()
                 caf_t = torch.as_tensor(caf).contiguous()
                 B = cif_t.shape[0]
                 step = max(1, min(int(sub), B))
                 for b0 in range(0, B, step):
-                    yield bid, cif_t, caf_t, b0, min(b0 + step, B), b0 + step >= B
+                    yield bid, cif_t, caf_t, b0, min(b0 + step, B), b0 + step >= B, inverse
 
         def submit(item):
-            bid, cif_t, caf_t, b0, b1, last = item
+            bid, cif_t, caf_t, b0, b1, last, inverse = item
             lane = lanes[n_sub[0] % n_lanes]
             if n_sub[0] < n_lanes:
                 lane.stream.wait_stream(cur)
-            buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], params, b1 - b0, keep=keep,
-                                                 p_c=p_all, stream_ptr=lane.stream_ptr)
+            if inverse is None:
+                buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], params, b1 - b0, keep=keep,
+                                                     p_c=p_all, stream_ptr=lane.stream_ptr)
+            else:       # this sub-batch's slice of the per-image records
+                meta, target = inverse
+                sub_params = dataclasses.replace(params, inverse=(meta[b0:b1].contiguous(), target))
+                with torch.cuda.stream(lane.stream):
+                    buf, _, _ = lane.engine.enqueue_host(cif_t[b0:b1], caf_t[b0:b1], sub_params, b1 - b0,
+                                                         keep=keep)
             pending.append((lane, buf, bid, b1 - b0, last))
             n_sub[0] += 1
 

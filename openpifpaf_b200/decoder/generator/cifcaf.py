@@ -9,6 +9,7 @@ the whole batch on the GPU (csrc/*.cu) and only the finished annotations come
 back to the host.
 """
 from collections import defaultdict
+import dataclasses
 import logging
 import time
 
@@ -57,6 +58,7 @@ class CifCaf(Generator):
     stream_chunk = 32
     stream_lanes = 4
     stream_stats = None           # host-time breakdown of the last decode_stream call
+    stage_profile = None          # engine.StageProfile while decoder.profiler.Profiler wraps a call
 
     def __init__(self, field_config: FieldConfig, *,
                  keypoints,
@@ -118,6 +120,7 @@ class CifCaf(Generator):
         kp = self.nms
         return DecoderParams(
             cif_threshold=CifHr.v_threshold,
+            cif_neighbors=CifHr.neighbors,
             seed_threshold=CifSeeds.threshold,
             seed_score_scale=CifSeeds.score_scale,
             caf_threshold=CafScored.default_score_th,
@@ -135,6 +138,7 @@ class CifCaf(Generator):
             deterministic_exp=self.deterministic_exp,
             seed_mask=cfg.seed_mask,
             host_mapped=self.host_transfer in ('mapped', 'auto'),
+            profile=self.stage_profile.handle if self.stage_profile is not None else None,
         )
 
     def _use_mapped(self, cif, caf, params):
@@ -251,7 +255,7 @@ class CifCaf(Generator):
                     orig.frontier_order = list(orig.frontier_order) + list(ann.frontier_order)
                     anns[r] = orig
 
-    def decode_stream(self, batches, *, n_lanes=8):
+    def decode_stream(self, batches, *, n_lanes=8, metas=None):
         """Generator over batches ``(cif, caf)``: yields each batch's List[List[Annotation]] in order,
         with the same results as ``decode_batch`` per batch.
 
@@ -262,6 +266,18 @@ class CifCaf(Generator):
         (``stream_chunk`` images per sub-batch on ``stream_lanes`` lanes)."""
         eng = self.engine()
         params = self.params()
+        if metas is not None:
+            # ``metas``: one list of the reference's preprocessing meta dicts per batch; the annotations
+            # then come back in original-image coordinates (Preprocess.annotations_inverse on the device)
+            from ...transforms.preprocess import hflip_target, pack_metas
+            device = eng._device()
+
+            def with_inverse(pairs, meta_lists):
+                for (cif, caf), m in zip(pairs, meta_lists):
+                    if len(m) != len(cif):
+                        raise ValueError('one meta dict per image')
+                    yield cif, caf, (pack_metas(m, device), hflip_target(m, len(self.keypoints), device))
+            batches = with_inverse(batches, metas)
         batches = iter(batches)
         first = next(batches, None)
         if first is None:
@@ -295,11 +311,12 @@ class CifCaf(Generator):
             stats['build_s'] += clock() - t1
             return out
 
-        for cif, caf in batches:
+        for batch in batches:
             if len(tickets) == n_lanes:
                 yield collect(tickets.pop(0))
             t0 = clock()
-            tickets.append(eng.submit(cif, caf, params, n_lanes=n_lanes, fetch=True))
+            p_b = params if len(batch) == 2 else dataclasses.replace(params, inverse=batch[2])
+            tickets.append(eng.submit(batch[0], batch[1], p_b, n_lanes=n_lanes, fetch=True))
             stats['submit_s'] += clock() - t0
         while tickets:
             yield collect(tickets.pop(0))

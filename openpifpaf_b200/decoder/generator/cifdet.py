@@ -88,16 +88,10 @@ def run_cifdet(field, stride, *, min_scale=0.0, with_nms=True, ann_cap=1024, wan
 
 
 class CifDetHr(CifHr):
-    """``CifDetHr(config).fill(fields).accumulated`` (cif_hr.py:84-100)."""
-
-    def fill_multiple(self, cifs, stride, min_scale=0.0):
-        if len(cifs) != 1 or self.accumulated_device is not None:
-            raise NotImplementedError('multi-head CifDetHr accumulation is not built')
-        field = _stage.to_device_f32(cifs[0])
-        t = run_cifdet(field[None], stride, min_scale=min_scale, with_nms=False, want=('hr',))
-        self.accumulated_device = t['hr'][0]
-        self._host = None
-        return self
+    """``CifDetHr(config).fill(fields).accumulated`` (cif_hr.py:84-100): CifHr.fill_multiple with the
+    detection sigma, ``max(1, 0.1 min(w, h) stride)``, and the min-scale filter on both sizes."""
+    _planes = 7
+    _det = 1
 
 
 class CifDetSeeds(CifSeeds):
@@ -105,12 +99,13 @@ class CifDetSeeds(CifSeeds):
     The hr map passed in is recomputed on the device (same kernels, same bits)."""
 
     def fill_cif(self, cif, stride, *, min_scale=0.0, seed_mask=None):
-        if seed_mask is not None:
-            raise NotImplementedError('seed_mask is not built for CifDet')
         field = _stage.to_device_f32(cif)
         t = run_cifdet(field[None], stride, min_scale=min_scale, with_nms=False,
                        want=('seeds', 'n_seeds'))
         block = t['seeds'][0, :int(t['n_seeds'][0].item())].cpu().numpy()
+        if seed_mask is not None:       # cif_seeds.py:72-73: masked categories contribute no seeds
+            keep = np.asarray(seed_mask, dtype=bool)[block[:, 1].astype(np.int64)]
+            block = block[keep]
         self._sorted_blocks.append(block)
         f = block[:, 1].astype(np.int64)
         self.seeds.extend((block[i, 0], int(f[i]), block[i, 2], block[i, 3], block[i, 4], block[i, 5])

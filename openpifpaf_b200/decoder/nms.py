@@ -61,18 +61,6 @@ class Keypoints:
 
 
 class Detection:
-    """Box NMS of the CifDet decoder (decoder/nms.py:60-102): not on the CifCaf path."""
-    suppression = 0.1
-    suppression_soft = 0.3
-    instance_threshold = 0.1
-    iou_threshold = 0.7
-    iou_threshold_soft = 0.5
-
-    def annotations(self, anns):
-        raise NotImplementedError('CifDet decoding is outside the CifCaf hot path (SURVEY.md 8f)')
-
-
-class Detection:
     """Soft NMS by IoU for detections (reference: decoder/nms.py:60-102).  Class attributes are
     the reference's knobs; inside ``CifDet`` the same routine runs fused after the seed loop."""
     suppression = 0.1

@@ -61,6 +61,7 @@ typedef struct {
   int do_nms;              /* nms is not None              cifcaf.py:117 */
   int exp_mode;            /* 0 libm, 1 deterministic      (see header)  */
   int stride;
+  float cif_neighbors;     /* CifHr.neighbors             cif_hr.py:15 (0 = 16) */
 } orc_config;
 
 /* ------------------------------------------------------------------------- */
@@ -134,7 +135,7 @@ static int g_threads = 0;     /* 0 = one per online core */
 void orc_set_threads(int n) { g_threads = n > 0 ? n : 0; }
 
 typedef struct {
-  const float *cif; int F, H, W; float stride, min_scale, cif_th, len_cifs; long hh, hw; float *ta;
+  const float *cif; int F, H, W; float stride, min_scale, cif_th, len_cifs, neighbors; long hh, hw; float *ta;
   int next, failed;
 } cifhr_job;
 
@@ -158,7 +159,7 @@ static void *cifhr_worker(void *arg) {
       float sg = 0.5f * p[4 * n + c];
       sg = sg * stride;
       ss[k] = (sg != sg) ? sg : (1.0f > sg ? 1.0f : sg);         /* np.maximum :34 */
-      sv[k] = p[c] / 16.0f / j->len_cifs;                        /* :40 */
+      sv[k] = p[c] / j->neighbors / j->len_cifs;                 /* :40 */
       k++;
     }
     splat_gauss_with_max(j->ta + (size_t)f * j->hh * j->hw, j->hh, j->hw, sx, sy, ss, sv, k, 1.0f, 1.0f);
@@ -168,8 +169,9 @@ static void *cifhr_worker(void *arg) {
 }
 
 static int cifhr_accumulate(const float *cif, int F, int H, int W, int istride, float min_scale,
-                            float cif_th, float len_cifs, long hh, long hw, float *ta) {
-  cifhr_job job = {cif, F, H, W, (float)istride, min_scale, cif_th, len_cifs, hh, hw, ta, 0, 0};
+                            float cif_th, float len_cifs, float neighbors, long hh, long hw, float *ta) {
+  cifhr_job job = {cif, F, H, W, (float)istride, min_scale, cif_th, len_cifs,
+                   neighbors > 0.0f ? neighbors : 16.0f, hh, hw, ta, 0, 0};
   long nt = g_threads > 0 ? g_threads : sysconf(_SC_NPROCESSORS_ONLN);
   if (nt > F) nt = F;
   if (nt > 64) nt = 64;
@@ -190,7 +192,8 @@ static int cifhr_accumulate(const float *cif, int F, int H, int W, int istride, 
 int orc_cifhr(const float *cif, int F, int H, int W, const orc_config *cfg, float *hr) {
   long hh = (long)(H - 1) * cfg->stride + 1, hw = (long)(W - 1) * cfg->stride + 1;
   memset(hr, 0, sizeof(float) * (size_t)F * hh * hw);
-  return cifhr_accumulate(cif, F, H, W, cfg->stride, cfg->cif_min_scale, cfg->cif_th, 1.0f, hh, hw, hr);
+  return cifhr_accumulate(cif, F, H, W, cfg->stride, cfg->cif_min_scale, cfg->cif_th, 1.0f, cfg->cif_neighbors,
+                          hh, hw, hr);
 }
 
 /* ------------------------------------------------------------------------- */
@@ -804,11 +807,11 @@ int orc_decode_ms(const orc_set *sets, int n_sets, int hflip_pairs, int F, int L
     const orc_set *a = &sets[gi];
     float len_cifs = hflip_pairs ? 2.0f : 1.0f;
     if ((rc = cifhr_accumulate(a->cif, F, a->H, a->W, a->stride, a->cif_min_scale, cfg->cif_th, len_cifs,
-                               hh, hw, dst))) return rc;
+                               cfg->cif_neighbors, hh, hw, dst))) return rc;
     if (hflip_pairs) {
       const orc_set *b = &sets[gi + n_groups];
       if ((rc = cifhr_accumulate(b->cif, F, b->H, b->W, a->stride, a->cif_min_scale, cfg->cif_th,
-                                 len_cifs, hh, hw, dst))) return rc;
+                                 len_cifs, cfg->cif_neighbors, hh, hw, dst))) return rc;
     }
     if (gi > 0)                                                                 /* np.maximum :62 */
       for (size_t i = 0; i < hr_n; i++) {

@@ -28,7 +28,7 @@ class Config(C.Structure):
         ('cif_min_scale', C.c_float), ('caf_min_distance', C.c_float),
         ('caf_max_distance', C.c_float),
         ('connection_method', C.c_int), ('greedy', C.c_int), ('force_complete', C.c_int),
-        ('do_nms', C.c_int), ('exp_mode', C.c_int), ('stride', C.c_int),
+        ('do_nms', C.c_int), ('exp_mode', C.c_int), ('stride', C.c_int), ('cif_neighbors', C.c_float),
     ]
 
     def __init__(self, **kw):
@@ -37,7 +37,7 @@ class Config(C.Structure):
                     caf_th=0.1, cif_floor=0.1, keypoint_th=0.001, nms_keypoint_th=0.001,
                     nms_suppression=0.0, cif_min_scale=0.0, caf_min_distance=0.0,
                     caf_max_distance=0.0, connection_method=0, greedy=0, force_complete=0,
-                    do_nms=1, exp_mode=0, stride=8)
+                    do_nms=1, exp_mode=0, stride=8, cif_neighbors=16.0)
         base.update(kw)
         for k, v in base.items():
             if not any(k == name for name, _ in self._fields_):

@@ -1051,3 +1051,141 @@ def test_parity_shim_primitives(oracle):
     for _ in range(256):                                # uint8 wrap: 256 sets -> free again
         wrap.set(0, 40.0, 40.0, 4.0)
     assert wrap.get(0, 40.0, 40.0) == 0
+
+
+# ---------------------------------------------------------------------------
+# stage-level mirrors: the cases round 1 left as NotImplementedError
+
+@pytest.mark.parametrize('name', ['ms_3scales_321x481', 'ms_10heads_321x481'])
+def test_cifhr_mirror_fill_multiple(oracle, configured_decoder, name):
+    """decoder.CifHr(config).fill(fields) with several scales (np.maximum merge inside the splat kernel)
+    and with ten heads (hflip pairs accumulated together with v / 16 / 2, cif_hr.py:66-72): the
+    accumulated map is the reference's (golden sha-256) and the oracle's, bit for bit."""
+    from conftest import ms_golden, sha256
+    decoder = configured_decoder
+    sets, g = ms_golden(name)
+    n = len(sets)
+    cfg = decoder.FieldConfig()
+    cfg.cif_indices, cfg.caf_indices = [2 * k for k in range(n)], [2 * k + 1 for k in range(n)]
+    cfg.cif_strides = cfg.caf_strides = [s[2] for s in sets]
+    cfg.cif_min_scales = [s[3] for s in sets]
+    cfg.caf_min_distances = [s[4] for s in sets]
+    cfg.caf_max_distances = [s[5] for s in sets]
+    fields_ = []
+    for s in sets:
+        fields_ += [s[0], s[1]]
+    hr = decoder.CifHr(cfg).fill(fields_).accumulated
+    assert sha256(hr) == str(g['hr_sha256']), 'CifHr mirror differs from the reference'
+
+
+def test_cifhr_neighbors_and_seed_mask(oracle, coco_skeleton, configured_decoder):
+    """CifHr.neighbors != 16 (v / neighbors, cif_hr.py:40) through the stage mirror and the whole
+    decode (the seeds then come from the field scan: conf = neighbors * v is no longer exact), and an
+    all-False FieldConfig.seed_mask (no field seeds => no annotations)."""
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    saved = decoder.CifHr.neighbors
+    try:
+        decoder.CifHr.neighbors = 12
+        o = oracle.decode(cif, caf, coco_skeleton, oracle.Config(exp_mode=1, cif_neighbors=12.0))
+        hr = decoder.CifHr(decoder.FieldConfig()).fill([cif, caf]).accumulated
+        assert np.array_equal(hr, o.hr)
+        dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+        anns = dec([cif, caf])
+        assert len(anns) == len(o.data) >= 8
+        for ann, d, js in zip(anns, o.data, o.joint_scales):
+            assert np.array_equal(ann.data, d) and np.array_equal(ann.joint_scales, js)
+        out = run_gpu(decoder, [cif], [caf], coco_skeleton, cif_neighbors=12.0)
+        assert np.array_equal(out['seeds'][0, :out['n_seeds'][0]], o.seeds)
+    finally:
+        decoder.CifHr.neighbors = saved
+    cfg = decoder.FieldConfig()
+    cfg.seed_mask = [0] * 17
+    assert decoder.CifCaf(cfg, keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)([cif, caf]) == []
+    cfg.seed_mask = [1] + [0] * 16          # only noses seed
+    anns = decoder.CifCaf(cfg, keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)([cif, caf])
+    assert 1 <= len(anns) <= 8 and all(a.decoding_order == [] or a.decoding_order[0][0] == 0 for a in anns)
+    with pytest.raises(ValueError):
+        from openpifpaf_b200.decoder.engine import DecoderParams
+        DecoderParams(seed_mask=[1] * 33).to_c()
+
+
+def test_cifdet_mirrors_pairs_merge_and_seed_mask(oracle, configured_det):
+    """CifDetHr.fill_multiple with two heads and a second call that merges (cif_hr.py:42-64,84-100), and
+    CifDetSeeds with a seed_mask (cif_seeds.py:72-73)."""
+    from conftest import det_golden
+    from openpifpaf_b200.decoder.generator.cifdet import CifDetHr, CifDetSeeds
+    decoder = configured_det
+    field, g = det_golden('det_321x481_8b')
+    other = field.copy()                                         # a second, different head: shifted boxes
+    other[:, 1] += 9.25
+    hr1 = CifDetHr(decoder.FieldConfig()).fill_multiple([field], 8).accumulated
+    hr2 = CifDetHr(decoder.FieldConfig()).fill_multiple([other], 8).accumulated
+    merged = CifDetHr(decoder.FieldConfig()).fill_multiple([field], 8).fill_multiple([other], 8).accumulated
+    assert np.array_equal(merged, np.maximum(hr1, hr2))
+    pair = CifDetHr(decoder.FieldConfig()).fill_multiple([field, other], 8).accumulated
+    assert pair.shape == hr1.shape and pair.max() <= 1.0
+    # v / 16 / 2 per head: where only one head contributes, every term -- and so the sum -- is exactly
+    # half of that head's own map (as long as that one is not clamped)
+    only1 = (hr1 > 0) & (hr2 == 0) & (hr1 < 1.0)
+    only2 = (hr2 > 0) & (hr1 == 0) & (hr2 < 1.0)
+    assert only1.any() and only2.any()
+    assert np.array_equal(pair[only1], hr1[only1] / 2) and np.array_equal(pair[only2], hr2[only2] / 2)
+    assert np.all(pair[(hr1 == 0) & (hr2 == 0)] == 0)
+    cfg = decoder.FieldConfig()
+    seeds_all = CifDetSeeds(hr1, cfg).fill([field]).get()
+    cfg_m = decoder.FieldConfig()
+    keep = [c % 2 for c in range(field.shape[0])]
+    cfg_m.seed_mask = keep
+    seeds_m = CifDetSeeds(hr1, cfg_m).fill([field]).get()
+    assert seeds_m == [s for s in seeds_all if keep[s[1]]] and 0 < len(seeds_m) < len(seeds_all)
+
+
+def test_decode_stream_with_metas(coco_skeleton, configured_decoder):
+    """decode_stream(batches, metas=...) == decode_batch(cif, caf, metas=...) per batch, for host
+    (pinned) and CUDA batches."""
+    from conftest import HorizontalSwap, inverse_inputs
+    from oracle.gen_golden_inverse import META_KINDS, make_meta
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    decoder = configured_decoder
+    swap = HorizontalSwap(inverse_inputs()[4])
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    dec.stream_chunk, dec.stream_lanes = 2, 3
+    batches, metas = [], []
+    for k in range(3):
+        items = [fields((161, 241), 1 + (b + k) % 3, pose_seed=600 + 10 * k + b, jitter_seed=700 + 10 * k + b)[:2]
+                 for b in range(5)]
+        batches.append((torch.from_numpy(np.stack([i[0] for i in items])).pin_memory(),
+                        torch.from_numpy(np.stack([i[1] for i in items])).pin_memory()))
+        metas.append([make_meta(META_KINDS[(b + k) % 4], swap) for b in range(5)])
+    want = [dec.decode_batch(c, a, metas=m) for (c, a), m in zip(batches, metas)]
+    for kind in ('host', 'cuda'):
+        src = batches if kind == 'host' else [(c.cuda(), a.cuda()) for c, a in batches]
+        got = list(dec.decode_stream(src, metas=metas, n_lanes=2))
+        assert len(got) == 3
+        for g_b, w_b in zip(got, want):
+            assert [len(x) for x in g_b] == [len(x) for x in w_b]
+            for g_img, w_img in zip(g_b, w_b):
+                for g, w in zip(g_img, w_img):
+                    assert np.array_equal(g.data, w.data) and np.array_equal(g.joint_scales, w.joint_scales)
+
+
+def test_profiler_wraps_stage_profile(coco_skeleton, configured_decoder, tmp_path, capsys):
+    """decoder.profiler.Profiler (the --profile-decoder wrapper): same result as the bare call, per-stage
+    device times reported and written."""
+    import json
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    from openpifpaf_b200.decoder.profiler import Profiler
+    decoder = configured_decoder
+    cif, caf, _ = fields((161, 161), 2, pose_seed=5, jitter_seed=6)
+    dec = decoder.CifCaf(decoder.FieldConfig(), keypoints=COCO_KEYPOINTS, skeleton=coco_skeleton)
+    plain = dec([cif, caf])
+    out = tmp_path / 'profile.json'
+    prof = Profiler(dec.__call__, out_name=str(out))
+    for _ in range(2):
+        got = prof([cif, caf])
+    assert len(got) == len(plain) and all(np.array_equal(g.data, p.data) for g, p in zip(got, plain))
+    rec = json.loads(out.read_text())
+    assert rec['calls'] == 2 and rec['stage_ms_per_call']['cifhr_splat'] > 0.0
+    assert 'cifhr_splat' in capsys.readouterr().out and decoder.CifCaf.stage_profile is None
