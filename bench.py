@@ -11,9 +11,10 @@ One JSON line is printed by rank 0 (contract in DESIGN.md section "Measurement")
   value         images/s, fields already resident in HBM, results left in HBM:
                 K steps (one pp_decode_batch = 8 kernels each) issued round-robin
                 over --lanes streams / workspaces and over as many DISTINCT input
-                batches, CUDA events around the K steps; the K-step pass is
-                repeated (`passes`) until >= 0.5 s have been timed and the MEDIAN
-                pass is reported;
+                batches, CUDA events around a region of R such K-step passes issued
+                back to back (the lanes fill and drain once per region); three
+                regions (>= 0.5 s in all) are timed and the median ms per K steps
+                is reported (`passes` = 3 R);
   value_one_lane, stages_ms
                 the same K steps strictly one at a time on one stream, with the
                 library's per-stage CUDA-event profile;
@@ -679,6 +680,8 @@ def run_b200(args):
     params = dec.params()
     if args.tuning:
         params.tuning = {k: int(v) for k, v in (kv.split('=') for kv in args.tuning.split(','))}
+        if 'gate' in params.tuning:                     # experiments: splat gate on / off
+            eng.use_splat_gate = bool(params.tuning.pop('gate'))
     d_batches = [(torch.from_numpy(np.ascontiguousarray(c)).to(device),
                   torch.from_numpy(np.ascontiguousarray(a)).to(device)) for c, a in zip(cifs, cafs)]
     h_batches = [(torch.from_numpy(np.ascontiguousarray(c)).pin_memory(),
@@ -726,12 +729,14 @@ def run_b200(args):
     for t in tickets:
         t.wait()
 
-    def value_pass():
+    def value_region(n_passes):
+        """n_passes x K steps issued back to back (no synchronisation between the passes, so the lanes fill
+        and drain once per region); returns the device time of the region in ms, max over ranks."""
         prof.reset()
         barrier()
         ev0.record()
         tickets = []
-        for k in range(steps):
+        for k in range(n_passes * steps):
             if len(tickets) == lanes:
                 tickets.pop(0).wait()
             tickets.append(eng.submit(*d_batches[k % n_distinct], params, n_lanes=lanes))
@@ -743,11 +748,10 @@ def run_b200(args):
             t.wait()
         return max_over_ranks(ev0.elapsed_time(ev1))
 
-    pass_ms = [value_pass()]
-    while sum(pass_ms) < 1e3 * MIN_TIMED_S and len(pass_ms) < 200:
-        pass_ms.append(value_pass())
-    while len(pass_ms) < 5:
-        pass_ms.append(value_pass())
+    est = value_region(1)
+    n_passes = int(min(400, max(1, np.ceil(1e3 * MIN_TIMED_S / 3 / est))))
+    region_ms = [value_region(n_passes) for _ in range(3)]
+    pass_ms = [r / n_passes for r in region_ms]
     dev_ms = _median(pass_ms)
     lane_stage_ms = prof.read().astype(np.float64)
     params.profile = None
@@ -920,8 +924,10 @@ def run_b200(args):
         # how `value` was issued (not part of the workload): streams / workspaces in flight and the distinct
         # input batches the steps cycle through
         'batches_in_flight': lanes, 'distinct_batches': n_distinct,
-        'passes': len(pass_ms), 'timed_region_s': sum(pass_ms) / 1e3,
-        'pass_ms': {'median': dev_ms, 'min': min(pass_ms), 'max': max(pass_ms)},
+        'passes': 3 * n_passes, 'timed_region_s': sum(region_ms) / 1e3,
+        'pass_ms': {'median': dev_ms, 'min': min(pass_ms), 'max': max(pass_ms),
+                    'how': '3 regions of %d K-step passes issued back to back (lanes fill and drain once per '
+                           'region); ms per K steps of each region, median reported' % n_passes},
         'value_note': 'device-resident: fields in HBM, results left in HBM (no copy, no Annotation objects); '
                       'the figure that compares like for like with the CPU reference is e2e / e2e_device_fields',
         'hbm_step': {'bytes_per_step': whole_step_bytes,
@@ -970,11 +976,11 @@ def run_b200(args):
                           'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
                           'pcie_floor_frac': h2d_ms / (1e3 * e2e_copy_s / steps)},
         # kernels of this library launched in the reported K-step pass: per decode compact, splat, seeds from
-        # sources, seed sort, CafScored, candidate binning, assembly + NMS, result gather (8 kernels, 3 memsets)
-        'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 3) * steps,
-        'gpu_launches_per_step': _lib.lib().pp_decode_launch_count(None) - 3,
-        'gpu_launches_all_passes': (_lib.lib().pp_decode_launch_count(None) - 3) * steps * len(pass_ms),
-        'gpu_memsets_per_step': 3,
+        # sources sorted per field, seed merge, CafScored scoring + binning, assembly + NMS, result gather (7 kernels, 2 memsets)
+        'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 2) * steps,
+        'gpu_launches_per_step': _lib.lib().pp_decode_launch_count(None) - 2,
+        'gpu_launches_all_passes': (_lib.lib().pp_decode_launch_count(None) - 2) * steps * 3 * n_passes,
+        'gpu_memsets_per_step': 2,
         'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
                      'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,
                      'peak_source': peak_src, 'algorithmic_bytes_per_launch': hr_bytes,
@@ -1179,7 +1185,7 @@ def run_shard(args):
                      'achieved_gbs': world * (hr_bytes_chunk + field_bytes) * n_chunks / dev_t / 1e9,
                      'frac_of_peak': (hr_bytes_chunk + field_bytes) * n_chunks / dev_t / 1e9 / peak,
                      'peak': peak, 'peak_source': peak_src},
-        'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 3) * n_chunks,
+        'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 2) * n_chunks,
         'annotations': n_ann, 'oracle_checked_images': checked,
         'field_generation_s': gen_s,
         'clocks': clock_info,

@@ -58,6 +58,14 @@ extern "C" {
 #define PP_STATUS_CAF_OVERFLOW 2
 #define PP_STATUS_ANN_OVERFLOW 4
 #define PP_STATUS_SRC_OVERFLOW 8
+#define PP_STATUS_OVERFLOW_MASK 15
+/* Not an error (host entries do not fail on it): an image produced a connection score above 1, which
+ * needs CAF confidences above 1 (raw, un-squashed head outputs).  The assembly evaluates frontier
+ * edges eagerly; that equals the reference's lazy PriorityQueue only while evaluated scores stay at
+ * or below their bound sqrt(v_start), i.e. while connection scores are <= 1 (cifcaf.py:258-285).
+ * With this bit set the annotations are still deterministic, but their decoding order is not proven
+ * to be the reference's. */
+#define PP_STATUS_SCORE_ABOVE_ONE 16
 
 typedef struct pp_shape {
   int32_t B, F, L, H, W, stride;
@@ -145,7 +153,19 @@ typedef struct pp_params {
   int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
   float cif_neighbors;           /* CifHr.neighbors (cif_hr.py:15,40): v / neighbors; 0 = 16            */
   int32_t seed_mask_enabled;     /* 1: seed_mask applies even when it is all zero (no field seeds)      */
+  struct pp_gate *splat_gate;    /* optional (NULL = off): decodes issued on different streams with the same
+                                    gate run their CifHr splat kernels one after the other (see pp_gate) */
 } pp_params;
+
+/* A splat gate.  With several batches in flight on their own streams, the HBM-bound splat kernels of
+ * different batches otherwise run side by side, finish together and leave the memory system idle while
+ * all of them are in their latency-bound stages (a convoy).  Decodes that share a gate order ONLY their
+ * splat kernels (event chain, submission order): each splat runs alone at full bandwidth, back to back
+ * with the next, and the other stages of the other batches fill the SMs around it.  A gate belongs to
+ * the host thread that submits the decodes; results never depend on it. */
+typedef struct pp_gate pp_gate;
+pp_gate *pp_gate_create(void);
+void pp_gate_destroy(pp_gate *gate);
 
 /* Skeleton: L links of 1-based joint ids (j1, j2), as in the reference's
  * COCO_PERSON_SKELETON; confidence_scales may be NULL (cifcaf.py:39,52). */
@@ -213,6 +233,10 @@ void pp_profile_destroy(pp_profile *prof);
 void pp_profile_reset(pp_profile *prof);
 /* Synchronises the recorded events; h_ms (max_steps, PP_N_STAGES) <- ms per stage. */
 int pp_profile_read(pp_profile *prof, float *h_ms, int32_t *n_steps);
+/* The same events as absolute times: h_ms (max_steps, PP_N_STAGES + 1) <- ms from the first event of
+ * step 0 to the start of every stage of every step and to the step's end (the steps may have run on
+ * different streams: a timeline of batches in flight). */
+int pp_profile_read_abs(pp_profile *prof, float *h_ms, int32_t *n_steps);
 const char *pp_stage_name(int stage);
 /* Kernel launches + memsets one pp_decode_batch enqueues (constant per call). */
 int pp_decode_launch_count(const pp_params *p);

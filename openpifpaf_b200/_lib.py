@@ -14,6 +14,8 @@ PP_MAX_F, PP_MAX_L = 32, 64
 PP_N_STAGES = 7
 PP_OK, PP_ERR_ARG, PP_ERR_CAPACITY, PP_ERR_CUDA, PP_ERR_WORKSPACE, PP_ERR_STATIC_LIMIT = 0, -1, -2, -3, -4, -5
 STATUS_BITS = {1: 'seed_cap', 2: 'caf_cap', 4: 'ann_cap', 8: 'src_cap'}
+PP_STATUS_OVERFLOW_MASK = 15
+PP_STATUS_SCORE_ABOVE_ONE = 16    # warning, not an error: see include/pifpaf_b200.h
 
 
 class Shape(C.Structure):
@@ -75,7 +77,7 @@ class Params(C.Structure):
         ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32), ('in_flight', C.c_int32),
         ('asm_heavy_seeds', C.c_int32), ('asm_stage_kb', C.c_int32), ('cifhr_group', C.c_int32),
         ('cifhr_ctas_per_sm', C.c_int32), ('cifhr_rshift', C.c_int32), ('cif_neighbors', C.c_float),
-        ('seed_mask_enabled', C.c_int32),
+        ('seed_mask_enabled', C.c_int32), ('splat_gate', C.c_void_p),
     ]
 
 
@@ -144,6 +146,7 @@ def lib():
     l.pp_profile_reset.restype = None
     l.pp_profile_reset.argtypes = [vp]
     l.pp_profile_read.argtypes = [vp, vp, vp]
+    l.pp_profile_read_abs.argtypes = [vp, vp, vp]
     l.pp_stage_name.restype = C.c_char_p
     l.pp_stage_name.argtypes = [i32]
     l.pp_decode_launch_count.argtypes = [P(Params)]
@@ -165,6 +168,10 @@ def lib():
     l.pp_decode_batch_multiscale.argtypes = [P(FieldSet), i32, i32, P(Skeleton), P(Outputs), vp, sz,
                                              P(Shape), P(Caps), P(Params), vp]
     l.pp_sizeof.argtypes = [i32]
+    l.pp_gate_create.restype = vp
+    l.pp_gate_create.argtypes = []
+    l.pp_gate_destroy.restype = None
+    l.pp_gate_destroy.argtypes = [vp]
     l.pp_packed_bytes.restype = sz
     l.pp_packed_bytes.argtypes = [P(Shape), P(Caps)]
     l.pp_packed_record_words.argtypes = [i32]
@@ -217,7 +224,7 @@ def lib():
 
 EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
-    'pp_stage_name', 'pp_decode_launch_count',
+    'pp_stage_name', 'pp_decode_launch_count', 'pp_profile_read_abs', 'pp_gate_create', 'pp_gate_destroy',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
     'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detections_inverse', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',

@@ -30,6 +30,47 @@ int num_sms() {
 
 }  // namespace pp
 
+// ---- splat gate -------------------------------------------------------------------
+struct pp_gate {
+  static constexpr int kRing = 64;
+  cudaEvent_t ev[kRing];
+  unsigned long long issued;      // splats recorded so far
+};
+
+namespace pp {
+// make `st` wait for the splat recorded last on this gate (any stream)
+int gate_wait(pp_gate *g, cudaStream_t st) {
+  if (!g || g->issued == 0) return PP_OK;
+  PP_CUDA_CHECK(cudaStreamWaitEvent(st, g->ev[(g->issued - 1) % pp_gate::kRing], 0));
+  return PP_OK;
+}
+// the splat just enqueued on `st` is the one the next decode waits for
+int gate_signal(pp_gate *g, cudaStream_t st) {
+  if (!g) return PP_OK;
+  PP_CUDA_CHECK(cudaEventRecord(g->ev[g->issued % pp_gate::kRing], st));
+  g->issued++;
+  return PP_OK;
+}
+}  // namespace pp
+
+extern "C" pp_gate *pp_gate_create(void) {
+  pp_gate *g = (pp_gate *)calloc(1, sizeof(pp_gate));
+  if (!g) return nullptr;
+  for (int i = 0; i < pp_gate::kRing; i++)
+    if (cudaEventCreateWithFlags(&g->ev[i], cudaEventDisableTiming) != cudaSuccess) {
+      for (int j = 0; j < i; j++) cudaEventDestroy(g->ev[j]);
+      free(g);
+      return nullptr;
+    }
+  return g;
+}
+
+extern "C" void pp_gate_destroy(pp_gate *g) {
+  if (!g) return;
+  for (int i = 0; i < pp_gate::kRing; i++) cudaEventDestroy(g->ev[i]);
+  free(g);
+}
+
 // ---- per-stage timer ----------------------------------------------------------
 struct pp_profile {
   int max_steps;
@@ -175,6 +216,18 @@ int pp_profile_read(pp_profile *prof, float *h_ms, int32_t *n_steps) {
   return PP_OK;
 }
 
+int pp_profile_read_abs(pp_profile *prof, float *h_ms, int32_t *n_steps) {
+  if (!prof || !h_ms || !n_steps) return PP_ERR_ARG;
+  *n_steps = prof->step;
+  for (int s = 0; s < prof->step; s++) {
+    cudaEvent_t *e = prof->ev + (size_t)s * (PP_N_STAGES + 1);
+    PP_CUDA_CHECK(cudaEventSynchronize(e[PP_N_STAGES]));
+    for (int k = 0; k <= PP_N_STAGES; k++)
+      PP_CUDA_CHECK(cudaEventElapsedTime(&h_ms[(size_t)s * (PP_N_STAGES + 1) + k], prof->ev[0], e[k]));
+  }
+  return PP_OK;
+}
+
 const char *pp_stage_name(int stage) {
   static const char *names[PP_N_STAGES] = {"cif_compact", "cifhr_splat", "seeds_collect", "seeds_sort",
                                            "caf_scored", "assemble", "nms"};
@@ -182,11 +235,10 @@ const char *pp_stage_name(int stage) {
 }
 
 /* Launches one single-scale pp_decode_batch enqueues with d_out->packed set (the bindings always set it):
- * 7 kernels (field scan = CIF compact + raw CAF candidates, splat, seeds from sources, seed sort, CafScored
- * scoring + binning, assembly with the NMS as its tail, result gather) + 3 memsets (status, work cursors,
- * raw seed counts). */
+ * 7 kernels (field scan = CIF compact + raw CAF candidates, splat, per-field seed sort, seed merge, CafScored
+ * scoring + binning, assembly with the NMS as its tail, result gather) + 2 memsets (status, work cursors). */
 int pp_decode_launch_count(const pp_params *p) {
-  int n = PP_N_STAGES + 3;
+  int n = PP_N_STAGES + 2;
   if (p && p->force_complete) n += 4;   // second CafScored, its binning, complete_kernel, nms_kernel
   if (p && p->inverse) n += 1;          // annotations_inverse_kernel
   return n;
@@ -483,20 +535,28 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
       return rc;
   }
   // CifSeeds.fill (cif_seeds.py:56-65): every head on its own, one sorted list
+  bool seeds_done = false;
   if (dbg_skip & 1) {
   } else if (n_sets == 1 && p->seed_threshold >= p->cif_threshold &&
              (p->cif_neighbors == 0.0f || p->cif_neighbors == 16.0f)) {
     // the seed candidates are a subset of the sources the CifHr stage compacted: skip the field scan
-    if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, *p,
-                                                st, 0)))
+    if (seeds_segmented_ok(*s, *c)) {
+      if ((rc = seeds_segmented_launch(cifhr_sources(w.stage, *s, *c), hr, seeds, n_seeds, w.seed_stage, *s, *c,
+                                       *p, st, 0)))
+        return rc;
+      seeds_done = true;
+    } else if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c,
+                                                       *p, st, 0))) {
       return rc;
+    }
   } else {
     for (int k = 0; k < n_sets; k++)
       if ((rc = seeds_collect_launch(sets[k].cif, hr, w.seed_stage, set_shape(k), *s, *c, *p,
                                      sets[k].cif_min_scale, k == 0, st, 0)))
         return rc;
   }
-  if (!(dbg_skip & 1) && (rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0)))
+  if (!(dbg_skip & 1) && !seeds_done &&
+      (rc = seeds_sort_launch(seeds, n_seeds, w.seed_stage, s->B, *c, *p, o->status, st, 0)))
     return rc;
   // CafScored.fill (caf_scored.py:89-98): lists concatenated over the heads
   for (int k = 0; k < n_sets && !(dbg_skip & 2) && !caf_split; k++)
@@ -696,7 +756,11 @@ int pp_cifdet_decode_batch(const float *d_field, const pp_det_outputs *o, void *
   if (rc) return rc;
   float *seeds = o->seeds ? o->seeds : w.seeds;
   int *n_seeds = o->n_seeds ? o->n_seeds : w.n_seeds;
-  if (q.seed_threshold >= q.cif_threshold) {      // seeds from the compacted sources (see decode_core)
+  if (q.seed_threshold >= q.cif_threshold && seeds_segmented_ok(*s, *c)) {
+    if ((rc = seeds_segmented_launch(cifhr_sources(w.stage, *s, *c), hr, seeds, n_seeds, w.seed_stage, *s, *c, q,
+                                     st, 1)))
+      return rc;
+  } else if (q.seed_threshold >= q.cif_threshold) {      // seeds from the compacted sources (see decode_core)
     if ((rc = seeds_collect_from_sources_launch(cifhr_sources(w.stage, *s, *c), hr, w.seed_stage, *s, *c, q,
                                                 st, 1)))
       return rc;
@@ -801,7 +865,7 @@ static size_t packed_prefix_bytes(size_t nb, int F, size_t records) {
 static bool packed_block_overflowed(const void *h_block, size_t nb) {
   const int32_t *w = (const int32_t *)h_block;
   for (size_t b = 0; b < nb; b++)
-    if (w[4 + nb + b] != 0) return true;
+    if ((w[4 + nb + b] & PP_STATUS_OVERFLOW_MASK) != 0) return true;
   return false;
 }
 
@@ -848,7 +912,7 @@ int pp_decode_batch_host(const float *h_cif, const float *h_caf, float *d_cif, f
   }
   if (h_out->status)
     for (size_t b = 0; b < B; b++)
-      if (h_out->status[b] != 0) return PP_ERR_CAPACITY;
+      if ((h_out->status[b] & PP_STATUS_OVERFLOW_MASK) != 0) return PP_ERR_CAPACITY;
   return PP_OK;
 }
 
@@ -1024,7 +1088,7 @@ int pp_pipeline_wait(pp_pipeline *q, int chunk) {
     const int b0 = k0 * q->chunk_images;
     const int b1 = k1 * q->chunk_images < q->B ? k1 * q->chunk_images : q->B;
     for (int b = b0; b < b1; b++)
-      if (q->h_status[b] != 0) return PP_ERR_CAPACITY;
+      if ((q->h_status[b] & PP_STATUS_OVERFLOW_MASK) != 0) return PP_ERR_CAPACITY;
   }
   return PP_OK;
 }

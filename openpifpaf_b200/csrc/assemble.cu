@@ -314,7 +314,7 @@ struct GrowView {
   int *p_start, *p_end;
   int *dec;          // (F, 2) decoding_order (start, end)
   int *scratch;      // (kScratch)
-  int *meta;         // [0] decoding steps
+  int *meta;         // [0] decoding steps, [1] a connection score above 1 was seen
 };
 
 __host__ __device__ inline int grow_words(int F, int E) {
@@ -349,6 +349,9 @@ __device__ Xysv warp_connection_value(const GrowView &w, const Graph &g, const C
   const float sx = w.data[3 * start], sy = w.data[3 * start + 1], sv = w.data[3 * start + 2];
   const float ss = w.js[start] > 0.0f ? w.js[start] : 0.0f;       // max(0.0, .)
   Xysv nw = scan_list(cf, l, fw, sx, sy, ss, w.scratch, method, exp_mode);
+  // the eager frontier equals the reference's lazy one as long as no evaluated score exceeds its
+  // bound sqrt(v_start), i.e. as long as connection scores stay <= 1
+  if (nw.v > 1.0f && lane_id() == 0) w.meta[1] = 1;
   float kp = __fsqrt_rn(__fmul_rn(nw.v, sv));                     // :201
   if (kp < keypoint_th) return zero;
   if (nw.v == 0.0f) return zero;
@@ -752,6 +755,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
   auto commit = [&](int k) {
     const GrowView v = grow_view(dyn_smem + (size_t)k * gw, F, n_edges);
     const int n_dec = v.meta[0];
+    if (threadIdx.x == 0 && v.meta[1]) atomicOr(&a.status[b], PP_STATUS_SCORE_ABOVE_ONE);
     for (int i = threadIdx.x; i < F * 3; i += blockDim.x) pre_data[(size_t)n_ann * F * 3 + i] = v.data[i];
     for (int i = threadIdx.x; i < F; i += blockDim.x) {
       pre_scales[(size_t)n_ann * F + i] = v.js[i];
@@ -828,7 +832,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
       const float *iscales = a.init_scales + ((size_t)b * a.init_cap + base + warp) * F;
       for (int i = lane; i < F * 3; i += 32) w.data[i] = idata[i];
       for (int i = lane; i < F; i += 32) w.js[i] = iscales[i];
-      if (lane == 0) w.meta[0] = 0;
+      if (lane == 0) { w.meta[0] = 0; w.meta[1] = 0; }
       __syncwarp();
       warp_grow(w, g, cscale, cf, true, p);
     }
@@ -882,6 +886,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
           w.data[3 * f] = sd[2]; w.data[3 * f + 1] = sd[3]; w.data[3 * f + 2] = sd[0];
           w.js[f] = sd[4];
           w.meta[0] = 0;
+          w.meta[1] = 0;
         }
         __syncwarp();
         warp_grow(w, g, cscale, cf, true, p);                       // :106
@@ -988,6 +993,7 @@ complete_kernel(AsmArgs a, const float *__restrict__ rows2, const int *__restric
       n1++;
     }
     w.meta[0] = n1;
+    w.meta[1] = 0;
   }
   n1 = __shfl_sync(0xffffffffu, n1, 0);
   const unsigned unfilled = __ballot_sync(0xffffffffu, lane < F && w.data[3 * lane + 2] == 0.0f);   // :340

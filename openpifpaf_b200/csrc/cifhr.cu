@@ -753,10 +753,12 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   int grid = num_sms() * per_sm;
   if (grid > bf * n_groups) grid = bf * n_groups;
   prof_mark(p.profile, kStSplat, st);
+  int rc = gate_wait(p.splat_gate, st);       // batches in flight: one splat at a time (pp_gate)
+  if (rc) return rc;
   cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
                                                     buf_floats, merge);
   PP_LAUNCH_CHECK("cifhr_splat_kernel");
-  return PP_OK;
+  return gate_signal(p.splat_gate, st);
 }
 
 int cifhr_launch(const float *d_cif, float *d_hr, void *d_ws, const pp_shape &s, const pp_caps &c,

@@ -4,6 +4,10 @@
 
 namespace pp {
 
+// splat gate (api.cu)
+int gate_wait(pp_gate *g, cudaStream_t st);
+int gate_signal(pp_gate *g, cudaStream_t st);
+
 size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c);
 // det = 1: CifDet fields (B,C,7,H,W) [v, x, y, _, w, h, _]; sigma / seed records follow
 // CifDetHr / CifDetSeeds (cif_hr.py:84-100, cif_seeds.py:67-90); seeds are 6 floats (v, f, x, y, w, h)
@@ -42,6 +46,10 @@ int seeds_collect_launch(const float *d_cif, const float *d_hr, void *d_ws, cons
 // cif_threshold, one field set, same min-scale filter): ~60 sources per plane instead of 6561 cells
 int seeds_collect_from_sources_launch(const CifSrcView &src, const float *d_hr, void *d_ws, const pp_shape &s,
                                       const pp_caps &c, const pp_params &p, cudaStream_t st, int det);
+// per-field sort + merge (seeds.cu): replaces collect-from-sources + sort when seeds_segmented_ok
+bool seeds_segmented_ok(const pp_shape &s, const pp_caps &c);
+int seeds_segmented_launch(const CifSrcView &src, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,
+                           const pp_shape &s, const pp_caps &c, const pp_params &p, cudaStream_t st, int det);
 int seeds_sort_launch(float *d_seeds, int *d_n_seeds, void *d_ws, int B, const pp_caps &c,
                       const pp_params &p, int *d_status, cudaStream_t st, int det);
 int seeds_launch(const float *d_cif, const float *d_hr, float *d_seeds, int *d_n_seeds, void *d_ws,

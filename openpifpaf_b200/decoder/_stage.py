@@ -52,7 +52,7 @@ def workspace(shape, caps, device):
 
 
 def raise_on_status(status):
-    words = status.cpu().numpy()
+    words = status.cpu().numpy() & _lib.PP_STATUS_OVERFLOW_MASK
     if words.any():
         from .engine import describe_status
         raise _lib.PifPafError(_lib.PP_ERR_CAPACITY, describe_status(words))

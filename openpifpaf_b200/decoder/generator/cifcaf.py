@@ -229,7 +229,7 @@ class CifCaf(Generator):
             else:
                 chunks = eng.run_host_chunked(cif, caf, params, self.host_chunk)
             for buf, b0, b1 in chunks:
-                result.extend(self._annotations_from(buf.host_result(b0, b1 - b0)))
+                result.extend(self._annotations_from(buf.host_result(b0, b1 - b0).check()))
             self.last_decoder_time = time.perf_counter() - start
             return result
         result = self._annotations_from(res)
@@ -292,7 +292,7 @@ class CifCaf(Generator):
             for _, buf, nb, last in eng.run_host_stream(itertools.chain([first], batches), params,
                                                         self.stream_chunk, self.stream_lanes, stats=stats):
                 t0 = clock()
-                result.extend(self._annotations_from(buf.host_result(0, nb)))
+                result.extend(self._annotations_from(buf.host_result(0, nb).check()))
                 stats['build_s'] += clock() - t0
                 if last:
                     yield result

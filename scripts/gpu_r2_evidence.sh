@@ -1,0 +1,18 @@
+#!/bin/bash
+# ncu evidence for round 2 (one GPU): launch list of the default step + one `--set full` capture of EVERY
+# kernel of a decode on the default, crowd, dense and tamed random-init workloads.  TAG=$1
+set -u
+TAG=${1:-r2n}; OUT=gpurun_out; mkdir -p $OUT
+K='fields_scan|cifhr_splat|seeds_from|seeds_collect|seeds_sort|caf_score_bin|caf_scored|caf_bin|assemble_kernel|pack_results|nms_kernel'
+BASE="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --value-only --distinct 1"
+$BASE > $OUT/${TAG}_plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv \
+    --log-file $OUT/${TAG}_launches.csv $BASE > $OUT/${TAG}_ncu_launches.log 2>&1
+for wl in coco17_641_5p crowd_1281_50p dense_641_5p randinit_641_tamed; do
+  CMD="$BASE --workload $wl"
+  $CMD > $OUT/${TAG}_plain_$wl.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k regex:"$K" -s 14 -c 7 \
+      -f -o $OUT/${TAG}_$wl $CMD > $OUT/${TAG}_ncu_$wl.log 2>&1
+  tail -2 $OUT/${TAG}_ncu_$wl.log
+done
+ls -la $OUT | grep $TAG

@@ -1,10 +1,10 @@
 #!/bin/bash
-# value under different schedule knobs (pp_params tuning fields); $1 = tag, rest = "knob=v,knob=v" sets
-OUT=gpurun_out; TAG=${1:-tune}; shift
+# value under different schedule knobs (pp_params tuning fields); $1 = tag, $2 = workload, rest = "knob=v,knob=v" sets
+OUT=gpurun_out; TAG=${1:-tune}; WL=${2:-coco17_641_5p}; shift; shift
 for t in "$@"; do
   arg=""; [ "$t" != "default" ] && arg="--tuning $t"
-  python bench.py --value-only --no-cpu-baseline $arg 2>/dev/null | python -c "
+  python bench.py --value-only --no-cpu-baseline --workload $WL --distinct 2 $arg 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1])
-print('%-44s value %7.0f  step %.4f  one-lane %.4f  in-flight %s' % ('$t', d['value'], d['ms_per_step'], d['one_lane_ms_per_step'], d['stages_ms_in_flight']))"
+print('%-40s value %7.0f  step %.4f  one-lane %.4f  stages %s' % ('$t', d['value'], d['ms_per_step'], d['one_lane_ms_per_step'], d['stages_ms']))"
 done | tee $OUT/${TAG}_sweep.log

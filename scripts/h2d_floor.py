@@ -2,8 +2,9 @@
 """Host -> device floor under the e2e legs of bench.py: every rank copies, concurrently with all the others,
 what one e2e step of the default workload moves from pinned host memory:
 
-  strided   the confidence planes only (one cudaMemcpy2D-style strided copy per tensor: 1 of 5 cif planes,
-            1 of 9 caf planes), 60 MB per 64 images -- what host_transfer='mapped' copies by DMA;
+  strided   the confidence planes only (one cudaMemcpy2DAsync per tensor, exactly the library's call: 1 of 5
+            cif planes, 1 of 9 caf planes), 60 MB per 64 images -- what host_transfer='mapped' copies by DMA
+            (strided_torch: the same bytes through torch's strided copy_, for comparison);
   plain     the same byte count as one contiguous copy;
   full      every plane (430 MB per 64 images) -- what host_transfer='copy' moves.
 
@@ -40,7 +41,19 @@ def main():
     h_plain = torch.rand((n_conf // 4,)).pin_memory()
     d_plain = torch.empty_like(h_plain, device=dev)
 
+    # the library's copy of the confidence planes: one cudaMemcpy2DAsync per tensor (csrc/api.cu,
+    # copy_conf_planes): rows = (image, field) blocks, pitch = all planes of a block, width = one plane
+    from cuda.bindings import runtime as cudart
+    stream = torch.cuda.current_stream().cuda_stream
+    cells = H * H * 4
+
     def strided():
+        for d, h, planes, blocks in ((d_cif, h_cif, 5, B * 17), (d_caf, h_caf, 9, B * 19)):
+            err, = cudart.cudaMemcpy2DAsync(d.data_ptr(), planes * cells, h.data_ptr(), planes * cells, cells, blocks,
+                                            cudart.cudaMemcpyKind.cudaMemcpyHostToDevice, stream)
+            assert int(err) == 0, err
+
+    def strided_torch():
         d_cif[:, :, 0].copy_(h_cif[:, :, 0], non_blocking=True)
         d_caf[:, :, 0].copy_(h_caf[:, :, 0], non_blocking=True)
 
@@ -52,7 +65,8 @@ def main():
         d_caf.copy_(h_caf, non_blocking=True)
 
     out = {}
-    for name, fn, nbytes, reps in (('strided', strided, n_conf, 50), ('plain', plain, n_conf, 50),
+    for name, fn, nbytes, reps in (('strided', strided, n_conf, 50), ('strided_torch', strided_torch, n_conf, 20),
+                                   ('plain', plain, n_conf, 50),
                                    ('full', full, h_cif.numel() * 4 + h_caf.numel() * 4, 10)):
         for _ in range(3):
             fn()

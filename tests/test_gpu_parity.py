@@ -1189,3 +1189,27 @@ def test_profiler_wraps_stage_profile(coco_skeleton, configured_decoder, tmp_pat
     rec = json.loads(out.read_text())
     assert rec['calls'] == 2 and rec['stage_ms_per_call']['cifhr_splat'] > 0.0
     assert 'cifhr_splat' in capsys.readouterr().out and decoder.CifCaf.stage_profile is None
+
+
+def test_scores_above_one_are_flagged(oracle, coco_skeleton, configured_decoder, caplog):
+    """CAF confidences above 1 (un-squashed head outputs): connection scores can then exceed their
+    frontier bound, the one precondition of the eager frontier.  Chosen
+    behaviour: decode anyway, deterministically, set PP_STATUS_SCORE_ABOVE_ONE for the image (a warning,
+    not PP_ERR_CAPACITY).  Ordinary fields never set it."""
+    import logging
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.datasets.constants import COCO_KEYPOINTS
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    hot = caf.copy()
+    hot[:, 0] *= 2.5
+    out = run_gpu(configured_decoder, [cif, cif], [caf, hot], coco_skeleton)
+    assert out['status'][0] == 0
+    assert out['status'][1] == _lib.PP_STATUS_SCORE_ABOVE_ONE and out['n_ann'][1] >= 1
+    again = run_gpu(configured_decoder, [cif], [hot], coco_skeleton)
+    n = again['n_ann'][0]
+    assert n == out['n_ann'][1] and np.array_equal(again['ann_data'][0, :n], out['ann_data'][1, :n])
+    dec = configured_decoder.CifCaf(configured_decoder.FieldConfig(), keypoints=COCO_KEYPOINTS,
+                                    skeleton=coco_skeleton)
+    with caplog.at_level(logging.WARNING):
+        anns = dec([cif, hot])            # no exception
+    assert len(anns) == n and any('above 1' in r.getMessage() for r in caplog.records)
