@@ -524,6 +524,9 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
     pre.L = s->L; pre.cap = c->caf_cap; pre.th = p->caf_threshold;
     pre.min_dist = sets[0].caf_min_distance / stride; pre.use_min = sets[0].caf_min_distance != 0.0f;
     pre.max_dist = sets[0].caf_max_distance / stride; pre.use_max = sets[0].caf_max_distance > 0.0f;
+    // host-mapped fields: every plane value read is a PCIe transaction; the two log-b rows only exist in
+    // the CafScored lists a caller may ask for
+    pre.skip_logb = sets[0].caf_rest != nullptr && !o->caf_fwd && !o->caf_bwd;
   }
   for (int g = 0; g < n_groups && !(dbg_skip & 16); g++) {
     const pp_shape q = set_shape(g);

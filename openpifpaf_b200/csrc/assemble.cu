@@ -197,6 +197,7 @@ __device__ __noinline__ Xysv warp_grow_connection(float x, float y, float s, con
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         const unsigned m = __ballot_sync(full, in[j]);
+        PP_DASSERT(n + 32 <= kScratch);
         if (in[j]) scratch[n + __popc(m & ((1u << lane) - 1u))] = seg + 32 * j + lane;
         n += __popc(m);
       }
@@ -315,6 +316,7 @@ struct GrowView {
   int *dec;          // (F, 2) decoding_order (start, end)
   int *scratch;      // (kScratch)
   int *meta;         // [0] decoding steps, [1] a connection score above 1 was seen
+  int n_edges;       // capacity of the p_* arrays
 };
 
 __host__ __device__ inline int grow_words(int F, int E) {
@@ -336,6 +338,7 @@ __device__ __forceinline__ GrowView grow_view(float *base, int F, int E) {
   w.dec = (int *)base;            base += 2 * F;
   w.scratch = (int *)base;        base += kScratch;
   w.meta = (int *)base;
+  w.n_edges = E;
   return w;
 }
 
@@ -413,6 +416,7 @@ __device__ __forceinline__ int queue_and_evaluate(const GrowView &w, const Graph
                                          p.connection_method, p.exp_mode);
     if (lane == 0) {
       const int q = n_pend;
+      PP_DASSERT(q < w.n_edges);
       float score = r.v;
       if (p.greedy) score = __fsqrt_rn(w.data[3 * start + 2]);                        // :258 (the bound)
       if (cscale.has) score = __fmul_rn(score, cscale.v[g.nb_link[start][k]]);        // :259-260, :282-284
@@ -479,6 +483,7 @@ __device__ void warp_grow(const GrowView &w, const Graph &g, const CScale &cscal
       w.data[3 * end] = w.p_x[best]; w.data[3 * end + 1] = w.p_y[best];               // :300-302
       w.data[3 * end + 2] = w.p_v[best];
       w.js[end] = w.p_s[best];
+      PP_DASSERT(n_dec < F && end >= 0 && end < F);
       w.dec[2 * n_dec] = w.p_start[best]; w.dec[2 * n_dec + 1] = end;                 // :303-304
       w.p_end[best] = -1;
     }
@@ -658,6 +663,7 @@ __device__ void pick_wave(AsmShared &sh, const SeedCtx &c, int found) {
       }
     }
   }
+  PP_DASSERT(n_pick >= 1 && n_pick <= kAsmWarps);
   if (lane == 0) sh.n_pick = n_pick;
 }
 
@@ -755,6 +761,7 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
   auto commit = [&](int k) {
     const GrowView v = grow_view(dyn_smem + (size_t)k * gw, F, n_edges);
     const int n_dec = v.meta[0];
+    PP_DASSERT(k >= 0 && k < kAsmWarps && n_ann < a.ann_cap && n_dec <= F);
     if (threadIdx.x == 0 && v.meta[1]) atomicOr(&a.status[b], PP_STATUS_SCORE_ABOVE_ONE);
     for (int i = threadIdx.x; i < F * 3; i += blockDim.x) pre_data[(size_t)n_ann * F * 3 + i] = v.data[i];
     for (int i = threadIdx.x; i < F; i += blockDim.x) {

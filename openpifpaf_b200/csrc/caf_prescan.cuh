@@ -34,7 +34,8 @@ __device__ __forceinline__ void caf_prescan_body(const CafPreArgs &a, const pp_s
         const int c = slab + s_cells[i];
         nine[0] = sp[s_cells[i]];
 #pragma unroll
-        for (int r = 1; r < 9; r++) nine[r] = __ldg(pr + (size_t)r * n + c);
+        for (int r = 1; r < 9; r++)
+          nine[r] = (a.skip_logb && (r == 3 || r == 7)) ? 0.0f : __ldg(pr + (size_t)r * n + c);
         if (filtered) {                                               // :47-55 (multi-scale only)
           const float dx = __fsub_rn(nine[1], nine[5]), dy = __fsub_rn(nine[2], nine[6]);
           const float d = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));

@@ -203,6 +203,7 @@ __device__ __forceinline__ void bin_one_list(const float *__restrict__ src, cons
   for (int k = tid; k < K; k += kCafThreads) {
     const float xs = src[(size_t)cap + k], ys = src[2 * (size_t)cap + k];
     const int pos = atomicAdd(&hist[bin_of(xs, ys, g, inv)], 1);
+    PP_DASSERT(pos >= 0 && pos < K);
     dst[pos] = src[k];
     dst[(size_t)cap + pos] = xs;
     dst[2 * (size_t)cap + pos] = ys;
@@ -282,6 +283,7 @@ caf_score_bin_kernel(const float *__restrict__ hr, pp_skeleton sk, float *__rest
     const unsigned below = (1u << lane) - 1u;
     if (kb) {
       const int k = cnt_b + base_b + __popc(mb & below);      // :68-69 row permutation
+      PP_DASSERT(k < cap);
       bo[k] = sb;
       bo[(size_t)1 * cap + k] = nine[5]; bo[(size_t)2 * cap + k] = nine[6];
       bo[(size_t)3 * cap + k] = nine[7]; bo[(size_t)4 * cap + k] = nine[8];
@@ -290,6 +292,7 @@ caf_score_bin_kernel(const float *__restrict__ hr, pp_skeleton sk, float *__rest
     }
     if (kf) {
       const int k = cnt_f + base_f + __popc(mf & below);      // :79-80
+      PP_DASSERT(k <= i && k < cap);                         // in place: never ahead of the entry just read
       fo[k] = sf;
 #pragma unroll
       for (int r = 1; r < 9; r++) fo[(size_t)r * cap + k] = nine[r];

@@ -203,6 +203,7 @@ __device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int
           int maxx = (int)clipf(__fadd_rn(__fadd_rn(cx, sigma), 1.0f), (float)(minx + 1), (float)hw);
           int miny = (int)clipf(__fsub_rn(cy, sigma), 0.0f, (float)(hh - 1));
           int maxy = (int)clipf(__fadd_rn(__fadd_rn(cy, sigma), 1.0f), (float)(miny + 1), (float)hh);
+          PP_DASSERT(k >= 0 && k < src_cap && (miny >> w.rshift) <= w.nstrips && ((maxy - 1) >> w.rshift) + 1 <= w.nstrips);
           oa[k] = make_float4(cx, cy, __fmul_rn(sigma, sigma), cv);
           ob[k] = make_int4(minx, maxx, miny, maxy);
           // what CifSeeds needs besides (cx, cy, cv): the scale(s) in pixels (cif_seeds.py:44,84)
@@ -568,6 +569,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
       const int off = consumer_flag_scan(keep, wide, warp_tot, &n_staged, &any_wide, &s_mask[0][0]);   // two barriers, masks cleared
       if (keep) {
         if (flat) a.z = -a.z;                              // only ever read by the wide path below
+        PP_DASSERT(off >= 0 && off < kGroupCap);
         s_a[off] = a;
         s_b[off] = bb;
       }

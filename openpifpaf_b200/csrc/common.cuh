@@ -21,6 +21,17 @@
 #error "libpifpaf_b200 is written for sm_100a (B200) only"
 #endif
 
+// Bounds / invariant checks in device code (build with PP_EXTRA_NVCC=-DPP_DEVICE_ASSERT: a violated
+// check traps, the launch fails and every test that follows reports the CUDA error).  compute-sanitizer
+// is closed on the B200 pool this library is developed on; these asserts over the whole GPU test suite
+// are the substitute for its memcheck (profiles/r2_device_assert.md).  Compiled out otherwise.
+#ifdef PP_DEVICE_ASSERT
+#include <assert.h>
+#define PP_DASSERT(cond) assert(cond)
+#else
+#define PP_DASSERT(cond) ((void)0)
+#endif
+
 namespace pp {
 
 constexpr int kWarp = 32;
@@ -241,6 +252,7 @@ __device__ __forceinline__ int block_active_cells_smem(const float *sp, int n, f
       const int c = base + lane;
       const bool hit = c < w1 && sp[c] > th;
       const unsigned m = __ballot_sync(0xffffffffu, hit);
+      PP_DASSERT(!hit || at + __popc(m & below) < n);
       if (hit) list[at + __popc(m & below)] = (unsigned short)c;
       at += __popc(m);
     }

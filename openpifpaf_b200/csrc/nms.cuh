@@ -173,6 +173,7 @@ __device__ __forceinline__ void nms_image(const NmsArgs &a, const int b, void *s
         if (!(score[j] >= a.inst_th)) continue;
         if (score[j] > score[i] || (score[j] == score[i] && j < i)) rank++;
       }
+      PP_DASSERT(rank >= 0 && rank < n);
       order[rank] = i;
       atomicAdd(&s_m, 1);
     }
@@ -238,6 +239,7 @@ __device__ __forceinline__ void nms_image(const NmsArgs &a, const int b, void *s
           long long maxy = miny + 1 > t ? miny + 1 : t;
           if (maxx > ow) maxx = ow;
           if (maxy > oh) maxy = oh;
+          PP_DASSERT(nb < box_stride);
           long long *bx = bxs + (size_t)nb * 4;
           bx[0] = minx; bx[1] = maxx; bx[2] = miny; bx[3] = maxy;
         }

@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(128) pack_results_kernel(PackArgs a) {
   const float *pre = a.pre_data ? a.pre_data + (size_t)b * cap * F * 3 : nullptr;
   const int *order = a.pre_order ? a.pre_order + (size_t)b * cap * F * 2 : nullptr;
   for (int r = warp; r < n; r += blockDim.x >> 5) {          // one warp per record
+    PP_DASSERT(first + r < a.B * cap);
     int32_t *rec = a.out + a.hdr_words + (size_t)(first + r) * a.rec_words;
     const int src = a.ann_source ? a.ann_source[(size_t)b * cap + r] : r;
     if (lane == 0) {

@@ -298,6 +298,7 @@ seeds_field_sort_kernel(CifSrcView src, const float *__restrict__ hr, float *__r
     }
     int total;
     const int off = block_flag_scan(keep, wtot, &total);
+    PP_DASSERT(!keep || nk + off < (npad_max <= kSegSmemKeys ? kSegSmemKeys : scratch_stride));
     if (keep) keys[nk + off] = ((uint64_t)orderable(v) << 32) | (uint32_t)i;
     nk += total;
   }
@@ -307,6 +308,7 @@ seeds_field_sort_kernel(CifSrcView src, const float *__restrict__ hr, float *__r
     const uint32_t i = (uint32_t)key;
     const float4 a = sa[i];
     const float2 e = sc[i];
+    PP_DASSERT(pos >= 0 && pos < src.src_cap && i < (uint32_t)src.src_cap);
     float *o = out + (size_t)pos * REC;
     o[0] = unorderable((uint32_t)(key >> 32)); o[1] = (float)f; o[2] = a.x; o[3] = a.y; o[4] = e.x;   // :44,47
     if (REC == 6) o[5] = e.y;                                                                        // :84

@@ -32,6 +32,8 @@ struct CafPreArgs {
   int L, cap;
   float th, min_dist, max_dist;      // distances in field cells
   int use_min, use_max;
+  int skip_logb;           // rows 3 and 7 (log-b, never used by the assembly) are written as 0 instead of
+                           // being read: host-mapped input whose CafScored lists the caller does not keep
 };
 int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *d_ws, const pp_shape &s,
                     const pp_shape &s_hr, const pp_caps &c, const pp_params &p, float min_scale,
