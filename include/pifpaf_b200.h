@@ -148,11 +148,14 @@ typedef struct pp_params {
   int32_t asm_heavy_seeds;       /* seeds per image above which the assembly indexes the seeds by
                                     (field, row band) for its occupancy updates (default 4096; < 0 = always) */
   int32_t asm_stage_kb;          /* KB of shared memory for the staged candidate lists (< 0 = none)      */
-  int32_t cifhr_group;           /* strips per splat work item (default 3)                               */
-  int32_t cifhr_ctas_per_sm;     /* persistent splat CTAs per SM (default 3)                             */
+  int32_t cifhr_group;           /* strips per work item of the empty-strip producer (default 8)         */
+  int32_t cifhr_ctas_per_sm;     /* persistent CTAs per SM of the strips kernel (default 1)              */
   int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
   float cif_neighbors;           /* CifHr.neighbors (cif_hr.py:15,40): v / neighbors; 0 = 16            */
   int32_t seed_mask_enabled;     /* 1: seed_mask applies even when it is all zero (no field seeds)      */
+  int32_t cifhr_warps;           /* tuning: warps per CTA of the strips kernel, one strip each (default 4,
+                                    max 8); < 0: the round-1 CTA-per-strip kernel does every strip       */
+  int32_t cifhr_depth;           /* tuning: bulk stores the empty-strip producer keeps queued (default 8; > 16 = no limit) */
   struct pp_gate *splat_gate;    /* optional (NULL = off): decodes issued on different streams with the same
                                     gate run their CifHr splat kernels one after the other (see pp_gate) */
 } pp_params;

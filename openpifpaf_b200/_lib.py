@@ -77,7 +77,7 @@ class Params(C.Structure):
         ('inverse', C.POINTER(Inverse)), ('host_mapped', C.c_int32), ('in_flight', C.c_int32),
         ('asm_heavy_seeds', C.c_int32), ('asm_stage_kb', C.c_int32), ('cifhr_group', C.c_int32),
         ('cifhr_ctas_per_sm', C.c_int32), ('cifhr_rshift', C.c_int32), ('cif_neighbors', C.c_float),
-        ('seed_mask_enabled', C.c_int32), ('splat_gate', C.c_void_p),
+        ('seed_mask_enabled', C.c_int32), ('cifhr_warps', C.c_int32), ('cifhr_depth', C.c_int32), ('splat_gate', C.c_void_p),
     ]
 
 

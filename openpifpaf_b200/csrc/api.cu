@@ -235,10 +235,12 @@ const char *pp_stage_name(int stage) {
 }
 
 /* Launches one single-scale pp_decode_batch enqueues with d_out->packed set (the bindings always set it):
- * 7 kernels (field scan = CIF compact + raw CAF candidates, splat, per-field seed sort, seed merge, CafScored
- * scoring + binning, assembly with the NMS as its tail, result gather) + 2 memsets (status, work cursors). */
+ * 8 kernels (field scan = CIF compact + raw CAF candidates, strips kernel, CTA-per-strip kernel for wide
+ * boxes [its work list is empty for ordinary pose fields], per-field seed sort, seed merge, CafScored scoring +
+ * binning, assembly with the NMS as its tail, result gather) + 2 memsets (status, work cursors). */
 int pp_decode_launch_count(const pp_params *p) {
-  int n = PP_N_STAGES + 2;
+  int n = PP_N_STAGES + 3;
+  if (p && p->cifhr_warps < 0) n -= 1;  // the CTA-per-strip kernel alone
   if (p && p->force_complete) n += 4;   // second CafScored, its binning, complete_kernel, nms_kernel
   if (p && p->inverse) n += 1;          // annotations_inverse_kernel
   return n;

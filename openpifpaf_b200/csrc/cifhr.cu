@@ -60,6 +60,14 @@ constexpr int kStripBytesMax = 24 * 1024;
 constexpr int kCompactThreads = 256;
 constexpr int kCompactSlab = 8192;     // cells per active-cell list (16 KiB of shared memory)
 constexpr int kBoundBlock = 64;        // sources per row-bound record (see CifHrWs::blk)
+// strips kernel (one warp per strip, see cifhr_strips_kernel)
+constexpr int kStripWarpsDefault = 4;  // consumer warps per CTA (pp_params.cifhr_warps)
+constexpr int kStripWarpsMax = 8;
+constexpr int kStripStage = 64;        // sources staged per warp between two flushes
+constexpr int kStripBatch = 4;         // rounds of 32 source records loaded together
+constexpr int kNarrowMaxCols = 48;     // a source box wider than this sends the strips it meets to the CTA-per-strip kernel
+constexpr int kNarrowMaxSrc = 160;     // so does a strip that meets more sources than this
+constexpr int kDiffWideShift = 20;     // per-strip difference array: sources in the low bits, wide sources above
 
 struct CifHrWs {
   float4 *src_a;    // (B,F,src_cap) cx, cy, sigma^2, v
@@ -69,9 +77,12 @@ struct CifHrWs {
   int2 *blk;        // (B,F,blk_cap) [min miny, max maxy) over each run of kBoundBlock sources: sources are in
                     // row-major cell order, so a strip only meets a short range of runs (crowded scenes)
   int blk_cap;
-  int *strip_cnt;   // (B,F,nstrips)
-  int *busy_list;   // (B*F*nstrips) ids (bf * nstrips + strip) of the strips with sources, any order
-  int *cursors;     // [0] number of busy strips, [1] producer group cursor, [2] consumer strip cursor
+  int *strip_cnt;   // (B,F,nstrips) sources meeting the strip | wide sources << kDiffWideShift; 0 = empty strip
+  int2 *busy_list;  // (B*F*nstrips) {bf * nstrips + strip, sources of that field} of the strips with sources, any
+                    // order: the narrow strips (one warp each, cifhr_strips_kernel) from the front, the wide ones
+                    // (one CTA each, cifhr_splat_kernel) from the back
+  int *cursors;     // [0] narrow strips, [1] producer group cursor, [2] narrow work cursor, [3] wide strips,
+                    // [4] wide work cursor
   int nstrips;
   int rshift;       // strip rows R = 1 << rshift
 };
@@ -93,7 +104,7 @@ size_t cifhr_ws_bytes(const pp_shape &s, const pp_caps &c) {
   n += align_up(bf * c.src_cap * sizeof(float2), 256);
   n += align_up(bf * sizeof(int), 256);
   n += align_up(bf * ((c.src_cap + kBoundBlock - 1) / kBoundBlock) * sizeof(int2), 256);
-  n += 2 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1
+  n += 3 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);   // worst case R = 1; counts + int2 work list
   n += 256;
   return n;
 }
@@ -109,7 +120,7 @@ static CifHrWs carve(void *ws, const pp_shape &s, const pp_caps &c, int rshift_p
   w.blk_cap = (c.src_cap + kBoundBlock - 1) / kBoundBlock;
   w.blk = (int2 *)p;     p += align_up(bf * w.blk_cap * sizeof(int2), 256);
   w.strip_cnt = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
-  w.busy_list = (int *)p; p += align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
+  w.busy_list = (int2 *)p; p += 2 * align_up(bf * num_strips(hr_h(s), 0) * sizeof(int), 256);
   w.cursors = (int *)p;
   w.rshift = strip_rshift(hr_w(s), rshift_pref);
   w.nstrips = num_strips(hr_h(s), w.rshift);
@@ -127,6 +138,8 @@ struct CompactArgs {
   int use_min_scale, det;
   int *status;
   float neighbors;       // CifHr.neighbors
+  int n_planes;          // B * F of the launch (the work list is shared by all of them)
+  int all_wide;          // every busy strip goes to the CTA-per-strip kernel (pp_params.cifhr_warps < 0)
 };
 
 // dynamic shared memory of a scan CTA (compact or CAF prescan): [nstrips + 1 ints, padded to 16 bytes]
@@ -208,8 +221,9 @@ __device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int
           ob[k] = make_int4(minx, maxx, miny, maxy);
           // what CifSeeds needs besides (cx, cy, cv): the scale(s) in pixels (cif_seeds.py:44,84)
           oc[k] = make_float2(__fmul_rn(c4, stride), det ? __fmul_rn(c5, stride) : 0.0f);
-          atomicAdd(&sm_diff[miny >> w.rshift], 1);
-          atomicAdd(&sm_diff[((maxy - 1) >> w.rshift) + 1], -1);
+          const int one = 1 + ((maxx - minx > kNarrowMaxCols) ? (1 << kDiffWideShift) : 0);
+          atomicAdd(&sm_diff[miny >> w.rshift], one);
+          atomicAdd(&sm_diff[((maxy - 1) >> w.rshift) + 1], -one);
         }
       }
       count += total;
@@ -246,8 +260,15 @@ __device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int
       }
       w.n_src[bf] = count;
     }
+    count = __shfl_sync(0xffffffffu, count, 0);
     int *sc = w.strip_cnt + (size_t)bf * w.nstrips;
-    int run = 0, n_busy = 0;
+    int run = 0, n_narrow = 0, n_wide = 0;
+    // a strip goes to the one-warp-per-strip kernel unless it meets a wide box or very many sources
+    // (either kernel gives the same map; this only decides who is faster)
+    const bool all_wide = a.all_wide != 0;
+    auto is_wide = [all_wide](int v) {
+      return all_wide || ((unsigned)v >> kDiffWideShift) != 0u || (v & ((1 << kDiffWideShift) - 1)) > kNarrowMaxSrc;
+    };
     for (int base = 0; base < w.nstrips; base += 32) {
       const int i = base + lane;
       int v = i < w.nstrips ? sm_diff[i] : 0;
@@ -259,18 +280,31 @@ __device__ __forceinline__ void cif_compact_body(const CompactArgs &a, const int
       v += run;
       if (i < w.nstrips) { sc[i] = v; sm_diff[i] = v; }
       run = __shfl_sync(0xffffffffu, v, 31);
-      n_busy += __popc(__ballot_sync(0xffffffffu, i < w.nstrips && v != 0));
+      const bool busy = i < w.nstrips && v != 0;
+      n_wide += __popc(__ballot_sync(0xffffffffu, busy && is_wide(v)));
+      n_narrow += __popc(__ballot_sync(0xffffffffu, busy && !is_wide(v)));
     }
-    if (n_busy) {
-      int at = 0;
-      if (lane == 0) at = atomicAdd(&w.cursors[0], n_busy);
-      at = __shfl_sync(0xffffffffu, at, 0);
+    if (n_narrow + n_wide) {
+      int at_n = 0, at_w = 0;
+      if (lane == 0) {
+        if (n_narrow) at_n = atomicAdd(&w.cursors[0], n_narrow);
+        if (n_wide) at_w = atomicAdd(&w.cursors[3], n_wide);
+      }
+      at_n = __shfl_sync(0xffffffffu, at_n, 0);
+      at_w = __shfl_sync(0xffffffffu, at_w, 0);
+      const int last = a.n_planes * w.nstrips - 1;
       for (int base = 0; base < w.nstrips; base += 32) {
         const int i = base + lane;
-        const bool busy = i < w.nstrips && sm_diff[i] != 0;
-        const unsigned m = __ballot_sync(0xffffffffu, busy);
-        if (busy) w.busy_list[at + __popc(m & ((1u << lane) - 1u))] = bf * w.nstrips + i;
-        at += __popc(m);
+        const int v = i < w.nstrips ? sm_diff[i] : 0;
+        const bool busy = v != 0, wide = busy && is_wide(v);
+        const unsigned mn = __ballot_sync(0xffffffffu, busy && !wide);
+        const unsigned mw = __ballot_sync(0xffffffffu, wide);
+        const unsigned below = (1u << lane) - 1u;
+        const int2 e = make_int2(bf * w.nstrips + i, count);
+        if (wide) w.busy_list[last - (at_w + __popc(mw & below))] = e;
+        else if (busy) w.busy_list[at_n + __popc(mn & below)] = e;
+        at_n += __popc(mn);
+        at_w += __popc(mw);
       }
     }
   }
@@ -311,8 +345,9 @@ fields_scan_kernel(CompactArgs a, CafPreArgs pa, int n_cif) {
 // ---------------------------------------------------------------------------
 // K2: strips -> HBM.
 
-__device__ __forceinline__ void splat_px(float &acc, int px, int py, const float4 a, const int4 b) {
-  if (px >= b.x && px < b.y && py >= b.z && py < b.w) {
+// one pixel inside the source's box: functional.pyx:127-140
+__device__ __forceinline__ void splat_core(float &acc, int px, int py, const float4 a) {
+  {
     float dx = __fsub_rn((float)px, a.x);
     float dy = __fsub_rn((float)py, a.y);
     float dx2 = __fmul_rn(dx, dx);
@@ -332,6 +367,10 @@ __device__ __forceinline__ void splat_px(float &acc, int px, int py, const float
       acc = __fadd_rn(acc, vv);                                   // :140
     }
   }
+}
+
+__device__ __forceinline__ void splat_px(float &acc, int px, int py, const float4 a, const int4 b) {
+  if (px >= b.x && px < b.y && py >= b.z && py < b.w) splat_core(acc, px, py, a);
 }
 
 __device__ __forceinline__ float clamp1(float v) { return (v < 1.0f) ? v : 1.0f; }  // :141
@@ -438,9 +477,9 @@ __device__ __forceinline__ int consumer_flag_scan(bool flag, bool wide, int *war
   return base + in_warp;
 }
 
-__global__ void __launch_bounds__(kSplatBlock)
+__global__ void __launch_bounds__(kSplatBlock, 3)
 cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
-                   int hh, int hw, int buf_floats, int merge) {
+                   int hh, int hw, int buf_floats, int merge, int produce) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float *zero = reinterpret_cast<float *>(smem_raw);
   float *tiles = zero + kZeroFloats;                      // two tile buffers
@@ -455,6 +494,8 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int rshift = w.rshift;
   const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
+  // the strips this kernel owns: the wide end of the work list (usually none: every CTA leaves at once)
+  if (!produce && __ldg(w.cursors + 3) == 0) return;
 
   for (int i = tid; i < (kZeroFloats >> 2); i += kSplatBlock)
     reinterpret_cast<float4 *>(zero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -465,7 +506,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
     // ---- producer warp: every empty strip, as TMA zero stores ---------------------
     // merge (multi-scale, cif_hr.py:62 accumulated = np.maximum(ta, accumulated)): an empty strip
     // of this scale leaves the map as it is
-    if (merge) return;
+    if (merge || !produce) return;
     const int total = n_planes * n_groups;
     for (;;) {
       int item = 0;
@@ -486,7 +527,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   }
 
   // ---- consumer warps: the strips that have sources ------------------------------------
-  const int n_busy = __ldg(w.cursors);
+  const int n_busy = __ldg(w.cursors + 3);
   const int cshift = 5 - rshift;            // patch = (1 << rshift) rows x (1 << cshift) cols, 1 px per lane
   const int n_patches = (hw + (1 << cshift) - 1) >> cshift;
   const int row = lane >> (5 - rshift);                   // lane's row inside the patch
@@ -494,13 +535,13 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   int n_tiles = 0;
 
   for (;;) {
-    if (tid == 0) s_item = atomicAdd(&w.cursors[2], 1);
+    if (tid == 0) s_item = atomicAdd(&w.cursors[4], 1);
     // the bulk store that last read the tile buffer about to be reused (two tiles ago) must have drained
     if (n_tiles >= 2 && tid == 0) bulk_wait_read<1>();
     consumer_sync();
     const int item = s_item;
     if (item >= n_busy) break;
-    const int id = __ldg(w.busy_list + item);
+    const int id = __ldg(w.busy_list + (n_planes * w.nstrips - 1 - item)).x;
     const int bf = id / w.nstrips;
     const StripGeo g = strip_geo((size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
     float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
@@ -705,6 +746,265 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
   if (tid == 0) bulk_wait_read<0>();
 }
 
+// ---------------------------------------------------------------------------
+// K2': the strips with narrow boxes (every strip of an ordinary pose field), ONE WARP PER STRIP and no CTA
+// barrier anywhere.  The CTA-per-strip kernel above spends a busy strip's time in five CTA barriers and a
+// chain of four dependent global loads (7.6 us per strip measured at one CTA per SM) for ~25 (patch, source)
+// evaluations; here a warp owns a tile of shared memory, walks the strip's sources in list order and adds
+// each source to the pixels of its box (lanes = pixels of the box, read-modify-write of the tile, clamp
+// after every add exactly like functional.pyx:140-141), and sends the tile off with one bulk store.  The
+// next work-list entry is fetched one strip ahead by lane 0, so the only load latency on a strip's path is
+// that of its source records.  The producer warp writes the empty strips, one bulk store each from a
+// strip-sized zero buffer.  Per-pixel add order = list order, as in the reference.
+// the increment of one pixel inside the source's box, branch-free so that several pixels' chains interleave:
+// the same operations as splat_core (functional.pyx:127-140), selects instead of branches.  dx, dx2: the
+// column part, shared by the pixels a lane owns in one pass.  Returns the new value of the pixel.
+__device__ __forceinline__ float splat_select(float acc, float dx2, int py, const float4 a) {
+  const float dy = __fsub_rn((float)py, a.y);
+  const float dy2 = __fmul_rn(dy, dy);
+  const float d2 = __fadd_rn(dx2, dy2);
+  const float arg = __fdiv_rn(__fmul_rn(-0.5f, d2), a.z);
+  float e = __fadd_rn(1.0f, __fmul_rn(arg, 0.125f));               // approx_exp, functional.pyx:57-64
+  e = __fmul_rn(e, e);
+  e = __fmul_rn(e, e);
+  e = __fmul_rn(e, e);
+  e = (arg > 2.0f || arg < -2.0f) ? 0.0f : e;
+  const float vv = (dx2 < 0.25f && dy2 < 0.25f) ? a.w : __fmul_rn(a.w, e);   // :134-138
+  const float sum = __fadd_rn(acc, vv);                             // :140
+  return (d2 > a.z) ? acc : sum;                                    // :131
+}
+
+constexpr int kStripIlp = 4;      // rows per lane in flight (two when the box has few rows in the strip)
+
+// ILP rows per lane in flight: rows r0 + u * rpr + rl of the box, column cx (x0 + cx in the map)
+template <int ILP>
+__device__ __forceinline__ void strip_pass(float *tile, int row0, int hw, int r0, int rpr, int rl, int nrows,
+                                           int cx, bool col_ok, float dx2, int y0, const float4 a) {
+  float acc[ILP];
+  int idx[ILP];
+  bool on[ILP];
+#pragma unroll
+  for (int u = 0; u < ILP; u++) {
+    const int ry = r0 + u * rpr + rl;
+    on[u] = col_ok && ry < nrows;
+    idx[u] = row0 + ry * hw + cx;
+    acc[u] = on[u] ? tile[idx[u]] : 1.0f;
+  }
+#pragma unroll
+  for (int u = 0; u < ILP; u++) {
+    const int ry = r0 + u * rpr + rl;
+    // at 1 nothing can change any more (the reference clamps after every add, :141); NaN -> 1
+    const float v = clamp1(splat_select(acc[u], dx2, y0 + ry, a));
+    if (on[u] && acc[u] < 1.0f) tile[idx[u]] = v;
+  }
+}
+
+// Lanes form a (rows x columns) grid over the source's box with a power-of-two column count (no division):
+// a box of 9..16 columns puts two rows on the warp, and four rows per lane in flight cover the 8 rows of a
+// strip in one pass.
+__device__ __forceinline__ void strip_flush(float *tile, int tile0, const float4 *sa, const int4 *sb, int n,
+                                            const StripGeo &g, int hw, int lane) {
+  __syncwarp();                                  // the staged records are visible to every lane
+  if (n == 0) return;
+  float4 a_next = sa[0];
+  int4 b_next = sb[0];
+  for (int s = 0; s < n; s++) {
+    const float4 a = a_next;
+    const int4 b = b_next;
+    if (s + 1 < n) { a_next = sa[s + 1]; b_next = sb[s + 1]; }   // the staged records do not change here
+    const int x0 = max(b.x, 0), wd = min(b.y, hw) - x0;
+    const int y0 = max(b.z, g.r0), nrows = min(b.w, g.r1) - y0;
+    const int sh = wd > 16 ? 5 : (wd > 8 ? 4 : (wd > 4 ? 3 : (wd > 2 ? 2 : (wd > 1 ? 1 : 0))));
+    const int rx = lane & ((1 << sh) - 1), rl = lane >> sh, rpr = 32 >> sh;
+    const int row0 = tile0 + (y0 - g.r0) * hw + x0;
+    for (int cb = 0; cb < wd; cb += 32) {          // one pass unless the box is wider than 32 columns
+      const int cx = cb + rx;
+      const float dx = __fsub_rn((float)(x0 + cx), a.x);
+      const float dx2 = __fmul_rn(dx, dx);
+      if (nrows <= 2 * rpr) {
+        strip_pass<2>(tile, row0, hw, 0, rpr, rl, nrows, cx, cx < wd, dx2, y0, a);
+      } else {
+        for (int r0 = 0; r0 < nrows; r0 += rpr * kStripIlp)
+          strip_pass<kStripIlp>(tile, row0, hw, r0, rpr, rl, nrows, cx, cx < wd, dx2, y0, a);
+      }
+    }
+    __syncwarp();                                // the next source may touch the same pixels from other lanes
+  }
+}
+
+__global__ void __launch_bounds__(32 * (kStripWarpsMax + 1), 1)
+cifhr_strips_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
+                    int hh, int hw, int buf_floats, int merge, int depth) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int n_warps = (int)(blockDim.x >> 5) - 1;         // consumer warps; the last warp is the producer
+  float *zero = reinterpret_cast<float *>(smem_raw);      // one strip of zeros
+  float *tiles = zero + buf_floats;                       // one tile per consumer warp
+  float4 *st_a = reinterpret_cast<float4 *>(tiles + (size_t)n_warps * buf_floats);
+  int4 *st_b = reinterpret_cast<int4 *>(st_a + n_warps * kStripStage);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rshift = w.rshift;
+  for (int i = tid; i < (buf_floats >> 2); i += blockDim.x)
+    reinterpret_cast<float4 *>(zero)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  fence_async_smem();
+  __syncthreads();
+
+  if (warp == n_warps) {
+    // ---- producer warp: every empty strip as one TMA store of zeros -----------------
+    if (merge) return;     // np.maximum merge of a further scale: its empty strips leave the map alone
+    const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
+    const int total = n_planes * n_groups;
+    // the work item after this one and its strip counts are in flight while this one's stores are issued
+    auto counts = [&](int item) {
+      const int bf = item / n_groups;
+      const int strip0 = (item - bf * n_groups) * kGroupStrips;
+      const int nloc = min(kGroupStrips, w.nstrips - strip0);
+      return (item < total && lane < nloc) ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + lane) : 1;
+    };
+    int it_b = 0, item = 0;
+    if (lane == 0) {
+      item = atomicAdd(&w.cursors[1], 1);
+      it_b = atomicAdd(&w.cursors[1], 1);
+    }
+    item = __shfl_sync(0xffffffffu, item, 0);
+    int cnt = counts(item);
+    for (;;) {
+      if (item >= total) break;
+      const int item_next = __shfl_sync(0xffffffffu, it_b, 0);     // asked for one round ago
+      if (lane == 0) it_b = atomicAdd(&w.cursors[1], 1);
+      const int cnt_next = counts(item_next);
+      const int bf = item / n_groups;
+      const int strip0 = (item - bf * n_groups) * kGroupStrips;
+      const size_t plane0 = (size_t)bf * hh * hw;
+      unsigned empty = __ballot_sync(0xffffffffu, cnt == 0);
+      for (; empty; empty &= empty - 1u) {
+        const StripGeo g = strip_geo(plane0, strip0 + __ffs(empty) - 1, rshift, hh, hw);
+        if (lane == 0) {
+          if (g.m1 > g.m0) bulk_store(hr + g.m0, zero, (uint32_t)((g.m1 - g.m0) * sizeof(float)));
+          // a short queue: the SM's bulk-copy unit serves requests in order, and the consumers' tiles
+          // wait behind whatever the producer has queued
+          if (depth <= 2) bulk_wait_read<2>(); else if (depth <= 4) bulk_wait_read<4>();
+          else if (depth <= 8) bulk_wait_read<8>(); else if (depth <= 16) bulk_wait_read<16>();
+        } else if (lane < 5) {
+          const size_t i = g.gs + (size_t)(lane - 1);
+          if (i < g.m0) hr[i] = 0.f;
+        } else if (lane < 9) {
+          const size_t i = g.m1 + (size_t)(lane - 5);
+          if (i < g.ge) hr[i] = 0.f;
+        }
+      }
+      item = item_next;
+      cnt = cnt_next;
+    }
+    if (lane == 0) bulk_wait_read<0>();     // smem must outlive the reads of the async proxy
+    return;
+  }
+
+  // ---- consumer warps ----------------------------------------------------------------
+  const int n_items = __ldg(w.cursors);
+  float *tile = tiles + (size_t)warp * buf_floats;
+  float4 *sa = st_a + warp * kStripStage;
+  int4 *sb = st_b + warp * kStripStage;
+  // lane 0 holds the work list entry of this strip and has the next one in flight
+  int it_a = 0, it_b = 0;
+  int2 ent = make_int2(0, 0);
+  if (lane == 0) {
+    it_a = atomicAdd(&w.cursors[2], 1);
+    it_b = atomicAdd(&w.cursors[2], 1);
+    if (it_a < n_items) ent = __ldg(w.busy_list + it_a);
+  }
+  for (;;) {
+    const int item = __shfl_sync(0xffffffffu, it_a, 0);
+    if (item >= n_items) break;
+    const int id = __shfl_sync(0xffffffffu, ent.x, 0);
+    const int nsrc = min(__shfl_sync(0xffffffffu, ent.y, 0), src_cap);
+    if (lane == 0) {
+      it_a = it_b;                                              // arrived while the last strip was computed
+      if (it_a < n_items) ent = __ldg(w.busy_list + it_a);      // used at the top of the next round
+      it_b = atomicAdd(&w.cursors[2], 1);                       // used as an address one round later
+    }
+    const int bf = id / w.nstrips;
+    const StripGeo g = strip_geo((size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
+    const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
+    const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
+    const int tile0 = (int)(g.gs - g.ga);
+
+    // long source lists (crowded scenes): the range of kBoundBlock-runs whose rows meet the strip
+    int i_lo = 0, i_hi = nsrc;
+    if (nsrc > 32 * kStripBatch) {
+      const int2 *bounds = w.blk + (size_t)bf * w.blk_cap;
+      int first = 0x7fffffff, last = -1;
+      for (int blk = lane; blk * kBoundBlock < nsrc; blk += 32) {
+        const int2 b = bounds[blk];
+        if (b.x < g.r1 && b.y > g.r0) { first = min(first, blk); last = max(last, blk); }
+      }
+      first = __reduce_min_sync(0xffffffffu, first);
+      last = __reduce_max_sync(0xffffffffu, last);
+      i_lo = last < 0 ? nsrc : first * kBoundBlock;
+      i_hi = last < 0 ? nsrc : min(nsrc, (last + 1) * kBoundBlock);
+    }
+    // kStripBatch x 32 records per round of loads (one load latency per 128 sources); the first round is
+    // on its way while the last strip's store drains and the tile is cleared
+    int4 bb[kStripBatch];
+    float4 aa[kStripBatch];
+    auto load_batch = [&](int base) {
+#pragma unroll
+      for (int j = 0; j < kStripBatch; j++) {
+        const int i = base + 32 * j + lane;
+        bb[j] = make_int4(0, 0, 0, 0);           // rows [0, 0): never kept
+        aa[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < i_hi) { bb[j] = gb_src[i]; aa[j] = ga_src[i]; }
+      }
+    };
+    load_batch(i_lo);
+    if (lane == 0) bulk_wait_read<0>();          // the store of this warp's last strip has finished reading the tile
+    __syncwarp();
+    for (int i = lane; i < (buf_floats >> 2); i += 32)
+      reinterpret_cast<float4 *>(tile)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int n_st = 0;
+    for (int base = i_lo; base < i_hi; base += 32 * kStripBatch) {
+      if (base != i_lo) load_batch(base);
+#pragma unroll
+      for (int j = 0; j < kStripBatch; j++) {
+        const bool keep = bb[j].z < g.r1 && bb[j].w > g.r0;
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m == 0u) continue;
+        if (n_st + __popc(m) > kStripStage) {
+          strip_flush(tile, tile0, sa, sb, n_st, g, hw, lane);
+          n_st = 0;
+        }
+        if (keep) {
+          const int k = n_st + __popc(m & ((1u << lane) - 1u));
+          PP_DASSERT(k < kStripStage);
+          sa[k] = aa[j];
+          sb[k] = bb[j];
+        }
+        n_st += __popc(m);
+      }
+    }
+    strip_flush(tile, tile0, sa, sb, n_st, g, hw, lane);
+    if (merge) {          // np.maximum with the map of the scales before (NaN from either side wins)
+      for (size_t i = g.gs + lane; i < g.ge; i += 32) {
+        const float a = tile[i - g.ga], o = hr[i];
+        tile[i - g.ga] = (a != a) ? a : ((o != o) ? o : fmaxf(a, o));
+      }
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      if (g.m1 > g.m0) bulk_store(hr + g.m0, tile + (g.m0 - g.ga), (uint32_t)((g.m1 - g.m0) * sizeof(float)));
+    } else if (lane < 5) {          // head: < 4 floats before the aligned middle
+      const size_t i = g.gs + (size_t)(lane - 1);
+      if (i < g.m0) hr[i] = tile[i - g.ga];
+    } else if (lane < 9) {          // tail
+      const size_t i = g.m1 + (size_t)(lane - 5);
+      if (i < g.ge) hr[i] = tile[i - g.ga];
+    }
+    __syncwarp();                   // the head / tail lanes have read the tile before it is cleared again
+  }
+  if (lane == 0) bulk_wait_read<0>();
+}
+
 // s: shape of the field set (B, F, H, W, stride); s_hr: the shape that defines the hr map (set 0 of a
 // multi-scale configuration, else s itself).  d_cif2: second field of an hflip pair or NULL.
 // merge: np.maximum into the existing map instead of overwriting it.
@@ -725,11 +1025,15 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   // (the bulk loads of the confidence planes round their range out to 16-byte boundaries: field tensors
   // must live in allocations whose base is 16-byte aligned -- cudaMalloc gives 256 -- see pifpaf_b200.h)
   const size_t smem = scan_smem_bytes(w.nstrips, s.H * s.W);
+  // pp_params.cifhr_warps: consumer warps per CTA of the strips kernel; < 0 = the CTA-per-strip kernel
+  // does every strip (the round-1 schedule, kept for comparison)
+  const bool legacy = p.cifhr_warps < 0;
+  int n_warps = (p.cifhr_warps >= 1 && p.cifhr_warps <= kStripWarpsMax) ? p.cifhr_warps : kStripWarpsDefault;
   prof_mark(p.profile, kStCompact, st);
-  PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 4 * sizeof(int), st));
+  PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 8 * sizeof(int), st));
   CompactArgs ca = {d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold,
                     min_scale / (float)s.stride, min_scale != 0.0f, det, d_status,
-                    p.cif_neighbors > 0.0f ? p.cif_neighbors : 16.0f};
+                    p.cif_neighbors > 0.0f ? p.cif_neighbors : 16.0f, bf, legacy ? 1 : 0};
   CafPreArgs pa = {};
   int n_caf = 0;
   if (caf_pre) {
@@ -742,24 +1046,47 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   PP_LAUNCH_CHECK("fields_scan_kernel");
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
-  const size_t dyn = ((size_t)kZeroFloats + 2 * (size_t)buf_floats) * sizeof(float);
-  // per device and cheap: set on every launch rather than caching per process
-  PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_splat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
-  const int kGroupStrips = group_strips(p);
-  const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
-  // persistent grid: 3 CTAs per SM.  Shared memory would allow 4 at 641 px and a kernel running alone is
-  // equally fast with either; 3 leave room for the assembly CTAs of another batch in flight
-  // (engine.submit lanes: 122 k -> 126 k images/s)
-  const int per_sm = p.cifhr_ctas_per_sm > 0 ? p.cifhr_ctas_per_sm : 3;
-  int grid = num_sms() * per_sm;
-  if (grid > bf * n_groups) grid = bf * n_groups;
   prof_mark(p.profile, kStSplat, st);
   int rc = gate_wait(p.splat_gate, st);       // batches in flight: one splat at a time (pp_gate)
   if (rc) return rc;
-  cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
-                                                    buf_floats, merge);
-  PP_LAUNCH_CHECK("cifhr_splat_kernel");
+  const int sms = num_sms();
+  if (!legacy) {
+    // the strips kernel: empty strips (producer warp) + narrow strips (one warp each).  Persistent, one
+    // CTA per SM by default: n_warps tiles + the zero strip + the staged records
+    constexpr size_t kStripsSmemMax = 226 * 1024;      // 227 KB per CTA minus the kernel's (tiny) static part
+    auto strips_smem = [&](int nw) {
+      return ((size_t)(nw + 1) * buf_floats) * sizeof(float) + (size_t)nw * kStripStage * (sizeof(float4) + sizeof(int4));
+    };
+    while (n_warps > 1 && strips_smem(n_warps) > kStripsSmemMax) n_warps--;
+    const size_t dyn = strips_smem(n_warps);
+    if (dyn > kStripsSmemMax) return PP_ERR_ARG;
+    PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_strips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kStripsSmemMax));
+    const int group = (p.cifhr_group >= 1 && p.cifhr_group <= kGroupStripsMax) ? p.cifhr_group : 8;
+    const int n_groups = (w.nstrips + group - 1) / group;
+    const int per_sm = p.cifhr_ctas_per_sm > 0 ? p.cifhr_ctas_per_sm : 1;
+    int grid = sms * per_sm;
+    if (grid > bf * n_groups) grid = bf * n_groups;
+    cifhr_strips_kernel<<<grid, 32 * (n_warps + 1), dyn, st>>>(d_hr, w, bf, group, c.src_cap, hh, hw,
+                                                                buf_floats, merge, p.cifhr_depth > 0 ? p.cifhr_depth : 8);
+    PP_LAUNCH_CHECK("cifhr_strips_kernel");
+  }
+  if (p.cifhr_depth != 99) {
+    // the CTA-per-strip kernel: the strips that meet wide boxes or very long lists (degenerate fields);
+    // with ordinary pose fields its list is empty and every CTA leaves at once
+    const size_t dyn = ((size_t)kZeroFloats + 2 * (size_t)buf_floats) * sizeof(float);
+    // per device and cheap: set on every launch rather than caching per process
+    PP_CUDA_CHECK(cudaFuncSetAttribute(cifhr_splat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       2 * kStripBytesMax + kZeroFloats * (int)sizeof(float)));
+    const int kGroupStrips = legacy ? group_strips(p) : 3;
+    const int n_groups = (w.nstrips + kGroupStrips - 1) / kGroupStrips;
+    const int per_sm = (legacy && p.cifhr_ctas_per_sm > 0) ? p.cifhr_ctas_per_sm : 3;
+    int grid = sms * per_sm;
+    if (grid > bf * n_groups) grid = bf * n_groups;
+    cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
+                                                      buf_floats, merge, legacy ? 1 : 0);
+    PP_LAUNCH_CHECK("cifhr_splat_kernel");
+  }
   return gate_signal(p.splat_gate, st);
 }
 

@@ -50,7 +50,7 @@ class DecoderParams:
     # batches kept in flight on other streams (pp_params.in_flight); set by submit / run_host_lanes
     in_flight: int = 1
     # schedule knobs of pp_params (0 = the library's choice; results never change): asm_heavy_seeds,
-    # asm_stage_kb, cifhr_group, cifhr_ctas_per_sm, cifhr_rshift
+    # asm_stage_kb, cifhr_group, cifhr_ctas_per_sm, cifhr_rshift, cifhr_warps
     tuning: Optional[dict] = None
     splat_gate: Optional[int] = None    # pp_gate* shared by the lanes of an engine (set by submit)
 
@@ -95,7 +95,7 @@ class DecoderParams:
         p.splat_gate = self.splat_gate
         for name, value in (self.tuning or {}).items():
             if name not in ('asm_heavy_seeds', 'asm_stage_kb', 'cifhr_group', 'cifhr_ctas_per_sm',
-                            'cifhr_rshift'):
+                            'cifhr_rshift', 'cifhr_warps', 'cifhr_depth'):
                 raise KeyError('unknown tuning knob %r' % name)
             setattr(p, name, int(value))
         if self.initial is not None:

@@ -12,7 +12,7 @@ tail -4 $OUT/${TAG}_determinism.log
 PP_EXTRA_NVCC=-DPP_DEVICE_ASSERT python -c "
 from openpifpaf_b200 import build
 print(build.build(force=True))" > $OUT/${TAG}_assert_build.log 2>&1
-cuobjdump -sass openpifpaf_b200/libpifpaf_b200.so | grep -c "__assertfail\|__assert_fail" > $OUT/${TAG}_assert_sites.txt
+cuobjdump -elf openpifpaf_b200/libpifpaf_b200.so | grep -c __assertfail > $OUT/${TAG}_assert_sites.txt
 timeout 1200 python -m pytest tests -m gpu -q > $OUT/${TAG}_assert_pytest.log 2>&1
 echo "pytest rc=$?" >> $OUT/${TAG}_assert_pytest.log
 tail -3 $OUT/${TAG}_assert_pytest.log

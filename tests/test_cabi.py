@@ -78,7 +78,7 @@ def test_host_only_entries(lib):
         [tuple(l) for l in COCO_PERSON_SKELETON]
     assert lib.pp_error_string(0) == b'ok'
     assert b'capacity' in lib.pp_error_string(-2)
-    assert lib.pp_decode_launch_count(None) == _lib.PP_N_STAGES + 2   # 7 kernels + 2 memsets
+    assert lib.pp_decode_launch_count(None) == _lib.PP_N_STAGES + 3   # 8 kernels + 2 memsets
     assert [lib.pp_stage_name(i) for i in range(7)][1] == b'cifhr_splat'
 
 
