@@ -680,6 +680,9 @@ def run_b200(args):
     params = dec.params()
     if args.tuning:
         params.tuning = {k: int(v) for k, v in (kv.split('=') for kv in args.tuning.split(','))}
+        if 'compress' in params.tuning:                 # experiments: hr maps in plain device memory
+            from openpifpaf_b200.decoder.engine import BatchBuffers
+            BatchBuffers.compress_hr = bool(params.tuning.pop('compress'))
         if 'gate' in params.tuning:                     # experiments: splat gate on / off
             eng.use_splat_gate = bool(params.tuning.pop('gate'))
     d_batches = [(torch.from_numpy(np.ascontiguousarray(c)).to(device),

@@ -153,7 +153,7 @@ typedef struct pp_params {
   int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
   float cif_neighbors;           /* CifHr.neighbors (cif_hr.py:15,40): v / neighbors; 0 = 16            */
   int32_t seed_mask_enabled;     /* 1: seed_mask applies even when it is all zero (no field seeds)      */
-  int32_t cifhr_warps;           /* tuning: warps per CTA of the strips kernel, one strip each (default 4,
+  int32_t cifhr_warps;           /* tuning: warps per CTA of the strips kernel, one strip each (default 3,
                                     max 8); < 0: the round-1 CTA-per-strip kernel does every strip       */
   int32_t cifhr_depth;           /* tuning: bulk stores the empty-strip producer keeps queued (default 8; > 16 = no limit) */
   struct pp_gate *splat_gate;    /* optional (NULL = off): decodes issued on different streams with the same
@@ -255,6 +255,19 @@ int pp_coco_skeleton(pp_skeleton *sk);
 
 /* Bytes of device scratch pp_decode_batch needs (includes hr when out->hr==NULL). */
 size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c);
+/* The same with the caller's own hr buffer in out->hr (hr_external != 0): the scratch without the hr map. */
+size_t pp_workspace_bytes_ex(const pp_shape *s, const pp_caps *c, int32_t hr_external);
+
+/* Device memory for hr maps (cif_hr.py:14-24 `accumulated`; B * F * hr_h * hr_w floats) that asks the driver
+ * for compute data compression: cuMemCreate with CU_MEM_ALLOCATION_COMP_GENERIC, which cudaMalloc cannot
+ * request.  The map is written once per decode, mostly with zeros, and B200 writes such data to HBM faster
+ * when the allocation is compressible (measured with the strips kernel's store pattern: 7.5 TB/s against
+ * 6.3 TB/s into a cudaMalloc buffer, scripts/micro/comp_probe.cu).  Pass the pointer as pp_outputs.hr.  On
+ * the current device; *compressed (may be NULL) <- 1 when the allocation is compressible, 0 when the device
+ * does not support it (the memory is then ordinary device memory).  Contents are identical either way.
+ * pp_hr_free: no work may be in flight on the buffer.  Returns PP_OK or PP_ERR_CUDA / PP_ERR_ARG. */
+int pp_hr_alloc(size_t bytes, void **d_ptr, int32_t *compressed);
+int pp_hr_free(void *d_ptr);
 
 /* ---- stage entry points (device pointers, enqueue only) ------------------ */
 

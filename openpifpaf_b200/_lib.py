@@ -168,6 +168,12 @@ def lib():
     l.pp_decode_batch_multiscale.argtypes = [P(FieldSet), i32, i32, P(Skeleton), P(Outputs), vp, sz,
                                              P(Shape), P(Caps), P(Params), vp]
     l.pp_sizeof.argtypes = [i32]
+    l.pp_workspace_bytes_ex.restype = C.c_size_t
+    l.pp_workspace_bytes_ex.argtypes = [C.POINTER(Shape), C.POINTER(Caps), i32]
+    l.pp_hr_alloc.restype = C.c_int
+    l.pp_hr_alloc.argtypes = [C.c_size_t, C.POINTER(vp), C.POINTER(i32)]
+    l.pp_hr_free.restype = C.c_int
+    l.pp_hr_free.argtypes = [vp]
     l.pp_gate_create.restype = vp
     l.pp_gate_create.argtypes = []
     l.pp_gate_destroy.restype = None
@@ -226,7 +232,7 @@ EXPORTS = (
     'pp_profile_create', 'pp_profile_destroy', 'pp_profile_reset', 'pp_profile_read',
     'pp_stage_name', 'pp_decode_launch_count', 'pp_profile_read_abs', 'pp_gate_create', 'pp_gate_destroy',
     'pp_error_string', 'pp_last_cuda_error', 'pp_version', 'pp_default_params', 'pp_default_caps',
-    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detections_inverse', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
+    'pp_coco_skeleton', 'pp_workspace_bytes', 'pp_workspace_bytes_ex', 'pp_hr_alloc', 'pp_hr_free', 'pp_sizeof', 'pp_decode_batch_multiscale', 'pp_det_default_params', 'pp_cifdet_workspace_bytes', 'pp_cifdet_decode_batch', 'pp_detections_inverse', 'pp_detection_nms_workspace_bytes', 'pp_detection_nms',
     'pp_head_epilogue', 'pp_annotations_inverse', 'pp_cifhr_accumulate', 'pp_cif_seeds',
     'pp_caf_scored', 'pp_cifcaf_assemble', 'pp_keypoint_nms', 'pp_decode_batch',
     'pp_keypoint_nms_noalloc', 'pp_keypoint_nms_noalloc_max_bytes', 'pp_keypoint_nms_noalloc_bytes',

@@ -12,7 +12,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libpifpaf_b200.so')
-SOURCES = ['api.cu', 'cifhr.cu', 'seeds.cu', 'caf_scored.cu', 'assemble.cu', 'nms.cu', 'shim.cu', 'head.cu', 'inverse.cu', 'det.cu', 'pack.cu']
+SOURCES = ['api.cu', 'cifhr.cu', 'seeds.cu', 'caf_scored.cu', 'assemble.cu', 'nms.cu', 'shim.cu', 'head.cu', 'inverse.cu', 'det.cu', 'pack.cu', 'hrmem.cu']
 HEADERS = ['common.cuh', 'stages.cuh', 'nms.cuh', 'occupancy.cuh', 'caf_prescan.cuh', '../../include/pifpaf_b200.h',
            '../../include/pifpaf_detmath.h']
 NVCC_FLAGS = [

@@ -294,6 +294,10 @@ size_t pp_workspace_bytes(const pp_shape *s, const pp_caps *c) {
   if (!shape_ok(s) || !caps_ok(s, c)) return 0;
   return layout(nullptr, *s, *c, true).total;
 }
+size_t pp_workspace_bytes_ex(const pp_shape *s, const pp_caps *c, int32_t hr_external) {
+  if (!shape_ok(s) || !caps_ok(s, c)) return 0;
+  return layout(nullptr, *s, *c, hr_external == 0).total;
+}
 
 size_t pp_packed_bytes(const pp_shape *s, const pp_caps *c) {
   if (!s || !c || s->B <= 0 || s->F <= 0 || s->F > PP_MAX_F || c->ann_cap <= 0) return 0;

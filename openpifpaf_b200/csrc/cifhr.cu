@@ -61,7 +61,7 @@ constexpr int kCompactThreads = 256;
 constexpr int kCompactSlab = 8192;     // cells per active-cell list (16 KiB of shared memory)
 constexpr int kBoundBlock = 64;        // sources per row-bound record (see CifHrWs::blk)
 // strips kernel (one warp per strip, see cifhr_strips_kernel)
-constexpr int kStripWarpsDefault = 4;  // consumer warps per CTA (pp_params.cifhr_warps)
+constexpr int kStripWarpsDefault = 3;  // consumer warps per CTA (pp_params.cifhr_warps)
 constexpr int kStripWarpsMax = 8;
 constexpr int kStripStage = 64;        // sources staged per warp between two flushes
 constexpr int kStripBatch = 4;         // rounds of 32 source records loaded together
@@ -479,7 +479,7 @@ __device__ __forceinline__ int consumer_flag_scan(bool flag, bool wide, int *war
 
 __global__ void __launch_bounds__(kSplatBlock, 3)
 cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
-                   int hh, int hw, int buf_floats, int merge, int produce) {
+                   int hh, int hw, int buf_floats, int merge, int produce, int hr_off) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float *zero = reinterpret_cast<float *>(smem_raw);
   float *tiles = zero + kZeroFloats;                      // two tile buffers
@@ -516,7 +516,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
       const int bf = item / n_groups;
       const int strip0 = (item - bf * n_groups) * kGroupStrips;
       const int nloc = min(kGroupStrips, w.nstrips - strip0);
-      const size_t plane0 = (size_t)bf * hh * hw;
+      const size_t plane0 = (size_t)hr_off + (size_t)bf * hh * hw;
       const int cnt = lane < nloc ? __ldg(w.strip_cnt + (size_t)bf * w.nstrips + strip0 + lane) : 1;
       unsigned empty = __ballot_sync(0xffffffffu, cnt == 0);
       for (; empty; empty &= empty - 1u)
@@ -543,7 +543,7 @@ cifhr_splat_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupSt
     if (item >= n_busy) break;
     const int id = __ldg(w.busy_list + (n_planes * w.nstrips - 1 - item)).x;
     const int bf = id / w.nstrips;
-    const StripGeo g = strip_geo((size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
+    const StripGeo g = strip_geo((size_t)hr_off + (size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
     float *tile = tiles + (size_t)(n_tiles & 1) * buf_floats;
     for (int i = tid; i < (buf_floats >> 2); i += kSplatThreads)
       reinterpret_cast<float4 *>(tile)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -834,7 +834,7 @@ __device__ __forceinline__ void strip_flush(float *tile, int tile0, const float4
 
 __global__ void __launch_bounds__(32 * (kStripWarpsMax + 1), 1)
 cifhr_strips_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupStrips, int src_cap,
-                    int hh, int hw, int buf_floats, int merge, int depth) {
+                    int hh, int hw, int buf_floats, int merge, int depth, int hr_off) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int n_warps = (int)(blockDim.x >> 5) - 1;         // consumer warps; the last warp is the producer
   float *zero = reinterpret_cast<float *>(smem_raw);      // one strip of zeros
@@ -875,7 +875,7 @@ cifhr_strips_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupS
       const int cnt_next = counts(item_next);
       const int bf = item / n_groups;
       const int strip0 = (item - bf * n_groups) * kGroupStrips;
-      const size_t plane0 = (size_t)bf * hh * hw;
+      const size_t plane0 = (size_t)hr_off + (size_t)bf * hh * hw;
       unsigned empty = __ballot_sync(0xffffffffu, cnt == 0);
       for (; empty; empty &= empty - 1u) {
         const StripGeo g = strip_geo(plane0, strip0 + __ffs(empty) - 1, rshift, hh, hw);
@@ -924,7 +924,7 @@ cifhr_strips_kernel(float *__restrict__ hr, CifHrWs w, int n_planes, int kGroupS
       it_b = atomicAdd(&w.cursors[2], 1);                       // used as an address one round later
     }
     const int bf = id / w.nstrips;
-    const StripGeo g = strip_geo((size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
+    const StripGeo g = strip_geo((size_t)hr_off + (size_t)bf * hh * hw, id - bf * w.nstrips, rshift, hh, hw);
     const float4 *ga_src = w.src_a + (size_t)bf * src_cap;
     const int4 *gb_src = w.src_b + (size_t)bf * src_cap;
     const int tile0 = (int)(g.gs - g.ga);
@@ -1021,7 +1021,11 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   const int hh = hr_h(s_hr), hw = hr_w(s_hr);
   const int bf = s.B * s.F;
   if (((size_t)hw << w.rshift) * sizeof(float) > (size_t)kStripBytesMax - 32) return PP_ERR_ARG;
-  if (((uintptr_t)d_hr & 15u) != 0) return PP_ERR_ARG;     // bulk stores need 16-byte alignment
+  // bulk stores need 16-byte alignment: the kernels index from the 16-byte boundary below the map (a
+  // sub-batch slice of a larger map starts at any multiple of 4 bytes) and never write below the map itself
+  if (((uintptr_t)d_hr & 3u) != 0) return PP_ERR_ARG;
+  const int hr_off = (int)(((uintptr_t)d_hr & 15u) >> 2);
+  d_hr -= hr_off;
   // (the bulk loads of the confidence planes round their range out to 16-byte boundaries: field tensors
   // must live in allocations whose base is 16-byte aligned -- cudaMalloc gives 256 -- see pifpaf_b200.h)
   const size_t smem = scan_smem_bytes(w.nstrips, s.H * s.W);
@@ -1068,7 +1072,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
     int grid = sms * per_sm;
     if (grid > bf * n_groups) grid = bf * n_groups;
     cifhr_strips_kernel<<<grid, 32 * (n_warps + 1), dyn, st>>>(d_hr, w, bf, group, c.src_cap, hh, hw,
-                                                                buf_floats, merge, p.cifhr_depth > 0 ? p.cifhr_depth : 8);
+                                                                buf_floats, merge, p.cifhr_depth > 0 ? p.cifhr_depth : 8, hr_off);
     PP_LAUNCH_CHECK("cifhr_strips_kernel");
   }
   if (p.cifhr_depth != 99) {
@@ -1084,7 +1088,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
     int grid = sms * per_sm;
     if (grid > bf * n_groups) grid = bf * n_groups;
     cifhr_splat_kernel<<<grid, kSplatBlock, dyn, st>>>(d_hr, w, bf, kGroupStrips, c.src_cap, hh, hw,
-                                                      buf_floats, merge, legacy ? 1 : 0);
+                                                      buf_floats, merge, legacy ? 1 : 0, hr_off);
     PP_LAUNCH_CHECK("cifhr_splat_kernel");
   }
   return gate_signal(p.splat_gate, st);

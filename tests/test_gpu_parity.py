@@ -28,7 +28,7 @@ def run_gpu(decoder, cifs, cafs, skeleton, keep=('ann', 'hr', 'seeds', 'caf'), a
     caf = torch.from_numpy(np.stack(cafs)).cuda()
     buf = eng.run_device(cif, caf, DecoderParams(**param_kw), keep=keep)
     torch.cuda.synchronize()
-    return {k: v.cpu().numpy() for k, v in buf.dev.items()}
+    return {k: v.cpu().numpy() for k, v in buf.dev.items() if k != 'hr' or 'hr' in keep}
 
 
 def check_image(orc, out, b, cif, caf, skeleton, **cfg_kw):
