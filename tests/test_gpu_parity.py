@@ -1213,3 +1213,119 @@ def test_scores_above_one_are_flagged(oracle, coco_skeleton, configured_decoder,
     with caplog.at_level(logging.WARNING):
         anns = dec([cif, hot])            # no exception
     assert len(anns) == n and any('above 1' in r.getMessage() for r in caplog.records)
+
+
+# ---- CifHr schedules: strips kernel (one warp per strip) / CTA-per-strip kernel ------------------------
+
+@pytest.mark.parametrize('tuning', [{'cifhr_warps': -1}, {'cifhr_warps': 1}, {'cifhr_warps': 2, 'cifhr_ctas_per_sm': 2},
+                                    {'cifhr_warps': 8, 'cifhr_group': 1, 'cifhr_depth': 2},
+                                    {'cifhr_warps': 4, 'cifhr_rshift': 3, 'cifhr_group': 32}])
+def test_cifhr_schedules_give_the_same_map(oracle, coco_skeleton, configured_decoder, tuning):
+    """Every schedule of the CifHr stage -- the round-1 CTA-per-strip kernel alone, the strips kernel with 1..8
+    warps, other strip heights and group sizes -- writes the oracle's map: narrow boxes (poses, a crowd whose
+    lists are long enough for the row-bound records) and fields that mix narrow and whole-map boxes."""
+    from openpifpaf_b200.encoder import random_init_like_fields
+    items = [fields((321, 481), 8, pose_seed=3, jitter_seed=4)[:2],
+             fields((641, 641), 30, pose_seed=8, jitter_seed=9)[:2]]
+    cif, caf = random_init_like_fields((29, 33), 5, scale_sigma=2.0)           # wide and narrow boxes side by side
+    items.append((cif, caf))
+    for cif, caf in items:
+        out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, keep=('ann', 'hr', 'seeds'), tuning=tuning,
+                      ann_cap=1024)
+        assert np.array_equal(out['hr'][0], oracle.cifhr(cif)), tuning
+
+
+def test_cifhr_narrow_and_wide_strips_in_one_field(oracle, coco_skeleton, configured_decoder):
+    """One field with ordinary pose sources AND a few sources whose boxes span the whole map: the strips they
+    meet go to the CTA-per-strip kernel, the others to the strips kernel, inside the same launch pair; a strip
+    with more than 160 sources changes kernels as well.  hr, seeds and annotations against the oracle."""
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    cif = cif.copy()
+    # wide sources in three fields: huge scale at a few active cells (box = whole map), one in every field row band
+    for f, (y, x) in ((0, (5, 7)), (5, (20, 40)), (16, (38, 3))):
+        cif[f, 0, y, x] = 0.9
+        cif[f, 1, y, x], cif[f, 2, y, x] = x + 0.3, y + 0.4
+        cif[f, 4, y, x] = 500.0
+    # a field with a very long list in a few strips: 300 weak narrow sources in two cell rows
+    rng = np.random.RandomState(5)
+    for k in range(300):
+        y, x = 10 + k % 2, k % 61
+        cif[3, 0, y, x] = 0.15 + 0.1 * rng.rand()
+        cif[3, 1, y, x], cif[3, 2, y, x] = x + rng.rand(), y + rng.rand()
+        cif[3, 4, y, x] = 0.3 + rng.rand()
+    out = run_gpu(configured_decoder, [cif], [caf], coco_skeleton)
+    check_image(oracle, out, 0, cif, caf, coco_skeleton)
+    legacy = run_gpu(configured_decoder, [cif], [caf], coco_skeleton, tuning={'cifhr_warps': -1})
+    assert np.array_equal(out['hr'], legacy['hr'])
+
+
+def test_hr_memory_allocator(oracle, coco_skeleton, configured_decoder):
+    """pp_hr_alloc / pp_hr_free: compressible allocations on B200, distinct live blocks, a free of an unknown
+    pointer is refused; a decode into compressible memory equals a decode into torch's memory and the oracle."""
+    import ctypes as C
+    from openpifpaf_b200 import _lib
+    from openpifpaf_b200.decoder import engine
+    lib = _lib.lib()
+    ptrs = []
+    for nbytes in (1, 4096, 3 << 20, 64 << 20):
+        p, comp = C.c_void_p(), C.c_int32(-1)
+        assert lib.pp_hr_alloc(nbytes, C.byref(p), C.byref(comp)) == _lib.PP_OK
+        assert p.value and p.value % 256 == 0 and comp.value == 1
+        ptrs.append(p)
+    assert len({p.value for p in ptrs}) == len(ptrs)
+    assert lib.pp_hr_alloc(0, C.byref(C.c_void_p()), None) == _lib.PP_ERR_ARG
+    assert lib.pp_hr_free(C.c_void_p(ptrs[0].value + 256)) == _lib.PP_ERR_ARG
+    for p in ptrs:
+        assert lib.pp_hr_free(p) == _lib.PP_OK
+    assert lib.pp_hr_free(ptrs[0]) == _lib.PP_ERR_ARG            # already gone
+    assert lib.pp_hr_free(None) == _lib.PP_OK
+    cif, caf, _ = fields((321, 481), 8, pose_seed=3, jitter_seed=4)
+    a = run_gpu(configured_decoder, [cif, cif], [caf, caf], coco_skeleton)
+    check_image(oracle, a, 1, cif, caf, coco_skeleton)
+    assert engine.BatchBuffers.compress_hr
+    engine.BatchBuffers.compress_hr = False
+    try:
+        b = run_gpu(configured_decoder, [cif, cif], [caf, caf], coco_skeleton)
+    finally:
+        engine.BatchBuffers.compress_hr = True
+    # (rows past the counts are uninitialised memory in both)
+    for k in ('hr', 'n_ann', 'n_seeds', 'status', 'n_pre'):
+        assert np.array_equal(a[k], b[k]), k
+    for i in range(2):
+        n, ns = int(a['n_ann'][i]), int(a['n_seeds'][i])
+        assert np.array_equal(a['ann_data'][i, :n], b['ann_data'][i, :n])
+        assert np.array_equal(a['ann_score'][i, :n], b['ann_score'][i, :n])
+        assert np.array_equal(a['seeds'][i, :ns], b['seeds'][i, :ns])
+
+
+def test_hr_slice_alignment(oracle, coco_skeleton):
+    """pp_cifhr_accumulate into a map that starts 4, 8 and 12 bytes past a 16-byte boundary (what a sub-batch
+    slice of a larger map looks like at odd image sizes): the bulk stores keep their alignment and nothing
+    outside the map is written."""
+    import ctypes as C
+    from openpifpaf_b200 import _lib
+    cif, _, _ = fields((161, 161), 2, pose_seed=5, jitter_seed=6)
+    want = oracle.cifhr(cif)
+    F, hh, hw = want.shape
+    lib = _lib.lib()
+    shape = _lib.Shape(1, F, 19, cif.shape[2], cif.shape[3], 8)
+    caps = _lib.Caps()
+    _lib.check(lib.pp_default_caps(C.byref(shape), C.byref(caps)))
+    ws = torch.empty((lib.pp_workspace_bytes(C.byref(shape), C.byref(caps)),), dtype=torch.uint8, device='cuda')
+    status = torch.zeros((1,), dtype=torch.int32, device='cuda')
+    d_cif = torch.from_numpy(cif[None]).cuda()
+    p = _lib.Params()
+    lib.pp_default_params(C.byref(p))
+    for shift in (1, 2, 3, 0):
+        big = torch.full((F * hh * hw + 64,), -7.0, dtype=torch.float32, device='cuda')
+        base = (-big.data_ptr() // 4) % 4                   # floats up to the next 16-byte boundary
+        lo = base + shift
+        view = big[lo:lo + F * hh * hw]
+        assert view.data_ptr() % 16 == 4 * shift
+        _lib.check(lib.pp_cifhr_accumulate(C.c_void_p(d_cif.data_ptr()), C.c_void_p(view.data_ptr()),
+                                           C.c_void_p(ws.data_ptr()), ws.numel(), C.byref(shape), C.byref(caps),
+                                           C.byref(p), C.c_void_p(status.data_ptr()), None))
+        torch.cuda.synchronize()
+        got = big.cpu().numpy()
+        assert np.array_equal(got[lo:lo + F * hh * hw].reshape(F, hh, hw), want), shift
+        assert (got[:lo] == -7.0).all() and (got[lo + F * hh * hw:] == -7.0).all(), shift
