@@ -882,6 +882,19 @@ def run_b200(args):
     ev1.record()
     torch.cuda.synchronize()
     write_peak_gbs = fill.numel() * 4 / (ev0.elapsed_time(ev1) / 5 * 1e-3) / 1e9
+    fill_shape = tuple(fill.shape)
+    del fill
+    # the same into compressible memory (pp_hr_alloc), where the hr maps of this run live
+    from openpifpaf_b200.decoder.engine import BatchBuffers, hr_tensor
+    fill, hr_compressed = hr_tensor(fill_shape, device)
+    fill.zero_()
+    torch.cuda.synchronize()
+    ev0.record()
+    for _ in range(5):
+        fill.zero_()
+    ev1.record()
+    torch.cuda.synchronize()
+    write_peak_comp_gbs = fill.numel() * 4 / (ev0.elapsed_time(ev1) / 5 * 1e-3) / 1e9
     del fill
 
     if rank != 0:
@@ -903,7 +916,7 @@ def run_b200(args):
     traffic = None
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
-            traffic = json.load(f).get('cifhr_splat_kernel', {}).get(args.workload)
+            traffic = json.load(f).get('cifhr_strips_kernel', {}).get(args.workload)
         if batch != default_batch:
             traffic = None       # the captured launch was at the workload's default batch
     except (OSError, ValueError):
@@ -978,18 +991,27 @@ def run_b200(args):
                                                 'host_chunk': decoder.CifCaf.host_chunk},
                           'h2d_only_ms_per_step': h2d_ms, 'h2d_gbs': h2d / h2d_ms / 1e6,
                           'pcie_floor_frac': h2d_ms / (1e3 * e2e_copy_s / steps)},
-        # kernels of this library launched in the reported K-step pass: per decode compact, splat, seeds from
-        # sources sorted per field, seed merge, CafScored scoring + binning, assembly + NMS, result gather (7 kernels, 2 memsets)
+        # kernels of this library launched in the reported K-step pass: per decode field scan, strips kernel, CTA-per-strip
+        # kernel (wide boxes; no work here), seeds sorted per field, seed merge, CafScored scoring + binning,
+        # assembly + NMS, result gather (8 kernels, 2 memsets)
         'gpu_launches': (_lib.lib().pp_decode_launch_count(None) - 2) * steps,
         'gpu_launches_per_step': _lib.lib().pp_decode_launch_count(None) - 2,
         'gpu_launches_all_passes': (_lib.lib().pp_decode_launch_count(None) - 2) * steps * 3 * n_passes,
         'gpu_memsets_per_step': 2,
-        'roofline': {'bound': 'hbm', 'kernel': 'cifhr_splat_kernel', 'achieved': splat_gbs,
+        'roofline': {'bound': 'hbm', 'kernel': 'cifhr_strips_kernel', 'achieved': splat_gbs,
                      'peak': peak, 'unit': 'GB/s', 'frac': splat_gbs / peak, 'traffic': traffic,
                      'peak_source': peak_src, 'algorithmic_bytes_per_launch': hr_bytes,
                      'write_only_peak': {'gbs': write_peak_gbs, 'frac': splat_gbs / write_peak_gbs,
                                          'how': 'memset of a buffer of the same size, timed here (5 runs): the '
                                                 'kernel only writes, the copy peak moves half its bytes as reads'},
+                     'hr_memory': {'compressible': bool(hr_compressed and BatchBuffers.compress_hr),
+                                   'memset_gbs': write_peak_comp_gbs,
+                                   'what': 'the hr maps live in an allocation made with compute data compression '
+                                           '(pp_hr_alloc: cuMemCreate, CU_MEM_ALLOCATION_COMP_GENERIC); the map is '
+                                           '~88 % zeros and B200 writes such data faster than into cudaMalloc '
+                                           'memory, which is how the kernel gets past the copy peak (a cudaMalloc '
+                                           'figure).  memset_gbs: a memset of the same size into such an '
+                                           'allocation'},
                      'ms_per_launch': float(mean_ms[i_splat]),
                      'timed': 'one batch at a time on one stream (%d steps, value_one_lane); with %d '
                               'batches in flight the event-bracketed duration also contains the time the '
