@@ -948,7 +948,7 @@ pp_pipeline *pp_pipeline_create(int max_chunks) {
   pp_pipeline *q = (pp_pipeline *)calloc(1, sizeof(pp_pipeline));
   if (!q) return nullptr;
   q->max_chunks = max_chunks;
-  q->rec_guess = 8;
+  q->rec_guess = 6;
   q->ev_in = (cudaEvent_t *)calloc(3 * (size_t)max_chunks, sizeof(cudaEvent_t));
   bool ok = q->ev_in != nullptr;
   if (ok) {

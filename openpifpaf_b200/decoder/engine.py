@@ -373,7 +373,7 @@ class DeviceDecoder:
             buf.enable_host()
         return buf
 
-    fetch_guess = 8       # records per image copied with the header; grows to what the batches need
+    fetch_guess = 6       # records per image copied with the header; grows to what the batches need
     # batches in flight: serialise the splat kernels of the lanes (pp_gate).  Off: measured on B200 the
     # gate keeps a splat running 100 % of the time but the step does not get shorter (0.425 vs 0.420 ms):
     # the other stages' kernels occupy whole SMs while they run, so their time adds to the splat's
