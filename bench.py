@@ -608,8 +608,9 @@ def run_b200(args):
     hw, _, default_batch, dense = WORKLOADS[args.workload]
     batch = args.batch or default_batch
     randinit = args.workload in RANDINIT_MAX_SCALE
-    lanes = args.lanes if args.lanes > 0 else (
-        16 if args.workload in ('crowd_1281_50p', 'dense_641_5p', 'dense_641_5p_b256') else 8)
+    # batches in flight: 8 (the optimum moved from 8-16 to 6-8 with the thin CifHr kernel); crowds have few
+    # images per batch and long latency-bound stages: 16; batch 256 holds 7 GB of hr maps per lane: 4
+    lanes = args.lanes if args.lanes > 0 else {'crowd_1281_50p': 16, 'dense_641_5p_b256': 4}.get(args.workload, 8)
     n_distinct = args.distinct if args.distinct > 0 else min(lanes, 8)
     if args.workload == 'dense_641_5p_b256':
         n_distinct = min(n_distinct, 2)          # 3.2 GB of fields per batch

@@ -1075,7 +1075,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
                                                                 buf_floats, merge, p.cifhr_depth > 0 ? p.cifhr_depth : 8, hr_off);
     PP_LAUNCH_CHECK("cifhr_strips_kernel");
   }
-  if (p.cifhr_depth != 99) {
+  {
     // the CTA-per-strip kernel: the strips that meet wide boxes or very long lists (degenerate fields);
     // with ordinary pose fields its list is empty and every CTA leaves at once
     const size_t dyn = ((size_t)kZeroFloats + 2 * (size_t)buf_floats) * sizeof(float);
