@@ -86,12 +86,42 @@ void prof_begin_step(pp_profile *prof) {
   prof->open = prof->step < prof->max_steps;
 }
 
+#ifdef PP_BREADCRUMB
+// Fault isolation (debug build): a one-thread kernel writes "stage about to start" into pinned host memory, one
+// slot per stream; after a sticky CUDA error the host reads what every stream had reached (pp_debug_crumbs).
+namespace {
+__global__ void crumb_kernel(volatile int *slot, int value) { *slot = value; }
+struct Crumbs { int *host = nullptr; int *dev = nullptr; cudaStream_t streams[64]; int n = 0; };
+Crumbs g_crumbs;
+}  // namespace
+void debug_crumb(cudaStream_t st, int value) {
+  Crumbs &c = g_crumbs;
+  if (!c.host) {
+    if (cudaHostAlloc((void **)&c.host, 64 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) return;
+    memset(c.host, 0, 64 * sizeof(int));
+    cudaHostGetDevicePointer((void **)&c.dev, c.host, 0);
+  }
+  int k = 0;
+  while (k < c.n && c.streams[k] != st) k++;
+  if (k == c.n) { if (c.n == 64) return; c.streams[c.n++] = st; }
+  crumb_kernel<<<1, 1, 0, st>>>(c.dev + k, value);
+}
+extern "C" int pp_debug_crumbs(int *out, int n) {
+  for (int k = 0; k < g_crumbs.n && k < n; k++) out[k] = g_crumbs.host[k];
+  return g_crumbs.n;
+}
+#else
+void debug_crumb(cudaStream_t, int) {}
+#endif
+
 void prof_mark(pp_profile *prof, int stage, cudaStream_t st) {
+  debug_crumb(st, 10 + stage);
   if (!prof || !prof->open) return;
   cudaEventRecord(prof->ev[(size_t)prof->step * (PP_N_STAGES + 1) + stage], st);
 }
 
 void prof_end_step(pp_profile *prof, cudaStream_t st) {
+  debug_crumb(st, 99);
   if (!prof || !prof->open) return;
   cudaEventRecord(prof->ev[(size_t)prof->step * (PP_N_STAGES + 1) + PP_N_STAGES], st);
   prof->step++;
@@ -631,6 +661,7 @@ static int decode_core(const pp_field_set *sets, int n_sets, int hflip_pairs, co
   if (!rc && p->inverse)      // optional Preprocess.annotations_inverse on the results (inside the nms stage time)
     rc = annotations_inverse_launch(o->ann_data, o->ann_scales, o->n_ann, a.pre_data, a.n_pre, *p->inverse,
                                     s->B, s->F, c->ann_cap, st);
+  debug_crumb(st, 50);
   if (!rc && o->packed) {      // one dense block of the live rows for the result copy
     pp_outputs po = *o;
     po.pre_data = a.pre_data; po.pre_scales = a.pre_scales; po.pre_order = a.pre_order; po.n_pre = a.n_pre;

@@ -683,6 +683,17 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
 #ifdef PP_ASM_TIMING
   if (threadIdx.x == 0) sh.tick = clock64();
 #endif
+#ifdef PP_POISON_SMEM
+  // debug build: shared memory starts as garbage (what another kernel's CTA may have left there), so that a
+  // read of a word this CTA never wrote shows up in every decode instead of once in 10^5
+  {
+    const int n_dyn = kAsmWarps * gw + a.stage_floats;
+    for (int i = threadIdx.x; i < n_dyn; i += blockDim.x) dyn_smem[i] = __int_as_float(0x4e6e6b28 + i);   // ~1e9
+    int *raw = reinterpret_cast<int *>(&sh);
+    for (int i = threadIdx.x; i < (int)(sizeof(AsmShared) / 4); i += blockDim.x) raw[i] = 0x4e6e6b28 + i;
+    __syncthreads();
+  }
+#endif
   const CafLists cf = load_lists(sh.ls, a.rows + (size_t)b * a.L * 2 * kBinRows * a.caf_cap,
                                  a.start + (size_t)b * a.L * 2 * (a.geo.nb + 1), a.geo,
                                  a.nfwd + (size_t)b * a.L, a.nbwd + (size_t)b * a.L, a.L, a.caf_cap,
@@ -877,6 +888,11 @@ assemble_kernel(AsmArgs a, Graph g, CScale cscale, pp_params p, int n_edges) {
       if (sh.pick_seed[q] == found) k = q;
     if (k < 0) {
       // ---- a new wave: `found` and the free seeds after it, one pose per warp
+      // Every warp must have finished looking `found` up in the OLD picks before warp 0 overwrites them:
+      // without this barrier a warp that is late (other kernels' warps share the SM's schedulers when
+      // batches are in flight) could read the new pick_seed[0] == found, take the "pose at hand" branch
+      // and leave the CTA's barriers out of step (seen as one illegal address in ~60,000 decodes)
+      __syncthreads();
       if (warp == 0) pick_wave(sh, ctx, found);
       __syncthreads();
       PP_TICK(2);

@@ -1046,11 +1046,18 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   }
   PP_CUDA_CHECK(cudaFuncSetAttribute(fields_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)scan_smem_bytes(4096, kCompactSlab)));
-  fields_scan_kernel<<<bf + n_caf, kCompactThreads, smem, st>>>(ca, pa, bf);
+#ifdef PP_DEBUG_SKIP
+  // timing / fault-isolation experiments only: 32 = no strips / splat kernels, 64 = no field scan
+  const int dbg_skip = getenv("PP_DEBUG_SKIP") ? atoi(getenv("PP_DEBUG_SKIP")) : 0;
+#else
+  const int dbg_skip = 0;
+#endif
+  if (!(dbg_skip & 64)) fields_scan_kernel<<<bf + n_caf, kCompactThreads, smem, st>>>(ca, pa, bf);
   PP_LAUNCH_CHECK("fields_scan_kernel");
+  if (dbg_skip & 32) return gate_signal(p.splat_gate, st);
   // one strip = R*hw floats, plus up to 3 floats of misalignment, rounded to 16 bytes
   const int buf_floats = (int)(((((size_t)hw << w.rshift) + 3 + 3) & ~(size_t)3));
-  prof_mark(p.profile, kStSplat, st);
+  prof_mark(p.profile, kStSplat, st);       // crumb 11
   int rc = gate_wait(p.splat_gate, st);       // batches in flight: one splat at a time (pp_gate)
   if (rc) return rc;
   const int sms = num_sms();
@@ -1075,6 +1082,7 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
                                                                 buf_floats, merge, p.cifhr_depth > 0 ? p.cifhr_depth : 8, hr_off);
     PP_LAUNCH_CHECK("cifhr_strips_kernel");
   }
+  debug_crumb(st, 30);
   {
     // the CTA-per-strip kernel: the strips that meet wide boxes or very long lists (degenerate fields);
     // with ordinary pose fields its list is empty and every CTA leaves at once

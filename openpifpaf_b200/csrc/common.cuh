@@ -67,6 +67,7 @@ int num_sms();
 enum Stage { kStCompact = 0, kStSplat, kStCollect, kStSort, kStCaf, kStAssemble, kStNms };
 void prof_begin_step(pp_profile *prof);
 void prof_mark(pp_profile *prof, int stage, cudaStream_t st);   // start of `stage`
+void debug_crumb(cudaStream_t st, int value);                      // no-op unless built with -DPP_BREADCRUMB
 void prof_end_step(pp_profile *prof, cudaStream_t st);
 
 // ---- exact float helpers ----------------------------------------------------
