@@ -798,7 +798,7 @@ def run_b200(args):
     def stream_pass(batches_fn, key):
         def run():
             total = 0
-            for anns_s in dec.decode_stream(batches_fn(steps)):
+            for anns_s in dec.decode_stream(batches_fn(steps), n_lanes=min(lanes, 8)):
                 total += sum(len(a) for a in anns_s)
             counted[key] = total
             counted[key + '_stats'] = dict(dec.stream_stats)
@@ -851,7 +851,9 @@ def run_b200(args):
     clock_info = clocks.stop() if clocks is not None else None
     # result bytes that cross PCIe per step: header + the records copied (live rows, at least the guess)
     rec_bytes = 4 * _lib.lib().pp_packed_record_words(cif.shape[1])
-    d2h = 4 * int(_lib.lib().pp_packed_header_words(batch)) + rec_bytes * max(int(ann_per_step), 8 * batch)
+    from openpifpaf_b200.decoder.engine import DeviceDecoder
+    guess = DeviceDecoder.fetch_guess           # records per image copied with the header (6, grown by the batches seen)
+    d2h = 4 * int(_lib.lib().pp_packed_header_words(batch)) + rec_bytes * max(int(ann_per_step), guess * batch)
     h2d = cif.nbytes + caf.nbytes
     h2d_dma = cif.nbytes // 5 + caf.nbytes // 9
     h2d_zero = int((cif[:, :, 0] > params.cif_threshold).sum()) * 4 * 4 + \
@@ -1185,7 +1187,8 @@ def run_shard(args):
     dev_t, host_t = _median(dev_s), _median(host_s)
     n_chunks = (n_local + chunk - 1) // chunk
     rec_bytes = 4 * _lib.lib().pp_packed_record_words(17)
-    d2h = 4 * int(_lib.lib().pp_packed_header_words(chunk)) + rec_bytes * 8 * chunk
+    from openpifpaf_b200.decoder.engine import DeviceDecoder
+    d2h = 4 * int(_lib.lib().pp_packed_header_words(chunk)) + rec_bytes * DeviceDecoder.fetch_guess * chunk
     field_bytes = (cif[:chunk].nbytes + caf[:chunk].nbytes)
     h2d_mapped = (cif[:chunk].nbytes // 5 + caf[:chunk].nbytes // 9 +
                   int((cif[:chunk, :, 0] > 0.1).sum()) * 16 + int((caf[:chunk, :, 0] > 0.1).sum()) * 32)
