@@ -153,8 +153,9 @@ typedef struct pp_params {
   int32_t cifhr_rshift;          /* log2 rows per strip + 1 (default 4 = 8 rows; clamped to what fits)   */
   float cif_neighbors;           /* CifHr.neighbors (cif_hr.py:15,40): v / neighbors; 0 = 16            */
   int32_t seed_mask_enabled;     /* 1: seed_mask applies even when it is all zero (no field seeds)      */
-  int32_t cifhr_warps;           /* tuning: warps per CTA of the strips kernel, one strip each (default 3,
-                                    max 8); < 0: the round-1 CTA-per-strip kernel does every strip       */
+  int32_t cifhr_warps;           /* tuning: warps per CTA of the strips kernel, one strip each (default 3; 4 for
+                                    images wider than 767 px; max 8); < 0: the round-1 CTA-per-strip kernel
+                                    does every strip                                                      */
   int32_t cifhr_depth;           /* tuning: bulk stores the empty-strip producer keeps queued (default 8; > 16 = no limit) */
   struct pp_gate *splat_gate;    /* optional (NULL = off): decodes issued on different streams with the same
                                     gate run their CifHr splat kernels one after the other (see pp_gate) */

@@ -1032,7 +1032,11 @@ int cifhr_launch_ex(const float *d_cif, const float *d_cif2, float *d_hr, void *
   // pp_params.cifhr_warps: consumer warps per CTA of the strips kernel; < 0 = the CTA-per-strip kernel
   // does every strip (the round-1 schedule, kept for comparison)
   const bool legacy = p.cifhr_warps < 0;
-  int n_warps = (p.cifhr_warps >= 1 && p.cifhr_warps <= kStripWarpsMax) ? p.cifhr_warps : kStripWarpsDefault;
+  // default: 3 warps at 8-row strips (the thinner kernel wins with batches in flight), 4 where the strips are
+  // 4 rows or fewer (images wider than 767 px: twice the strips, each meeting as many sources; measured on
+  // 16 x 1281 px / 50 persons: 25.7 k -> 27-28 k img/s, profiles/r3_strips_sweeps.md)
+  int n_warps = (p.cifhr_warps >= 1 && p.cifhr_warps <= kStripWarpsMax) ? p.cifhr_warps
+                : (w.rshift < 3 ? kStripWarpsDefault + 1 : kStripWarpsDefault);
   prof_mark(p.profile, kStCompact, st);
   PP_CUDA_CHECK(cudaMemsetAsync(w.cursors, 0, 8 * sizeof(int), st));
   CompactArgs ca = {d_cif, d_cif2, cif_rest, w, s, c.src_cap, hh, hw, p.cif_threshold,
