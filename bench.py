@@ -32,9 +32,11 @@ One JSON line is printed by rank 0 (contract in DESIGN.md section "Measurement")
                 CifCaf.decode_stream -> List[List[Annotation]] on the host;
   e2e_full_copy the e2e call with host_transfer='copy': every plane of every
                 field is copied (PCIe-bound: 430 MB per 64 images);
-  roofline      the CifHr splat kernel (the kernel that writes the hr maps)
-                against the measured HBM copy peak of MEASURED_PEAKS.json,
-                timed in the one-lane pass; in_flight = while lanes overlap;
+  roofline      the CifHr strips kernel (the kernel that writes the hr maps, into
+                compressible memory: pp_hr_alloc) against the measured HBM copy peak
+                of MEASURED_PEAKS.json, timed in the one-lane pass; a memset of the
+                same size into plain and into compressible memory beside it;
+                in_flight = while lanes overlap;
   cpu_baseline  the UNMODIFIED reference decoder (oracle/_ref, its Cython
                 functional module) on this box's host cores, bounded sample;
   --impl reference   the same reference decoder as its own arm.
