@@ -1329,3 +1329,39 @@ def test_hr_slice_alignment(oracle, coco_skeleton):
         got = big.cpu().numpy()
         assert np.array_equal(got[lo:lo + F * hh * hw].reshape(F, hh, hw), want), shift
         assert (got[:lo] == -7.0).all() and (got[lo + F * hh * hw:] == -7.0).all(), shift
+
+
+def test_batches_in_flight_soak(oracle, coco_skeleton, configured_decoder):
+    """Three seconds of decodes with 8 batches in flight (about 8,000 decodes of 16 images): no CUDA fault,
+    and every lane's result equals the first one's.  The race this guards against (a missing barrier in the
+    assembly's wave lookup, profiles/r3_race_hunt.md) showed once in ~60,000 decodes, so this is a smoke
+    check of the in-flight path; `scripts/soak.py` is the long version."""
+    import time
+    from openpifpaf_b200.decoder.engine import DecoderParams, DeviceDecoder
+    items = [fields((641, 641), 5, pose_seed=b, jitter_seed=b + 1)[:2] for b in range(16)]
+    cif = torch.from_numpy(np.stack([i[0] for i in items])).cuda()
+    caf = torch.from_numpy(np.stack([i[1] for i in items])).cuda()
+    eng = DeviceDecoder(coco_skeleton, ann_cap=64)
+    params = DecoderParams()
+    first = None
+    tickets, done, t0 = [], 0, time.time()
+    while time.time() - t0 < 3.0:
+        for _ in range(32):
+            if len(tickets) == 8:
+                buf = tickets.pop(0).wait()
+                done += 1
+                if done % 500 == 1:
+                    got = (buf.dev['n_ann'].cpu().numpy().copy(), buf.dev['ann_data'][:, :4].cpu().numpy().copy())
+                    if first is None:
+                        first = got
+                    assert np.array_equal(got[0], first[0])
+                    for b in range(16):
+                        n = min(int(got[0][b]), 4)
+                        assert np.array_equal(got[1][b, :n], first[1][b, :n])
+            tickets.append(eng.submit(cif, caf, params, n_lanes=8))
+    for t in tickets:
+        t.wait()
+    torch.cuda.synchronize()
+    assert done > 1000
+    o = oracle.decode(items[0][0], items[0][1], coco_skeleton, oracle.Config(exp_mode=1))
+    assert int(first[0][0]) == len(o.data) and np.array_equal(first[1][0, :min(4, len(o.data))], o.data[:4])
