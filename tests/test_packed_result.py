@@ -97,3 +97,18 @@ def test_annotation_lists_from_a_packed_block():
         for (s, e, xs, xe) in ann.decoding_order:
             assert np.array_equal(xs, pre[s]) and np.array_equal(xe, pre[e])
         assert ann.score() == pytest.approx(float(np.sum(ann.score_weights * np.sort(data[:, 2])[::-1])), rel=1e-6)
+
+
+def test_decoder_params_tuning_knobs_reach_the_struct():
+    """DecoderParams.tuning -> pp_params (the schedule knobs are struct fields, nothing is read from the
+    environment); an unknown knob is refused."""
+    from openpifpaf_b200.decoder.engine import DecoderParams
+    knobs = {'asm_heavy_seeds': -1, 'asm_stage_kb': 48, 'cifhr_group': 16, 'cifhr_ctas_per_sm': 2,
+             'cifhr_rshift': 3, 'cifhr_warps': 5, 'cifhr_depth': 12}
+    p = DecoderParams(tuning=knobs).to_c()
+    for name, value in knobs.items():
+        assert getattr(p, name) == value
+    q = DecoderParams().to_c()
+    assert all(getattr(q, name) == 0 for name in knobs)          # 0 = the library's choice
+    with pytest.raises(KeyError):
+        DecoderParams(tuning={'cifhr_wraps': 2}).to_c()
